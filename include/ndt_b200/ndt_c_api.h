@@ -1,0 +1,143 @@
+/* ndt_c_api.h -- C ABI of the B200-native NDT scan-matching backend (libndt_b200.so).
+ *
+ * Drop-in boundary for the one hot path of lowmee/xchu_slam: the registration backend that
+ * odom_node calls.  The reference has no FFI; its interface for this path is the C++ class
+ * pclomp::NormalDistributionsTransform (reference xchu_mapping/include/pclomp/ndt_omp.h:70-204,
+ * NDT_H below) over pcl::Registration.  Every entry point cites the member it replaces.
+ * include/pclomp/ndt_omp.h in this repo re-creates that class on top of this ABI so that
+ * xchu_mapping/src/odom_node.cpp:55-83, 263-284 compiles unchanged.
+ *
+ * Conventions: every function returns 0 on success, non-zero on failure (ndtb_last_error
+ * gives the text); nothing throws across the ABI.  All pointers are HOST pointers unless a
+ * function says otherwise; the library copies inside the call and retains no caller pointer.
+ * Point clouds are arrays of records whose first three floats are x, y, z; `stride_bytes`
+ * is the record size (16 for float4 / pcl::PointXYZ, 32 for pcl::PointXYZI).  4x4 matrices
+ * are float, COLUMN-major (Eigen::Matrix4f memory order).  A handle owns one CUDA stream and
+ * is not thread-safe; distinct handles may be used from distinct threads.
+ * There is NO CPU fallback: without a CUDA device ndtb_create fails.
+ */
+#ifndef NDT_B200_C_API_H_
+#define NDT_B200_C_API_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ndtb_handle ndtb_handle;
+typedef struct ndtb_batch ndtb_batch;
+
+/* pclomp::NeighborSearchMethod, NDT_H:52-57 (same numeric values). */
+enum { NDTB_KDTREE = 0, NDTB_DIRECT26 = 1, NDTB_DIRECT7 = 2, NDTB_DIRECT1 = 3 };
+
+/* Everything the reference configures through setters.  Defaults = the reference ctor
+ * (ndt_omp_impl.hpp:46-69) and VoxelGridCovariance ctor (voxel_grid_covariance_omp.h:199-207). */
+typedef struct ndtb_params {
+  float resolution;      /* setResolution,            NDT_H:127-137   default 1.0  */
+  double step_size;      /* setStepSize,              NDT_H:160-164   default 0.1  */
+  double trans_eps;      /* setTransformationEpsilon, pcl::Registration default 0.1 (ctor NDT_I:64) */
+  int max_iter;          /* setMaximumIterations,     default 35 (ctor NDT_I:65)   */
+  double outlier_ratio;  /* setOulierRatio,           NDT_H:178-182   default 0.55 */
+  int search_method;     /* setNeighborhoodSearchMethod, NDT_H:184-186 default DIRECT7 */
+  int min_points;        /* min_points_per_voxel_,    VGC_H:204       default 6    */
+  double eig_mult;       /* min_covar_eigvalue_mult_, VGC_H:205       default 0.01 */
+} ndtb_params;
+
+typedef struct ndtb_result {
+  float T[16];              /* getFinalTransformation()                                   */
+  int iterations;           /* getFinalNumIteration(), NDT_H:200-204                      */
+  int converged;            /* hasConverged()                                             */
+  double score;             /* last computeDerivatives score                              */
+  double trans_probability; /* getTransformationProbability(), NDT_H:191-195              */
+  int n_evals;              /* computeDerivatives/computeHessian evaluations performed    */
+} ndtb_result;
+
+/* ---- lifetime ------------------------------------------------------------------------ */
+int ndtb_create(int device, ndtb_handle** out);            /* NormalDistributionsTransform(), NDT_I:46-69 */
+int ndtb_destroy(ndtb_handle* h);
+const char* ndtb_last_error(const ndtb_handle* h);          /* h may be NULL: last create error */
+void ndtb_default_params(ndtb_params* p);
+
+/* ---- configuration (NDT_H:110-186 setters; a change of resolution rebuilds the voxel grid
+ *      when a target is present, as init() does, NDT_H:127-137, 271-278) ------------------ */
+int ndtb_set_params(ndtb_handle* h, const ndtb_params* p);
+int ndtb_get_params(const ndtb_handle* h, ndtb_params* p);
+
+/* ---- target: VoxelGridCovariance build (NDT_H:117-122 setInputTarget -> init() ->
+ *      voxel_grid_covariance_omp_impl.hpp:48-370 applyFilter) ----------------------------- */
+int ndtb_set_target(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes);
+/* If the first points of `pts` are bit-identical to the current target (odom_node only ever
+ * appends between window resets, src/odom_node.cpp:336), only the new tail is merged into the
+ * voxel table; otherwise a full rebuild.  *was_incremental (may be NULL) reports which. */
+int ndtb_set_target_auto(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes, int* was_incremental);
+/* Append points to the current target: cpu::NormalDistributionsTransform::updateVoxelGrid
+ * semantics (include/ndt_cpu/NormalDistributionsTransform.h:39); result == full rebuild over the
+ * concatenated cloud. */
+int ndtb_update_target(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes);
+
+/* ---- source + align (pcl::Registration::setInputSource / align ->
+ *      ndt_omp_impl.hpp:73-164 computeTransformation) ------------------------------------- */
+int ndtb_set_source(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes);
+int ndtb_align(ndtb_handle* h, const float guess[16], ndtb_result* out);
+/* Transformed source of the last align (the `output` cloud of align()); x,y,z written at the
+ * start of each `stride_bytes` record, other bytes untouched. */
+int ndtb_get_output(ndtb_handle* h, void* pts, size_t stride_bytes);
+/* pcl::Registration::getFitnessScore(max_range): mean squared 1-NN distance of the source moved
+ * by the final transformation (or by T if not NULL) to the RAW target cloud. */
+int ndtb_fitness(ndtb_handle* h, double max_range, const float* T, double* out);
+/* calculateScore, ndt_omp_impl.hpp:919-952 (cloud = source transformed by T). */
+int ndtb_calculate_score(ndtb_handle* h, const float T[16], double* out);
+
+/* ---- inspection hooks used by the parity tests ----------------------------------------- */
+int ndtb_num_voxels(ndtb_handle* h, size_t* n_all);  /* all occupied voxels (any point count)  */
+/* Arrays of n_all entries (any may be NULL): absolute cell coordinates, nr_points (-1 = flagged
+ * invalid, VGC_I:337-341/360-364), inserted point count, mean (f64), inverse covariance as the
+ * derivative kernel reads it (f32, row-major 3x3), f32 centroid (VGC_I:242-243, 289). */
+int ndtb_dump_voxels(ndtb_handle* h, int* ijk, int* nr_points, int* n_raw, double* mean, float* icov,
+                     float* centroid);
+/* Neighbour voxels (VGC_I:373-442 / VGC_H:470-499) of n already transformed xyz points;
+ * cnt[n], ijk[n][27][3] in visiting order. */
+int ndtb_neighbors(ndtb_handle* h, const float* xyz, size_t n, int method, int* cnt, int* ijk);
+/* One computeDerivatives (ndt_omp_impl.hpp:175-283) at transform T and pose vector p. */
+int ndtb_eval_derivatives(ndtb_handle* h, const float T[16], const double p[6], int compute_hessian,
+                          double* score, double g[6], double H[36]);
+/* computeHessian (ndt_omp_impl.hpp:551-641): FP64, radius-search neighbours. */
+int ndtb_compute_hessian(ndtb_handle* h, const float T[16], const double p[6], double H[36]);
+/* Per-evaluation trace of the last ndtb_align: records of 52 doubles
+ * {p[6], score, g[6], H[36], step, compute_hessian, kind}; kind 0 = initial, 1 = first trial of a
+ * line search, 2 = More-Thuente trial, 3 = computeHessian.  *n = records available. */
+int ndtb_get_trace(ndtb_handle* h, double* out, int max_recs, int* n);
+/* Device time (ms, CUDA events on the handle's stream) of the last set_target / update / align. */
+int ndtb_last_timing(ndtb_handle* h, double* build_ms, double* align_ms);
+
+/* ---- batched registration on one device (north_star item 4) ------------------------------
+ * A batch holds targets (submaps) and sources (scans) resident in HBM and runs any number of
+ * independent registrations {target id, source id, initial guess} concurrently; no collective
+ * inside a registration.  `on_device` != 0 means `pts` is a DEVICE pointer on the batch's
+ * device (copied device-to-device); otherwise a host pointer. */
+int ndtb_batch_create(int device, ndtb_batch** out);
+int ndtb_batch_destroy(ndtb_batch* b);
+const char* ndtb_batch_last_error(const ndtb_batch* b);
+int ndtb_batch_set_params(ndtb_batch* b, const ndtb_params* p);
+int ndtb_batch_clear(ndtb_batch* b);
+int ndtb_batch_add_target(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int on_device, int* id);
+int ndtb_batch_add_source(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int on_device, int* id);
+/* Builds every target's voxel table (if not built yet) and runs n_items registrations.
+ * guesses: n_items x 16 floats.  results: n_items records (host). */
+int ndtb_batch_run(ndtb_batch* b, int n_items, const int* item_target, const int* item_source,
+                   const float* guesses, ndtb_result* results);
+/* Device times (ms) of the last run: voxel-table builds, derivative kernels, whole run; number of
+ * kernels launched; derivative-kernel launches; (point, voxel) pairs and points evaluated. */
+typedef struct ndtb_batch_stats {
+  double build_ms, deriv_ms, total_ms;
+  long long kernel_launches, deriv_launches;
+  long long points_evaluated, pairs_evaluated, probes;
+} ndtb_batch_stats;
+int ndtb_batch_get_stats(ndtb_batch* b, ndtb_batch_stats* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NDT_B200_C_API_H_ */

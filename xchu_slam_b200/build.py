@@ -1,0 +1,58 @@
+"""Builds the in-tree native libraries: libndt_b200.so (CUDA, sm_100a) and _lidar_synth.so.
+
+nvcc cross-compiles without a GPU.  -fmad=false is part of the numerics contract (DESIGN.md
+section 5): float expressions are evaluated as written, like the reference's x86-64 build.
+"""
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libndt_b200.so")
+SOURCES = ["voxel_build.cu", "ndt_core.cu", "ndt_api.cu"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
+              "-Xcompiler", "-fPIC", "-ccbin", "g++"]
+
+
+def _stale(target, deps):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build_cuda(force=False, verbose=False):
+    hdrs = [os.path.join(CSRC, "ndt_internal.h"), os.path.join(HERE, "..", "include", "ndt_b200", "ndt_c_api.h")]
+    objs = []
+    procs = []
+    for src in SOURCES:
+        s = os.path.join(CSRC, src)
+        o = os.path.join(CSRC, src.replace(".cu", ".o"))
+        objs.append(o)
+        if force or _stale(o, [s] + hdrs):
+            cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
+            procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    for src, p in procs:
+        out, _ = p.communicate()
+        if p.returncode != 0:
+            sys.stderr.write(out)
+            raise RuntimeError("nvcc failed on " + src)
+        if verbose:
+            sys.stderr.write(out)
+    if force or procs or _stale(LIB, objs):
+        subprocess.check_call(["nvcc", "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a",
+                                                                       "-Xcompiler", "-fPIC", "-ccbin", "g++", "-lcudart"])
+    return LIB
+
+
+def build_all(force=False, verbose=False):
+    from . import synth
+    synth.build(force)
+    return build_cuda(force, verbose)
+
+
+if __name__ == "__main__":
+    sys.path.insert(0, os.path.dirname(HERE))
+    build_cuda(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    print(LIB)

@@ -1,0 +1,728 @@
+// ndt_api.cu -- host side of libndt_b200.so: the registration engine (targets, sources, batched
+// Newton loop driver) and the extern "C" ABI declared in include/ndt_b200/ndt_c_api.h.
+// Host logic mirrors pcl::Registration::align + pclomp::NormalDistributionsTransform
+// (reference xchu_mapping/include/pclomp/ndt_omp.h:110-278, ndt_omp_impl.hpp:73-164).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/ndt_b200/ndt_c_api.h"
+#include "ndt_internal.h"
+
+using namespace ndtb;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+#define CKE(x)                                                                                       \
+  do {                                                                                               \
+    cudaError_t e_ = (x);                                                                            \
+    if (e_ != cudaSuccess) { return fail(std::string(#x) + ": " + cudaGetErrorString(e_)); }         \
+  } while (0)
+
+struct Target {
+  float4* pts = nullptr;
+  size_t n = 0, cap = 0;
+  TableStorage ts;
+  bool built = false;
+};
+struct Source { long long offset; size_t n; };
+
+// Eigen 3.3 MatrixBase::eulerAngles(0,1,2) on the float rotation block (NDT_I:102)
+static void euler_012(const float T[16], float out[3]) {
+  auto m = [&](int r, int c) { return T[c * 4 + r]; };
+  const float pi = (float)M_PI;
+  float r0 = std::atan2(m(1, 2), m(2, 2));
+  const float c2 = std::sqrt(m(0, 0) * m(0, 0) + m(0, 1) * m(0, 1));
+  float r1;
+  if (r0 > 0.f) { r0 -= pi; r1 = std::atan2(-m(0, 2), -c2); }
+  else r1 = std::atan2(-m(0, 2), c2);
+  const float s1 = std::sin(r0), c1 = std::cos(r0);
+  const float r2 = std::atan2(s1 * m(2, 0) - c1 * m(1, 0), c1 * m(1, 1) - s1 * m(2, 1));
+  out[0] = -r0; out[1] = -r1; out[2] = -r2;
+}
+
+struct Engine {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  ndtb_params params;
+  BuildWorkspace* ws = nullptr;
+  NNGridStorage* nn = nullptr;
+  bool nn_valid = false;
+  std::vector<Target> targets;
+  int n_targets_live = 0;
+  VoxelTable* d_tables = nullptr;
+  size_t d_tables_cap = 0;
+  float4* src_pool = nullptr;
+  size_t src_cap = 0, src_used = 0;
+  std::vector<Source> sources;
+  AlignState* d_states = nullptr;
+  size_t states_cap = 0;
+  std::vector<AlignState> h_states;
+  int2* d_blockmap = nullptr;
+  size_t blockmap_cap = 0;
+  double* d_partials = nullptr;
+  size_t partials_cap = 0;
+  double* d_trace = nullptr;
+  size_t trace_doubles = 0;
+  int trace_cap = 0;
+  int* d_active = nullptr;
+  int* h_active = nullptr;
+  float* d_T16 = nullptr;
+  double* d_p6 = nullptr;
+  float4* d_output = nullptr;
+  size_t output_cap = 0;
+  float* d_d2 = nullptr;
+  size_t d2_cap = 0;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  std::vector<cudaEvent_t> deriv_events;
+  ndtb_batch_stats stats{};
+  double last_build_ms = 0, last_align_ms = 0;
+  // single-handle state (pcl::Registration members)
+  ndtb_result last{};
+  bool have_result = false;
+  std::vector<double> h_trace;
+  int h_trace_n = 0;
+
+  int fail(const std::string& m) { err = m; return 1; }
+
+  int init(int dev) {
+    device = dev;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return fail("no CUDA device available (this library has no CPU fallback)");
+    if (dev < 0 || dev >= count) return fail("invalid device ordinal");
+    CKE(cudaSetDevice(dev));
+    CKE(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    ws = build_ws_create();
+    if (!ws) return fail("workspace allocation failed");
+    nn = nn_create();
+    CKE(cudaMalloc(&d_active, sizeof(int)));
+    CKE(cudaMallocHost(&h_active, sizeof(int)));
+    CKE(cudaMalloc(&d_T16, 16 * sizeof(float)));
+    CKE(cudaMalloc(&d_p6, 6 * sizeof(double)));
+    for (auto& e : ev) CKE(cudaEventCreate(&e));
+    ndtb_default_params(&params);
+    return 0;
+  }
+  void destroy() {
+    cudaSetDevice(device);
+    for (auto& t : targets) { cudaFree(t.pts); table_free(t.ts); }
+    targets.clear();
+    build_ws_destroy(ws);
+    nn_destroy(nn);
+    cudaFree(d_tables); cudaFree(src_pool); cudaFree(d_states); cudaFree(d_blockmap); cudaFree(d_partials);
+    cudaFree(d_trace); cudaFree(d_active); cudaFreeHost(h_active); cudaFree(d_T16); cudaFree(d_p6);
+    cudaFree(d_output); cudaFree(d_d2);
+    for (auto& e : ev) if (e) cudaEventDestroy(e);
+    for (auto& e : deriv_events) cudaEventDestroy(e);
+    if (stream) cudaStreamDestroy(stream);
+  }
+
+  // copy n records (xyz = first three floats) into a float4 device array
+  int upload_points(float4* dst, const void* pts, size_t n, size_t stride, bool on_device) {
+    if (n == 0) return 0;
+    if (stride < 12) return fail("stride_bytes must be >= 12");
+    const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    if (stride == 16) {
+      CKE(cudaMemcpyAsync(dst, pts, n * 16, kind, stream));
+    } else if (stride > 16) {
+      CKE(cudaMemcpy2DAsync(dst, 16, pts, stride, 16, n, kind, stream));
+    } else {  // packed xyz (12..15 bytes): widen on the way
+      CKE(cudaMemsetAsync(dst, 0, n * 16, stream));
+      CKE(cudaMemcpy2DAsync(dst, 16, pts, stride, 12, n, kind, stream));
+    }
+    return 0;
+  }
+
+  int reserve_target(Target& t, size_t n) {
+    if (n <= t.cap) return 0;
+    float4* q = nullptr;
+    const size_t nc = n + n / 4 + 1024;
+    CKE(cudaMalloc(&q, nc * sizeof(float4)));
+    if (t.pts && t.n) CKE(cudaMemcpyAsync(q, t.pts, t.n * sizeof(float4), cudaMemcpyDeviceToDevice, stream));
+    CKE(cudaStreamSynchronize(stream));
+    cudaFree(t.pts);
+    t.pts = q;
+    t.cap = nc;
+    return 0;
+  }
+
+  void table_config(Target& t) {
+    t.ts.t.leaf = params.resolution;
+    t.ts.t.inv_leaf = 1.0f / params.resolution;   // pcl::VoxelGrid::setLeafSize: inverse_leaf_size_ = 1 / leaf (float)
+    t.ts.t.min_points = params.min_points;
+    t.ts.t.eig_mult = params.eig_mult;
+  }
+
+  // full (re)build of a target's voxel table from its resident points: init(), NDT_H:271-278
+  int build_target(Target& t) {
+    table_config(t);
+    CKE(table_clear(t.ts, stream, &stats.kernel_launches));
+    CKE(table_append(t.ts, ws, t.pts, t.n, stream, &stats.kernel_launches));
+    t.built = true;
+    return 0;
+  }
+
+  int sync_tables() {
+    if (targets.size() > d_tables_cap) {
+      cudaFree(d_tables);
+      d_tables = nullptr;
+      d_tables_cap = targets.size() + 8;
+      CKE(cudaMalloc(&d_tables, d_tables_cap * sizeof(VoxelTable)));
+    }
+    std::vector<VoxelTable> h(targets.size());
+    for (size_t i = 0; i < targets.size(); ++i) h[i] = targets[i].ts.t;
+    if (!h.empty()) CKE(cudaMemcpyAsync(d_tables, h.data(), h.size() * sizeof(VoxelTable), cudaMemcpyHostToDevice, stream));
+    CKE(cudaStreamSynchronize(stream));
+    return 0;
+  }
+
+  int add_source(const void* pts, size_t n, size_t stride, bool on_device, int* id) {
+    if (src_used + n > src_cap) {
+      const size_t nc = (src_used + n) + (src_used + n) / 2 + 4096;
+      float4* q = nullptr;
+      CKE(cudaMalloc(&q, nc * sizeof(float4)));
+      if (src_pool && src_used) CKE(cudaMemcpyAsync(q, src_pool, src_used * sizeof(float4), cudaMemcpyDeviceToDevice, stream));
+      CKE(cudaStreamSynchronize(stream));
+      cudaFree(src_pool);
+      src_pool = q;
+      src_cap = nc;
+    }
+    if (upload_points(src_pool + src_used, pts, n, stride, on_device)) return 1;
+    sources.push_back(Source{(long long)src_used, n});
+    if (id) *id = (int)sources.size() - 1;
+    src_used += n;
+    return 0;
+  }
+
+  template <typename T>
+  int ensure(T*& p, size_t& cap, size_t need) {
+    if (need <= cap) return 0;
+    cudaFree(p);
+    p = nullptr;
+    cap = need + need / 4 + 16;
+    CKE(cudaMalloc(&p, cap * sizeof(T)));
+    return 0;
+  }
+
+  void fill_state(AlignState& st, int target, const Source& src, const float* guess) {
+    std::memset(&st, 0, sizeof(st));
+    st.n_src = (int)src.n;
+    st.target = target;
+    st.src_offset = src.offset;
+    st.step_size = params.step_size;
+    st.trans_eps = params.trans_eps;
+    st.max_iter = params.max_iter;
+    st.resolution = params.resolution;
+    // gauss constants, recomputed at every computeTransformation (NDT_I:80-87)
+    const double c1 = 10 * (1 - params.outlier_ratio);
+    const double c2 = params.outlier_ratio / std::pow((double)params.resolution, 3);
+    const double d3 = -std::log(c2);
+    const double d1 = -std::log(c1 + c2) - d3;
+    const double d2 = -2 * std::log((-std::log(c1 * std::exp(-0.5) + c2) - d3) / d1);
+    st.req.d1 = d1; st.req.d2 = d2; st.req.d3 = d3;
+    st.req.search_method = params.search_method;
+    st.req.mode = 0;
+    // final_transformation_ = guess (Identity when guess == Identity: same bits either way, NDT_I:89-94)
+    std::memcpy(st.final_T, guess, 16 * sizeof(float));
+    float e[3];
+    euler_012(st.final_T, e);                                    // NDT_I:96-104
+    st.p[0] = st.final_T[12]; st.p[1] = st.final_T[13]; st.p[2] = st.final_T[14];
+    st.p[3] = e[0]; st.p[4] = e[1]; st.p[5] = e[2];
+    st.phase = kPhaseStart;
+  }
+
+  // Run n_items registrations to completion on the device.  want_trace: per-evaluation records.
+  int run_items(int n_items, const int* item_target, const int* item_source, const float* guesses, ndtb_result* results,
+                bool want_trace) {
+    if (n_items <= 0) return 0;
+    CKE(cudaSetDevice(device));
+    stats = ndtb_batch_stats{};
+    CKE(cudaEventRecord(ev[0], stream));
+    for (auto& t : targets)
+      if (!t.built && t.n > 0 && build_target(t)) return 1;
+    CKE(cudaEventRecord(ev[1], stream));
+    if (sync_tables()) return 1;
+    // work decomposition: one block per `chunk` source points of one registration
+    size_t total_pts = 0;
+    for (int i = 0; i < n_items; ++i) {
+      if (item_target[i] < 0 || item_target[i] >= (int)targets.size()) return fail("item target id out of range");
+      if (item_source[i] < 0 || item_source[i] >= (int)sources.size()) return fail("item source id out of range");
+      total_pts += sources[item_source[i]].n;
+    }
+    int chunk = (int)((total_pts / (148 * 4) + 255) / 256 * 256);
+    if (chunk < 256) chunk = 256;
+    if (chunk > 2048) chunk = 2048;
+    h_states.resize(n_items);
+    std::vector<int2> bmap;
+    for (int i = 0; i < n_items; ++i) {
+      AlignState& st = h_states[i];
+      fill_state(st, item_target[i], sources[item_source[i]], guesses + (size_t)i * 16);
+      if (!targets[item_target[i]].ts.valid) st.req.search_method = params.search_method;  // empty grid: no neighbours at all
+      st.first_block = (int)bmap.size();
+      st.n_blocks = (st.n_src + chunk - 1) / chunk;
+      for (int b = 0; b < st.n_blocks; ++b) bmap.push_back(make_int2(i, b * chunk));
+    }
+    const int n_blocks = (int)bmap.size();
+    if (ensure(d_states, states_cap, (size_t)n_items)) return 1;
+    if (ensure(d_blockmap, blockmap_cap, bmap.size())) return 1;
+    if (ensure(d_partials, partials_cap, bmap.size() * 44)) return 1;
+    const bool mt_live = !((params.step_size - params.trans_eps / 2) > 0);   // NDT_I:807: the inner loop runs only then
+    const int evals_per_iter = mt_live ? 12 : 1;
+    const int max_evals = 1 + (params.max_iter + 2) * evals_per_iter;
+    trace_cap = want_trace ? max_evals + 1 : 0;
+    if (want_trace && ensure(d_trace, trace_doubles, (size_t)n_items * trace_cap * kTraceRec)) return 1;
+    CKE(cudaMemcpyAsync(d_states, h_states.data(), (size_t)n_items * sizeof(AlignState), cudaMemcpyHostToDevice, stream));
+    if (!bmap.empty()) CKE(cudaMemcpyAsync(d_blockmap, bmap.data(), bmap.size() * sizeof(int2), cudaMemcpyHostToDevice, stream));
+    *h_active = n_items;
+    CKE(cudaMemcpyAsync(d_active, h_active, sizeof(int), cudaMemcpyHostToDevice, stream));
+    CKE(cudaEventRecord(ev[2], stream));
+    // PH_START: set up the first evaluation request
+    CKE(launch_newton(d_states, n_items, d_partials, want_trace ? d_trace : nullptr, trace_cap, d_active, stream));
+    stats.kernel_launches++;
+    size_t ev_used = 0;
+    const int poll = 4;
+    for (int it = 0; it < max_evals; ++it) {
+      if (deriv_events.size() < ev_used + 2) {
+        cudaEvent_t a, b;
+        CKE(cudaEventCreate(&a)); CKE(cudaEventCreate(&b));
+        deriv_events.push_back(a); deriv_events.push_back(b);
+      }
+      CKE(cudaEventRecord(deriv_events[ev_used], stream));
+      CKE(launch_derivatives(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk, d_partials, stream));
+      CKE(cudaEventRecord(deriv_events[ev_used + 1], stream));
+      ev_used += 2;
+      stats.kernel_launches++; stats.deriv_launches++;
+      if (mt_live) {
+        CKE(launch_hessian_f64(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk, d_partials, stream));
+        stats.kernel_launches++;
+      }
+      CKE(launch_newton(d_states, n_items, d_partials, want_trace ? d_trace : nullptr, trace_cap, d_active, stream));
+      stats.kernel_launches++;
+      if ((it + 1) % poll == 0 || it + 1 == max_evals) {
+        CKE(cudaMemcpyAsync(h_active, d_active, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        CKE(cudaStreamSynchronize(stream));
+        if (*h_active <= 0) break;
+      }
+    }
+    CKE(cudaEventRecord(ev[3], stream));
+    CKE(cudaMemcpyAsync(h_states.data(), d_states, (size_t)n_items * sizeof(AlignState), cudaMemcpyDeviceToHost, stream));
+    if (want_trace) {
+      h_trace.resize((size_t)n_items * trace_cap * kTraceRec);
+      CKE(cudaMemcpyAsync(h_trace.data(), d_trace, h_trace.size() * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    }
+    CKE(cudaStreamSynchronize(stream));
+    float ms = 0;
+    CKE(cudaEventElapsedTime(&ms, ev[0], ev[1])); stats.build_ms = ms;
+    CKE(cudaEventElapsedTime(&ms, ev[0], ev[3])); stats.total_ms = ms;
+    CKE(cudaEventElapsedTime(&ms, ev[2], ev[3])); last_align_ms = ms;
+    stats.deriv_ms = 0;
+    for (size_t k = 0; k + 1 < ev_used; k += 2) { CKE(cudaEventElapsedTime(&ms, deriv_events[k], deriv_events[k + 1])); stats.deriv_ms += ms; }
+    for (int i = 0; i < n_items; ++i) {
+      const AlignState& st = h_states[i];
+      ndtb_result& r = results[i];
+      std::memcpy(r.T, st.final_T, sizeof(r.T));
+      r.iterations = st.nr_iterations;
+      r.converged = st.converged;
+      r.score = st.score;
+      r.trans_probability = st.trans_probability;
+      r.n_evals = st.n_evals;
+      if (!st.done) { r.converged = 0; }
+      stats.points_evaluated += (long long)st.n_src * st.n_evals;
+      stats.pairs_evaluated += st.pairs_total;
+    }
+    return 0;
+  }
+};
+
+}  // namespace
+
+struct ndtb_handle { Engine e; };
+struct ndtb_batch { Engine e; };
+
+extern "C" {
+
+void ndtb_default_params(ndtb_params* p) {
+  p->resolution = 1.0f; p->step_size = 0.1; p->trans_eps = 0.1; p->max_iter = 35; p->outlier_ratio = 0.55;
+  p->search_method = NDTB_DIRECT7; p->min_points = 6; p->eig_mult = 0.01;
+}
+
+static int create_engine(int device, Engine& e) { return e.init(device); }
+
+int ndtb_create(int device, ndtb_handle** out) {
+  if (!out) return 1;
+  ndtb_handle* h = new ndtb_handle();
+  if (create_engine(device, h->e)) { g_create_error = h->e.err; delete h; *out = nullptr; return 1; }
+  h->e.targets.resize(1);
+  *out = h;
+  return 0;
+}
+int ndtb_destroy(ndtb_handle* h) {
+  if (!h) return 0;
+  h->e.destroy();
+  delete h;
+  return 0;
+}
+const char* ndtb_last_error(const ndtb_handle* h) { return h ? h->e.err.c_str() : g_create_error.c_str(); }
+
+static int check_params(Engine& e, const ndtb_params* p) {
+  if (!p) return e.fail("null params");
+  if (!(p->resolution > 0)) return e.fail("resolution must be > 0");
+  if (p->search_method < 0 || p->search_method > 3) return e.fail("unknown search method");
+  return 0;
+}
+
+int ndtb_set_params(ndtb_handle* h, const ndtb_params* p) {
+  Engine& e = h->e;
+  if (check_params(e, p)) return 1;
+  cudaSetDevice(e.device);
+  const bool rebuild = p->resolution != e.params.resolution || p->min_points != e.params.min_points || p->eig_mult != e.params.eig_mult;
+  e.params = *p;
+  Target& t = e.targets[0];
+  if (rebuild && t.n > 0) {   // setResolution -> init() (NDT_H:127-137)
+    t.ts.have_bbox = false;
+    if (e.build_target(t)) return 1;
+    if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  }
+  return 0;
+}
+int ndtb_get_params(const ndtb_handle* h, ndtb_params* p) { *p = h->e.params; return 0; }
+
+int ndtb_set_target(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  Target& t = e.targets[0];
+  if (e.reserve_target(t, n)) return 1;
+  t.n = 0;
+  cudaEventRecord(e.ev[0], e.stream);
+  if (e.upload_points(t.pts, pts, n, stride_bytes, false)) return 1;
+  t.n = n;
+  e.nn_valid = false;
+  t.ts.have_bbox = false;
+  if (e.build_target(t)) return 1;
+  cudaEventRecord(e.ev[1], e.stream);
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e.ev[0], e.ev[1]);
+  e.last_build_ms = ms;
+  return 0;
+}
+
+int ndtb_update_target(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  Target& t = e.targets[0];
+  if (!t.built || t.n == 0) return ndtb_set_target(h, pts, n, stride_bytes);
+  if (n == 0) return 0;
+  if (e.reserve_target(t, t.n + n)) return 1;
+  cudaEventRecord(e.ev[0], e.stream);
+  if (e.upload_points(t.pts + t.n, pts, n, stride_bytes, false)) return 1;
+  e.table_config(t);
+  cudaError_t ce = table_append(t.ts, e.ws, t.pts + t.n, n, e.stream, &e.stats.kernel_launches);
+  if (ce != cudaSuccess) return e.fail(std::string("table_append: ") + cudaGetErrorString(ce));
+  t.n += n;
+  e.nn_valid = false;
+  cudaEventRecord(e.ev[1], e.stream);
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e.ev[0], e.ev[1]);
+  e.last_build_ms = ms;
+  return 0;
+}
+
+int ndtb_set_target_auto(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes, int* was_incremental) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  Target& t = e.targets[0];
+  if (was_incremental) *was_incremental = 0;
+  if (!t.built || t.n == 0 || n < t.n || n - t.n > t.n || !t.ts.valid) return ndtb_set_target(h, pts, n, stride_bytes);
+  // upload behind the current points, compare the shared prefix on the device
+  const size_t old_n = t.n;
+  if (e.reserve_target(t, old_n + n)) return 1;
+  cudaEventRecord(e.ev[0], e.stream);
+  float4* fresh = t.pts + old_n;
+  if (e.upload_points(fresh, pts, n, stride_bytes, false)) return 1;
+  *e.h_active = 1;
+  cudaMemcpyAsync(e.d_active, e.h_active, sizeof(int), cudaMemcpyHostToDevice, e.stream);
+  cudaError_t ce = launch_prefix_equal(t.pts, fresh, old_n, e.d_active, e.stream);
+  if (ce != cudaSuccess) return e.fail("prefix compare failed");
+  cudaMemcpyAsync(e.h_active, e.d_active, sizeof(int), cudaMemcpyDeviceToHost, e.stream);
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  if (*e.h_active == 1) {
+    // the tail [old_n, n) of the fresh copy already sits at t.pts + old_n + old_n; move it down
+    const size_t tail = n - old_n;
+    if (tail > 0) {
+      // regions may overlap when tail > old_n: go through the (free) upper half safely with memmove semantics
+      cudaMemcpyAsync(t.pts + old_n, fresh + old_n, tail * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+      e.table_config(t);
+      ce = table_append(t.ts, e.ws, t.pts + old_n, tail, e.stream, &e.stats.kernel_launches);
+      if (ce != cudaSuccess) return e.fail(std::string("table_append: ") + cudaGetErrorString(ce));
+      t.n = n;
+      e.nn_valid = false;
+    }
+    if (was_incremental) *was_incremental = 1;
+  } else {
+    cudaMemcpyAsync(t.pts, fresh, n * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+    t.n = n;
+    e.nn_valid = false;
+    t.ts.have_bbox = false;
+    if (e.build_target(t)) return 1;
+  }
+  cudaEventRecord(e.ev[1], e.stream);
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e.ev[0], e.ev[1]);
+  e.last_build_ms = ms;
+  return 0;
+}
+
+int ndtb_set_source(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  e.sources.clear();
+  e.src_used = 0;
+  e.have_result = false;
+  return e.add_source(pts, n, stride_bytes, false, nullptr);
+}
+
+int ndtb_align(ndtb_handle* h, const float guess[16], ndtb_result* out) {
+  Engine& e = h->e;
+  if (e.sources.empty()) return e.fail("no source cloud set");
+  if (!e.targets[0].built) return e.fail("no target cloud set");
+  const int zero = 0;
+  if (e.run_items(1, &zero, &zero, guess, &e.last, true)) return 1;
+  e.have_result = true;
+  e.h_trace_n = e.last.n_evals;
+  if (out) *out = e.last;
+  return 0;
+}
+
+int ndtb_get_output(ndtb_handle* h, void* pts, size_t stride_bytes) {
+  Engine& e = h->e;
+  if (!e.have_result) return e.fail("no align result");
+  cudaSetDevice(e.device);
+  const size_t n = e.sources[0].n;
+  if (n > e.output_cap) { cudaFree(e.d_output); e.d_output = nullptr; if (cudaMalloc(&e.d_output, n * sizeof(float4)) != cudaSuccess) return e.fail("alloc"); e.output_cap = n; }
+  cudaMemcpyAsync(e.d_T16, e.last.T, 64, cudaMemcpyHostToDevice, e.stream);
+  if (launch_transform(e.src_pool + e.sources[0].offset, n, e.d_T16, e.d_output, e.stream) != cudaSuccess) return e.fail("transform failed");
+  if (cudaMemcpy2DAsync(pts, stride_bytes, e.d_output, 16, 12, n, cudaMemcpyDeviceToHost, e.stream) != cudaSuccess) return e.fail("copy failed");
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  return 0;
+}
+
+int ndtb_fitness(ndtb_handle* h, double max_range, const float* T, double* out) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  Target& t = e.targets[0];
+  if (e.sources.empty() || t.n == 0) return e.fail("fitness needs a source and a target");
+  if (!T && !e.have_result) return e.fail("no align result");
+  if (!e.nn_valid) {
+    const float cell = e.params.resolution > 0.25f ? e.params.resolution : 0.25f;
+    cudaError_t ce = nn_build(e.nn, e.ws, t.pts, t.n, cell, e.stream, &e.stats.kernel_launches);
+    if (ce != cudaSuccess) return e.fail(std::string("nn_build: ") + cudaGetErrorString(ce));
+    e.nn_valid = true;
+  }
+  const size_t n = e.sources[0].n;
+  if (n > e.d2_cap) { cudaFree(e.d_d2); e.d_d2 = nullptr; if (cudaMalloc(&e.d_d2, n * sizeof(float)) != cudaSuccess) return e.fail("alloc"); e.d2_cap = n; }
+  cudaMemcpyAsync(e.d_T16, T ? T : e.last.T, 64, cudaMemcpyHostToDevice, e.stream);
+  if (nn_query(e.nn, e.src_pool + e.sources[0].offset, n, e.d_T16, e.d_d2, e.stream) != cudaSuccess) return e.fail("nn_query failed");
+  std::vector<float> d(n);
+  cudaMemcpyAsync(d.data(), e.d_d2, n * sizeof(float), cudaMemcpyDeviceToHost, e.stream);
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  // pcl::Registration::getFitnessScore: double accumulation in point order over d <= max_range
+  double s = 0;
+  long nr = 0;
+  for (size_t i = 0; i < n; ++i)
+    if ((double)d[i] <= max_range) { s += d[i]; ++nr; }
+  *out = nr > 0 ? s / nr : 1.7976931348623157e308;
+  return 0;
+}
+
+// shared by eval_derivatives / compute_hessian / calculate_score: one evaluation in `mode`
+static int single_eval(Engine& e, const float T[16], const double p[6], int mode, AlignState* out_state) {
+  cudaSetDevice(e.device);
+  if (e.sources.empty()) return e.fail("no source cloud set");
+  Target& t = e.targets[0];
+  if (!t.built) return e.fail("no target cloud set");
+  if (e.sync_tables()) return 1;
+  const int chunk = 256;
+  AlignState st;
+  static const float I16[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+  e.fill_state(st, 0, e.sources[0], I16);
+  st.first_block = 0;
+  st.n_blocks = (st.n_src + chunk - 1) / chunk;
+  std::vector<int2> bmap;
+  for (int b = 0; b < st.n_blocks; ++b) bmap.push_back(make_int2(0, b * chunk));
+  if (e.ensure(e.d_states, e.states_cap, (size_t)1)) return 1;
+  if (e.ensure(e.d_blockmap, e.blockmap_cap, bmap.size())) return 1;
+  if (e.ensure(e.d_partials, e.partials_cap, bmap.size() * 44)) return 1;
+  cudaMemcpyAsync(e.d_states, &st, sizeof(st), cudaMemcpyHostToDevice, e.stream);
+  cudaMemcpyAsync(e.d_blockmap, bmap.data(), bmap.size() * sizeof(int2), cudaMemcpyHostToDevice, e.stream);
+  cudaMemcpyAsync(e.d_T16, T, 64, cudaMemcpyHostToDevice, e.stream);
+  cudaMemcpyAsync(e.d_p6, p, 48, cudaMemcpyHostToDevice, e.stream);
+  *e.h_active = 1;
+  cudaMemcpyAsync(e.d_active, e.h_active, sizeof(int), cudaMemcpyHostToDevice, e.stream);
+  if (launch_prepare_eval(e.d_states, e.d_T16, e.d_p6, mode, e.stream) != cudaSuccess) return e.fail("prepare failed");
+  cudaError_t ce;
+  if (mode == 1 || mode == 2) ce = launch_derivatives(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.stream);
+  else ce = launch_hessian_f64(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.stream);
+  if (ce != cudaSuccess) return e.fail(std::string("eval launch: ") + cudaGetErrorString(ce));
+  if (launch_newton(e.d_states, 1, e.d_partials, nullptr, 0, e.d_active, e.stream) != cudaSuccess) return e.fail("reduce failed");
+  cudaMemcpyAsync(out_state, e.d_states, sizeof(AlignState), cudaMemcpyDeviceToHost, e.stream);
+  ce = cudaStreamSynchronize(e.stream);
+  if (ce != cudaSuccess) return e.fail(std::string("eval: ") + cudaGetErrorString(ce));
+  return 0;
+}
+
+int ndtb_eval_derivatives(ndtb_handle* h, const float T[16], const double p[6], int compute_hessian, double* score, double g[6],
+                          double H[36]) {
+  AlignState st;
+  if (single_eval(h->e, T, p, compute_hessian ? 1 : 2, &st)) return 1;
+  if (score) *score = st.score;
+  if (g) std::memcpy(g, st.g, 48);
+  if (H) std::memcpy(H, st.H, 288);
+  h->e.stats.pairs_evaluated = st.pairs;
+  return 0;
+}
+int ndtb_compute_hessian(ndtb_handle* h, const float T[16], const double p[6], double H[36]) {
+  AlignState st;
+  if (single_eval(h->e, T, p, 3, &st)) return 1;
+  std::memcpy(H, st.H, 288);
+  return 0;
+}
+int ndtb_calculate_score(ndtb_handle* h, const float T[16], double* out) {
+  AlignState st;
+  const double p0[6] = {0, 0, 0, 0, 0, 0};
+  if (single_eval(h->e, T, p0, 4, &st)) return 1;
+  *out = st.score / (double)h->e.sources[0].n;   // NDT_I:951
+  return 0;
+}
+
+int ndtb_num_voxels(ndtb_handle* h, size_t* n_all) { *n_all = h->e.targets[0].ts.valid ? (size_t)h->e.targets[0].ts.n_vox : 0; return 0; }
+
+int ndtb_dump_voxels(ndtb_handle* h, int* ijk, int* nr_points, int* n_raw, double* mean, float* icov, float* centroid) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  Target& t = e.targets[0];
+  const size_t n = t.ts.valid ? (size_t)t.ts.n_vox : 0;
+  if (n == 0) return 0;
+  std::vector<unsigned long long> keys(n);
+  std::vector<VoxelRec> rec(n);
+  std::vector<float4> cen(n);
+  std::vector<int> vn(n);
+  cudaMemcpy(keys.data(), t.ts.t.vkey, n * 8, cudaMemcpyDeviceToHost);
+  cudaMemcpy(rec.data(), t.ts.t.rec, n * sizeof(VoxelRec), cudaMemcpyDeviceToHost);
+  cudaMemcpy(cen.data(), t.ts.t.centroid, n * sizeof(float4), cudaMemcpyDeviceToHost);
+  if (cudaMemcpy(vn.data(), t.ts.t.vn, n * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return e.fail("dump copy failed");
+  for (size_t v = 0; v < n; ++v) {
+    int a, b, c;
+    unpack_key(keys[v], a, b, c);
+    if (ijk) { ijk[v * 3] = a; ijk[v * 3 + 1] = b; ijk[v * 3 + 2] = c; }
+    if (nr_points) nr_points[v] = rec[v].nr_points;
+    if (n_raw) n_raw[v] = vn[v];
+    if (mean) for (int k = 0; k < 3; ++k) mean[v * 3 + k] = rec[v].mean[k];
+    if (icov) for (int k = 0; k < 9; ++k) icov[v * 9 + k] = rec[v].icov[k];
+    if (centroid) { centroid[v * 3] = cen[v].x; centroid[v * 3 + 1] = cen[v].y; centroid[v * 3 + 2] = cen[v].z; }
+  }
+  return 0;
+}
+
+int ndtb_neighbors(ndtb_handle* h, const float* xyz, size_t n, int method, int* cnt, int* ijk) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  if (!e.targets[0].built) return e.fail("no target cloud set");
+  if (e.sync_tables()) return 1;
+  float* d_xyz = nullptr; int* d_cnt = nullptr; int* d_ijk = nullptr;
+  if (cudaMalloc(&d_xyz, n * 12) != cudaSuccess || cudaMalloc(&d_cnt, n * 4) != cudaSuccess || cudaMalloc(&d_ijk, n * 27 * 3 * 4) != cudaSuccess)
+    return e.fail("alloc failed");
+  cudaMemcpyAsync(d_xyz, xyz, n * 12, cudaMemcpyHostToDevice, e.stream);
+  cudaMemsetAsync(d_ijk, 0, n * 27 * 3 * 4, e.stream);
+  cudaError_t ce = launch_neighbors(e.d_tables, d_xyz, n, method, d_cnt, d_ijk, e.stream);
+  cudaMemcpyAsync(cnt, d_cnt, n * 4, cudaMemcpyDeviceToHost, e.stream);
+  cudaMemcpyAsync(ijk, d_ijk, n * 27 * 3 * 4, cudaMemcpyDeviceToHost, e.stream);
+  cudaError_t ce2 = cudaStreamSynchronize(e.stream);
+  cudaFree(d_xyz); cudaFree(d_cnt); cudaFree(d_ijk);
+  if (ce != cudaSuccess || ce2 != cudaSuccess) return e.fail("neighbors kernel failed");
+  return 0;
+}
+
+int ndtb_get_trace(ndtb_handle* h, double* out, int max_recs, int* n) {
+  Engine& e = h->e;
+  if (!e.have_result) return e.fail("no align result");
+  const int avail = e.h_trace_n < e.trace_cap ? e.h_trace_n : e.trace_cap;
+  if (n) *n = avail;
+  const int m = avail < max_recs ? avail : max_recs;
+  if (out && m > 0) std::memcpy(out, e.h_trace.data(), (size_t)m * kTraceRec * sizeof(double));
+  return 0;
+}
+
+int ndtb_last_timing(ndtb_handle* h, double* build_ms, double* align_ms) {
+  if (build_ms) *build_ms = h->e.last_build_ms;
+  if (align_ms) *align_ms = h->e.last_align_ms;
+  return 0;
+}
+
+// ---- batch -------------------------------------------------------------------------------
+int ndtb_batch_create(int device, ndtb_batch** out) {
+  if (!out) return 1;
+  ndtb_batch* b = new ndtb_batch();
+  if (create_engine(device, b->e)) { g_create_error = b->e.err; delete b; *out = nullptr; return 1; }
+  *out = b;
+  return 0;
+}
+int ndtb_batch_destroy(ndtb_batch* b) {
+  if (!b) return 0;
+  b->e.destroy();
+  delete b;
+  return 0;
+}
+const char* ndtb_batch_last_error(const ndtb_batch* b) { return b ? b->e.err.c_str() : g_create_error.c_str(); }
+int ndtb_batch_set_params(ndtb_batch* b, const ndtb_params* p) {
+  if (check_params(b->e, p)) return 1;
+  b->e.params = *p;
+  for (auto& t : b->e.targets) { t.built = false; t.ts.have_bbox = false; }
+  return 0;
+}
+int ndtb_batch_clear(ndtb_batch* b) {
+  Engine& e = b->e;
+  cudaSetDevice(e.device);
+  // keep the allocations (grow-only pools); forget the contents
+  for (auto& t : e.targets) { t.n = 0; t.built = false; t.ts.have_bbox = false; }
+  e.n_targets_live = 0;
+  e.sources.clear();
+  e.src_used = 0;
+  return 0;
+}
+int ndtb_batch_add_target(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int on_device, int* id) {
+  Engine& e = b->e;
+  cudaSetDevice(e.device);
+  if (e.n_targets_live == (int)e.targets.size()) e.targets.emplace_back();
+  Target& t = e.targets[e.n_targets_live];
+  if (e.reserve_target(t, n)) return 1;
+  t.n = 0;
+  if (e.upload_points(t.pts, pts, n, stride_bytes, on_device != 0)) return 1;
+  t.n = n;
+  t.built = false;
+  t.ts.have_bbox = false;
+  if (id) *id = e.n_targets_live;
+  e.n_targets_live++;
+  return 0;
+}
+int ndtb_batch_add_source(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int on_device, int* id) {
+  cudaSetDevice(b->e.device);
+  return b->e.add_source(pts, n, stride_bytes, on_device != 0, id);
+}
+int ndtb_batch_run(ndtb_batch* b, int n_items, const int* item_target, const int* item_source, const float* guesses,
+                   ndtb_result* results) {
+  Engine& e = b->e;
+  for (int i = 0; i < n_items; ++i)
+    if (item_target[i] < 0 || item_target[i] >= e.n_targets_live) return e.fail("item target id out of range");
+  return e.run_items(n_items, item_target, item_source, guesses, results, false);
+}
+int ndtb_batch_get_stats(ndtb_batch* b, ndtb_batch_stats* s) { *s = b->e.stats; return 0; }
+
+}  // extern "C"

@@ -1,0 +1,820 @@
+// ndt_core.cu -- the per-iteration hot path: fused derivative kernel (K3), FP64 Hessian / score
+// variants (K4), device-resident Newton + More-Thuente state machine (K7), neighbour-set and
+// transform helpers.  Compiled with -fmad=false: every float expression below is evaluated in the
+// written order with separate multiplies and adds, which is what makes the voxel assignment of
+// transformed points and each (point, voxel) term bit-identical to the reference arithmetic
+// (reference built for baseline x86-64: no FMA contraction).
+//
+// Reference: xchu_mapping/include/pclomp/ndt_omp_impl.hpp (NDT_I), ndt_omp.h (NDT_H),
+// voxel_grid_covariance_omp_impl.hpp (VGC_I), voxel_grid_covariance_omp.h (VGC_H).
+#include <cfloat>
+#include <cmath>
+
+#include "ndt_internal.h"
+
+namespace ndtb {
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
+
+constexpr int kThreads = 256;
+constexpr int kPartialStride = 44;  // 43 accumulators + pair count
+
+__constant__ int c_off7[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};  // VGC_I:423-430
+// pcl::getAllNeighborCellIndices(): 13 "half" neighbours followed by their negations (VGC_I:413)
+__constant__ int c_off26[26][3] = {
+    {-1, -1, -1}, {-1, 0, -1}, {-1, 1, -1}, {0, -1, -1}, {0, 0, -1}, {0, 1, -1}, {1, -1, -1}, {1, 0, -1}, {1, 1, -1},
+    {-1, -1, 0}, {0, -1, 0}, {1, -1, 0}, {-1, 0, 0},
+    {1, 1, 1}, {1, 0, 1}, {1, -1, 1}, {0, 1, 1}, {0, 0, 1}, {0, -1, 1}, {-1, 1, 1}, {-1, 0, 1}, {-1, -1, 1},
+    {1, 1, 0}, {0, 1, 0}, {-1, 1, 0}, {1, 0, 0}};
+
+// ---------------------------------------------------------------------------------------
+// hash probe: one 128-bit load per probed slot
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ HashSlot load_slot(const HashSlot* p) {
+  const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+  HashSlot s;
+  s.key = ((unsigned long long)v.y << 32) | v.x;
+  s.vidx = (int)v.z;
+  s.nr_points = (int)v.w;
+  return s;
+}
+__device__ __forceinline__ bool probe(const VoxelTable& t, int i, int j, int k, HashSlot& out) {
+  if (!coord_ok(i) || !coord_ok(j) || !coord_ok(k)) return false;
+  const unsigned long long key = pack_key(i, j, k);
+  uint32_t h = hash_key(key) & t.mask;
+  while (true) {
+    const HashSlot s = load_slot(t.slots + h);
+    if (s.key == key) { out = s; return true; }
+    if (s.key == kEmptyKey) return false;
+    h = (h + 1) & t.mask;
+  }
+}
+
+// Query-time cell: floor(x / leaf_size) (VGC_I:379-381) -- a float DIVISION, unlike the build key.
+__device__ __forceinline__ int query_cell(float x, float leaf) { return (int)floorf(x / leaf); }
+
+// Neighbour voxels of a transformed point in the reference's visiting order.
+// DIRECT1/7/26: VGC_I:373-442 (found && nr_points >= min_points).
+// KDTREE: VGC_H:470-499 over the centroid cloud (every voxel that had >= min_points inserted points,
+// flagged-invalid ones included), squared float distance < float(r*r), ascending distance.
+__device__ int find_neighbors(const VoxelTable& t, int method, float x, float y, float z, int* vout) {
+  if (t.slots == nullptr) return 0;   // empty grid (no target, or the overflow guard of VGC_I:79-84 tripped)
+  const int ci = query_cell(x, t.leaf), cj = query_cell(y, t.leaf), ck = query_cell(z, t.leaf);
+  int cnt = 0;
+  HashSlot s;
+  if (method == 2) {
+#pragma unroll
+    for (int o = 0; o < 7; ++o)
+      if (probe(t, ci + c_off7[o][0], cj + c_off7[o][1], ck + c_off7[o][2], s) && s.nr_points >= t.min_points) vout[cnt++] = s.vidx;
+  } else if (method == 3) {
+    if (probe(t, ci, cj, ck, s) && s.nr_points >= t.min_points) vout[cnt++] = s.vidx;
+  } else if (method == 1) {
+    for (int o = 0; o < 26; ++o)
+      if (probe(t, ci + c_off26[o][0], cj + c_off26[o][1], ck + c_off26[o][2], s) && s.nr_points >= t.min_points) vout[cnt++] = s.vidx;
+  } else {
+    const double rr = (double)t.leaf * (double)t.leaf;  // radius = resolution_ (NDT_I:233), r*r in double then float
+    const float r2 = (float)rr;
+    float d2s[27];
+    unsigned long long keys[27];
+    for (int dz = -1; dz <= 1; ++dz)
+      for (int dy = -1; dy <= 1; ++dy)
+        for (int dx = -1; dx <= 1; ++dx) {
+          if (!probe(t, ci + dx, cj + dy, ck + dz, s)) continue;
+          const float4 c = __ldg(t.centroid + s.vidx);
+          if (__float_as_int(c.w) < t.min_points) continue;
+          const float ex = x - c.x, ey = y - c.y, ez = z - c.z;
+          const float d2 = (ex * ex + ey * ey) + ez * ez;
+          if (!(d2 < r2)) continue;
+          // insertion sort by (d2, cell key): ascending distance, ties by ascending linear index
+          int pos = cnt;
+          while (pos > 0 && (d2s[pos - 1] > d2 || (d2s[pos - 1] == d2 && keys[pos - 1] > s.key))) {
+            d2s[pos] = d2s[pos - 1]; keys[pos] = keys[pos - 1]; vout[pos] = vout[pos - 1]; --pos;
+          }
+          d2s[pos] = d2; keys[pos] = s.key; vout[pos] = s.vidx;
+          ++cnt;
+        }
+  }
+  return cnt;
+}
+
+// pcl::transformPointCloud (NDT_I:93, 822, 866): x' = ((m00 x + m01 y) + m02 z) + m03, float
+__device__ __forceinline__ void xform(const float* T /*row-major 3x4*/, float x, float y, float z, float& ox, float& oy, float& oz) {
+  ox = ((T[0] * x + T[1] * y) + T[2] * z) + T[3];
+  oy = ((T[4] * x + T[5] * y) + T[6] * z) + T[7];
+  oz = ((T[8] * x + T[9] * y) + T[10] * z) + T[11];
+}
+
+struct EvalShared {
+  float T[12];
+  float jang[24];
+  float hang[45];
+  float d2f;
+  double d1, d2, d3;
+  int mode, method;
+  VoxelTable tab;
+};
+
+// ---------------------------------------------------------------------------------------
+// K3: computeDerivatives (NDT_I:175-283) = transform + neighbour lookup + computePointDerivatives
+// (NDT_I:401-445) + updateDerivatives (NDT_I:491-548), float per-term math, double accumulation,
+// warp-shuffle + shared-memory block reduction to one partial per block (fixed order, no atomics).
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void pair_update(double* acc, const VoxelRec* __restrict__ recp, float xtx, float xty, float xtz,
+                                            const float* pgv /*8*/, const float* phv /*15*/, float d2f, double d1,
+                                            bool compute_hessian) {
+  // 64 B record = four 128-bit loads
+  const double2 m01 = __ldg(reinterpret_cast<const double2*>(recp));
+  const double2 m2c = __ldg(reinterpret_cast<const double2*>(recp) + 1);
+  const float4 c1 = __ldg(reinterpret_cast<const float4*>(recp) + 2);
+  const float4 c2 = __ldg(reinterpret_cast<const float4*>(recp) + 3);
+  const float C00 = __int_as_float(__double2loint(m2c.y)), C01 = __int_as_float(__double2hiint(m2c.y));
+  const float C02 = c1.x, C10 = c1.y, C11 = c1.z, C12 = c1.w, C20 = c2.x, C21 = c2.y, C22 = c2.z;
+  // x_trans = f64(x_trans_pt) - mean, narrowed to float (NDT_I:257-260, 500)
+  const float x0 = (float)((double)xtx - m01.x), x1 = (float)((double)xty - m01.y), x2 = (float)((double)xtz - m2c.x);
+  const float xC0 = (x0 * C00 + x1 * C10) + x2 * C20;
+  const float xC1 = (x0 * C01 + x1 * C11) + x2 * C21;
+  const float xC2 = (x0 * C02 + x1 * C12) + x2 * C22;
+  const float q = (x0 * xC0 + x1 * xC1) + x2 * xC2;
+  float e = (float)exp((double)((-d2f * q) * 0.5f));            // NDT_I:507
+  const float score_inc = (float)(-d1 * (double)e);             // NDT_I:509
+  e = d2f * e;                                                  // NDT_I:511
+  if (e > 1.f || e < 0.f || e != e) return;                     // NDT_I:514-515 (score not counted either)
+  e = (float)((double)e * d1);                                  // NDT_I:518
+  acc[0] += (double)score_inc;
+  const float g13 = pgv[0], g23 = pgv[1], g04 = pgv[2], g14 = pgv[3], g24 = pgv[4], g05 = pgv[5], g15 = pgv[6], g25 = pgv[7];
+  // CJ = c_inv4 * point_gradient4 (NDT_I:520); columns 0..2 are the columns of C
+  float CJ[3][6];
+  CJ[0][0] = C00; CJ[0][1] = C01; CJ[0][2] = C02;
+  CJ[1][0] = C10; CJ[1][1] = C11; CJ[1][2] = C12;
+  CJ[2][0] = C20; CJ[2][1] = C21; CJ[2][2] = C22;
+  CJ[0][3] = C01 * g13 + C02 * g23; CJ[1][3] = C11 * g13 + C12 * g23; CJ[2][3] = C21 * g13 + C22 * g23;
+  CJ[0][4] = (C00 * g04 + C01 * g14) + C02 * g24; CJ[1][4] = (C10 * g04 + C11 * g14) + C12 * g24; CJ[2][4] = (C20 * g04 + C21 * g14) + C22 * g24;
+  CJ[0][5] = (C00 * g05 + C01 * g15) + C02 * g25; CJ[1][5] = (C10 * g05 + C11 * g15) + C12 * g25; CJ[2][5] = (C20 * g05 + C21 * g15) + C22 * g25;
+  float xCJ[6];
+  xCJ[0] = xC0; xCJ[1] = xC1; xCJ[2] = xC2;
+#pragma unroll
+  for (int c = 3; c < 6; ++c) xCJ[c] = (x0 * CJ[0][c] + x1 * CJ[1][c]) + x2 * CJ[2][c];   // NDT_I:521
+#pragma unroll
+  for (int c = 0; c < 6; ++c) acc[1 + c] += (double)(e * xCJ[c]);                          // NDT_I:523
+  if (!compute_hessian) return;
+  // xCH(i,j) = (x_trans4 * c_inv4) * point_hessian_.block<4,1>(4i, j)  (NDT_I:534-535); non-zero for i,j >= 3
+  const float ha = xC1 * phv[0] + xC2 * phv[1];
+  const float hb = xC1 * phv[2] + xC2 * phv[3];
+  const float hc = xC1 * phv[4] + xC2 * phv[5];
+  const float hd = (xC0 * phv[6] + xC1 * phv[7]) + xC2 * phv[8];
+  const float he = (xC0 * phv[9] + xC1 * phv[10]) + xC2 * phv[11];
+  const float hf = (xC0 * phv[12] + xC1 * phv[13]) + xC2 * phv[14];
+  const float xCH[3][3] = {{ha, hb, hc}, {hb, hd, he}, {hc, he, hf}};
+  const float nd2 = -d2f;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      // JtCJ(j,i) = point_gradient4.col(j) . CJ.col(i)   (NDT_I:527-528, 542)
+      float jt;
+      if (j < 3) jt = CJ[j][i];
+      else if (j == 3) jt = g13 * CJ[1][i] + g23 * CJ[2][i];
+      else if (j == 4) jt = (g04 * CJ[0][i] + g14 * CJ[1][i]) + g24 * CJ[2][i];
+      else jt = (g05 * CJ[0][i] + g15 * CJ[1][i]) + g25 * CJ[2][i];
+      float v = (nd2 * xCJ[i]) * xCJ[j];
+      if (i >= 3 && j >= 3) v = v + xCH[i - 3][j - 3];
+      v = v + jt;
+      acc[7 + i * 6 + j] += (double)(e * v);                                               // NDT_I:539-542
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) k_derivatives(const AlignState* __restrict__ states, const VoxelTable* __restrict__ tables,
+                                                          const float4* __restrict__ src_pool, const int2* __restrict__ blockmap,
+                                                          int chunk, double* __restrict__ partials) {
+  const int2 bm = blockmap[blockIdx.x];
+  const AlignState& st = states[bm.x];
+  const int mode = st.req.mode;
+  if ((mode != 1 && mode != 2) || st.done) return;
+  __shared__ EvalShared sh;
+  __shared__ double red[kThreads / 32][kPartialStride];
+  const int tid = threadIdx.x;
+  if (tid < 12) sh.T[tid] = st.req.T[tid];
+  if (tid >= 32 && tid < 56) sh.jang[tid - 32] = (&st.req.jang[0][0])[tid - 32];
+  if (tid >= 64 && tid < 109) sh.hang[tid - 64] = (&st.req.hang[0][0])[tid - 64];
+  if (tid == 128) {
+    sh.d1 = st.req.d1; sh.d2 = st.req.d2; sh.d2f = (float)st.req.d2;   // float gauss_d2 = gauss_d2_ (NDT_I:504)
+    sh.mode = mode; sh.method = st.req.search_method;
+    sh.tab = tables[st.target];
+  }
+  __syncthreads();
+  double acc[kAccN];
+#pragma unroll
+  for (int k = 0; k < kAccN; ++k) acc[k] = 0.0;
+  int npairs = 0;
+  const float4* __restrict__ src = src_pool + st.src_offset;
+  const int end = min(bm.y + chunk, st.n_src);
+  const bool ch = mode == 1;
+  const int method = sh.method;
+  for (int i = bm.y + tid; i < end; i += kThreads) {
+    const float4 p = __ldg(src + i);
+    float xt, yt, zt;
+    xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
+    int nb[27];
+    const int cnt = find_neighbors(sh.tab, method, xt, yt, zt, nb);
+    if (cnt == 0) continue;
+    // computePointDerivatives (NDT_I:401-445): x_j_ang = j_ang * x4, x_h_ang = h_ang * x4
+    float pgv[8], phv[15];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) pgv[r] = (sh.jang[r * 3] * p.x + sh.jang[r * 3 + 1] * p.y) + sh.jang[r * 3 + 2] * p.z;
+    if (ch) {
+#pragma unroll
+      for (int r = 0; r < 15; ++r) phv[r] = (sh.hang[r * 3] * p.x + sh.hang[r * 3 + 1] * p.y) + sh.hang[r * 3 + 2] * p.z;
+    }
+    for (int k = 0; k < cnt; ++k) pair_update(acc, sh.tab.rec + nb[k], xt, yt, zt, pgv, phv, sh.d2f, sh.d1, ch);
+    npairs += cnt;
+  }
+  // block reduction: butterfly within the warp, then a fixed-order sum over the warps
+  const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+  for (int k = 0; k < kAccN; ++k) {
+    double v = acc[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[warp][k] = v;
+  }
+  {
+    int v = npairs;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[warp][kAccN] = (double)v;
+  }
+  __syncthreads();
+  if (tid < kPartialStride) {
+    double v = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) v += red[w][tid];
+    partials[(size_t)blockIdx.x * kPartialStride + tid] = v;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// K4: computeHessian / updateHessian (NDT_I:551-641) and calculateScore (NDT_I:919-952): all FP64,
+// neighbours always by radius search.  Only launched when the More-Thuente loop can run
+// (step_size <= trans_eps / 2) or on explicit request.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_hessian_f64(const AlignState* __restrict__ states, const VoxelTable* __restrict__ tables,
+                                                     const float4* __restrict__ src_pool, const int2* __restrict__ blockmap, int chunk,
+                                                     double* __restrict__ partials) {
+  const int2 bm = blockmap[blockIdx.x];
+  const AlignState& st = states[bm.x];
+  const int mode = st.req.mode;
+  if ((mode != 3 && mode != 4) || st.done) return;
+  __shared__ double red[4][kPartialStride];
+  const VoxelTable tab = tables[st.target];
+  const int tid = threadIdx.x;
+  double acc[kAccN];
+  for (int k = 0; k < kAccN; ++k) acc[k] = 0.0;
+  int npairs = 0;
+  const float4* __restrict__ src = src_pool + st.src_offset;
+  const int end = min(bm.y + chunk, st.n_src);
+  const double d1 = st.req.d1, d2 = st.req.d2, d3 = st.req.d3;
+  for (int i = bm.y + tid; i < end; i += 128) {
+    const float4 p = src[i];
+    float xt, yt, zt;
+    xform(st.req.T, p.x, p.y, p.z, xt, yt, zt);
+    int nb[27];
+    const int cnt = find_neighbors(tab, 0, xt, yt, zt, nb);
+    npairs += cnt;
+    const double x[3] = {(double)p.x, (double)p.y, (double)p.z};
+    double pg[3][6];
+    double hv[6][3];  // a b c d e f
+    if (mode == 3 && cnt > 0) {
+      for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 6; ++c) pg[r][c] = (r == c) ? 1.0 : 0.0;
+      auto dj = [&](int r) { return (x[0] * st.req.jang_d[r][0] + x[1] * st.req.jang_d[r][1]) + x[2] * st.req.jang_d[r][2]; };
+      auto dh = [&](int r) { return (x[0] * st.req.hang_d[r][0] + x[1] * st.req.hang_d[r][1]) + x[2] * st.req.hang_d[r][2]; };
+      pg[1][3] = dj(0); pg[2][3] = dj(1); pg[0][4] = dj(2); pg[1][4] = dj(3); pg[2][4] = dj(4); pg[0][5] = dj(5); pg[1][5] = dj(6); pg[2][5] = dj(7);
+      hv[0][0] = 0; hv[0][1] = dh(0); hv[0][2] = dh(1);
+      hv[1][0] = 0; hv[1][1] = dh(2); hv[1][2] = dh(3);
+      hv[2][0] = 0; hv[2][1] = dh(4); hv[2][2] = dh(5);
+      hv[3][0] = dh(6); hv[3][1] = dh(7); hv[3][2] = dh(8);
+      hv[4][0] = dh(9); hv[4][1] = dh(10); hv[4][2] = dh(11);
+      hv[5][0] = dh(12); hv[5][1] = dh(13); hv[5][2] = dh(14);
+    }
+    for (int k = 0; k < cnt; ++k) {
+      const int v = nb[k];
+      const VoxelRec* r = tab.rec + v;
+      const double* C = tab.icov64 + (size_t)v * 9;
+      const double xr[3] = {(double)xt - r->mean[0], (double)yt - r->mean[1], (double)zt - r->mean[2]};
+      double Cx[3];
+      for (int a = 0; a < 3; ++a) Cx[a] = (C[a * 3] * xr[0] + C[a * 3 + 1] * xr[1]) + C[a * 3 + 2] * xr[2];
+      const double q = (xr[0] * Cx[0] + xr[1] * Cx[1]) + xr[2] * Cx[2];
+      if (mode == 4) {
+        const double e = exp(-d2 * q / 2);
+        const double score_inc = -d1 * e - d3;
+        acc[0] += score_inc / cnt;
+        continue;
+      }
+      double e = d2 * exp(-d2 * q / 2);   // NDT_I:619
+      if (e > 1 || e < 0 || e != e) continue;
+      e *= d1;
+      // block (i, j) of point_hessian_: rows 3i..3i+2, column j (NDT_I:478-486)
+      const int hidx[3][3] = {{0, 1, 2}, {1, 3, 4}, {2, 4, 5}};
+      for (int a = 0; a < 6; ++a) {
+        double cd[3];
+        for (int rr = 0; rr < 3; ++rr) cd[rr] = (C[rr * 3] * pg[0][a] + C[rr * 3 + 1] * pg[1][a]) + C[rr * 3 + 2] * pg[2][a];
+        const double xcd = (xr[0] * cd[0] + xr[1] * cd[1]) + xr[2] * cd[2];
+        for (int b = 0; b < 6; ++b) {
+          double cb[3];
+          for (int rr = 0; rr < 3; ++rr) cb[rr] = (C[rr * 3] * pg[0][b] + C[rr * 3 + 1] * pg[1][b]) + C[rr * 3 + 2] * pg[2][b];
+          const double xcb = (xr[0] * cb[0] + xr[1] * cb[1]) + xr[2] * cb[2];
+          double xch = 0.0;
+          if (a >= 3 && b >= 3) {
+            const double* h = hv[hidx[a - 3][b - 3]];
+            double chh[3];
+            for (int rr = 0; rr < 3; ++rr) chh[rr] = (C[rr * 3] * h[0] + C[rr * 3 + 1] * h[1]) + C[rr * 3 + 2] * h[2];
+            xch = (xr[0] * chh[0] + xr[1] * chh[1]) + xr[2] * chh[2];
+          }
+          const double pc = (pg[0][b] * cd[0] + pg[1][b] * cd[1]) + pg[2][b] * cd[2];
+          acc[7 + a * 6 + b] += e * (-d2 * xcd * xcb + xch + pc);   // NDT_I:634-637
+        }
+      }
+    }
+  }
+  const int lane = tid & 31, warp = tid >> 5;
+  for (int k = 0; k < kAccN; ++k) {
+    double v = acc[k];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[warp][k] = v;
+  }
+  {
+    int v = npairs;
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[warp][kAccN] = (double)v;
+  }
+  __syncthreads();
+  if (tid < kPartialStride) {
+    double v = 0;
+    for (int w = 0; w < 4; ++w) v += red[w][tid];
+    partials[(size_t)blockIdx.x * kPartialStride + tid] = v;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// pose helpers (float; Eigen::Translation * AngleAxis(x) * AngleAxis(y) * AngleAxis(z))
+// ---------------------------------------------------------------------------------------
+__device__ void angle_axis_matrix(float angle, int axis_id, float R[3][3]) {
+  // Eigen AngleAxis<float>::toRotationMatrix() for a unit coordinate axis; sinf/cosf evaluated in
+  // double and rounded (the libm-independent definition shared with the oracle)
+  float ax[3] = {0.f, 0.f, 0.f};
+  ax[axis_id] = 1.f;
+  const float s = (float)sin((double)angle), c = (float)cos((double)angle);
+  const float sa[3] = {s * ax[0], s * ax[1], s * ax[2]};
+  const float one_c = 1.f - c;
+  const float ca[3] = {one_c * ax[0], one_c * ax[1], one_c * ax[2]};
+  float tmp;
+  tmp = ca[0] * ax[1]; R[0][1] = tmp - sa[2]; R[1][0] = tmp + sa[2];
+  tmp = ca[0] * ax[2]; R[0][2] = tmp + sa[1]; R[2][0] = tmp - sa[1];
+  tmp = ca[1] * ax[2]; R[1][2] = tmp - sa[0]; R[2][1] = tmp + sa[0];
+  for (int i = 0; i < 3; ++i) R[i][i] = ca[i] * ax[i] + c;
+}
+__device__ void mul3f(const float A[3][3], const float B[3][3], float C[3][3]) {
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) C[i][j] = (A[i][0] * B[0][j] + A[i][1] * B[1][j]) + A[i][2] * B[2][j];
+}
+// NDT_H:210-217, NDT_I:815-819: column-major float 4x4
+__device__ void pose_to_matrix(const double p[6], float T[16]) {
+  float Rx[3][3], Ry[3][3], Rz[3][3], Rxy[3][3], R[3][3];
+  angle_axis_matrix((float)p[3], 0, Rx);
+  angle_axis_matrix((float)p[4], 1, Ry);
+  angle_axis_matrix((float)p[5], 2, Rz);
+  mul3f(Rx, Ry, Rxy);
+  mul3f(Rxy, Rz, R);
+  for (int c = 0; c < 3; ++c) {
+    for (int r = 0; r < 3; ++r) T[c * 4 + r] = R[r][c];
+    T[c * 4 + 3] = 0.f;
+  }
+  T[12] = (float)p[0]; T[13] = (float)p[1]; T[14] = (float)p[2]; T[15] = 1.f;
+}
+
+// computeAngleDerivatives (NDT_I:286-398)
+__device__ void angle_derivatives(const double p[6], EvalReq& rq) {
+  double cx, cy, cz, sx, sy, sz;
+  if (fabs(p[3]) < 10e-5) { cx = 1.0; sx = 0.0; } else { cx = cos(p[3]); sx = sin(p[3]); }
+  if (fabs(p[4]) < 10e-5) { cy = 1.0; sy = 0.0; } else { cy = cos(p[4]); sy = sin(p[4]); }
+  if (fabs(p[5]) < 10e-5) { cz = 1.0; sz = 0.0; } else { cz = cos(p[5]); sz = sin(p[5]); }
+  const double J[8][3] = {
+      {(-sx * sz + cx * sy * cz), (-sx * cz - cx * sy * sz), (-cx * cy)},
+      {(cx * sz + sx * sy * cz), (cx * cz - sx * sy * sz), (-sx * cy)},
+      {(-sy * cz), sy * sz, cy},
+      {sx * cy * cz, (-sx * cy * sz), sx * sy},
+      {(-cx * cy * cz), cx * cy * sz, (-cx * sy)},
+      {(-cy * sz), (-cy * cz), 0},
+      {(cx * cz - sx * sy * sz), (-cx * sz - sx * sy * cz), 0},
+      {(sx * cz + cx * sy * sz), (cx * sy * cz - sx * sz), 0}};
+  for (int r = 0; r < 8; ++r)
+    for (int c = 0; c < 3; ++c) { rq.jang_d[r][c] = J[r][c]; rq.jang[r][c] = (float)J[r][c]; }
+  const double Hh[15][3] = {
+      {(-cx * sz - sx * sy * cz), (-cx * cz + sx * sy * sz), sx * cy},
+      {(-sx * sz + cx * sy * cz), (-cx * sy * sz - sx * cz), (-cx * cy)},
+      {(cx * cy * cz), (-cx * cy * sz), (cx * sy)},
+      {(sx * cy * cz), (-sx * cy * sz), (sx * sy)},
+      {(-sx * cz - cx * sy * sz), (sx * sz - cx * sy * cz), 0},
+      {(cx * cz - sx * sy * sz), (-sx * sy * cz - cx * sz), 0},
+      {(-cy * cz), (cy * sz), (sy)},
+      {(-sx * sy * cz), (sx * sy * sz), (sx * cy)},
+      {(cx * sy * cz), (-cx * sy * sz), (-cx * cy)},
+      {(sy * sz), (sy * cz), 0},
+      {(-sx * cy * sz), (-sx * cy * cz), 0},
+      {(cx * cy * sz), (cx * cy * cz), 0},
+      {(-cy * cz), (cy * sz), 0},
+      {(-cx * sz - sx * sy * cz), (-cx * cz + sx * sy * sz), 0},
+      {(-sx * sz + cx * sy * cz), (-cx * sy * sz - sx * cz), 0}};
+  for (int r = 0; r < 15; ++r)
+    for (int c = 0; c < 3; ++c) { rq.hang_d[r][c] = Hh[r][c]; rq.hang[r][c] = (float)Hh[r][c]; }
+}
+
+__device__ void set_req_transform(AlignState& st) {
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 4; ++c) st.req.T[r * 4 + c] = st.final_T[c * 4 + r];
+}
+
+// x = pinv(H) b by a one-sided Jacobi SVD -- Eigen::JacobiSVD(H, FullU|FullV).solve(b), NDT_I:119-121.
+__device__ void svd_solve6(const double* H, const double* b, double* x) {
+  double U[6][6], V[6][6];
+  for (int i = 0; i < 6; ++i)
+    for (int j = 0; j < 6; ++j) { U[i][j] = H[i * 6 + j]; V[i][j] = (i == j) ? 1.0 : 0.0; }
+  for (int sweep = 0; sweep < 60; ++sweep) {
+    bool rotated = false;
+    for (int p = 0; p < 5; ++p)
+      for (int q = p + 1; q < 6; ++q) {
+        double alpha = 0, beta = 0, gamma = 0;
+        for (int k = 0; k < 6; ++k) { alpha += U[k][p] * U[k][p]; beta += U[k][q] * U[k][q]; gamma += U[k][p] * U[k][q]; }
+        if (gamma == 0.0 || fabs(gamma) <= 1e-16 * sqrt(alpha * beta)) continue;
+        rotated = true;
+        const double zeta = (beta - alpha) / (2.0 * gamma);
+        const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+        const double c = 1.0 / sqrt(1.0 + t * t), s = c * t;
+        for (int k = 0; k < 6; ++k) {
+          const double up = U[k][p], uq = U[k][q];
+          U[k][p] = c * up - s * uq; U[k][q] = s * up + c * uq;
+          const double vp = V[k][p], vq = V[k][q];
+          V[k][p] = c * vp - s * vq; V[k][q] = s * vp + c * vq;
+        }
+      }
+    if (!rotated) break;
+  }
+  double sig[6], smax = 0;
+  for (int j = 0; j < 6; ++j) {
+    double n2 = 0;
+    for (int k = 0; k < 6; ++k) n2 += U[k][j] * U[k][j];
+    sig[j] = sqrt(n2);
+    smax = fmax(smax, sig[j]);
+  }
+  const double thresh = 6.0 * DBL_EPSILON * smax;   // Eigen's default rank threshold: diagSize * epsilon
+  for (int i = 0; i < 6; ++i) x[i] = 0;
+  for (int j = 0; j < 6; ++j) {
+    if (!(sig[j] > thresh)) continue;
+    double ub = 0;
+    for (int k = 0; k < 6; ++k) ub += U[k][j] * b[k];
+    const double coef = ub / (sig[j] * sig[j]);
+    for (int i = 0; i < 6; ++i) x[i] += V[i][j] * coef;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// More-Thuente pieces (NDT_I:644-757), verbatim semantics
+// ---------------------------------------------------------------------------------------
+__device__ bool update_interval_mt(double& a_l, double& f_l, double& g_l, double& a_u, double& f_u, double& g_u, double a_t,
+                                   double f_t, double g_t) {
+  if (f_t > f_l) { a_u = a_t; f_u = f_t; g_u = g_t; return false; }
+  else if (g_t * (a_l - a_t) > 0) { a_l = a_t; f_l = f_t; g_l = g_t; return false; }
+  else if (g_t * (a_l - a_t) < 0) { a_u = a_l; f_u = f_l; g_u = g_l; a_l = a_t; f_l = f_t; g_l = g_t; return false; }
+  return true;
+}
+__device__ double trial_value_mt(double a_l, double f_l, double g_l, double a_u, double f_u, double g_u, double a_t, double f_t,
+                                 double g_t) {
+  if (f_t > f_l) {
+    const double z = 3 * (f_t - f_l) / (a_t - a_l) - g_t - g_l;
+    const double w = sqrt(z * z - g_t * g_l);
+    const double a_c = a_l + (a_t - a_l) * (w - g_l - z) / (g_t - g_l + 2 * w);
+    const double a_q = a_l - 0.5 * (a_l - a_t) * g_l / (g_l - (f_l - f_t) / (a_l - a_t));
+    if (fabs(a_c - a_l) < fabs(a_q - a_l)) return a_c;
+    return 0.5 * (a_q + a_c);
+  } else if (g_t * g_l < 0) {
+    const double z = 3 * (f_t - f_l) / (a_t - a_l) - g_t - g_l;
+    const double w = sqrt(z * z - g_t * g_l);
+    const double a_c = a_l + (a_t - a_l) * (w - g_l - z) / (g_t - g_l + 2 * w);
+    const double a_s = a_l - (a_l - a_t) / (g_l - g_t) * g_l;
+    if (fabs(a_c - a_t) >= fabs(a_s - a_t)) return a_c;
+    return a_s;
+  } else if (fabs(g_t) <= fabs(g_l)) {
+    const double z = 3 * (f_t - f_l) / (a_t - a_l) - g_t - g_l;
+    const double w = sqrt(z * z - g_t * g_l);
+    const double a_c = a_l + (a_t - a_l) * (w - g_l - z) / (g_t - g_l + 2 * w);
+    const double a_s = a_l - (a_l - a_t) / (g_l - g_t) * g_l;
+    const double a_t_next = (fabs(a_c - a_t) < fabs(a_s - a_t)) ? a_c : a_s;
+    if (a_t > a_l) return fmin(a_t + 0.66 * (a_u - a_t), a_t_next);
+    return fmax(a_t + 0.66 * (a_u - a_t), a_t_next);
+  } else {
+    const double z = 3 * (f_t - f_u) / (a_t - a_u) - g_t - g_u;
+    const double w = sqrt(z * z - g_t * g_u);
+    return a_u + (a_t - a_u) * (w - g_u - z) / (g_t - g_u + 2 * w);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// K7: the device-resident Newton / line-search state machine.  One block per registration; after
+// every derivative launch it (1) sums that registration's per-block partials in a fixed order and
+// (2) advances computeTransformation / computeStepLengthMT (NDT_I:73-164, 760-916) until the next
+// evaluation request is ready, with no host round trip.
+// ---------------------------------------------------------------------------------------
+constexpr int PH_START = kPhaseStart, PH_EVAL_ONLY = kPhaseEvalOnly;
+
+struct NewtonCtx {
+  AlignState* st;
+  double* trace;
+  int trace_cap;
+  int* n_active;
+};
+
+__device__ void record(NewtonCtx& c, const double* p, double step, int chflag, int kind) {
+  AlignState& st = *c.st;
+  if (c.trace && st.n_evals < c.trace_cap) {
+    double* d = c.trace + (size_t)st.n_evals * kTraceRec;
+    for (int k = 0; k < 6; ++k) d[k] = p[k];
+    d[6] = st.score;
+    for (int k = 0; k < 6; ++k) d[7 + k] = st.g[k];
+    for (int k = 0; k < 36; ++k) d[13 + k] = st.H[k];
+    d[49] = step; d[50] = chflag; d[51] = kind;
+  }
+  st.n_evals++;
+}
+__device__ void finish(NewtonCtx& c, int converged) {
+  AlignState& st = *c.st;
+  st.trans_probability = st.score / (double)st.n_src;   // NDT_I:127, 163
+  st.converged = converged;
+  st.done = 1;
+  st.phase = PH_DONE;
+  st.req.mode = 0;
+  atomicSub(c.n_active, 1);
+}
+__device__ void request_eval(AlignState& st, int mode) {
+  pose_to_matrix(st.x_t, st.final_T);     // final_transformation_ = T(x_t), NDT_I:815-819 / 857-862
+  set_req_transform(st);
+  angle_derivatives(st.x_t, st.req);      // computeDerivatives -> computeAngleDerivatives(p), NDT_I:199
+  st.req.mode = mode;
+}
+
+// top of the while loop of computeTransformation (NDT_I:114-134) + prologue of computeStepLengthMT
+__device__ void newton_top(NewtonCtx& c) {
+  AlignState& st = *c.st;
+  while (true) {
+    double neg_g[6], delta[6];
+    for (int k = 0; k < 6; ++k) neg_g[k] = -st.g[k];
+    svd_solve6(st.H, neg_g, delta);
+    double n2 = 0;
+    for (int k = 0; k < 6; ++k) n2 += delta[k] * delta[k];
+    const double norm = sqrt(n2);
+    if (norm == 0 || norm != norm) { finish(c, norm == norm ? 1 : 0); return; }   // NDT_I:126-130
+    for (int k = 0; k < 6; ++k) st.dir[k] = delta[k] / norm;                       // delta_p.normalize()
+    st.dir_norm = norm;
+    // computeStepLengthMT(p, dir, norm, step_size_, eps/2, ...)
+    const double step_max = st.step_size, step_min = st.trans_eps / 2;
+    st.phi_0 = -st.score;
+    double dp = 0;
+    for (int k = 0; k < 6; ++k) dp += st.g[k] * st.dir[k];
+    st.d_phi_0 = -dp;
+    if (st.d_phi_0 >= 0) {
+      if (st.d_phi_0 == 0) {
+        // return 0 (NDT_I:776-777): delta_p = 0, p unchanged, no evaluation
+        const double a = 0.0;
+        if (st.nr_iterations > st.max_iter || (st.nr_iterations && (fabs(a) < st.trans_eps))) { st.nr_iterations++; finish(c, 1); return; }
+        st.nr_iterations++;
+        continue;
+      }
+      st.d_phi_0 *= -1;
+      for (int k = 0; k < 6; ++k) st.dir[k] *= -1;
+    }
+    const double mu = 1.e-4;
+    st.step_iterations = 0;
+    st.a_l = 0; st.a_u = 0;
+    st.f_l = st.phi_0 - st.phi_0 - mu * st.d_phi_0 * st.a_l;   // auxilaryFunction_PsiMT, NDT_H:425-429
+    st.g_l = st.d_phi_0 - mu * st.d_phi_0;                     // auxilaryFunction_dPsiMT, NDT_H:437-441
+    st.f_u = st.phi_0 - st.phi_0 - mu * st.d_phi_0 * st.a_u;
+    st.g_u = st.d_phi_0 - mu * st.d_phi_0;
+    st.interval_converged = (step_max - step_min) > 0 ? 1 : 0;  // NDT_I:807 (the reference's inverted test, kept)
+    st.open_interval = 1;
+    double a_t = norm;
+    a_t = fmin(a_t, step_max);
+    a_t = fmax(a_t, step_min);
+    st.a_t = a_t;
+    for (int k = 0; k < 6; ++k) st.x_t[k] = st.p[k] + st.dir[k] * a_t;
+    request_eval(st, 1);
+    st.phase = PH_MT_FIRST;
+    return;
+  }
+}
+
+// after the line search returned a_t (NDT_I:135-157)
+__device__ void post_step(NewtonCtx& c) {
+  AlignState& st = *c.st;
+  const double a = st.a_t;
+  for (int k = 0; k < 6; ++k) st.p[k] = st.p[k] + st.dir[k] * a;
+  int conv = 0;
+  if (st.nr_iterations > st.max_iter || (st.nr_iterations && (fabs(a) < st.trans_eps))) conv = 1;
+  st.nr_iterations++;
+  if (conv) { finish(c, 1); return; }
+  newton_top(c);
+}
+
+__device__ void mt_continue(NewtonCtx& c, double phi_t, double d_phi_t, double psi_t, double d_psi_t) {
+  AlignState& st = *c.st;
+  const double nu = 0.9;
+  const double step_max = st.step_size, step_min = st.trans_eps / 2;
+  if (!st.interval_converged && st.step_iterations < 10 && !(psi_t <= 0 && d_phi_t <= -nu * st.d_phi_0)) {   // NDT_I:839-840
+    double a_t;
+    if (st.open_interval) a_t = trial_value_mt(st.a_l, st.f_l, st.g_l, st.a_u, st.f_u, st.g_u, st.a_t, psi_t, d_psi_t);
+    else a_t = trial_value_mt(st.a_l, st.f_l, st.g_l, st.a_u, st.f_u, st.g_u, st.a_t, phi_t, d_phi_t);
+    a_t = fmin(a_t, step_max);
+    a_t = fmax(a_t, step_min);
+    st.a_t = a_t;
+    for (int k = 0; k < 6; ++k) st.x_t[k] = st.p[k] + st.dir[k] * a_t;
+    request_eval(st, 2);
+    st.phase = PH_MT_LOOP;
+    return;
+  }
+  if (st.step_iterations) {   // NDT_I:912-913
+    st.req.mode = 3;          // same transform, same angle tables ("unnecessary", NDT_I:574)
+    st.phase = PH_MT_HESS;
+    return;
+  }
+  post_step(c);
+}
+
+__global__ void __launch_bounds__(64) k_newton(AlignState* __restrict__ states, int n_items, const double* __restrict__ partials,
+                                               double* __restrict__ trace, int trace_cap, int* __restrict__ n_active) {
+  const int item = blockIdx.x;
+  if (item >= n_items) return;
+  AlignState& st = states[item];
+  if (st.done) return;
+  __shared__ double sums[kPartialStride];
+  const int tid = threadIdx.x;
+  const int mode = st.req.mode;
+  if (mode != 0 && tid < kPartialStride) {
+    double v = 0;
+    const double* p = partials + (size_t)st.first_block * kPartialStride + tid;
+    for (int b = 0; b < st.n_blocks; ++b) v += p[(size_t)b * kPartialStride];   // fixed order: deterministic
+    sums[tid] = v;
+  }
+  __syncthreads();
+  if (tid != 0) return;
+  NewtonCtx c{&st, trace ? trace + (size_t)item * trace_cap * kTraceRec : nullptr, trace_cap, n_active};
+  const double mu = 1.e-4;
+  if (st.phase == PH_START) {
+    // first computeDerivatives of computeTransformation (NDT_I:112): cloud already moved by the guess
+    set_req_transform(st);
+    angle_derivatives(st.p, st.req);
+    st.req.mode = 1;
+    st.phase = PH_INIT;
+    return;
+  }
+  st.pairs = (long long)sums[kAccN];
+  st.pairs_total += st.pairs;
+  switch (st.phase) {
+    case PH_EVAL_ONLY: {
+      st.score = sums[0];
+      for (int k = 0; k < 6; ++k) st.g[k] = sums[1 + k];
+      for (int k = 0; k < 36; ++k) st.H[k] = sums[7 + k];
+      st.req.mode = 0;
+      st.done = 1;
+      atomicSub(n_active, 1);
+      return;
+    }
+    case PH_INIT: {
+      st.score = sums[0];
+      for (int k = 0; k < 6; ++k) st.g[k] = sums[1 + k];
+      for (int k = 0; k < 36; ++k) st.H[k] = sums[7 + k];
+      record(c, st.p, 0.0, 1, 0);
+      newton_top(c);
+      return;
+    }
+    case PH_MT_FIRST:
+    case PH_MT_LOOP: {
+      st.score = sums[0];
+      for (int k = 0; k < 6; ++k) st.g[k] = sums[1 + k];
+      for (int k = 0; k < 36; ++k) st.H[k] = sums[7 + k];   // zeros when compute_hessian == false (NDT_I:184)
+      record(c, st.x_t, st.a_t, st.phase == PH_MT_FIRST ? 1 : 0, st.phase == PH_MT_FIRST ? 1 : 2);
+      const double phi_t = -st.score;
+      double dp = 0;
+      for (int k = 0; k < 6; ++k) dp += st.g[k] * st.dir[k];
+      const double d_phi_t = -dp;
+      const double psi_t = phi_t - st.phi_0 - mu * st.d_phi_0 * st.a_t;
+      const double d_psi_t = d_phi_t - mu * st.d_phi_0;
+      if (st.phase == PH_MT_LOOP) {   // tail of the loop body, NDT_I:881-906
+        if (st.open_interval && (psi_t <= 0 && d_psi_t >= 0)) {
+          st.open_interval = 0;
+          st.f_l = st.f_l + st.phi_0 - mu * st.d_phi_0 * st.a_l;
+          st.g_l = st.g_l + mu * st.d_phi_0;
+          st.f_u = st.f_u + st.phi_0 - mu * st.d_phi_0 * st.a_u;
+          st.g_u = st.g_u + mu * st.d_phi_0;
+        }
+        if (st.open_interval) st.interval_converged = update_interval_mt(st.a_l, st.f_l, st.g_l, st.a_u, st.f_u, st.g_u, st.a_t, psi_t, d_psi_t) ? 1 : 0;
+        else st.interval_converged = update_interval_mt(st.a_l, st.f_l, st.g_l, st.a_u, st.f_u, st.g_u, st.a_t, phi_t, d_phi_t) ? 1 : 0;
+        st.step_iterations++;
+      }
+      mt_continue(c, phi_t, d_phi_t, psi_t, d_psi_t);
+      return;
+    }
+    case PH_MT_HESS: {
+      for (int k = 0; k < 36; ++k) st.H[k] = sums[7 + k];
+      record(c, st.x_t, st.a_t, 1, 3);
+      post_step(c);
+      return;
+    }
+    default: return;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// small utility kernels
+// ---------------------------------------------------------------------------------------
+__global__ void k_neighbors(const VoxelTable* __restrict__ table, const float* __restrict__ xyz, size_t n, int method,
+                            int* __restrict__ cnt, int* __restrict__ ijk) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const VoxelTable t = *table;
+  int nb[27];
+  const int c = find_neighbors(t, method, xyz[i * 3], xyz[i * 3 + 1], xyz[i * 3 + 2], nb);
+  cnt[i] = c;
+  for (int k = 0; k < c; ++k) {
+    int a, b, d;
+    unpack_key(t.vkey[nb[k]], a, b, d);
+    ijk[(i * 27 + k) * 3] = a; ijk[(i * 27 + k) * 3 + 1] = b; ijk[(i * 27 + k) * 3 + 2] = d;
+  }
+}
+__global__ void k_transform(const float4* __restrict__ src, size_t n, const float* __restrict__ T16, float4* __restrict__ out) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float T[12];
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 4; ++c) T[r * 4 + c] = T16[c * 4 + r];
+  const float4 p = src[i];
+  float4 o;
+  xform(T, p.x, p.y, p.z, o.x, o.y, o.z);
+  o.w = p.w;
+  out[i] = o;
+}
+__global__ void k_prepare_eval(AlignState* st, const float* T16, const double* p6, int mode) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  for (int k = 0; k < 16; ++k) st->final_T[k] = T16[k];
+  set_req_transform(*st);
+  double p[6];
+  for (int k = 0; k < 6; ++k) p[k] = p6[k];
+  angle_derivatives(p, st->req);
+  st->req.mode = mode;
+  st->phase = PH_EVAL_ONLY;
+  st->done = 0;
+}
+__global__ void k_prefix_equal(const uint4* __restrict__ a, const uint4* __restrict__ b, size_t n, int* __restrict__ flag) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const uint4 x = a[i], y = b[i];
+    if (x.x != y.x || x.y != y.y || x.z != y.z) { *flag = 0; }
+  }
+}
+
+cudaError_t launch_derivatives(const AlignState* states, const VoxelTable* tables, const float4* src_pool, const int2* blockmap,
+                               int n_blocks, int chunk, double* partials, cudaStream_t s) {
+  if (n_blocks <= 0) return cudaSuccess;
+  k_derivatives<<<n_blocks, kThreads, 0, s>>>(states, tables, src_pool, blockmap, chunk, partials);
+  return cudaGetLastError();
+}
+cudaError_t launch_hessian_f64(const AlignState* states, const VoxelTable* tables, const float4* src_pool, const int2* blockmap,
+                               int n_blocks, int chunk, double* partials, cudaStream_t s) {
+  if (n_blocks <= 0) return cudaSuccess;
+  k_hessian_f64<<<n_blocks, 128, 0, s>>>(states, tables, src_pool, blockmap, chunk, partials);
+  return cudaGetLastError();
+}
+cudaError_t launch_newton(AlignState* states, int n_items, const double* partials, double* trace, int trace_cap, int* n_active,
+                          cudaStream_t s) {
+  if (n_items <= 0) return cudaSuccess;
+  k_newton<<<n_items, 64, 0, s>>>(states, n_items, partials, trace, trace_cap, n_active);
+  return cudaGetLastError();
+}
+cudaError_t launch_neighbors(const VoxelTable* table, const float* xyz, size_t n, int method, int* cnt, int* ijk, cudaStream_t s) {
+  if (n == 0) return cudaSuccess;
+  k_neighbors<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(table, xyz, n, method, cnt, ijk);
+  return cudaGetLastError();
+}
+cudaError_t launch_transform(const float4* src, size_t n, const float* T16, float4* out, cudaStream_t s) {
+  if (n == 0) return cudaSuccess;
+  k_transform<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(src, n, T16, out);
+  return cudaGetLastError();
+}
+cudaError_t launch_prepare_eval(AlignState* st, const float* T16, const double* p6, int mode, cudaStream_t s) {
+  k_prepare_eval<<<1, 32, 0, s>>>(st, T16, p6, mode);
+  return cudaGetLastError();
+}
+cudaError_t launch_prefix_equal(const float4* a, const float4* b, size_t n, int* flag, cudaStream_t s) {
+  if (n == 0) return cudaSuccess;
+  k_prefix_equal<<<296, 256, 0, s>>>(reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b), n, flag);
+  return cudaGetLastError();
+}
+
+}  // namespace ndtb

@@ -1,0 +1,150 @@
+// ndt_internal.h -- device data layout and kernel launch interfaces shared by the .cu files.
+//
+// HBM layout:
+//   points      float4[n]            x, y, z, (unused)            16 B / point, coalesced
+//   HashSlot    16 B                 {packed cell key, voxel index, nr_points}; open addressing,
+//                                    linear probing, load factor <= 0.25, one 128-bit load / probe
+//   VoxelRec    64 B, 64 B-aligned   {mean f64[3], icov f32[9], nr_points}: what one (point, voxel)
+//                                    pair of the derivative kernel reads -- four 128-bit loads
+//   VoxelAcc    per voxel running sums (n, sum x f64[3], sum xx^T f64[6], f32 centroid sum[3]) kept so
+//                                    that an incremental append continues the SAME sequential sums
+//                                    a full rebuild would form (reference VGC_I:233-243)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ndtb {
+
+constexpr int kCoordBias = 1 << 20;               // cell coordinates must lie in (-2^20, 2^20)
+constexpr uint64_t kEmptyKey = 0xFFFFFFFFFFFFFFFFull;
+constexpr int kAccN = 43;                         // score + g[6] + H[36]
+
+__host__ __device__ inline uint64_t pack_key(int i, int j, int k) {
+  return ((uint64_t)(uint32_t)(k + kCoordBias) << 42) | ((uint64_t)(uint32_t)(j + kCoordBias) << 21) |
+         (uint64_t)(uint32_t)(i + kCoordBias);
+}
+__host__ __device__ inline bool coord_ok(int c) { return c > -kCoordBias && c < kCoordBias; }
+__host__ __device__ inline void unpack_key(uint64_t key, int& i, int& j, int& k) {
+  i = (int)(key & 0x1FFFFF) - kCoordBias;
+  j = (int)((key >> 21) & 0x1FFFFF) - kCoordBias;
+  k = (int)((key >> 42) & 0x1FFFFF) - kCoordBias;
+}
+__host__ __device__ inline uint32_t hash_key(uint64_t k) {
+  k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
+  return (uint32_t)k;
+}
+
+struct __align__(16) HashSlot {
+  unsigned long long key;
+  int vidx;
+  int nr_points;   // reference Leaf::nr_points after pass 2 (-1 = flagged invalid)
+};
+
+struct __align__(64) VoxelRec {
+  double mean[3];  // Leaf::mean_
+  float icov[9];   // Leaf::icov_ narrowed to float (NDT_I:502), row-major
+  int nr_points;
+};
+
+struct VoxelTable {          // all pointers device
+  HashSlot* slots;
+  uint32_t mask;             // capacity - 1 (capacity is a power of two)
+  VoxelRec* rec;
+  double* icov64;            // [v][9] Leaf::icov_ in f64, read only by the FP64 computeHessian / calculateScore kernels
+  float4* centroid;          // x, y, z (f32, VGC_I:289), w = bit pattern of inserted point count
+  unsigned long long* vkey;  // packed absolute cell of voxel v
+  int* vn;                   // inserted point count
+  double* vsum;              // [v][3]  sum x
+  double* vsxx;              // [v][6]  Identity + sum xx^T (xx xy xz yy yz zz): Leaf::cov_ starts at I (VGC_H:101)
+  float* vcsum;              // [v][3]  f32 running centroid sum
+  float leaf;                // resolution
+  float inv_leaf;            // 1.0f / leaf (pcl::VoxelGrid::setLeafSize)
+  int min_points;
+  double eig_mult;
+};
+
+// Everything one computeDerivatives launch needs to know about one registration.
+struct EvalReq {
+  float T[12];               // row-major 3x4 float transform applied to the source
+  float jang[8][3];          // NDT_I:329-336
+  float hang[15][3];         // NDT_I:362-396
+  double jang_d[8][3];       // f64 twins for computeHessian (NDT_I:319-326, 340-359)
+  double hang_d[15][3];
+  double d1, d2, d3;         // gauss constants, NDT_I:80-87
+  int mode;                  // 0 idle, 1 derivatives + hessian, 2 derivatives only, 3 computeHessian (f64),
+                             // 4 calculateScore
+  int search_method;
+};
+
+enum Phase { PH_INIT = 0, PH_MT_FIRST = 1, PH_MT_LOOP = 2, PH_MT_HESS = 3, PH_DONE = 4 };
+
+struct AlignState {
+  EvalReq req;
+  // problem
+  int n_src, target, first_block, n_blocks;
+  long long src_offset;      // into the batch's source point pool
+  double step_size, trans_eps;
+  int max_iter;
+  float resolution;
+  // Newton state (NDT_I:73-164)
+  double p[6], score, g[6], H[36], dir[6], dir_norm;
+  int nr_iterations, converged, done, phase, n_evals;
+  float final_T[16];         // column-major, final_transformation_
+  double trans_probability;
+  // More-Thuente state (NDT_I:760-916)
+  double phi_0, d_phi_0, a_l, f_l, g_l, a_u, f_u, g_u, a_t, x_t[6];
+  int step_iterations, open_interval, interval_converged;
+  long long pairs;           // (point, voxel) pairs of the last evaluation (diagnostics)
+  long long pairs_total;     // ... summed over all evaluations of this registration
+};
+
+constexpr int kTraceRec = 52;  // doubles per trace record (see ndtb_get_trace)
+
+// ---- launch wrappers (definitions in the .cu files) --------------------------------------
+struct BuildWorkspace;  // opaque; owns CUB temp storage and sort buffers
+BuildWorkspace* build_ws_create();
+void build_ws_destroy(BuildWorkspace* ws);
+
+// Table storage management
+struct TableStorage {
+  VoxelTable t{};
+  size_t vox_cap = 0;        // capacity of per-voxel arrays
+  size_t slot_cap = 0;       // hash capacity (power of two)
+  int n_vox = 0;             // voxels in use (host mirror)
+  bool valid = false;        // false = empty grid (no target / overflow guard VGC_I:79-84)
+  int min_b[3] = {0, 0, 0}, max_b[3] = {0, 0, 0};
+  float mn[3], mx[3];        // float bounding box of all inserted points
+  bool have_bbox = false;
+};
+cudaError_t table_reserve(TableStorage& ts, size_t n_vox_needed, cudaStream_t s, long long* launches);
+void table_free(TableStorage& ts);
+cudaError_t table_clear(TableStorage& ts, cudaStream_t s, long long* launches);
+// Merge n points (device float4, input order preserved) into the table: new voxels appended,
+// touched voxels re-finalised.  Equivalent to a full rebuild over (old points ++ new points).
+cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts, size_t n, cudaStream_t s,
+                         long long* launches);
+
+cudaError_t launch_derivatives(const AlignState* states, const VoxelTable* tables, const float4* src_pool,
+                               const int2* blockmap, int n_blocks, int chunk, double* partials,
+                               cudaStream_t s);
+cudaError_t launch_hessian_f64(const AlignState* states, const VoxelTable* tables, const float4* src_pool,
+                               const int2* blockmap, int n_blocks, int chunk, double* partials, cudaStream_t s);
+cudaError_t launch_newton(AlignState* states, int n_items, const double* partials, double* trace, int trace_cap,
+                          int* n_active, cudaStream_t s);
+cudaError_t launch_neighbors(const VoxelTable* table, const float* xyz, size_t n, int method, int* cnt, int* ijk,
+                             cudaStream_t s);
+cudaError_t launch_transform(const float4* src, size_t n, const float* T16_colmajor_dev, float4* out, cudaStream_t s);
+cudaError_t launch_prepare_eval(AlignState* st, const float* T16_dev, const double* p6_dev, int mode, cudaStream_t s);
+cudaError_t launch_prefix_equal(const float4* a, const float4* b, size_t n, int* flag, cudaStream_t s);
+
+// fitness (exact 1-NN over the raw target, grid of key-sorted points)
+struct NNGridStorage;
+NNGridStorage* nn_create();
+void nn_destroy(NNGridStorage* g);
+cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, size_t n, float cell, cudaStream_t s,
+                     long long* launches);
+cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float* T16_dev, float* d2_out,
+                     cudaStream_t s);
+constexpr int kPhaseStart = 10, kPhaseEvalOnly = 11;   // AlignState::phase values used by the host
+
+}  // namespace ndtb

@@ -1,0 +1,649 @@
+// voxel_build.cu -- target VoxelGridCovariance build on the GPU (K1/K2 of SURVEY.md 2.3).
+//
+// Replaces pclomp::VoxelGridCovariance::applyFilter (reference
+// xchu_mapping/include/pclomp/voxel_grid_covariance_omp_impl.hpp:48-370, VGC_I below):
+//   pass 1 (VGC_I:209-264, std::map insert per point)  ->  packed-key radix sort + run detection,
+//          then ONE thread per voxel walks its points in input order (the sort is stable), forming
+//          exactly the sequential f64 / f32 sums the reference forms, so the single-pass covariance
+//          (which cancels catastrophically, VGC_I:329) sees the same rounded sums;
+//   pass 2 (VGC_I:282-367) -> per-voxel finalise: mean, covariance, symmetric 3x3 eigen
+//          decomposition, eigenvalue inflation, inverse, validity flags, written to a 64 B record
+//          and an open-addressing hash table keyed by the absolute cell coordinate.
+// Appending points (incremental rebuild on localmap refresh) runs the same kernels on the new
+// points only and continues the stored running sums of the voxels they touch; the result is
+// bit-identical to a full rebuild over the concatenated cloud.
+#include <cub/cub.cuh>
+
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+
+#include "ndt_internal.h"
+
+namespace ndtb {
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
+
+struct BuildWorkspace {
+  size_t cap = 0;
+  unsigned long long *keys_in = nullptr, *keys_out = nullptr;
+  unsigned int *idx_in = nullptr, *idx_out = nullptr;
+  int *flags = nullptr, *scan = nullptr, *run_start = nullptr, *run_vidx = nullptr, *run_slot = nullptr,
+      *run_isnew = nullptr, *new_prefix = nullptr;
+  void* cub_temp = nullptr;
+  size_t cub_bytes = 0;
+  float* mm = nullptr;      // device: 6 floats (min xyz, max xyz)
+  int* counts = nullptr;    // device: [0] = num_runs, [1] = n_new
+  float* h_mm = nullptr;    // pinned
+  int* h_counts = nullptr;  // pinned
+};
+
+BuildWorkspace* build_ws_create() {
+  BuildWorkspace* ws = new BuildWorkspace();
+  if (cudaMalloc(&ws->mm, 6 * sizeof(float)) != cudaSuccess || cudaMalloc(&ws->counts, 4 * sizeof(int)) != cudaSuccess ||
+      cudaMallocHost(&ws->h_mm, 6 * sizeof(float)) != cudaSuccess || cudaMallocHost(&ws->h_counts, 4 * sizeof(int)) != cudaSuccess) {
+    delete ws;
+    return nullptr;
+  }
+  return ws;
+}
+static void ws_free_arrays(BuildWorkspace* ws) {
+  cudaFree(ws->keys_in); cudaFree(ws->keys_out); cudaFree(ws->idx_in); cudaFree(ws->idx_out);
+  cudaFree(ws->flags); cudaFree(ws->scan); cudaFree(ws->run_start); cudaFree(ws->run_vidx); cudaFree(ws->run_slot);
+  cudaFree(ws->run_isnew); cudaFree(ws->new_prefix); cudaFree(ws->cub_temp);
+  ws->keys_in = ws->keys_out = nullptr; ws->idx_in = ws->idx_out = nullptr;
+  ws->flags = ws->scan = ws->run_start = ws->run_vidx = ws->run_slot = ws->run_isnew = ws->new_prefix = nullptr;
+  ws->cub_temp = nullptr; ws->cub_bytes = 0; ws->cap = 0;
+}
+void build_ws_destroy(BuildWorkspace* ws) {
+  if (!ws) return;
+  ws_free_arrays(ws);
+  cudaFree(ws->mm); cudaFree(ws->counts); cudaFreeHost(ws->h_mm); cudaFreeHost(ws->h_counts);
+  delete ws;
+}
+static cudaError_t ws_reserve(BuildWorkspace* ws, size_t n) {
+  if (n <= ws->cap) return cudaSuccess;
+  ws_free_arrays(ws);
+  const size_t cap = n + n / 4 + 1024;
+  CK(cudaMalloc(&ws->keys_in, cap * 8)); CK(cudaMalloc(&ws->keys_out, cap * 8));
+  CK(cudaMalloc(&ws->idx_in, cap * 4)); CK(cudaMalloc(&ws->idx_out, cap * 4));
+  CK(cudaMalloc(&ws->flags, cap * 4)); CK(cudaMalloc(&ws->scan, cap * 4));
+  CK(cudaMalloc(&ws->run_start, (cap + 1) * 4)); CK(cudaMalloc(&ws->run_vidx, cap * 4)); CK(cudaMalloc(&ws->run_slot, cap * 4));
+  CK(cudaMalloc(&ws->run_isnew, cap * 4)); CK(cudaMalloc(&ws->new_prefix, cap * 4));
+  size_t b1 = 0, b2 = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, b1, ws->keys_in, ws->keys_out, ws->idx_in, ws->idx_out, (int)cap, 0, 64);
+  cub::DeviceScan::InclusiveSum(nullptr, b2, ws->flags, ws->scan, (int)cap);
+  ws->cub_bytes = (b1 > b2 ? b1 : b2) + 256;
+  CK(cudaMalloc(&ws->cub_temp, ws->cub_bytes));
+  ws->cap = cap;
+  return cudaSuccess;
+}
+
+// ---------------------------------------------------------------------------------------
+// table storage
+// ---------------------------------------------------------------------------------------
+void table_free(TableStorage& ts) {
+  VoxelTable& t = ts.t;
+  cudaFree(t.slots); cudaFree(t.rec); cudaFree(t.icov64); cudaFree(t.centroid); cudaFree(t.vkey); cudaFree(t.vn);
+  cudaFree(t.vsum); cudaFree(t.vsxx); cudaFree(t.vcsum);
+  t.slots = nullptr; t.rec = nullptr; t.icov64 = nullptr; t.centroid = nullptr; t.vkey = nullptr; t.vn = nullptr;
+  t.vsum = nullptr; t.vsxx = nullptr; t.vcsum = nullptr;
+  ts.vox_cap = ts.slot_cap = 0; ts.n_vox = 0; ts.valid = false; ts.have_bbox = false;
+}
+
+__global__ void k_fill_slots(HashSlot* slots, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { HashSlot s; s.key = kEmptyKey; s.vidx = -1; s.nr_points = 0; slots[i] = s; }
+}
+__global__ void k_rehash(HashSlot* slots, uint32_t mask, const unsigned long long* vkey, const VoxelRec* rec, int n_vox) {
+  int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_vox) return;
+  const unsigned long long key = vkey[v];
+  uint32_t h = hash_key(key) & mask;
+  while (true) {
+    unsigned long long prev = atomicCAS(&slots[h].key, kEmptyKey, key);
+    if (prev == kEmptyKey || prev == key) { slots[h].vidx = v; slots[h].nr_points = rec[v].nr_points; return; }
+    h = (h + 1) & mask;
+  }
+}
+
+template <typename T>
+static cudaError_t grow(T*& p, size_t old_n, size_t new_n, cudaStream_t s) {
+  T* q = nullptr;
+  CK(cudaMalloc(&q, new_n * sizeof(T)));
+  if (p && old_n) CK(cudaMemcpyAsync(q, p, old_n * sizeof(T), cudaMemcpyDeviceToDevice, s));
+  CK(cudaStreamSynchronize(s));
+  cudaFree(p);
+  p = q;
+  return cudaSuccess;
+}
+
+cudaError_t table_reserve(TableStorage& ts, size_t need, cudaStream_t s, long long* launches) {
+  VoxelTable& t = ts.t;
+  if (need > ts.vox_cap) {
+    const size_t nc = need + need / 2 + 4096;
+    const size_t used = (size_t)ts.n_vox;
+    CK(grow(t.rec, used, nc, s)); CK(grow(t.icov64, used * 9, nc * 9, s)); CK(grow(t.centroid, used, nc, s)); CK(grow(t.vkey, used, nc, s)); CK(grow(t.vn, used, nc, s));
+    CK(grow(t.vsum, used * 3, nc * 3, s)); CK(grow(t.vsxx, used * 6, nc * 6, s)); CK(grow(t.vcsum, used * 3, nc * 3, s));
+    ts.vox_cap = nc;
+  }
+  size_t want = 1024;
+  while (want < need * 4) want <<= 1;   // load factor <= 0.25
+  if (want > ts.slot_cap) {
+    cudaFree(t.slots);
+    t.slots = nullptr;
+    CK(cudaMalloc(&t.slots, want * sizeof(HashSlot)));
+    ts.slot_cap = want;
+    t.mask = (uint32_t)(want - 1);
+    k_fill_slots<<<(unsigned)((want + 255) / 256), 256, 0, s>>>(t.slots, want);
+    if (launches) ++*launches;
+    if (ts.n_vox > 0) {
+      k_rehash<<<(ts.n_vox + 255) / 256, 256, 0, s>>>(t.slots, t.mask, t.vkey, t.rec, ts.n_vox);
+      if (launches) ++*launches;
+    }
+    CK(cudaGetLastError());
+  }
+  return cudaSuccess;
+}
+
+cudaError_t table_clear(TableStorage& ts, cudaStream_t s, long long* launches) {
+  ts.n_vox = 0;
+  ts.valid = false;
+  ts.have_bbox = false;
+  if (ts.slot_cap) {
+    k_fill_slots<<<(unsigned)((ts.slot_cap + 255) / 256), 256, 0, s>>>(ts.t.slots, ts.slot_cap);
+    if (launches) ++*launches;
+    CK(cudaGetLastError());
+  }
+  return cudaSuccess;
+}
+
+// ---------------------------------------------------------------------------------------
+// kernels
+// ---------------------------------------------------------------------------------------
+__global__ void k_minmax(const float4* __restrict__ pts, size_t n, float* __restrict__ out6, int first) {
+  // single-block-per-grid-stride reduction; launched with a modest grid, finished with atomics on
+  // order-preserving integer images of the floats.
+  float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 p = pts[i];
+    mn[0] = fminf(mn[0], p.x); mn[1] = fminf(mn[1], p.y); mn[2] = fminf(mn[2], p.z);
+    mx[0] = fmaxf(mx[0], p.x); mx[1] = fmaxf(mx[1], p.y); mx[2] = fmaxf(mx[2], p.z);
+  }
+  for (int a = 0; a < 3; ++a)
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[a] = fminf(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+      mx[a] = fmaxf(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+    }
+  if ((threadIdx.x & 31) == 0) {
+    auto enc = [](float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7FFFFFFF; };
+    int* o = reinterpret_cast<int*>(out6);
+    for (int a = 0; a < 3; ++a) { atomicMin(&o[a], enc(mn[a])); atomicMax(&o[3 + a], enc(mx[a])); }
+  }
+}
+__global__ void k_minmax_init(float* out6) {
+  int* o = reinterpret_cast<int*>(out6);
+  if (threadIdx.x < 3) o[threadIdx.x] = 0x7FFFFFFF;
+  else if (threadIdx.x < 6) o[threadIdx.x] = (int)0x80000000;
+}
+__global__ void k_minmax_decode(float* out6) {
+  int* o = reinterpret_cast<int*>(out6);
+  if (threadIdx.x < 6) { int i = o[threadIdx.x]; i = i >= 0 ? i : i ^ 0x7FFFFFFF; out6[threadIdx.x] = __int_as_float(i); }
+}
+
+// Build-time cell coordinate: floor(x * inverse_leaf_size) (VGC_I:218-220; the subtraction of
+// float(min_b) there is exact for |cell| < 2^24, so the absolute cell is the same integer).
+__device__ __forceinline__ int build_cell(float x, float inv_leaf) { return (int)floorf(x * inv_leaf); }
+
+__global__ void k_keys(const float4* __restrict__ pts, size_t n, float inv_leaf, int i0, int j0, int k0, int bi, int bj,
+                       unsigned long long* __restrict__ keys, unsigned int* __restrict__ idx) {
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const float4 p = pts[t];
+  const unsigned long long i = (unsigned long long)(build_cell(p.x, inv_leaf) - i0);
+  const unsigned long long j = (unsigned long long)(build_cell(p.y, inv_leaf) - j0);
+  const unsigned long long k = (unsigned long long)(build_cell(p.z, inv_leaf) - k0);
+  keys[t] = (k << (bi + bj)) | (j << bi) | i;   // ascending == reference linear index order (k, j, i)
+  idx[t] = (unsigned int)t;
+}
+__global__ void k_flags(const unsigned long long* __restrict__ keys, size_t n, int* __restrict__ flags) {
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  flags[t] = (t == 0 || keys[t] != keys[t - 1]) ? 1 : 0;
+}
+__global__ void k_run_starts(const int* __restrict__ flags, const int* __restrict__ scan, size_t n, int* __restrict__ run_start,
+                             int* __restrict__ counts) {
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  if (flags[t]) run_start[scan[t] - 1] = (int)t;
+  if (t == n - 1) { run_start[scan[t]] = (int)n; counts[0] = scan[t]; }
+}
+
+__device__ __forceinline__ int probe_find(const HashSlot* slots, uint32_t mask, unsigned long long key, int* slot_out) {
+  uint32_t h = hash_key(key) & mask;
+  while (true) {
+    const unsigned long long k = slots[h].key;
+    if (k == key) { *slot_out = (int)h; return slots[h].vidx; }
+    if (k == kEmptyKey) { *slot_out = -1; return -1; }
+    h = (h + 1) & mask;
+  }
+}
+
+__global__ void k_run_lookup(const float4* __restrict__ pts, const unsigned int* __restrict__ sorted_idx,
+                             const int* __restrict__ run_start, int n_runs, VoxelTable t, int* __restrict__ run_vidx,
+                             int* __restrict__ run_slot, int* __restrict__ run_isnew) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_runs) return;
+  const float4 p = pts[sorted_idx[run_start[r]]];
+  const unsigned long long key = pack_key(build_cell(p.x, t.inv_leaf), build_cell(p.y, t.inv_leaf), build_cell(p.z, t.inv_leaf));
+  int slot;
+  const int v = probe_find(t.slots, t.mask, key, &slot);
+  run_vidx[r] = v;
+  run_slot[r] = slot;
+  run_isnew[r] = v < 0 ? 1 : 0;
+}
+
+// ---- per-voxel finalisation (VGC_I:282-367) ---------------------------------------------
+struct Mat3 { double a[3][3]; };
+
+__device__ __forceinline__ double cof3(const Mat3& m, int i, int j) {
+  const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+  return m.a[i1][j1] * m.a[i2][j2] - m.a[i1][j2] * m.a[i2][j1];
+}
+// general 3x3 inverse by cofactors (what Matrix3d::inverse() evaluates, VGC_I:355, 359)
+__device__ void inverse3(const Mat3& m, Mat3& r) {
+  const double c00 = cof3(m, 0, 0), c10 = cof3(m, 1, 0), c20 = cof3(m, 2, 0);
+  const double det = (c00 * m.a[0][0] + c10 * m.a[1][0]) + c20 * m.a[2][0];
+  const double invdet = 1.0 / det;
+  r.a[0][0] = c00 * invdet; r.a[0][1] = c10 * invdet; r.a[0][2] = c20 * invdet;
+  for (int j = 1; j < 3; ++j)
+    for (int i = 0; i < 3; ++i) r.a[j][i] = cof3(m, i, j) * invdet;
+}
+__device__ void mul3(const Mat3& x, const Mat3& y, Mat3& r) {
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) r.a[i][j] = (x.a[i][0] * y.a[0][j] + x.a[i][1] * y.a[1][j]) + x.a[i][2] * y.a[2][j];
+}
+
+// Symmetric 3x3 eigen-decomposition of the lower triangle of `in` by cyclic Jacobi rotations
+// (each rotation is a closed-form 2x2 diagonalisation; 3-5 sweeps reach full double accuracy).
+// A one-shot trigonometric closed form was rejected: the parity bar on icov is 1e-10 relative and
+// the trigonometric eigenvectors lose that for the near-degenerate (planar / linear) voxels that
+// dominate LiDAR maps.  Eigenvalues ascending, eigenvectors in the columns of V.
+__device__ void eigh3(const Mat3& in, double w[3], Mat3& V) {
+  double A[3][3];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j <= i; ++j) A[i][j] = A[j][i] = in.a[i][j];
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) V.a[i][j] = (i == j) ? 1.0 : 0.0;
+  for (int sweep = 0; sweep < 32; ++sweep) {
+    const double off = A[0][1] * A[0][1] + A[0][2] * A[0][2] + A[1][2] * A[1][2];
+    const double dia = A[0][0] * A[0][0] + A[1][1] * A[1][1] + A[2][2] * A[2][2];
+    if (off == 0.0 || off <= 1e-34 * dia) break;
+#pragma unroll
+    for (int pq = 0; pq < 3; ++pq) {
+      const int p = pq == 2 ? 1 : 0, q = pq == 0 ? 1 : 2;
+      const double apq = A[p][q];
+      if (apq == 0.0) continue;
+      const double theta = (A[q][q] - A[p][p]) / (2.0 * apq);
+      const double t = (theta >= 0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+      const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
+      for (int k = 0; k < 3; ++k) { const double x = A[k][p], y = A[k][q]; A[k][p] = c * x - s * y; A[k][q] = s * x + c * y; }
+      for (int k = 0; k < 3; ++k) { const double x = A[p][k], y = A[q][k]; A[p][k] = c * x - s * y; A[q][k] = s * x + c * y; }
+      for (int k = 0; k < 3; ++k) { const double x = V.a[k][p], y = V.a[k][q]; V.a[k][p] = c * x - s * y; V.a[k][q] = s * x + c * y; }
+    }
+  }
+  // ascending order (3-element sorting network on the diagonal)
+  double d[3] = {A[0][0], A[1][1], A[2][2]};
+  int o[3] = {0, 1, 2};
+  if (d[o[1]] < d[o[0]]) { int x = o[0]; o[0] = o[1]; o[1] = x; }
+  if (d[o[2]] < d[o[1]]) { int x = o[1]; o[1] = o[2]; o[2] = x; }
+  if (d[o[1]] < d[o[0]]) { int x = o[0]; o[0] = o[1]; o[1] = x; }
+  Mat3 Vs;
+  for (int k = 0; k < 3; ++k) {
+    w[k] = d[o[k]];
+    for (int i = 0; i < 3; ++i) Vs.a[i][k] = V.a[i][o[k]];
+  }
+  V = Vs;
+}
+
+__device__ void finalize_voxel(const VoxelTable& t, int v, int n, const double sum[3], const double sxx[6], const float csum[3],
+                               int slot) {
+  VoxelRec rec;
+  const float nf = (float)n;
+  float4 c;
+  c.x = csum[0] / nf; c.y = csum[1] / nf; c.z = csum[2] / nf; c.w = __int_as_float(n);
+  double mean[3];
+  for (int a = 0; a < 3; ++a) mean[a] = sum[a] / (double)n;
+  for (int a = 0; a < 3; ++a) rec.mean[a] = mean[a];
+  for (int a = 0; a < 9; ++a) rec.icov[a] = 0.f;
+  double ic64[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  int nr = n;
+  if (n >= t.min_points) {
+    Mat3 cov;
+    const int sidx[3][3] = {{0, 1, 2}, {1, 3, 4}, {2, 4, 5}};
+    for (int a = 0; a < 3; ++a)
+      for (int b = 0; b < 3; ++b)
+        cov.a[a][b] = (sxx[sidx[a][b]] - 2 * (sum[a] * mean[b])) / (double)n + mean[a] * mean[b];  // VGC_I:329
+    const double f = ((double)n - 1.0) / (double)n;                                                 // VGC_I:330
+    for (int a = 0; a < 3; ++a)
+      for (int b = 0; b < 3; ++b) cov.a[a][b] *= f;
+    double w[3];
+    Mat3 V;
+    eigh3(cov, w, V);
+    if (w[0] < 0 || w[1] < 0 || w[2] <= 0) {
+      nr = -1;  // VGC_I:337-341: icov_ stays Zero
+    } else {
+      const double min_ev = t.eig_mult * w[2];
+      if (w[0] < min_ev) {  // VGC_I:346-356
+        w[0] = min_ev;
+        if (w[1] < min_ev) w[1] = min_ev;
+        Mat3 D, VD, Vi;
+        for (int a = 0; a < 3; ++a)
+          for (int b = 0; b < 3; ++b) D.a[a][b] = (a == b) ? w[a] : 0.0;
+        mul3(V, D, VD);
+        inverse3(V, Vi);
+        mul3(VD, Vi, cov);
+      }
+      Mat3 icov;
+      inverse3(cov, icov);
+      double mxc = -INFINITY, mnc = INFINITY;
+      for (int a = 0; a < 3; ++a)
+        for (int b = 0; b < 3; ++b) { mxc = fmax(mxc, icov.a[a][b]); mnc = fmin(mnc, icov.a[a][b]); rec.icov[a * 3 + b] = (float)icov.a[a][b]; ic64[a * 3 + b] = icov.a[a][b]; }
+      // fmax/fmin ignore NaN like Eigen's maxCoeff does not; the +-inf test is what VGC_I:360-364 checks
+      if (mxc == INFINITY || mnc == -INFINITY) nr = -1;
+    }
+  }
+  rec.nr_points = nr;
+  t.rec[v] = rec;
+  for (int a = 0; a < 9; ++a) t.icov64[(size_t)v * 9 + a] = ic64[a];
+  t.centroid[v] = c;
+  t.slots[slot].nr_points = nr;
+}
+
+__global__ void k_run_merge(const float4* __restrict__ pts, const unsigned int* __restrict__ sorted_idx,
+                            const int* __restrict__ run_start, const int* __restrict__ run_vidx,
+                            const int* __restrict__ run_slot, const int* __restrict__ new_prefix, int n_runs, int n_vox_old,
+                            VoxelTable t, int* __restrict__ counts) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_runs) return;
+  const int s0 = run_start[r], s1 = run_start[r + 1];
+  int v = run_vidx[r];
+  int slot = run_slot[r];
+  double sum[3] = {0, 0, 0};
+  double sxx[6] = {1.0, 0, 0, 1.0, 0, 1.0};  // Leaf::cov_ starts at Identity (VGC_H:101) and is accumulated onto
+  float cs[3] = {0.f, 0.f, 0.f};
+  int n = 0;
+  if (v >= 0) {
+    n = t.vn[v];
+    for (int a = 0; a < 3; ++a) { sum[a] = t.vsum[(size_t)v * 3 + a]; cs[a] = t.vcsum[(size_t)v * 3 + a]; }
+    for (int a = 0; a < 6; ++a) sxx[a] = t.vsxx[(size_t)v * 6 + a];
+  } else {
+    v = n_vox_old + new_prefix[r];
+    const float4 p = pts[sorted_idx[s0]];
+    const unsigned long long key = pack_key(build_cell(p.x, t.inv_leaf), build_cell(p.y, t.inv_leaf), build_cell(p.z, t.inv_leaf));
+    t.vkey[v] = key;
+    uint32_t h = hash_key(key) & t.mask;
+    while (true) {
+      const unsigned long long prev = atomicCAS(&t.slots[h].key, kEmptyKey, key);
+      if (prev == kEmptyKey) break;
+      h = (h + 1) & t.mask;
+    }
+    t.slots[h].vidx = v;
+    slot = (int)h;
+    if (r == n_runs - 1) counts[1] = new_prefix[r] + 1;
+  }
+  if (r == n_runs - 1 && run_vidx[r] >= 0) counts[1] = new_prefix[r];
+  for (int s = s0; s < s1; ++s) {  // input order within the voxel (stable sort) == reference order
+    const float4 p = pts[sorted_idx[s]];
+    const double x = (double)p.x, y = (double)p.y, z = (double)p.z;
+    sum[0] += x; sum[1] += y; sum[2] += z;
+    sxx[0] += x * x; sxx[1] += x * y; sxx[2] += x * z; sxx[3] += y * y; sxx[4] += y * z; sxx[5] += z * z;
+    cs[0] += p.x; cs[1] += p.y; cs[2] += p.z;
+  }
+  n += s1 - s0;
+  t.vn[v] = n;
+  for (int a = 0; a < 3; ++a) { t.vsum[(size_t)v * 3 + a] = sum[a]; t.vcsum[(size_t)v * 3 + a] = cs[a]; }
+  for (int a = 0; a < 6; ++a) t.vsxx[(size_t)v * 6 + a] = sxx[a];
+  finalize_voxel(t, v, n, sum, sxx, cs, slot);
+}
+
+static int bits_for(long long range) {
+  int b = 1;
+  while ((1ll << b) < range) ++b;
+  return b;
+}
+
+cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts, size_t n, cudaStream_t s, long long* launches) {
+  if (n == 0) return cudaSuccess;
+  VoxelTable& t = ts.t;
+  CK(ws_reserve(ws, n));
+  long long dummy = 0;
+  long long& L = launches ? *launches : dummy;
+  // bounding box of the new points
+  k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
+  k_minmax<<<296, 256, 0, s>>>(pts, n, ws->mm, 1);
+  k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
+  L += 3;
+  CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  float nmn[3], nmx[3];
+  for (int a = 0; a < 3; ++a) { nmn[a] = ws->h_mm[a]; nmx[a] = ws->h_mm[3 + a]; }
+  for (int a = 0; a < 3; ++a) {
+    ts.mn[a] = ts.have_bbox ? fminf(ts.mn[a], nmn[a]) : nmn[a];
+    ts.mx[a] = ts.have_bbox ? fmaxf(ts.mx[a], nmx[a]) : nmx[a];
+  }
+  ts.have_bbox = true;
+  // overflow guard of the reference, on the bounding box of the WHOLE target (VGC_I:75-84)
+  const float inv = t.inv_leaf;
+  const long long dx = (long long)((ts.mx[0] - ts.mn[0]) * inv) + 1, dy = (long long)((ts.mx[1] - ts.mn[1]) * inv) + 1,
+                  dz = (long long)((ts.mx[2] - ts.mn[2]) * inv) + 1;
+  bool ok = dx * dy * dz <= 2147483647ll;
+  for (int a = 0; a < 3; ++a) {
+    ts.min_b[a] = (int)floorf(ts.mn[a] * inv);   // VGC_I:87-92
+    ts.max_b[a] = (int)floorf(ts.mx[a] * inv);
+    if (!coord_ok(ts.min_b[a]) || !coord_ok(ts.max_b[a])) ok = false;
+    if (!(ts.mn[a] == ts.mn[a]) || !(ts.mx[a] == ts.mx[a])) ok = false;
+  }
+  if (!ok) {  // "Leaf size is too small for the input dataset": the reference leaves an EMPTY grid
+    ts.valid = false;
+    ts.n_vox = 0;
+    if (ts.slot_cap) { k_fill_slots<<<(unsigned)((ts.slot_cap + 255) / 256), 256, 0, s>>>(t.slots, ts.slot_cap); ++L; }
+    return cudaGetLastError();
+  }
+  ts.valid = true;
+  int c0[3], c1[3];
+  for (int a = 0; a < 3; ++a) { c0[a] = (int)floorf(nmn[a] * inv); c1[a] = (int)floorf(nmx[a] * inv); }
+  const int bi = bits_for((long long)c1[0] - c0[0] + 1), bj = bits_for((long long)c1[1] - c0[1] + 1), bk = bits_for((long long)c1[2] - c0[2] + 1);
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  k_keys<<<nb, 256, 0, s>>>(pts, n, inv, c0[0], c0[1], c0[2], bi, bj, ws->keys_in, ws->idx_in);
+  ++L;
+  size_t tb = ws->cub_bytes;
+  CK(cub::DeviceRadixSort::SortPairs(ws->cub_temp, tb, ws->keys_in, ws->keys_out, ws->idx_in, ws->idx_out, (int)n, 0, bi + bj + bk, s));
+  L += (bi + bj + bk + 7) / 8 + 2;  // CUB onesweep: histogram + scan + one pass per 8 key bits (library kernels)
+  k_flags<<<nb, 256, 0, s>>>(ws->keys_out, n, ws->flags);
+  tb = ws->cub_bytes;
+  CK(cub::DeviceScan::InclusiveSum(ws->cub_temp, tb, ws->flags, ws->scan, (int)n, s));
+  k_run_starts<<<nb, 256, 0, s>>>(ws->flags, ws->scan, n, ws->run_start, ws->counts);
+  L += 4;
+  CK(cudaMemcpyAsync(ws->h_counts, ws->counts, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  const int n_runs = ws->h_counts[0];
+  CK(table_reserve(ts, (size_t)ts.n_vox + n_runs, s, launches));
+  const unsigned rb = (unsigned)((n_runs + 127) / 128);
+  k_run_lookup<<<rb, 128, 0, s>>>(pts, ws->idx_out, ws->run_start, n_runs, t, ws->run_vidx, ws->run_slot, ws->run_isnew);
+  tb = ws->cub_bytes;
+  CK(cub::DeviceScan::ExclusiveSum(ws->cub_temp, tb, ws->run_isnew, ws->new_prefix, n_runs, s));
+  k_run_merge<<<rb, 128, 0, s>>>(pts, ws->idx_out, ws->run_start, ws->run_vidx, ws->run_slot, ws->new_prefix, n_runs, ts.n_vox, t,
+                                 ws->counts);
+  L += 4;
+  CK(cudaMemcpyAsync(ws->h_counts + 1, ws->counts + 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  ts.n_vox += ws->h_counts[1];
+  return cudaGetLastError();
+}
+
+
+// ---------------------------------------------------------------------------------------
+// Exact 1-NN over the raw target for pcl::Registration::getFitnessScore (K6): target points
+// sorted by cell, cell -> [start, end) in a hash table, ring search with the same stopping rule
+// as a kd-tree search would give (exact minimum of the float squared distances).
+// ---------------------------------------------------------------------------------------
+struct __align__(16) CellSlot { unsigned long long key; int start; int end; };
+struct NNGridStorage {
+  float4* sorted = nullptr;
+  size_t pts_cap = 0, n = 0;
+  CellSlot* slots = nullptr;
+  size_t slot_cap = 0;
+  uint32_t mask = 0;
+  float cell = 1.f;
+};
+NNGridStorage* nn_create() { return new NNGridStorage(); }
+void nn_destroy(NNGridStorage* g) {
+  if (!g) return;
+  cudaFree(g->sorted); cudaFree(g->slots);
+  delete g;
+}
+__global__ void k_nn_keys(const float4* __restrict__ pts, size_t n, float cell, int i0, int j0, int k0, int bi, int bj,
+                          unsigned long long* __restrict__ keys, unsigned int* __restrict__ idx) {
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const float4 p = pts[t];
+  const unsigned long long i = (unsigned long long)((int)floorf(p.x / cell) - i0), j = (unsigned long long)((int)floorf(p.y / cell) - j0),
+                           k = (unsigned long long)((int)floorf(p.z / cell) - k0);
+  keys[t] = (k << (bi + bj)) | (j << bi) | i;
+  idx[t] = (unsigned int)t;
+}
+__global__ void k_nn_gather(const float4* __restrict__ pts, const unsigned int* __restrict__ idx, size_t n, float4* __restrict__ out) {
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) out[t] = pts[idx[t]];
+}
+__global__ void k_nn_fill(CellSlot* slots, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { CellSlot s; s.key = kEmptyKey; s.start = 0; s.end = 0; slots[i] = s; }
+}
+__global__ void k_nn_insert(const float4* __restrict__ sorted, const int* __restrict__ run_start, int n_runs, float cell,
+                            CellSlot* __restrict__ slots, uint32_t mask) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_runs) return;
+  const float4 p = sorted[run_start[r]];
+  const unsigned long long key = pack_key((int)floorf(p.x / cell), (int)floorf(p.y / cell), (int)floorf(p.z / cell));
+  uint32_t h = hash_key(key) & mask;
+  while (true) {
+    const unsigned long long prev = atomicCAS(&slots[h].key, kEmptyKey, key);
+    if (prev == kEmptyKey) break;
+    h = (h + 1) & mask;
+  }
+  slots[h].start = run_start[r];
+  slots[h].end = run_start[r + 1];
+}
+cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, size_t n, float cell, cudaStream_t s, long long* launches) {
+  long long dummy = 0;
+  long long& L = launches ? *launches : dummy;
+  g->n = n;
+  g->cell = cell;
+  if (n == 0) return cudaSuccess;
+  CK(ws_reserve(ws, n));
+  if (n > g->pts_cap) {
+    cudaFree(g->sorted);
+    g->sorted = nullptr;
+    CK(cudaMalloc(&g->sorted, (n + n / 4) * sizeof(float4)));
+    g->pts_cap = n + n / 4;
+  }
+  k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
+  k_minmax<<<296, 256, 0, s>>>(pts, n, ws->mm, 1);
+  k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
+  CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  int c0[3], c1[3];
+  for (int a = 0; a < 3; ++a) {
+    c0[a] = (int)floorf(ws->h_mm[a] / cell); c1[a] = (int)floorf(ws->h_mm[3 + a] / cell);
+    if (!coord_ok(c0[a]) || !coord_ok(c1[a])) return cudaErrorInvalidValue;
+  }
+  const int bi = bits_for((long long)c1[0] - c0[0] + 1), bj = bits_for((long long)c1[1] - c0[1] + 1), bk = bits_for((long long)c1[2] - c0[2] + 1);
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  k_nn_keys<<<nb, 256, 0, s>>>(pts, n, cell, c0[0], c0[1], c0[2], bi, bj, ws->keys_in, ws->idx_in);
+  size_t tb = ws->cub_bytes;
+  CK(cub::DeviceRadixSort::SortPairs(ws->cub_temp, tb, ws->keys_in, ws->keys_out, ws->idx_in, ws->idx_out, (int)n, 0, bi + bj + bk, s));
+  k_nn_gather<<<nb, 256, 0, s>>>(pts, ws->idx_out, n, g->sorted);
+  k_flags<<<nb, 256, 0, s>>>(ws->keys_out, n, ws->flags);
+  tb = ws->cub_bytes;
+  CK(cub::DeviceScan::InclusiveSum(ws->cub_temp, tb, ws->flags, ws->scan, (int)n, s));
+  k_run_starts<<<nb, 256, 0, s>>>(ws->flags, ws->scan, n, ws->run_start, ws->counts);
+  CK(cudaMemcpyAsync(ws->h_counts, ws->counts, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  const int n_runs = ws->h_counts[0];
+  size_t want = 1024;
+  while (want < (size_t)n_runs * 4) want <<= 1;
+  if (want > g->slot_cap) {
+    cudaFree(g->slots);
+    g->slots = nullptr;
+    CK(cudaMalloc(&g->slots, want * sizeof(CellSlot)));
+    g->slot_cap = want;
+  }
+  g->mask = (uint32_t)(g->slot_cap - 1);
+  k_nn_fill<<<(unsigned)((g->slot_cap + 255) / 256), 256, 0, s>>>(g->slots, g->slot_cap);
+  k_nn_insert<<<(n_runs + 127) / 128, 128, 0, s>>>(g->sorted, ws->run_start, n_runs, cell, g->slots, g->mask);
+  L += 11 + (bi + bj + bk + 7) / 8;
+  return cudaGetLastError();
+}
+
+__global__ void k_nn_query(const float4* __restrict__ sorted, size_t n_tgt, const CellSlot* __restrict__ slots, uint32_t mask, float cell,
+                           const float4* __restrict__ src, size_t n, const float* __restrict__ T16, float* __restrict__ d2_out) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 p = src[i];
+  // pcl::transformPointCloud by final_transformation_ (float, left to right)
+  const float qx = ((T16[0] * p.x + T16[4] * p.y) + T16[8] * p.z) + T16[12];
+  const float qy = ((T16[1] * p.x + T16[5] * p.y) + T16[9] * p.z) + T16[13];
+  const float qz = ((T16[2] * p.x + T16[6] * p.y) + T16[10] * p.z) + T16[14];
+  const int ci = (int)floorf(qx / cell), cj = (int)floorf(qy / cell), ck = (int)floorf(qz / cell);
+  float best = FLT_MAX;
+  bool certain = false;
+  for (int ring = 0; ring <= 8; ++ring) {
+    if (ring >= 1) {
+      const float lim = (float)(ring - 1) * cell;   // every point in rings >= `ring` is at least this far
+      if (best <= lim * lim) { certain = true; break; }
+    }
+    for (int dz = -ring; dz <= ring; ++dz)
+      for (int dy = -ring; dy <= ring; ++dy)
+        for (int dx = -ring; dx <= ring; ++dx) {
+          if (max(abs(dx), max(abs(dy), abs(dz))) != ring) continue;
+          const int a = ci + dx, b = cj + dy, c = ck + dz;
+          if (!coord_ok(a) || !coord_ok(b) || !coord_ok(c)) continue;
+          const unsigned long long key = pack_key(a, b, c);
+          uint32_t h = hash_key(key) & mask;
+          int s0 = 0, s1 = 0;
+          while (true) {
+            const CellSlot sl = slots[h];
+            if (sl.key == key) { s0 = sl.start; s1 = sl.end; break; }
+            if (sl.key == kEmptyKey) break;
+            h = (h + 1) & mask;
+          }
+          for (int t = s0; t < s1; ++t) {
+            const float4 tp = sorted[t];
+            const float ex = qx - tp.x, ey = qy - tp.y, ez = qz - tp.z;
+            const float d = (ex * ex + ey * ey) + ez * ez;
+            if (d < best) best = d;
+          }
+        }
+  }
+  if (!certain) {
+    const float lim = 8.f * cell;
+    if (!(best <= lim * lim)) {   // far-away query: exhaustive scan (rare)
+      for (size_t t = 0; t < n_tgt; ++t) {
+        const float4 tp = sorted[t];
+        const float ex = qx - tp.x, ey = qy - tp.y, ez = qz - tp.z;
+        const float d = (ex * ex + ey * ey) + ez * ez;
+        if (d < best) best = d;
+      }
+    }
+  }
+  d2_out[i] = best;
+}
+cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float* T16_dev, float* d2_out, cudaStream_t s) {
+  if (n == 0) return cudaSuccess;
+  k_nn_query<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(g->sorted, g->n, g->slots, g->mask, g->cell, src, n, T16_dev, d2_out);
+  return cudaGetLastError();
+}
+
+}  // namespace ndtb

@@ -1,0 +1,371 @@
+"""Python mirror of pclomp::NormalDistributionsTransform over the C ABI of libndt_b200.so.
+
+Method names and argument meaning follow the reference class (reference
+xchu_mapping/include/pclomp/ndt_omp.h:110-204 and the pcl::Registration members odom_node uses,
+src/odom_node.cpp:55-83, 263-284), so the parity tests read like reference usage.  All compute
+happens in the CUDA library; there is no CPU fallback -- a missing library or GPU raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libndt_b200.so")
+
+KDTREE, DIRECT26, DIRECT7, DIRECT1 = 0, 1, 2, 3
+
+
+class NdtError(RuntimeError):
+    pass
+
+
+class Params(C.Structure):
+    _fields_ = [("resolution", C.c_float), ("step_size", C.c_double), ("trans_eps", C.c_double), ("max_iter", C.c_int),
+                ("outlier_ratio", C.c_double), ("search_method", C.c_int), ("min_points", C.c_int), ("eig_mult", C.c_double)]
+
+
+class Result(C.Structure):
+    _fields_ = [("T", C.c_float * 16), ("iterations", C.c_int), ("converged", C.c_int), ("score", C.c_double),
+                ("trans_probability", C.c_double), ("n_evals", C.c_int)]
+
+
+class BatchStats(C.Structure):
+    _fields_ = [("build_ms", C.c_double), ("deriv_ms", C.c_double), ("total_ms", C.c_double),
+                ("kernel_launches", C.c_longlong), ("deriv_launches", C.c_longlong),
+                ("points_evaluated", C.c_longlong), ("pairs_evaluated", C.c_longlong), ("probes", C.c_longlong)]
+
+
+# every symbol include/ndt_b200/ndt_c_api.h declares
+SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_params", "ndtb_set_params", "ndtb_get_params",
+           "ndtb_set_target", "ndtb_set_target_auto", "ndtb_update_target", "ndtb_set_source", "ndtb_align", "ndtb_get_output",
+           "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_neighbors",
+           "ndtb_eval_derivatives", "ndtb_compute_hessian", "ndtb_get_trace", "ndtb_last_timing", "ndtb_batch_create",
+           "ndtb_batch_destroy", "ndtb_batch_last_error", "ndtb_batch_set_params", "ndtb_batch_clear", "ndtb_batch_add_target",
+           "ndtb_batch_add_source", "ndtb_batch_run", "ndtb_batch_get_stats"]
+
+_lib = None
+
+
+def load_library():
+    """dlopen the in-tree CUDA library.  Raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise NdtError("%s is missing: run `python -m xchu_slam_b200.build` (nvcc, sm_100a). "
+                       "There is no CPU fallback." % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, sz = C.c_void_p, C.c_size_t
+    L.ndtb_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.ndtb_destroy.argtypes = [vp]
+    L.ndtb_last_error.argtypes = [vp]
+    L.ndtb_last_error.restype = C.c_char_p
+    L.ndtb_default_params.argtypes = [C.POINTER(Params)]
+    L.ndtb_default_params.restype = None
+    L.ndtb_set_params.argtypes = [vp, C.POINTER(Params)]
+    L.ndtb_get_params.argtypes = [vp, C.POINTER(Params)]
+    L.ndtb_set_target.argtypes = [vp, vp, sz, sz]
+    L.ndtb_set_target_auto.argtypes = [vp, vp, sz, sz, C.POINTER(C.c_int)]
+    L.ndtb_update_target.argtypes = [vp, vp, sz, sz]
+    L.ndtb_set_source.argtypes = [vp, vp, sz, sz]
+    L.ndtb_align.argtypes = [vp, vp, C.POINTER(Result)]
+    L.ndtb_get_output.argtypes = [vp, vp, sz]
+    L.ndtb_fitness.argtypes = [vp, C.c_double, vp, C.POINTER(C.c_double)]
+    L.ndtb_calculate_score.argtypes = [vp, vp, C.POINTER(C.c_double)]
+    L.ndtb_num_voxels.argtypes = [vp, C.POINTER(sz)]
+    L.ndtb_dump_voxels.argtypes = [vp] + [vp] * 6
+    L.ndtb_neighbors.argtypes = [vp, vp, sz, C.c_int, vp, vp]
+    L.ndtb_eval_derivatives.argtypes = [vp, vp, vp, C.c_int, C.POINTER(C.c_double), vp, vp]
+    L.ndtb_compute_hessian.argtypes = [vp, vp, vp, vp]
+    L.ndtb_get_trace.argtypes = [vp, vp, C.c_int, C.POINTER(C.c_int)]
+    L.ndtb_last_timing.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.ndtb_batch_create.argtypes = [C.c_int, C.POINTER(vp)]
+    L.ndtb_batch_destroy.argtypes = [vp]
+    L.ndtb_batch_last_error.argtypes = [vp]
+    L.ndtb_batch_last_error.restype = C.c_char_p
+    L.ndtb_batch_set_params.argtypes = [vp, C.POINTER(Params)]
+    L.ndtb_batch_clear.argtypes = [vp]
+    L.ndtb_batch_add_target.argtypes = [vp, vp, sz, sz, C.c_int, C.POINTER(C.c_int)]
+    L.ndtb_batch_add_source.argtypes = [vp, vp, sz, sz, C.c_int, C.POINTER(C.c_int)]
+    L.ndtb_batch_run.argtypes = [vp, C.c_int, vp, vp, vp, vp]
+    L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
+    _lib = L
+    return L
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _cloud(a):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    if a.ndim != 2 or a.shape[1] < 3:
+        raise ValueError("point cloud must be (n, >=3) float32")
+    return a
+
+
+def _colmajor(T):
+    return np.ascontiguousarray(np.asarray(T, dtype=np.float32).reshape(4, 4).T).reshape(-1)
+
+
+class NormalDistributionsTransform:
+    """pclomp::NormalDistributionsTransform<PointXYZI, PointXYZI> drop-in (reference NDT_H:70-204)."""
+
+    def __init__(self, device=0):
+        self._L = load_library()
+        self._h = C.c_void_p()
+        if self._L.ndtb_create(device, C.byref(self._h)):
+            raise NdtError(self._L.ndtb_last_error(None).decode())
+        self._params = Params()
+        self._L.ndtb_get_params(self._h, C.byref(self._params))
+        self._result = None
+        self._n_source = 0
+        self._src_stride = 16
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._L.ndtb_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc:
+            raise NdtError(self._L.ndtb_last_error(self._h).decode())
+
+    def _push(self):
+        self._ck(self._L.ndtb_set_params(self._h, C.byref(self._params)))
+
+    # ---- setters / getters of the reference class ------------------------------------------
+    def setNumThreads(self, n):          # NDT_H:110-112 -- CPU threads have no meaning here
+        pass
+
+    def setResolution(self, r):          # NDT_H:127-137
+        self._params.resolution = float(r)
+        self._push()
+
+    def getResolution(self):
+        return self._params.resolution
+
+    def setStepSize(self, s):            # NDT_H:160-164
+        self._params.step_size = float(s)
+        self._push()
+
+    def getStepSize(self):
+        return self._params.step_size
+
+    def setOulierRatio(self, o):         # NDT_H:178-182 (sic)
+        self._params.outlier_ratio = float(o)
+        self._push()
+
+    def getOulierRatio(self):
+        return self._params.outlier_ratio
+
+    def setTransformationEpsilon(self, e):
+        self._params.trans_eps = float(e)
+        self._push()
+
+    def setMaximumIterations(self, n):
+        self._params.max_iter = int(n)
+        self._push()
+
+    def setNeighborhoodSearchMethod(self, m):   # NDT_H:184-186
+        self._params.search_method = int(m)
+        self._push()
+
+    def setVoxelParams(self, min_points=6, eig_mult=0.01):
+        self._params.min_points, self._params.eig_mult = int(min_points), float(eig_mult)
+        self._push()
+
+    def setInputTarget(self, cloud):     # NDT_H:117-122
+        cloud = _cloud(cloud)
+        self._ck(self._L.ndtb_set_target(self._h, _p(cloud), cloud.shape[0], cloud.strides[0]))
+
+    def setInputTargetAuto(self, cloud):
+        """setInputTarget that merges only the appended tail when the cloud extends the current one."""
+        cloud = _cloud(cloud)
+        inc = C.c_int()
+        self._ck(self._L.ndtb_set_target_auto(self._h, _p(cloud), cloud.shape[0], cloud.strides[0], C.byref(inc)))
+        return bool(inc.value)
+
+    def updateVoxelGrid(self, cloud):    # cpu::NormalDistributionsTransform::updateVoxelGrid
+        cloud = _cloud(cloud)
+        self._ck(self._L.ndtb_update_target(self._h, _p(cloud), cloud.shape[0], cloud.strides[0]))
+
+    def setInputSource(self, cloud):
+        cloud = _cloud(cloud)
+        self._n_source = cloud.shape[0]
+        self._ck(self._L.ndtb_set_source(self._h, _p(cloud), cloud.shape[0], cloud.strides[0]))
+
+    def align(self, guess=None):
+        """pcl::Registration::align(output, guess).  Returns the transformed source (n, 3)."""
+        G = np.eye(4, dtype=np.float32) if guess is None else np.asarray(guess, dtype=np.float32)
+        g = _colmajor(G)
+        r = Result()
+        self._ck(self._L.ndtb_align(self._h, _p(g), C.byref(r)))
+        self._result = r
+        return self.getOutput()
+
+    def getOutput(self):
+        out = np.zeros((self._n_source, 3), np.float32)
+        self._ck(self._L.ndtb_get_output(self._h, _p(out), 12))
+        return out
+
+    def getFinalTransformation(self):
+        return np.array(self._result.T, dtype=np.float32).reshape(4, 4).T.copy()
+
+    def hasConverged(self):
+        return bool(self._result.converged)
+
+    def getFinalNumIteration(self):      # NDT_H:200-204
+        return int(self._result.iterations)
+
+    def getTransformationProbability(self):  # NDT_H:191-195
+        return float(self._result.trans_probability)
+
+    def getFitnessScore(self, max_range=float(np.finfo(np.float64).max), T=None):
+        out = C.c_double()
+        Tp = None if T is None else _p(_colmajor(T))
+        if T is not None:
+            self._Tkeep = _colmajor(T)
+            Tp = _p(self._Tkeep)
+        self._ck(self._L.ndtb_fitness(self._h, float(max_range), Tp, C.byref(out)))
+        return out.value
+
+    def calculateScore(self, T):         # NDT_I:919-952 with cloud = T * source
+        out = C.c_double()
+        Tc = _colmajor(T)
+        self._ck(self._L.ndtb_calculate_score(self._h, _p(Tc), C.byref(out)))
+        return out.value
+
+    # ---- inspection hooks -----------------------------------------------------------------
+    def result(self):
+        r = self._result
+        return dict(T=self.getFinalTransformation(), iterations=r.iterations, converged=bool(r.converged), score=r.score,
+                    trans_probability=r.trans_probability, n_evals=r.n_evals)
+
+    def trace(self):
+        n = C.c_int()
+        self._ck(self._L.ndtb_get_trace(self._h, None, 0, C.byref(n)))
+        buf = np.zeros((max(n.value, 1), 52))
+        self._ck(self._L.ndtb_get_trace(self._h, _p(buf), buf.shape[0], C.byref(n)))
+        return [dict(p=t[0:6].copy(), score=t[6], g=t[7:13].copy(), H=t[13:49].reshape(6, 6).copy(), step=t[49],
+                     compute_hessian=int(t[50]), kind=int(t[51])) for t in buf[:n.value]]
+
+    def dumpVoxels(self):
+        n = C.c_size_t()
+        self._ck(self._L.ndtb_num_voxels(self._h, C.byref(n)))
+        n = n.value
+        out = dict(ijk=np.zeros((n, 3), np.int32), nr_points=np.zeros(n, np.int32), n_raw=np.zeros(n, np.int32),
+                   mean=np.zeros((n, 3)), icov=np.zeros((n, 3, 3), np.float32), centroid=np.zeros((n, 3), np.float32))
+        if n:
+            self._ck(self._L.ndtb_dump_voxels(self._h, _p(out["ijk"]), _p(out["nr_points"]), _p(out["n_raw"]), _p(out["mean"]),
+                                              _p(out["icov"]), _p(out["centroid"])))
+        return out
+
+    def neighbors(self, xyz, method=None):
+        xyz = np.ascontiguousarray(np.asarray(xyz, dtype=np.float32)[:, :3])
+        n = xyz.shape[0]
+        cnt = np.zeros(n, np.int32)
+        ijk = np.zeros((n, 27, 3), np.int32)
+        m = self._params.search_method if method is None else method
+        self._ck(self._L.ndtb_neighbors(self._h, _p(xyz), n, m, _p(cnt), _p(ijk)))
+        return cnt, ijk
+
+    def evalDerivatives(self, T, p, compute_hessian=True):
+        Tc = _colmajor(T)
+        p = np.ascontiguousarray(p, dtype=np.float64)
+        s = C.c_double()
+        g, H = np.zeros(6), np.zeros((6, 6))
+        self._ck(self._L.ndtb_eval_derivatives(self._h, _p(Tc), _p(p), int(compute_hessian), C.byref(s), _p(g), _p(H)))
+        return s.value, g, H
+
+    def computeHessian(self, T, p):
+        Tc = _colmajor(T)
+        p = np.ascontiguousarray(p, dtype=np.float64)
+        H = np.zeros((6, 6))
+        self._ck(self._L.ndtb_compute_hessian(self._h, _p(Tc), _p(p), _p(H)))
+        return H
+
+    def lastTiming(self):
+        b, a = C.c_double(), C.c_double()
+        self._L.ndtb_last_timing(self._h, C.byref(b), C.byref(a))
+        return dict(build_ms=b.value, align_ms=a.value)
+
+
+class BatchNDT:
+    """Batched registration on one device (north_star item 4): targets and sources resident in HBM,
+    any number of {target, source, guess} items per run."""
+
+    def __init__(self, device=0):
+        self._L = load_library()
+        self._h = C.c_void_p()
+        if self._L.ndtb_batch_create(device, C.byref(self._h)):
+            raise NdtError(self._L.ndtb_batch_last_error(None).decode())
+        self.params = Params()
+        self._L.ndtb_default_params(C.byref(self.params))
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._L.ndtb_batch_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc:
+            raise NdtError(self._L.ndtb_batch_last_error(self._h).decode())
+
+    def set_params(self, **kw):
+        for k, v in kw.items():
+            if not hasattr(self.params, k):
+                raise KeyError(k)
+            setattr(self.params, k, v)
+        self._ck(self._L.ndtb_batch_set_params(self._h, C.byref(self.params)))
+
+    def clear(self):
+        self._ck(self._L.ndtb_batch_clear(self._h))
+
+    def add_target(self, cloud):
+        cloud = _cloud(cloud)
+        i = C.c_int()
+        self._ck(self._L.ndtb_batch_add_target(self._h, _p(cloud), cloud.shape[0], cloud.strides[0], 0, C.byref(i)))
+        return i.value
+
+    def add_source(self, cloud):
+        cloud = _cloud(cloud)
+        i = C.c_int()
+        self._ck(self._L.ndtb_batch_add_source(self._h, _p(cloud), cloud.shape[0], cloud.strides[0], 0, C.byref(i)))
+        return i.value
+
+    def add_target_ptr(self, ptr, n, stride=16, on_device=True):
+        i = C.c_int()
+        self._ck(self._L.ndtb_batch_add_target(self._h, C.c_void_p(ptr), n, stride, int(on_device), C.byref(i)))
+        return i.value
+
+    def add_source_ptr(self, ptr, n, stride=16, on_device=True):
+        i = C.c_int()
+        self._ck(self._L.ndtb_batch_add_source(self._h, C.c_void_p(ptr), n, stride, int(on_device), C.byref(i)))
+        return i.value
+
+    def run(self, item_target, item_source, guesses):
+        it = np.ascontiguousarray(item_target, dtype=np.int32)
+        isrc = np.ascontiguousarray(item_source, dtype=np.int32)
+        n = it.shape[0]
+        G = np.ascontiguousarray(np.asarray(guesses, dtype=np.float32).reshape(n, 4, 4).transpose(0, 2, 1)).reshape(n, 16)
+        res = (Result * n)()
+        self._ck(self._L.ndtb_batch_run(self._h, n, _p(it), _p(isrc), _p(G), C.cast(res, C.c_void_p)))
+        out = []
+        for r in res:
+            out.append(dict(T=np.array(r.T, dtype=np.float32).reshape(4, 4).T.copy(), iterations=r.iterations,
+                            converged=bool(r.converged), score=r.score, trans_probability=r.trans_probability,
+                            n_evals=r.n_evals))
+        return out
+
+    def stats(self):
+        s = BatchStats()
+        self._ck(self._L.ndtb_batch_get_stats(self._h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in BatchStats._fields_}
