@@ -1,0 +1,314 @@
+#!/usr/bin/env python
+"""bench.py -- NDT aligns/sec (20k-pt scan vs 1M-pt map) on N B200s; % HBM roofline.
+
+One "step" = one pass of the hot path over one batch of synthetic registrations: BASELINE
+configs[4] shape -- S distinct 1M-pt submaps x (scans x hypotheses) independent aligns of 20k-pt
+scans (res 1.0 m, DIRECT7, step 0.1, eps 0.01, <= 30 iterations), INCLUDING the voxel-table
+build of every submap.  Every rank runs the same per-GPU batch (weak scaling: per-GPU work
+fixed), no collective on the data path; value = all ranks' aligns / max-over-ranks device time.
+
+  value : inputs resident in HBM when the timed region starts (device pointers handed to the C ABI)
+  e2e   : same batch through the C ABI with HOST (pinned) buffers; H2D of every cloud and D2H of
+          the results inside the timed region
+  --impl reference : the reference algorithm's CPU restatement (oracle/, OpenMP on all host cores)
+          on a bounded sample of the same workload
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "NDT aligns/sec (20k-pt scan vs 1M-pt map)"
+UNIT = "aligns/s"
+CACHE = os.environ.get("NDT_BENCH_CACHE", "/tmp/ndt_b200_bench_cache")
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--submaps", type=int, default=int(os.environ.get("NDT_BENCH_SUBMAPS", 64)))
+    ap.add_argument("--scans", type=int, default=8, help="distinct scans per submap")
+    ap.add_argument("--hyps", type=int, default=8, help="initial-guess hypotheses per scan")
+    ap.add_argument("--n-target", type=int, default=1000000)
+    ap.add_argument("--n-source", type=int, default=20000)
+    ap.add_argument("--cpu-aligns", type=int, default=24, help="aligns in the bounded CPU sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(a, n_gpus):
+    return {"workload": "C5 batched registration: %d submaps x %d scans x %d hypotheses = %d aligns per GPU per step, "
+                        "%d-pt scan vs %d-pt submap, res 1.0 m, DIRECT7, step 0.1, eps 0.01, max_iter 30, voxel-table build "
+                        "of every submap included" % (a.submaps, a.scans, a.hyps, a.submaps * a.scans * a.hyps, a.n_source, a.n_target),
+            "aligns_per_gpu_per_step": a.submaps * a.scans * a.hyps, "n_source": a.n_source, "n_target": a.n_target,
+            "resolution": 1.0, "search": "DIRECT7", "parallelism": "independent aligns sharded per GPU, no collective (x%d)" % n_gpus,
+            "l2_policy": "inputs_exceed_l2 (%.2f GB of clouds per step vs 126 MB L2)"
+                         % ((a.submaps * a.n_target + a.submaps * a.scans * a.n_source) * 16 / 1e9)}
+
+
+def get_workload(a, rank, barrier):
+    from xchu_slam_b200 import synth
+    kw = dict(n_submaps=a.submaps, scans_per_submap=a.scans, hyps_per_scan=a.hyps, n_target=a.n_target, n_source=a.n_source,
+              cache_dir=CACHE)
+    if rank == 0:
+        w = synth.batch_workload(**kw)
+        barrier()
+    else:
+        barrier()
+        w = synth.batch_workload(**kw)
+    return w
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+                for k, nme in enumerate(names):
+                    if r[5 + k].lower().startswith("active"):
+                        reasons.add(nme)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_sample(a, w, n_aligns):
+    """Oracle (CPU restatement of ndt_omp, OpenMP on all host cores): build one submap's grid, then
+    n_aligns registrations against it; aligns/s = n / (build_amortised + align time) on the same
+    64-aligns-per-submap amortisation as the GPU workload."""
+    from oracle import oracle
+    nthreads = oracle.max_threads()
+    o = oracle.OracleNDT()
+    o.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=oracle.DIRECT7, num_threads=nthreads)
+    t0 = time.perf_counter()
+    o.set_target(w["targets"][0])
+    t_build = time.perf_counter() - t0
+    per_submap = a.scans * a.hyps
+    idx = [i for i in range(len(w["item_target"])) if w["item_target"][i] == 0][:n_aligns]
+    t_align, evals = 0.0, 0
+    for i in idx:
+        o.set_source(w["sources"][w["item_source"][i]])
+        t0 = time.perf_counter()
+        r = o.align(w["guesses"][i])
+        t_align += time.perf_counter() - t0
+        evals += len(r["trace"])
+    n = len(idx)
+    per_align = t_align / n + t_build / per_submap
+    return {"value": 1.0 / per_align, "unit": UNIT, "cores": nthreads, "kind": "port",
+            "sample": "%d aligns vs submap 0 (%.3f s serial grid build amortised over %d aligns/submap as in the workload; "
+                      "%.1f ms/align, %.1f evaluations/align); oracle = dependency-free restatement of ndt_omp, "
+                      "g++ -O2 -fopenmp, %d threads" % (n, t_build, per_submap, 1e3 * t_align / n, evals / n, nthreads),
+            "build_s": t_build, "align_ms": 1e3 * t_align / n}
+
+
+def run_reference(a):
+    """Reference arm: the reference algorithm on the host cores (oracle port; the reference's own
+    sources need PCL/Eigen/FLANN/Boost, absent here -- DESIGN.md section 7)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from xchu_slam_b200 import synth
+    small = argparse.Namespace(**vars(a))
+    # bounded sample: one submap is enough for the CPU arm; reuse the full cache when it exists
+    try:
+        w = synth.batch_workload(n_submaps=a.submaps, scans_per_submap=a.scans, hyps_per_scan=a.hyps, n_target=a.n_target,
+                                 n_source=a.n_source, cache_dir=CACHE)
+    except MemoryError:
+        w = synth.batch_workload(n_submaps=1, scans_per_submap=a.scans, hyps_per_scan=a.hyps, n_target=a.n_target,
+                                 n_source=a.n_source)
+    per_step = max(2, a.cpu_aligns // max(1, a.steps))
+    for _ in range(max(0, min(a.warmup, 1))):
+        cpu_sample(a, w, 2)
+    t0 = time.perf_counter()
+    vals = [cpu_sample(a, w, per_step) for _ in range(a.steps)]
+    dt = time.perf_counter() - t0
+    v = float(np.mean([x["value"] for x in vals]))
+    cb = dict(vals[-1]); cb["value"] = v
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 terms, f64 accumulate",
+            "data": "synthetic", "config": workload_config(a, a.gpus), "cpu_baseline": cb,
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+        return
+    import torch
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    from xchu_slam_b200 import ndt
+    w = get_workload(a, rank, barrier)
+    n_items = len(w["item_target"])
+    dev = torch.device("cuda", local)
+
+    # ---- inputs: device-resident copies (value) and pinned host copies (e2e) -------------------
+    tg_host = [torch.from_numpy(t).pin_memory() for t in w["targets"]]
+    sc_host = [torch.from_numpy(s).pin_memory() for s in w["sources"]]
+    tg_dev = [t.to(dev) for t in tg_host]
+    sc_dev = [s.to(dev) for s in sc_host]
+    h2d_bytes = sum(t.numel() * 4 for t in tg_host) + sum(s.numel() * 4 for s in sc_host) + n_items * 64
+    d2h_bytes = n_items * C.sizeof(ndt.Result)
+    torch.cuda.synchronize()
+
+    b = ndt.BatchNDT(device=local)
+    b.set_stream(torch.cuda.current_stream().cuda_stream)   # torch's events then bracket the library's work
+    b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=ndt.DIRECT7)
+    it, isrc, G = w["item_target"], w["item_source"], w["guesses"]
+
+    def step(resident):
+        b.clear()
+        if resident:
+            for t in tg_dev:
+                b.add_target_ptr(t.data_ptr(), t.shape[0], 16, True)
+            for s in sc_dev:
+                b.add_source_ptr(s.data_ptr(), s.shape[0], 16, True)
+        else:
+            for t in tg_host:
+                b.add_target_ptr(t.data_ptr(), t.shape[0], 16, False)
+            for s in sc_host:
+                b.add_source_ptr(s.data_ptr(), s.shape[0], 16, False)
+        res = b.run(it, isrc, G)      # returns after the device finished and results are on the host
+        return res, b.stats()
+
+    def timed(resident, steps):
+        barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        agg = dict(deriv_ms=0.0, build_ms=0.0, total_ms=0.0, kernel_launches=0, deriv_launches=0, points=0, pairs=0)
+        res = None
+        for _ in range(steps):
+            res, st = step(resident)
+            agg["deriv_ms"] += st["deriv_ms"]; agg["build_ms"] += st["build_ms"]; agg["total_ms"] += st["total_ms"]
+            agg["kernel_launches"] += st["kernel_launches"]; agg["deriv_launches"] += st["deriv_launches"]
+            agg["points"] += st["points_evaluated"]; agg["pairs"] += st["pairs_evaluated"]
+        e1.record()
+        torch.cuda.synchronize()
+        barrier()
+        wall = time.perf_counter() - t0
+        # device time: CUDA events on the stream the library launches on (set_stream above)
+        ms = e0.elapsed_time(e1)
+        agg["wall_ms"] = wall * 1e3
+        if dist is not None:
+            tt = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ms = float(tt.item())
+        return ms, agg, res
+
+    for _ in range(a.warmup):
+        step(True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms, agg, res = timed(True, a.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    for _ in range(min(a.warmup, 1)):
+        step(False)
+    ms_e2e, agg_e2e, _ = timed(False, a.steps)
+
+    if rank == 0:
+        value = world * n_items * a.steps / (ms / 1e3)
+        e2e = world * n_items * a.steps / (ms_e2e / 1e3)
+        # roofline of the derivative kernel: B_pt = 16 + 8*K + 48*h  per evaluated point
+        K = 7
+        alg_bytes = agg["points"] * (16 + 8 * K) + 48 * agg["pairs"]
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = alg_bytes / (agg["deriv_ms"] / 1e3) / 1e9 if agg["deriv_ms"] > 0 else 0.0
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+        conv = sum(1 for r in res if r["converged"])
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32 terms, f64 accumulate", "data": "synthetic", "config": workload_config(a, world),
+                "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                        "ms_per_step": ms_e2e / a.steps},
+                "gpu_launches": int(agg["kernel_launches"]),
+                "roofline": {"bound": "hbm", "kernel": "k_derivatives", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                             "frac": achieved / peak if peak else None, "traffic": traffic,
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
+                             "algorithmic_bytes_per_launch": alg_bytes / max(1, agg["deriv_launches"]),
+                             "launches": int(agg["deriv_launches"]), "kernel_ms_per_launch": agg["deriv_ms"] / max(1, agg["deriv_launches"]),
+                             "mean_neighbours_per_point": agg["pairs"] / max(1, agg["points"]),
+                             "kernel_share_of_step": agg["deriv_ms"] / ms},
+                "breakdown_ms_per_step": {"voxel_build": agg["build_ms"] / a.steps, "derivatives": agg["deriv_ms"] / a.steps,
+                                          "device_total": agg["total_ms"] / a.steps},
+                "clocks": clocks, "converged_frac": conv / len(res),
+                "mean_iterations": float(np.mean([r["iterations"] for r in res]))}
+        if not a.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_sample(a, w, a.cpu_aligns)
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -136,6 +136,9 @@ typedef struct ndtb_batch_stats {
   long long points_evaluated, pairs_evaluated, probes;
 } ndtb_batch_stats;
 int ndtb_batch_get_stats(ndtb_batch* b, ndtb_batch_stats* s);
+/* Run all of the batch's copies and kernels on the caller's CUDA stream (a cudaStream_t) instead of
+ * the batch's own, so that the caller's CUDA events bracket the work. */
+int ndtb_batch_set_stream(ndtb_batch* b, void* cuda_stream);
 
 #ifdef __cplusplus
 }

@@ -22,7 +22,19 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_cuda(force=False, verbose=False):
+def build_cuda(force=False, verbose=False, defines=(), lib=None):
+    """defines: extra -D macros (kernel tuning variants); lib: output path override."""
+    global LIB
+    if lib:
+        LIB_SAVE, LIB = LIB, lib
+        try:
+            return _build_cuda(True, verbose, defines)
+        finally:
+            LIB = LIB_SAVE
+    return _build_cuda(force, verbose, defines)
+
+
+def _build_cuda(force=False, verbose=False, defines=()):
     hdrs = [os.path.join(CSRC, "ndt_internal.h"), os.path.join(HERE, "..", "include", "ndt_b200", "ndt_c_api.h")]
     objs = []
     procs = []
@@ -31,7 +43,7 @@ def build_cuda(force=False, verbose=False):
         o = os.path.join(CSRC, src.replace(".cu", ".o"))
         objs.append(o)
         if force or _stale(o, [s] + hdrs):
-            cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
+            cmd = ["nvcc"] + NVCC_FLAGS + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
             procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     for src, p in procs:
         out, _ = p.communicate()

@@ -4,6 +4,7 @@
 // (reference xchu_mapping/include/pclomp/ndt_omp.h:110-278, ndt_omp_impl.hpp:73-164).
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -48,6 +49,7 @@ static void euler_012(const float T[16], float out[3]) {
 struct Engine {
   int device = 0;
   cudaStream_t stream = nullptr;
+  bool own_stream = true;
   std::string err;
   ndtb_params params;
   BuildWorkspace* ws = nullptr;
@@ -119,7 +121,7 @@ struct Engine {
     cudaFree(d_output); cudaFree(d_d2);
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     for (auto& e : deriv_events) cudaEventDestroy(e);
-    if (stream) cudaStreamDestroy(stream);
+    if (stream && own_stream) cudaStreamDestroy(stream);
   }
 
   // copy n records (xyz = first three floats) into a float4 device array
@@ -254,9 +256,11 @@ struct Engine {
       if (item_source[i] < 0 || item_source[i] >= (int)sources.size()) return fail("item source id out of range");
       total_pts += sources[item_source[i]].n;
     }
-    int chunk = (int)((total_pts / (148 * 4) + 255) / 256 * 256);
+    // small blocks keep the tail iterations (few registrations still active) balanced over the 148 SMs
+    int chunk = (int)((total_pts / (148 * 8) + 255) / 256 * 256);
     if (chunk < 256) chunk = 256;
-    if (chunk > 2048) chunk = 2048;
+    if (chunk > 512) chunk = 512;
+    if (const char* ev = getenv("NDTB_CHUNK")) { const int c = atoi(ev); if (c >= 128) chunk = c; }   // tuning knob
     h_states.resize(n_items);
     std::vector<int2> bmap;
     for (int i = 0; i < n_items; ++i) {
@@ -293,10 +297,10 @@ struct Engine {
         deriv_events.push_back(a); deriv_events.push_back(b);
       }
       CKE(cudaEventRecord(deriv_events[ev_used], stream));
-      CKE(launch_derivatives(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk, d_partials, stream));
+      CKE(launch_derivatives(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk, d_partials, params.search_method, mt_live, stream));
       CKE(cudaEventRecord(deriv_events[ev_used + 1], stream));
       ev_used += 2;
-      stats.kernel_launches++; stats.deriv_launches++;
+      stats.kernel_launches += mt_live ? 2 : 1; stats.deriv_launches++;
       if (mt_live) {
         CKE(launch_hessian_f64(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk, d_partials, stream));
         stats.kernel_launches++;
@@ -568,7 +572,7 @@ static int single_eval(Engine& e, const float T[16], const double p[6], int mode
   cudaMemcpyAsync(e.d_active, e.h_active, sizeof(int), cudaMemcpyHostToDevice, e.stream);
   if (launch_prepare_eval(e.d_states, e.d_T16, e.d_p6, mode, e.stream) != cudaSuccess) return e.fail("prepare failed");
   cudaError_t ce;
-  if (mode == 1 || mode == 2) ce = launch_derivatives(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.stream);
+  if (mode == 1 || mode == 2) ce = launch_derivatives(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.params.search_method, true, e.stream);
   else ce = launch_hessian_f64(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.stream);
   if (ce != cudaSuccess) return e.fail(std::string("eval launch: ") + cudaGetErrorString(ce));
   if (launch_newton(e.d_states, 1, e.d_partials, nullptr, 0, e.d_active, e.stream) != cudaSuccess) return e.fail("reduce failed");
@@ -724,5 +728,13 @@ int ndtb_batch_run(ndtb_batch* b, int n_items, const int* item_target, const int
   return e.run_items(n_items, item_target, item_source, guesses, results, false);
 }
 int ndtb_batch_get_stats(ndtb_batch* b, ndtb_batch_stats* s) { *s = b->e.stats; return 0; }
+int ndtb_batch_set_stream(ndtb_batch* b, void* cuda_stream) {
+  Engine& e = b->e;
+  cudaSetDevice(e.device);
+  if (e.stream && e.own_stream) { cudaStreamSynchronize(e.stream); cudaStreamDestroy(e.stream); }
+  e.stream = (cudaStream_t)cuda_stream;
+  e.own_stream = false;
+  return 0;
+}
 
 }  // extern "C"

@@ -16,7 +16,19 @@ namespace ndtb {
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
 
-constexpr int kThreads = 256;
+#ifndef NDTB_THREADS
+#define NDTB_THREADS 256
+#endif
+#ifndef NDTB_MINBLOCKS
+#define NDTB_MINBLOCKS 1
+#endif
+#ifndef NDTB_PD_SMEM      // 1: per-point derivative vectors parked in shared memory, 0: in registers
+#define NDTB_PD_SMEM 0
+#endif
+#ifndef NDTB_PREFETCH     // 1: fetch the next voxel record behind the current pair's math
+#define NDTB_PREFETCH 1
+#endif
+constexpr int kThreads = NDTB_THREADS;
 constexpr int kPartialStride = 44;  // 43 accumulators + pair count
 
 __constant__ int c_off7[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};  // VGC_I:423-430
@@ -184,22 +196,139 @@ __device__ __forceinline__ void pair_update(double* acc, const VoxelRec* __restr
   }
 }
 
-__global__ void __launch_bounds__(kThreads) k_derivatives(const AlignState* __restrict__ states, const VoxelTable* __restrict__ tables,
+// Record fetch: the 64 B record as four 128-bit loads (issued together, consumed later)
+struct RecRegs { double2 a, b; float4 c, d; };
+__device__ __forceinline__ RecRegs load_rec(const VoxelRec* __restrict__ recp) {
+  RecRegs r;
+  r.a = __ldg(reinterpret_cast<const double2*>(recp));
+  r.b = __ldg(reinterpret_cast<const double2*>(recp) + 1);
+  r.c = __ldg(reinterpret_cast<const float4*>(recp) + 2);
+  r.d = __ldg(reinterpret_cast<const float4*>(recp) + 3);
+  return r;
+}
+
+template <bool CH>
+__device__ __forceinline__ void pair_update_r(double* acc, const RecRegs& rr, float xtx, float xty, float xtz,
+                                              const float* __restrict__ pd /* smem column, stride kThreads */, float d2f, double d1) {
+#if NDTB_PD_SMEM
+#define PGV(r) pd[(r) * kThreads]
+#define PHV(r) pd[(8 + (r)) * kThreads]
+#else
+#define PGV(r) pd[(r)]
+#define PHV(r) pd[8 + (r)]
+#endif
+  const double2 m01 = rr.a, m2c = rr.b;
+  const float4 c1 = rr.c, c2 = rr.d;
+  const float C00 = __int_as_float(__double2loint(m2c.y)), C01 = __int_as_float(__double2hiint(m2c.y));
+  const float C02 = c1.x, C10 = c1.y, C11 = c1.z, C12 = c1.w, C20 = c2.x, C21 = c2.y, C22 = c2.z;
+  // x_trans = f64(x_trans_pt) - mean, narrowed to float (NDT_I:257-260, 500)
+  const float x0 = (float)((double)xtx - m01.x), x1 = (float)((double)xty - m01.y), x2 = (float)((double)xtz - m2c.x);
+  const float xC0 = (x0 * C00 + x1 * C10) + x2 * C20;
+  const float xC1 = (x0 * C01 + x1 * C11) + x2 * C21;
+  const float xC2 = (x0 * C02 + x1 * C12) + x2 * C22;
+  const float q = (x0 * xC0 + x1 * xC1) + x2 * xC2;
+  float e = (float)exp((double)((-d2f * q) * 0.5f));            // NDT_I:507
+  const float score_inc = (float)(-d1 * (double)e);             // NDT_I:509
+  e = d2f * e;                                                  // NDT_I:511
+  if (e > 1.f || e < 0.f || e != e) return;                     // NDT_I:514-515 (score not counted either)
+  e = (float)((double)e * d1);                                  // NDT_I:518
+  acc[0] += (double)score_inc;
+  const float g13 = PGV(0), g23 = PGV(1), g04 = PGV(2), g14 = PGV(3), g24 = PGV(4), g05 = PGV(5), g15 = PGV(6), g25 = PGV(7);
+  // CJ = c_inv4 * point_gradient4 (NDT_I:520); columns 0..2 are the columns of C
+  float CJ[3][6];
+  CJ[0][0] = C00; CJ[0][1] = C01; CJ[0][2] = C02;
+  CJ[1][0] = C10; CJ[1][1] = C11; CJ[1][2] = C12;
+  CJ[2][0] = C20; CJ[2][1] = C21; CJ[2][2] = C22;
+  CJ[0][3] = C01 * g13 + C02 * g23; CJ[1][3] = C11 * g13 + C12 * g23; CJ[2][3] = C21 * g13 + C22 * g23;
+  CJ[0][4] = (C00 * g04 + C01 * g14) + C02 * g24; CJ[1][4] = (C10 * g04 + C11 * g14) + C12 * g24; CJ[2][4] = (C20 * g04 + C21 * g14) + C22 * g24;
+  CJ[0][5] = (C00 * g05 + C01 * g15) + C02 * g25; CJ[1][5] = (C10 * g05 + C11 * g15) + C12 * g25; CJ[2][5] = (C20 * g05 + C21 * g15) + C22 * g25;
+  float xCJ[6];
+  xCJ[0] = xC0; xCJ[1] = xC1; xCJ[2] = xC2;
+#pragma unroll
+  for (int c = 3; c < 6; ++c) xCJ[c] = (x0 * CJ[0][c] + x1 * CJ[1][c]) + x2 * CJ[2][c];   // NDT_I:521
+#pragma unroll
+  for (int c = 0; c < 6; ++c) acc[1 + c] += (double)(e * xCJ[c]);                          // NDT_I:523
+  if (!CH) return;
+  // xCH(i,j) = (x_trans4 * c_inv4) * point_hessian_.block<4,1>(4i, j)  (NDT_I:534-535); non-zero for i,j >= 3
+  const float ha = xC1 * PHV(0) + xC2 * PHV(1);
+  const float hb = xC1 * PHV(2) + xC2 * PHV(3);
+  const float hc = xC1 * PHV(4) + xC2 * PHV(5);
+  const float hd = (xC0 * PHV(6) + xC1 * PHV(7)) + xC2 * PHV(8);
+  const float he = (xC0 * PHV(9) + xC1 * PHV(10)) + xC2 * PHV(11);
+  const float hf = (xC0 * PHV(12) + xC1 * PHV(13)) + xC2 * PHV(14);
+  const float xCH[3][3] = {{ha, hb, hc}, {hb, hd, he}, {hc, he, hf}};
+  const float nd2 = -d2f;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    const float nda = nd2 * xCJ[i];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+      // JtCJ(j,i) = point_gradient4.col(j) . CJ.col(i)   (NDT_I:527-528, 542)
+      float jt;
+      if (j < 3) jt = CJ[j][i];
+      else if (j == 3) jt = g13 * CJ[1][i] + g23 * CJ[2][i];
+      else if (j == 4) jt = (g04 * CJ[0][i] + g14 * CJ[1][i]) + g24 * CJ[2][i];
+      else jt = (g05 * CJ[0][i] + g15 * CJ[1][i]) + g25 * CJ[2][i];
+      float v = nda * xCJ[j];
+      if (i >= 3 && j >= 3) v = v + xCH[i - 3][j - 3];
+      v = v + jt;
+      acc[7 + i * 6 + j] += (double)(e * v);                                               // NDT_I:539-542
+    }
+  }
+}
+#undef PGV
+#undef PHV
+
+// Block reduction of the 44 per-thread accumulators through shared memory: every warp parks its
+// accumulators column-wise, 44 lanes each add one column in lane order, then 44 threads add the
+// warps in warp order.  Fixed order => bit-reproducible regardless of batch layout.
+constexpr int kRedPad = 33;
+__device__ __forceinline__ void block_reduce_store(const double* acc, int npairs, double* __restrict__ out) {
+  extern __shared__ double red_sm[];                 // [warps][44][33] + [warps][44]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+  double* mine = red_sm + (size_t)warp * kPartialStride * kRedPad;
+#pragma unroll
+  for (int k = 0; k < kAccN; ++k) mine[k * kRedPad + lane] = acc[k];
+  mine[kAccN * kRedPad + lane] = (double)npairs;
+  __syncwarp();
+  double* wsum = red_sm + (size_t)nwarps * kPartialStride * kRedPad;
+  for (int k = lane; k < kPartialStride; k += 32) {
+    double v = 0;
+#pragma unroll 8
+    for (int l = 0; l < 32; ++l) v += mine[k * kRedPad + l];
+    wsum[warp * kPartialStride + k] = v;
+  }
+  __syncthreads();
+  if (tid < kPartialStride) {
+    double v = 0;
+    for (int w = 0; w < nwarps; ++w) v += wsum[w * kPartialStride + tid];
+    out[tid] = v;
+  }
+}
+static size_t reduce_smem_bytes(int threads) {
+  const int nw = threads / 32;
+  return ((size_t)nw * kPartialStride * kRedPad + (size_t)nw * kPartialStride) * sizeof(double);
+}
+
+template <int METHOD, bool CH>
+__global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const AlignState* __restrict__ states, const VoxelTable* __restrict__ tables,
                                                           const float4* __restrict__ src_pool, const int2* __restrict__ blockmap,
                                                           int chunk, double* __restrict__ partials) {
   const int2 bm = blockmap[blockIdx.x];
   const AlignState& st = states[bm.x];
   const int mode = st.req.mode;
-  if ((mode != 1 && mode != 2) || st.done) return;
+  if (mode != (CH ? 1 : 2) || st.done || st.req.search_method != METHOD) return;
   __shared__ EvalShared sh;
-  __shared__ double red[kThreads / 32][kPartialStride];
+#if NDTB_PD_SMEM
+  __shared__ float pd_sm[23 * kThreads];
+#endif
   const int tid = threadIdx.x;
-  if (tid < 12) sh.T[tid] = st.req.T[tid];
-  if (tid >= 32 && tid < 56) sh.jang[tid - 32] = (&st.req.jang[0][0])[tid - 32];
-  if (tid >= 64 && tid < 109) sh.hang[tid - 64] = (&st.req.hang[0][0])[tid - 64];
-  if (tid == 128) {
+  for (int k = tid; k < 12; k += kThreads) sh.T[k] = st.req.T[k];
+  for (int k = tid; k < 24; k += kThreads) sh.jang[k] = (&st.req.jang[0][0])[k];
+  for (int k = tid; k < 45; k += kThreads) sh.hang[k] = (&st.req.hang[0][0])[k];
+  if (tid == kThreads - 1) {
     sh.d1 = st.req.d1; sh.d2 = st.req.d2; sh.d2f = (float)st.req.d2;   // float gauss_d2 = gauss_d2_ (NDT_I:504)
-    sh.mode = mode; sh.method = st.req.search_method;
+    sh.mode = mode; sh.method = METHOD;
     sh.tab = tables[st.target];
   }
   __syncthreads();
@@ -209,48 +338,86 @@ __global__ void __launch_bounds__(kThreads) k_derivatives(const AlignState* __re
   int npairs = 0;
   const float4* __restrict__ src = src_pool + st.src_offset;
   const int end = min(bm.y + chunk, st.n_src);
-  const bool ch = mode == 1;
-  const int method = sh.method;
+  const HashSlot* __restrict__ slots = sh.tab.slots;
+  const VoxelRec* __restrict__ recs = sh.tab.rec;
+  const uint32_t mask = sh.tab.mask;
+  const int min_points = sh.tab.min_points;
+  const float leaf = sh.tab.leaf;
+  const float d2f = sh.d2f;
+  const double d1 = sh.d1;
   for (int i = bm.y + tid; i < end; i += kThreads) {
     const float4 p = __ldg(src + i);
     float xt, yt, zt;
     xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
-    int nb[27];
-    const int cnt = find_neighbors(sh.tab, method, xt, yt, zt, nb);
-    if (cnt == 0) continue;
-    // computePointDerivatives (NDT_I:401-445): x_j_ang = j_ang * x4, x_h_ang = h_ang * x4
-    float pgv[8], phv[15];
+    int nb[METHOD == 2 ? 7 : 27];
+    int cnt = 0;
+    if (METHOD == 2) {
+      // DIRECT7 (VGC_I:419-433): all seven first-probe slot loads are issued before any is consumed
+      if (slots != nullptr) {
+        const int ci = query_cell(xt, leaf), cj = query_cell(yt, leaf), ck = query_cell(zt, leaf);
+        uint4 s7[7];
+        unsigned long long key7[7];
+        uint32_t h7[7];
 #pragma unroll
-    for (int r = 0; r < 8; ++r) pgv[r] = (sh.jang[r * 3] * p.x + sh.jang[r * 3 + 1] * p.y) + sh.jang[r * 3 + 2] * p.z;
-    if (ch) {
+        for (int o = 0; o < 7; ++o) {
+          const int a = ci + c_off7[o][0], b = cj + c_off7[o][1], c = ck + c_off7[o][2];
+          const bool ok = coord_ok(a) && coord_ok(b) && coord_ok(c);
+          key7[o] = ok ? pack_key(a, b, c) : kEmptyKey;
+          h7[o] = hash_fields((uint32_t)(a + kCoordBias), (uint32_t)(b + kCoordBias), (uint32_t)(c + kCoordBias)) & mask;
+          s7[o] = __ldg(reinterpret_cast<const uint4*>(slots + h7[o]));
+        }
 #pragma unroll
-      for (int r = 0; r < 15; ++r) phv[r] = (sh.hang[r * 3] * p.x + sh.hang[r * 3 + 1] * p.y) + sh.hang[r * 3 + 2] * p.z;
+        for (int o = 0; o < 7; ++o) {
+          unsigned long long k = ((unsigned long long)s7[o].y << 32) | s7[o].x;
+          int vidx = (int)s7[o].z, nr = (int)s7[o].w;
+          uint32_t h = h7[o];
+          while (k != key7[o] && k != kEmptyKey) {   // linear probing past a collision (rare at load <= 0.25)
+            h = (h + 1) & mask;
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(slots + h));
+            k = ((unsigned long long)v.y << 32) | v.x; vidx = (int)v.z; nr = (int)v.w;
+          }
+          if (k == key7[o] && key7[o] != kEmptyKey && nr >= min_points) nb[cnt++] = vidx;
+        }
+      }
+    } else {
+      cnt = find_neighbors(sh.tab, METHOD, xt, yt, zt, nb);
     }
-    for (int k = 0; k < cnt; ++k) pair_update(acc, sh.tab.rec + nb[k], xt, yt, zt, pgv, phv, sh.d2f, sh.d1, ch);
+    if (cnt == 0) continue;
+    // computePointDerivatives (NDT_I:401-445): x_j_ang = j_ang * x4, x_h_ang = h_ang * x4.  The 23
+    // per-point values are parked in shared memory (one column per thread) instead of registers.
+#if NDTB_PD_SMEM
+    float* pdv = pd_sm + tid;
+#define PDI(r) pdv[(r) * kThreads]
+#else
+    float pdv[23];
+#define PDI(r) pdv[(r)]
+#endif
+#pragma unroll
+    for (int r = 0; r < 8; ++r) PDI(r) = (sh.jang[r * 3] * p.x + sh.jang[r * 3 + 1] * p.y) + sh.jang[r * 3 + 2] * p.z;
+    if (CH) {
+#pragma unroll
+      for (int r = 0; r < 15; ++r) PDI(8 + r) = (sh.hang[r * 3] * p.x + sh.hang[r * 3 + 1] * p.y) + sh.hang[r * 3 + 2] * p.z;
+    }
+#undef PDI
+#if NDTB_PREFETCH
+    RecRegs cur = load_rec(recs + nb[0]);
+#ifdef NDTB_NOUNROLL
+#pragma unroll 1
+#endif
+    for (int k = 0; k < cnt; ++k) {
+      const RecRegs use = cur;
+      if (k + 1 < cnt) cur = load_rec(recs + nb[k + 1]);
+      pair_update_r<CH>(acc, use, xt, yt, zt, pdv, d2f, d1);
+    }
+#else
+    for (int k = 0; k < cnt; ++k) {
+      const RecRegs use = load_rec(recs + nb[k]);
+      pair_update_r<CH>(acc, use, xt, yt, zt, pdv, d2f, d1);
+    }
+#endif
     npairs += cnt;
   }
-  // block reduction: butterfly within the warp, then a fixed-order sum over the warps
-  const int lane = tid & 31, warp = tid >> 5;
-#pragma unroll
-  for (int k = 0; k < kAccN; ++k) {
-    double v = acc[k];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) red[warp][k] = v;
-  }
-  {
-    int v = npairs;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) red[warp][kAccN] = (double)v;
-  }
-  __syncthreads();
-  if (tid < kPartialStride) {
-    double v = 0;
-#pragma unroll
-    for (int w = 0; w < kThreads / 32; ++w) v += red[w][tid];
-    partials[(size_t)blockIdx.x * kPartialStride + tid] = v;
-  }
+  block_reduce_store(acc, npairs, partials + (size_t)blockIdx.x * kPartialStride);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -779,11 +946,31 @@ __global__ void k_prefix_equal(const uint4* __restrict__ a, const uint4* __restr
   }
 }
 
-cudaError_t launch_derivatives(const AlignState* states, const VoxelTable* tables, const float4* src_pool, const int2* blockmap,
-                               int n_blocks, int chunk, double* partials, cudaStream_t s) {
-  if (n_blocks <= 0) return cudaSuccess;
-  k_derivatives<<<n_blocks, kThreads, 0, s>>>(states, tables, src_pool, blockmap, chunk, partials);
+template <int METHOD>
+static cudaError_t launch_deriv_m(const AlignState* states, const VoxelTable* tables, const float4* src_pool, const int2* blockmap,
+                                  int n_blocks, int chunk, double* partials, bool both, cudaStream_t s) {
+  const size_t sm = reduce_smem_bytes(kThreads);
+  static bool configured = false;
+  if (!configured) {
+    cudaFuncSetAttribute(k_derivatives<METHOD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    cudaFuncSetAttribute(k_derivatives<METHOD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    configured = true;
+  }
+  k_derivatives<METHOD, true><<<n_blocks, kThreads, sm, s>>>(states, tables, src_pool, blockmap, chunk, partials);
+  if (both) k_derivatives<METHOD, false><<<n_blocks, kThreads, sm, s>>>(states, tables, src_pool, blockmap, chunk, partials);
   return cudaGetLastError();
+}
+// `method` = the batch's neighbour search method; `with_gradient_only` additionally launches the
+// compute_hessian == false variant (More-Thuente trial evaluations, NDT_I:869).
+cudaError_t launch_derivatives(const AlignState* states, const VoxelTable* tables, const float4* src_pool, const int2* blockmap,
+                               int n_blocks, int chunk, double* partials, int method, bool with_gradient_only, cudaStream_t s) {
+  if (n_blocks <= 0) return cudaSuccess;
+  switch (method) {
+    case 0: return launch_deriv_m<0>(states, tables, src_pool, blockmap, n_blocks, chunk, partials, with_gradient_only, s);
+    case 1: return launch_deriv_m<1>(states, tables, src_pool, blockmap, n_blocks, chunk, partials, with_gradient_only, s);
+    case 3: return launch_deriv_m<3>(states, tables, src_pool, blockmap, n_blocks, chunk, partials, with_gradient_only, s);
+    default: return launch_deriv_m<2>(states, tables, src_pool, blockmap, n_blocks, chunk, partials, with_gradient_only, s);
+  }
 }
 cudaError_t launch_hessian_f64(const AlignState* states, const VoxelTable* tables, const float4* src_pool, const int2* blockmap,
                                int n_blocks, int chunk, double* partials, cudaStream_t s) {

@@ -29,9 +29,14 @@ __host__ __device__ inline void unpack_key(uint64_t key, int& i, int& j, int& k)
   j = (int)((key >> 21) & 0x1FFFFF) - kCoordBias;
   k = (int)((key >> 42) & 0x1FFFFF) - kCoordBias;
 }
+// Spatial hash of the three biased 21-bit cell fields: three 32-bit multiplies and one xor-shift.
+__host__ __device__ inline uint32_t hash_fields(uint32_t fi, uint32_t fj, uint32_t fk) {
+  uint32_t h = fi * 0x9E3779B1u + fj * 0x85EBCA77u + fk * 0xC2B2AE3Du;
+  h ^= h >> 15;
+  return h;
+}
 __host__ __device__ inline uint32_t hash_key(uint64_t k) {
-  k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
-  return (uint32_t)k;
+  return hash_fields((uint32_t)(k & 0x1FFFFF), (uint32_t)((k >> 21) & 0x1FFFFF), (uint32_t)((k >> 42) & 0x1FFFFF));
 }
 
 struct __align__(16) HashSlot {
@@ -125,8 +130,8 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
                          long long* launches);
 
 cudaError_t launch_derivatives(const AlignState* states, const VoxelTable* tables, const float4* src_pool,
-                               const int2* blockmap, int n_blocks, int chunk, double* partials,
-                               cudaStream_t s);
+                               const int2* blockmap, int n_blocks, int chunk, double* partials, int method,
+                               bool with_gradient_only, cudaStream_t s);
 cudaError_t launch_hessian_f64(const AlignState* states, const VoxelTable* tables, const float4* src_pool,
                                const int2* blockmap, int n_blocks, int chunk, double* partials, cudaStream_t s);
 cudaError_t launch_newton(AlignState* states, int n_items, const double* partials, double* trace, int trace_cap,

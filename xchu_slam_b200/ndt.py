@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libndt_b200.so")
+LIB_PATH = os.environ.get("NDTB_LIB", os.path.join(_HERE, "libndt_b200.so"))   # NDTB_LIB: kernel-variant experiments
 
 KDTREE, DIRECT26, DIRECT7, DIRECT1 = 0, 1, 2, 3
 
@@ -42,7 +42,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_neighbors",
            "ndtb_eval_derivatives", "ndtb_compute_hessian", "ndtb_get_trace", "ndtb_last_timing", "ndtb_batch_create",
            "ndtb_batch_destroy", "ndtb_batch_last_error", "ndtb_batch_set_params", "ndtb_batch_clear", "ndtb_batch_add_target",
-           "ndtb_batch_add_source", "ndtb_batch_run", "ndtb_batch_get_stats"]
+           "ndtb_batch_add_source", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream"]
 
 _lib = None
 
@@ -90,6 +90,7 @@ def load_library():
     L.ndtb_batch_add_source.argtypes = [vp, vp, sz, sz, C.c_int, C.POINTER(C.c_int)]
     L.ndtb_batch_run.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
+    L.ndtb_batch_set_stream.argtypes = [vp, vp]
     _lib = L
     return L
 
@@ -328,6 +329,10 @@ class BatchNDT:
 
     def clear(self):
         self._ck(self._L.ndtb_batch_clear(self._h))
+
+    def set_stream(self, cuda_stream_ptr):
+        """Run on the caller's stream (e.g. torch.cuda.current_stream().cuda_stream)."""
+        self._ck(self._L.ndtb_batch_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
 
     def add_target(self, cloud):
         cloud = _cloud(cloud)

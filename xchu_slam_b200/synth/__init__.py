@@ -196,3 +196,67 @@ def make_case(n_source=20000, n_target=300000, n_keyframes=None, spacing=2, traj
     src = source_scan(w, q, seed + 7, n_source, dense=dense)
     gt = sensor_pose(q)
     return src, target, gt, perturbed_guess(gt, seed + 13)
+
+
+def batch_workload(n_submaps=64, scans_per_submap=8, hyps_per_scan=8, n_target=1000000, n_source=20000,
+                   seed=BASE_SEED, keyframe_leaf=0.5, kf_every=2, submap_stride=4, cache_dir=None, verbose=False):
+    """BASELINE configs[4] (C5): n_submaps distinct localmaps (consecutive GT-posed keyframes along one
+    drive, windows shifted by submap_stride keyframes), scans_per_submap scans taken inside each
+    submap, hyps_per_scan perturbed initial guesses per scan.
+    Returns dict(targets=[(n_target,4) f32], sources=[(n_source,4) f32], item_target, item_source,
+    guesses (n_items,4,4) f32, gt (n_items,6)).  Cached as .npz under cache_dir when given."""
+    tag = "c5_%d_%d_%d_%d_%d_%d_%s_%d_%d" % (n_submaps, scans_per_submap, hyps_per_scan, n_target, n_source, seed,
+                                             keyframe_leaf, kf_every, submap_stride)
+    path = os.path.join(cache_dir, tag + ".npz") if cache_dir else None
+    if path and os.path.exists(path):
+        z = np.load(path)
+        return dict(targets=list(z["targets"]), sources=list(z["sources"]), item_target=z["item_target"],
+                    item_source=z["item_source"], guesses=z["guesses"], gt=z["gt"])
+    w = World(seed)
+    est_kf = int(n_target / (9000 if keyframe_leaf <= 0.5 else 4000)) + 40
+    n_kf = n_submaps * submap_stride + est_kf * 2
+    poses = w.trajectory(60 + n_kf * kf_every + 16, seed=seed & 0xFFFF)
+    kf_cache = {}
+
+    def kf(k):
+        if k not in kf_cache:
+            kf_cache[k] = keyframe(w, poses[50 + k * kf_every], seed + 1000 + k, keyframe_leaf)
+        return kf_cache[k]
+
+    targets, sources, it, isrc, guesses, gts = [], [], [], [], [], []
+    for s in range(n_submaps):
+        k0, total, chunks = s * submap_stride, 0, []
+        k = k0
+        while total < n_target:
+            chunks.append(kf(k))
+            total += chunks[-1].shape[0]
+            k += 1
+        targets.append(exact_count(np.concatenate(chunks, axis=0), n_target, seed + 77 + s))
+        for dead in [d for d in kf_cache if d < k0 + submap_stride]:
+            if s + 1 < n_submaps and dead < (s + 1) * submap_stride:
+                del kf_cache[dead]
+        nk = k - k0
+        for j in range(scans_per_submap):
+            # a scan pose strictly between two keyframe poses, spread over the middle half of the submap
+            kq = k0 + nk // 4 + (j * max(1, (nk // 2) // scans_per_submap))
+            pi = 50 + kq * kf_every + 1
+            src = source_scan(w, poses[pi], seed + 500000 + s * 97 + j, n_source)
+            sid = len(sources)
+            sources.append(src)
+            gt = sensor_pose(poses[pi])
+            for hh in range(hyps_per_scan):
+                it.append(s)
+                isrc.append(sid)
+                guesses.append(perturbed_guess(gt, seed + 900000 + len(it)))
+                gts.append(gt)
+        if verbose:
+            print("[synth] submap %d/%d: %d keyframes" % (s + 1, n_submaps, nk), flush=True)
+    out = dict(targets=targets, sources=sources, item_target=np.array(it, np.int32), item_source=np.array(isrc, np.int32),
+               guesses=np.stack(guesses).astype(np.float32), gt=np.stack(gts))
+    if path:
+        os.makedirs(cache_dir, exist_ok=True)
+        tmp = path + ".tmp%d.npz" % os.getpid()
+        np.savez(tmp, targets=np.stack(targets), sources=np.stack(sources), item_target=out["item_target"],
+                 item_source=out["item_source"], guesses=out["guesses"], gt=out["gt"])
+        os.replace(tmp, path)
+    return out
