@@ -43,6 +43,9 @@ typedef struct ndtb_params {
   int search_method;     /* setNeighborhoodSearchMethod, NDT_H:184-186 default DIRECT7 */
   int min_points;        /* min_points_per_voxel_,    VGC_H:204       default 6    */
   double eig_mult;       /* min_covar_eigvalue_mult_, VGC_H:205       default 0.01 */
+  int strict_math;       /* 0 (default): per-point factorised derivative kernel (results within the 1e-6
+                            parity tolerance of the reference arithmetic); 1: term-by-term kernel that
+                            reproduces every float operation of NDT_I:491-548 in the reference's order */
 } ndtb_params;
 
 typedef struct ndtb_result {

@@ -10,7 +10,9 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libndt_b200.so")
-SOURCES = ["voxel_build.cu", "ndt_core.cu", "ndt_api.cu"]
+SOURCES = ["voxel_build.cu", "ndt_core.cu", "ndt_fast.cu", "ndt_api.cu"]
+# ndt_fast.cu carries explicit round-to-nearest intrinsics where bits matter and wants FMA contraction elsewhere
+NO_FMAD_FALSE = {"ndt_fast.cu"}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
               "-Xcompiler", "-fPIC", "-ccbin", "g++"]
 
@@ -35,7 +37,7 @@ def build_cuda(force=False, verbose=False, defines=(), lib=None):
 
 
 def _build_cuda(force=False, verbose=False, defines=()):
-    hdrs = [os.path.join(CSRC, "ndt_internal.h"), os.path.join(HERE, "..", "include", "ndt_b200", "ndt_c_api.h")]
+    hdrs = [os.path.join(CSRC, "ndt_internal.h"), os.path.join(CSRC, "ndt_device.cuh"), os.path.join(HERE, "..", "include", "ndt_b200", "ndt_c_api.h")]
     objs = []
     procs = []
     for src in SOURCES:
@@ -43,7 +45,8 @@ def _build_cuda(force=False, verbose=False, defines=()):
         o = os.path.join(CSRC, src.replace(".cu", ".o"))
         objs.append(o)
         if force or _stale(o, [s] + hdrs):
-            cmd = ["nvcc"] + NVCC_FLAGS + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
+            flags = [f for f in NVCC_FLAGS if not (f == "-fmad=false" and src in NO_FMAD_FALSE)]
+            cmd = ["nvcc"] + flags + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
             procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     for src, p in procs:
         out, _ = p.communicate()

@@ -297,7 +297,8 @@ struct Engine {
         deriv_events.push_back(a); deriv_events.push_back(b);
       }
       CKE(cudaEventRecord(deriv_events[ev_used], stream));
-      CKE(launch_derivatives(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk, d_partials, params.search_method, mt_live, stream));
+      CKE((params.strict_math ? launch_derivatives : launch_derivatives_fast)(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk,
+                                                                                d_partials, params.search_method, mt_live, stream));
       CKE(cudaEventRecord(deriv_events[ev_used + 1], stream));
       ev_used += 2;
       stats.kernel_launches += mt_live ? 2 : 1; stats.deriv_launches++;
@@ -352,7 +353,7 @@ extern "C" {
 
 void ndtb_default_params(ndtb_params* p) {
   p->resolution = 1.0f; p->step_size = 0.1; p->trans_eps = 0.1; p->max_iter = 35; p->outlier_ratio = 0.55;
-  p->search_method = NDTB_DIRECT7; p->min_points = 6; p->eig_mult = 0.01;
+  p->search_method = NDTB_DIRECT7; p->min_points = 6; p->eig_mult = 0.01; p->strict_math = 0;
 }
 
 static int create_engine(int device, Engine& e) { return e.init(device); }
@@ -572,7 +573,7 @@ static int single_eval(Engine& e, const float T[16], const double p[6], int mode
   cudaMemcpyAsync(e.d_active, e.h_active, sizeof(int), cudaMemcpyHostToDevice, e.stream);
   if (launch_prepare_eval(e.d_states, e.d_T16, e.d_p6, mode, e.stream) != cudaSuccess) return e.fail("prepare failed");
   cudaError_t ce;
-  if (mode == 1 || mode == 2) ce = launch_derivatives(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.params.search_method, true, e.stream);
+  if (mode == 1 || mode == 2) ce = (e.params.strict_math ? launch_derivatives : launch_derivatives_fast)(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.params.search_method, true, e.stream);
   else ce = launch_hessian_f64(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.stream);
   if (ce != cudaSuccess) return e.fail(std::string("eval launch: ") + cudaGetErrorString(ce));
   if (launch_newton(e.d_states, 1, e.d_partials, nullptr, 0, e.d_active, e.stream) != cudaSuccess) return e.fail("reduce failed");

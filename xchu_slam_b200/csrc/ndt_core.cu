@@ -11,6 +11,7 @@
 #include <cmath>
 
 #include "ndt_internal.h"
+#include "ndt_device.cuh"
 
 namespace ndtb {
 
@@ -29,92 +30,6 @@ namespace ndtb {
 #define NDTB_PREFETCH 1
 #endif
 constexpr int kThreads = NDTB_THREADS;
-constexpr int kPartialStride = 44;  // 43 accumulators + pair count
-
-__constant__ int c_off7[7][3] = {{0, 0, 0}, {1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};  // VGC_I:423-430
-// pcl::getAllNeighborCellIndices(): 13 "half" neighbours followed by their negations (VGC_I:413)
-__constant__ int c_off26[26][3] = {
-    {-1, -1, -1}, {-1, 0, -1}, {-1, 1, -1}, {0, -1, -1}, {0, 0, -1}, {0, 1, -1}, {1, -1, -1}, {1, 0, -1}, {1, 1, -1},
-    {-1, -1, 0}, {0, -1, 0}, {1, -1, 0}, {-1, 0, 0},
-    {1, 1, 1}, {1, 0, 1}, {1, -1, 1}, {0, 1, 1}, {0, 0, 1}, {0, -1, 1}, {-1, 1, 1}, {-1, 0, 1}, {-1, -1, 1},
-    {1, 1, 0}, {0, 1, 0}, {-1, 1, 0}, {1, 0, 0}};
-
-// ---------------------------------------------------------------------------------------
-// hash probe: one 128-bit load per probed slot
-// ---------------------------------------------------------------------------------------
-__device__ __forceinline__ HashSlot load_slot(const HashSlot* p) {
-  const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
-  HashSlot s;
-  s.key = ((unsigned long long)v.y << 32) | v.x;
-  s.vidx = (int)v.z;
-  s.nr_points = (int)v.w;
-  return s;
-}
-__device__ __forceinline__ bool probe(const VoxelTable& t, int i, int j, int k, HashSlot& out) {
-  if (!coord_ok(i) || !coord_ok(j) || !coord_ok(k)) return false;
-  const unsigned long long key = pack_key(i, j, k);
-  uint32_t h = hash_key(key) & t.mask;
-  while (true) {
-    const HashSlot s = load_slot(t.slots + h);
-    if (s.key == key) { out = s; return true; }
-    if (s.key == kEmptyKey) return false;
-    h = (h + 1) & t.mask;
-  }
-}
-
-// Query-time cell: floor(x / leaf_size) (VGC_I:379-381) -- a float DIVISION, unlike the build key.
-__device__ __forceinline__ int query_cell(float x, float leaf) { return (int)floorf(x / leaf); }
-
-// Neighbour voxels of a transformed point in the reference's visiting order.
-// DIRECT1/7/26: VGC_I:373-442 (found && nr_points >= min_points).
-// KDTREE: VGC_H:470-499 over the centroid cloud (every voxel that had >= min_points inserted points,
-// flagged-invalid ones included), squared float distance < float(r*r), ascending distance.
-__device__ int find_neighbors(const VoxelTable& t, int method, float x, float y, float z, int* vout) {
-  if (t.slots == nullptr) return 0;   // empty grid (no target, or the overflow guard of VGC_I:79-84 tripped)
-  const int ci = query_cell(x, t.leaf), cj = query_cell(y, t.leaf), ck = query_cell(z, t.leaf);
-  int cnt = 0;
-  HashSlot s;
-  if (method == 2) {
-#pragma unroll
-    for (int o = 0; o < 7; ++o)
-      if (probe(t, ci + c_off7[o][0], cj + c_off7[o][1], ck + c_off7[o][2], s) && s.nr_points >= t.min_points) vout[cnt++] = s.vidx;
-  } else if (method == 3) {
-    if (probe(t, ci, cj, ck, s) && s.nr_points >= t.min_points) vout[cnt++] = s.vidx;
-  } else if (method == 1) {
-    for (int o = 0; o < 26; ++o)
-      if (probe(t, ci + c_off26[o][0], cj + c_off26[o][1], ck + c_off26[o][2], s) && s.nr_points >= t.min_points) vout[cnt++] = s.vidx;
-  } else {
-    const double rr = (double)t.leaf * (double)t.leaf;  // radius = resolution_ (NDT_I:233), r*r in double then float
-    const float r2 = (float)rr;
-    float d2s[27];
-    unsigned long long keys[27];
-    for (int dz = -1; dz <= 1; ++dz)
-      for (int dy = -1; dy <= 1; ++dy)
-        for (int dx = -1; dx <= 1; ++dx) {
-          if (!probe(t, ci + dx, cj + dy, ck + dz, s)) continue;
-          const float4 c = __ldg(t.centroid + s.vidx);
-          if (__float_as_int(c.w) < t.min_points) continue;
-          const float ex = x - c.x, ey = y - c.y, ez = z - c.z;
-          const float d2 = (ex * ex + ey * ey) + ez * ez;
-          if (!(d2 < r2)) continue;
-          // insertion sort by (d2, cell key): ascending distance, ties by ascending linear index
-          int pos = cnt;
-          while (pos > 0 && (d2s[pos - 1] > d2 || (d2s[pos - 1] == d2 && keys[pos - 1] > s.key))) {
-            d2s[pos] = d2s[pos - 1]; keys[pos] = keys[pos - 1]; vout[pos] = vout[pos - 1]; --pos;
-          }
-          d2s[pos] = d2; keys[pos] = s.key; vout[pos] = s.vidx;
-          ++cnt;
-        }
-  }
-  return cnt;
-}
-
-// pcl::transformPointCloud (NDT_I:93, 822, 866): x' = ((m00 x + m01 y) + m02 z) + m03, float
-__device__ __forceinline__ void xform(const float* T /*row-major 3x4*/, float x, float y, float z, float& ox, float& oy, float& oz) {
-  ox = ((T[0] * x + T[1] * y) + T[2] * z) + T[3];
-  oy = ((T[4] * x + T[5] * y) + T[6] * z) + T[7];
-  oz = ((T[8] * x + T[9] * y) + T[10] * z) + T[11];
-}
 
 struct EvalShared {
   float T[12];
@@ -131,71 +46,6 @@ struct EvalShared {
 // (NDT_I:401-445) + updateDerivatives (NDT_I:491-548), float per-term math, double accumulation,
 // warp-shuffle + shared-memory block reduction to one partial per block (fixed order, no atomics).
 // ---------------------------------------------------------------------------------------
-__device__ __forceinline__ void pair_update(double* acc, const VoxelRec* __restrict__ recp, float xtx, float xty, float xtz,
-                                            const float* pgv /*8*/, const float* phv /*15*/, float d2f, double d1,
-                                            bool compute_hessian) {
-  // 64 B record = four 128-bit loads
-  const double2 m01 = __ldg(reinterpret_cast<const double2*>(recp));
-  const double2 m2c = __ldg(reinterpret_cast<const double2*>(recp) + 1);
-  const float4 c1 = __ldg(reinterpret_cast<const float4*>(recp) + 2);
-  const float4 c2 = __ldg(reinterpret_cast<const float4*>(recp) + 3);
-  const float C00 = __int_as_float(__double2loint(m2c.y)), C01 = __int_as_float(__double2hiint(m2c.y));
-  const float C02 = c1.x, C10 = c1.y, C11 = c1.z, C12 = c1.w, C20 = c2.x, C21 = c2.y, C22 = c2.z;
-  // x_trans = f64(x_trans_pt) - mean, narrowed to float (NDT_I:257-260, 500)
-  const float x0 = (float)((double)xtx - m01.x), x1 = (float)((double)xty - m01.y), x2 = (float)((double)xtz - m2c.x);
-  const float xC0 = (x0 * C00 + x1 * C10) + x2 * C20;
-  const float xC1 = (x0 * C01 + x1 * C11) + x2 * C21;
-  const float xC2 = (x0 * C02 + x1 * C12) + x2 * C22;
-  const float q = (x0 * xC0 + x1 * xC1) + x2 * xC2;
-  float e = (float)exp((double)((-d2f * q) * 0.5f));            // NDT_I:507
-  const float score_inc = (float)(-d1 * (double)e);             // NDT_I:509
-  e = d2f * e;                                                  // NDT_I:511
-  if (e > 1.f || e < 0.f || e != e) return;                     // NDT_I:514-515 (score not counted either)
-  e = (float)((double)e * d1);                                  // NDT_I:518
-  acc[0] += (double)score_inc;
-  const float g13 = pgv[0], g23 = pgv[1], g04 = pgv[2], g14 = pgv[3], g24 = pgv[4], g05 = pgv[5], g15 = pgv[6], g25 = pgv[7];
-  // CJ = c_inv4 * point_gradient4 (NDT_I:520); columns 0..2 are the columns of C
-  float CJ[3][6];
-  CJ[0][0] = C00; CJ[0][1] = C01; CJ[0][2] = C02;
-  CJ[1][0] = C10; CJ[1][1] = C11; CJ[1][2] = C12;
-  CJ[2][0] = C20; CJ[2][1] = C21; CJ[2][2] = C22;
-  CJ[0][3] = C01 * g13 + C02 * g23; CJ[1][3] = C11 * g13 + C12 * g23; CJ[2][3] = C21 * g13 + C22 * g23;
-  CJ[0][4] = (C00 * g04 + C01 * g14) + C02 * g24; CJ[1][4] = (C10 * g04 + C11 * g14) + C12 * g24; CJ[2][4] = (C20 * g04 + C21 * g14) + C22 * g24;
-  CJ[0][5] = (C00 * g05 + C01 * g15) + C02 * g25; CJ[1][5] = (C10 * g05 + C11 * g15) + C12 * g25; CJ[2][5] = (C20 * g05 + C21 * g15) + C22 * g25;
-  float xCJ[6];
-  xCJ[0] = xC0; xCJ[1] = xC1; xCJ[2] = xC2;
-#pragma unroll
-  for (int c = 3; c < 6; ++c) xCJ[c] = (x0 * CJ[0][c] + x1 * CJ[1][c]) + x2 * CJ[2][c];   // NDT_I:521
-#pragma unroll
-  for (int c = 0; c < 6; ++c) acc[1 + c] += (double)(e * xCJ[c]);                          // NDT_I:523
-  if (!compute_hessian) return;
-  // xCH(i,j) = (x_trans4 * c_inv4) * point_hessian_.block<4,1>(4i, j)  (NDT_I:534-535); non-zero for i,j >= 3
-  const float ha = xC1 * phv[0] + xC2 * phv[1];
-  const float hb = xC1 * phv[2] + xC2 * phv[3];
-  const float hc = xC1 * phv[4] + xC2 * phv[5];
-  const float hd = (xC0 * phv[6] + xC1 * phv[7]) + xC2 * phv[8];
-  const float he = (xC0 * phv[9] + xC1 * phv[10]) + xC2 * phv[11];
-  const float hf = (xC0 * phv[12] + xC1 * phv[13]) + xC2 * phv[14];
-  const float xCH[3][3] = {{ha, hb, hc}, {hb, hd, he}, {hc, he, hf}};
-  const float nd2 = -d2f;
-#pragma unroll
-  for (int i = 0; i < 6; ++i) {
-#pragma unroll
-    for (int j = 0; j < 6; ++j) {
-      // JtCJ(j,i) = point_gradient4.col(j) . CJ.col(i)   (NDT_I:527-528, 542)
-      float jt;
-      if (j < 3) jt = CJ[j][i];
-      else if (j == 3) jt = g13 * CJ[1][i] + g23 * CJ[2][i];
-      else if (j == 4) jt = (g04 * CJ[0][i] + g14 * CJ[1][i]) + g24 * CJ[2][i];
-      else jt = (g05 * CJ[0][i] + g15 * CJ[1][i]) + g25 * CJ[2][i];
-      float v = (nd2 * xCJ[i]) * xCJ[j];
-      if (i >= 3 && j >= 3) v = v + xCH[i - 3][j - 3];
-      v = v + jt;
-      acc[7 + i * 6 + j] += (double)(e * v);                                               // NDT_I:539-542
-    }
-  }
-}
-
 // Record fetch: the 64 B record as four 128-bit loads (issued together, consumed later)
 struct RecRegs { double2 a, b; float4 c, d; };
 __device__ __forceinline__ RecRegs load_rec(const VoxelRec* __restrict__ recp) {
@@ -352,33 +202,7 @@ __global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const 
     int nb[METHOD == 2 ? 7 : 27];
     int cnt = 0;
     if (METHOD == 2) {
-      // DIRECT7 (VGC_I:419-433): all seven first-probe slot loads are issued before any is consumed
-      if (slots != nullptr) {
-        const int ci = query_cell(xt, leaf), cj = query_cell(yt, leaf), ck = query_cell(zt, leaf);
-        uint4 s7[7];
-        unsigned long long key7[7];
-        uint32_t h7[7];
-#pragma unroll
-        for (int o = 0; o < 7; ++o) {
-          const int a = ci + c_off7[o][0], b = cj + c_off7[o][1], c = ck + c_off7[o][2];
-          const bool ok = coord_ok(a) && coord_ok(b) && coord_ok(c);
-          key7[o] = ok ? pack_key(a, b, c) : kEmptyKey;
-          h7[o] = hash_fields((uint32_t)(a + kCoordBias), (uint32_t)(b + kCoordBias), (uint32_t)(c + kCoordBias)) & mask;
-          s7[o] = __ldg(reinterpret_cast<const uint4*>(slots + h7[o]));
-        }
-#pragma unroll
-        for (int o = 0; o < 7; ++o) {
-          unsigned long long k = ((unsigned long long)s7[o].y << 32) | s7[o].x;
-          int vidx = (int)s7[o].z, nr = (int)s7[o].w;
-          uint32_t h = h7[o];
-          while (k != key7[o] && k != kEmptyKey) {   // linear probing past a collision (rare at load <= 0.25)
-            h = (h + 1) & mask;
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(slots + h));
-            k = ((unsigned long long)v.y << 32) | v.x; vidx = (int)v.z; nr = (int)v.w;
-          }
-          if (k == key7[o] && key7[o] != kEmptyKey && nr >= min_points) nb[cnt++] = vidx;
-        }
-      }
+      cnt = neighbors_direct7(slots, mask, min_points, leaf, xt, yt, zt, nb);
     } else {
       cnt = find_neighbors(sh.tab, METHOD, xt, yt, zt, nb);
     }
@@ -645,6 +469,73 @@ __device__ void svd_solve6(const double* H, const double* b, double* x) {
   }
 }
 
+// Newton step H x = b.  Eigen::JacobiSVD::solve is a pseudo-inverse solve; for the full-rank,
+// moderately conditioned Hessians of a registration that is the ordinary solution, which Gaussian
+// elimination with FULL pivoting plus one step of iterative refinement delivers to the same ~1e-15
+// in a few hundred serial FP64 operations instead of the ~10^5 of the Jacobi sweeps (the sweeps were
+// 15 % of a batched step).  Rank-deficient or non-finite systems (empty grid: H = 0) return false
+// and take the SVD path, which keeps the minimum-norm / zero-step behaviour of NDT_I:119-130.
+__device__ bool lu_solve6(const double* H, const double* b, double* x) {
+  double A[6][6], rhs[6];
+  int cperm[6];
+  double pmax = 0.0, pmin = DBL_MAX;
+  for (int i = 0; i < 6; ++i) {
+    cperm[i] = i;
+    rhs[i] = b[i];
+    for (int j = 0; j < 6; ++j) A[i][j] = H[i * 6 + j];
+  }
+  for (int k = 0; k < 6; ++k) {
+    int pi = k, pj = k;
+    double best = -1.0;
+    for (int i = k; i < 6; ++i)
+      for (int j = k; j < 6; ++j) {
+        const double v = fabs(A[i][j]);
+        if (!(v <= DBL_MAX)) return false;   // NaN / inf
+        if (v > best) { best = v; pi = i; pj = j; }
+      }
+    if (!(best > 0.0)) return false;
+    if (pi != k) {
+      for (int j = 0; j < 6; ++j) { const double t = A[k][j]; A[k][j] = A[pi][j]; A[pi][j] = t; }
+      const double t = rhs[k]; rhs[k] = rhs[pi]; rhs[pi] = t;
+    }
+    if (pj != k) {
+      for (int i = 0; i < 6; ++i) { const double t = A[i][k]; A[i][k] = A[i][pj]; A[i][pj] = t; }
+      const int t = cperm[k]; cperm[k] = cperm[pj]; cperm[pj] = t;
+    }
+    pmax = fmax(pmax, best);
+    pmin = fmin(pmin, best);
+    const double inv = 1.0 / A[k][k];
+    for (int i = k + 1; i < 6; ++i) {
+      const double m = A[i][k] * inv;
+      A[i][k] = m;
+      for (int j = k + 1; j < 6; ++j) A[i][j] -= m * A[k][j];
+      rhs[i] -= m * rhs[k];
+    }
+  }
+  if (!(pmin > 1e-10 * pmax)) return false;
+  double y[6];
+  for (int i = 5; i >= 0; --i) {
+    double v = rhs[i];
+    for (int j = i + 1; j < 6; ++j) v -= A[i][j] * y[j];
+    y[i] = v / A[i][i];
+  }
+  for (int i = 0; i < 6; ++i) x[cperm[i]] = y[i];
+  return true;
+}
+__device__ void solve6(const double* H, const double* b, double* x) {
+  if (!lu_solve6(H, b, x)) { svd_solve6(H, b, x); return; }
+  double r[6], d[6];
+  for (int i = 0; i < 6; ++i) {   // one refinement step: r = b - H x
+    double v = b[i];
+    for (int j = 0; j < 6; ++j) v -= H[i * 6 + j] * x[j];
+    r[i] = v;
+  }
+  if (lu_solve6(H, r, d))
+    for (int i = 0; i < 6; ++i) x[i] += d[i];
+  for (int i = 0; i < 6; ++i)
+    if (!(fabs(x[i]) <= DBL_MAX)) { svd_solve6(H, b, x); return; }
+}
+
 // ---------------------------------------------------------------------------------------
 // More-Thuente pieces (NDT_I:644-757), verbatim semantics
 // ---------------------------------------------------------------------------------------
@@ -735,7 +626,7 @@ __device__ void newton_top(NewtonCtx& c) {
   while (true) {
     double neg_g[6], delta[6];
     for (int k = 0; k < 6; ++k) neg_g[k] = -st.g[k];
-    svd_solve6(st.H, neg_g, delta);
+    solve6(st.H, neg_g, delta);
     double n2 = 0;
     for (int k = 0; k < 6; ++k) n2 += delta[k] * delta[k];
     const double norm = sqrt(n2);

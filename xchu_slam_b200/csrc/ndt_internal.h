@@ -51,10 +51,22 @@ struct __align__(64) VoxelRec {
   int nr_points;
 };
 
+// 48 B record of the fast derivative kernel: exactly the 48 B per (point, voxel) pair of the
+// algorithmic-bytes model (mean 24 B + symmetric inverse covariance 24 B), three 128-bit loads.
+// The f64 mean is carried as an unevaluated float sum hi + lo (48 significant bits) so that
+// x - mean is formed in two float subtractions to the same float the reference's double
+// subtraction rounds to (NDT_I:257-260, 500).
+struct __align__(16) FastRec {
+  float mh[3];     // (float)mean
+  float ml[3];     // (float)(mean - (double)mh)
+  float c[6];      // icov (float) upper triangle: 00 01 02 11 12 22
+};
+
 struct VoxelTable {          // all pointers device
   HashSlot* slots;
   uint32_t mask;             // capacity - 1 (capacity is a power of two)
   VoxelRec* rec;
+  FastRec* frec;             // same voxels, layout of the fast kernel
   double* icov64;            // [v][9] Leaf::icov_ in f64, read only by the FP64 computeHessian / calculateScore kernels
   float4* centroid;          // x, y, z (f32, VGC_I:289), w = bit pattern of inserted point count
   unsigned long long* vkey;  // packed absolute cell of voxel v
@@ -132,6 +144,11 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
 cudaError_t launch_derivatives(const AlignState* states, const VoxelTable* tables, const float4* src_pool,
                                const int2* blockmap, int n_blocks, int chunk, double* partials, int method,
                                bool with_gradient_only, cudaStream_t s);
+// Fast variant of launch_derivatives: same outputs within the 1e-6 parity tolerance, per-point
+// factorised math with FMAs (ndt_fast.cu).  Writes the same 44-double per-block partials.
+cudaError_t launch_derivatives_fast(const AlignState* states, const VoxelTable* tables, const float4* src_pool,
+                                    const int2* blockmap, int n_blocks, int chunk, double* partials, int method,
+                                    bool with_gradient_only, cudaStream_t s);
 cudaError_t launch_hessian_f64(const AlignState* states, const VoxelTable* tables, const float4* src_pool,
                                const int2* blockmap, int n_blocks, int chunk, double* partials, cudaStream_t s);
 cudaError_t launch_newton(AlignState* states, int n_items, const double* partials, double* trace, int trace_cap,

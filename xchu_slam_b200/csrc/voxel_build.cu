@@ -84,9 +84,9 @@ static cudaError_t ws_reserve(BuildWorkspace* ws, size_t n) {
 // ---------------------------------------------------------------------------------------
 void table_free(TableStorage& ts) {
   VoxelTable& t = ts.t;
-  cudaFree(t.slots); cudaFree(t.rec); cudaFree(t.icov64); cudaFree(t.centroid); cudaFree(t.vkey); cudaFree(t.vn);
+  cudaFree(t.slots); cudaFree(t.rec); cudaFree(t.frec); cudaFree(t.icov64); cudaFree(t.centroid); cudaFree(t.vkey); cudaFree(t.vn);
   cudaFree(t.vsum); cudaFree(t.vsxx); cudaFree(t.vcsum);
-  t.slots = nullptr; t.rec = nullptr; t.icov64 = nullptr; t.centroid = nullptr; t.vkey = nullptr; t.vn = nullptr;
+  t.slots = nullptr; t.rec = nullptr; t.frec = nullptr; t.icov64 = nullptr; t.centroid = nullptr; t.vkey = nullptr; t.vn = nullptr;
   t.vsum = nullptr; t.vsxx = nullptr; t.vcsum = nullptr;
   ts.vox_cap = ts.slot_cap = 0; ts.n_vox = 0; ts.valid = false; ts.have_bbox = false;
 }
@@ -123,7 +123,7 @@ cudaError_t table_reserve(TableStorage& ts, size_t need, cudaStream_t s, long lo
   if (need > ts.vox_cap) {
     const size_t nc = need + need / 2 + 4096;
     const size_t used = (size_t)ts.n_vox;
-    CK(grow(t.rec, used, nc, s)); CK(grow(t.icov64, used * 9, nc * 9, s)); CK(grow(t.centroid, used, nc, s)); CK(grow(t.vkey, used, nc, s)); CK(grow(t.vn, used, nc, s));
+    CK(grow(t.rec, used, nc, s)); CK(grow(t.frec, used, nc, s)); CK(grow(t.icov64, used * 9, nc * 9, s)); CK(grow(t.centroid, used, nc, s)); CK(grow(t.vkey, used, nc, s)); CK(grow(t.vn, used, nc, s));
     CK(grow(t.vsum, used * 3, nc * 3, s)); CK(grow(t.vsxx, used * 6, nc * 6, s)); CK(grow(t.vcsum, used * 3, nc * 3, s));
     ts.vox_cap = nc;
   }
@@ -355,6 +355,13 @@ __device__ void finalize_voxel(const VoxelTable& t, int v, int n, const double s
   }
   rec.nr_points = nr;
   t.rec[v] = rec;
+  FastRec fr;
+  for (int a = 0; a < 3; ++a) {
+    fr.mh[a] = (float)mean[a];
+    fr.ml[a] = (float)(mean[a] - (double)fr.mh[a]);
+  }
+  fr.c[0] = rec.icov[0]; fr.c[1] = rec.icov[1]; fr.c[2] = rec.icov[2]; fr.c[3] = rec.icov[4]; fr.c[4] = rec.icov[5]; fr.c[5] = rec.icov[8];
+  t.frec[v] = fr;
   for (int a = 0; a < 9; ++a) t.icov64[(size_t)v * 9 + a] = ic64[a];
   t.centroid[v] = c;
   t.slots[slot].nr_points = nr;

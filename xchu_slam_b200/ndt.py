@@ -22,7 +22,8 @@ class NdtError(RuntimeError):
 
 class Params(C.Structure):
     _fields_ = [("resolution", C.c_float), ("step_size", C.c_double), ("trans_eps", C.c_double), ("max_iter", C.c_int),
-                ("outlier_ratio", C.c_double), ("search_method", C.c_int), ("min_points", C.c_int), ("eig_mult", C.c_double)]
+                ("outlier_ratio", C.c_double), ("search_method", C.c_int), ("min_points", C.c_int), ("eig_mult", C.c_double),
+                ("strict_math", C.c_int)]
 
 
 class Result(C.Structure):
@@ -178,6 +179,11 @@ class NormalDistributionsTransform:
 
     def setVoxelParams(self, min_points=6, eig_mult=0.01):
         self._params.min_points, self._params.eig_mult = int(min_points), float(eig_mult)
+        self._push()
+
+    def setStrictMath(self, on):
+        """1: term-by-term derivative kernel in the reference's float operation order; 0: fast kernel."""
+        self._params.strict_math = int(bool(on))
         self._push()
 
     def setInputTarget(self, cloud):     # NDT_H:117-122
