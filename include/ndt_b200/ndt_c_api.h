@@ -46,6 +46,9 @@ typedef struct ndtb_params {
   int strict_math;       /* 0 (default): per-point factorised derivative kernel (results within the 1e-6
                             parity tolerance of the reference arithmetic); 1: term-by-term kernel that
                             reproduces every float operation of NDT_I:491-548 in the reference's order */
+  long long dense_max_cells; /* cell -> voxel lookups go through a dense int32 index over the target's bounding box
+                            when that box (padded by 2 cells) holds at most this many cells, else through the
+                            hash table; 0 = hash only.  default 2^26 (256 MB of index per target at most) */
 } ndtb_params;
 
 typedef struct ndtb_result {

@@ -158,6 +158,7 @@ struct Engine {
     t.ts.t.inv_leaf = 1.0f / params.resolution;   // pcl::VoxelGrid::setLeafSize: inverse_leaf_size_ = 1 / leaf (float)
     t.ts.t.min_points = params.min_points;
     t.ts.t.eig_mult = params.eig_mult;
+    t.ts.dense_max_cells = params.dense_max_cells;
   }
 
   // full (re)build of a target's voxel table from its resident points: init(), NDT_H:271-278
@@ -353,7 +354,7 @@ extern "C" {
 
 void ndtb_default_params(ndtb_params* p) {
   p->resolution = 1.0f; p->step_size = 0.1; p->trans_eps = 0.1; p->max_iter = 35; p->outlier_ratio = 0.55;
-  p->search_method = NDTB_DIRECT7; p->min_points = 6; p->eig_mult = 0.01; p->strict_math = 0;
+  p->search_method = NDTB_DIRECT7; p->min_points = 6; p->eig_mult = 0.01; p->strict_math = 0; p->dense_max_cells = 1ll << 26;
 }
 
 static int create_engine(int device, Engine& e) { return e.init(device); }
@@ -385,7 +386,8 @@ int ndtb_set_params(ndtb_handle* h, const ndtb_params* p) {
   Engine& e = h->e;
   if (check_params(e, p)) return 1;
   cudaSetDevice(e.device);
-  const bool rebuild = p->resolution != e.params.resolution || p->min_points != e.params.min_points || p->eig_mult != e.params.eig_mult;
+  const bool rebuild = p->resolution != e.params.resolution || p->min_points != e.params.min_points || p->eig_mult != e.params.eig_mult ||
+                       p->dense_max_cells != e.params.dense_max_cells;
   e.params = *p;
   Target& t = e.targets[0];
   if (rebuild && t.n > 0) {   // setResolution -> init() (NDT_H:127-137)

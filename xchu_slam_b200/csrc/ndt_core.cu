@@ -188,11 +188,7 @@ __global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const 
   int npairs = 0;
   const float4* __restrict__ src = src_pool + st.src_offset;
   const int end = min(bm.y + chunk, st.n_src);
-  const HashSlot* __restrict__ slots = sh.tab.slots;
   const VoxelRec* __restrict__ recs = sh.tab.rec;
-  const uint32_t mask = sh.tab.mask;
-  const int min_points = sh.tab.min_points;
-  const float leaf = sh.tab.leaf;
   const float d2f = sh.d2f;
   const double d1 = sh.d1;
   for (int i = bm.y + tid; i < end; i += kThreads) {
@@ -201,11 +197,7 @@ __global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const 
     xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
     int nb[METHOD == 2 ? 7 : 27];
     int cnt = 0;
-    if (METHOD == 2) {
-      cnt = neighbors_direct7(slots, mask, min_points, leaf, xt, yt, zt, nb);
-    } else {
-      cnt = find_neighbors(sh.tab, METHOD, xt, yt, zt, nb);
-    }
+    cnt = find_neighbors(sh.tab, METHOD, xt, yt, zt, nb);
     if (cnt == 0) continue;
     // computePointDerivatives (NDT_I:401-445): x_j_ang = j_ang * x4, x_h_ang = h_ang * x4.  The 23
     // per-point values are parked in shared memory (one column per thread) instead of registers.

@@ -123,50 +123,70 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
   int npairs = 0;
   const float4* __restrict__ src = src_pool + st.src_offset;
   const int end = min(bm.y + chunk, st.n_src);
-  const HashSlot* __restrict__ slots = sh.tab.slots;
   const FastRec* __restrict__ recs = sh.tab.frec;
-  const uint32_t mask = sh.tab.mask;
-  const int min_points = sh.tab.min_points;
-  const float leaf = sh.tab.leaf;
   const float d2f = sh.d2f, nhalf_d2f = sh.nhalf_d2f, d1d2f = sh.d1d2f;
   for (int i = bm.y + tid; i < end; i += kFT) {
     const float4 p = __ldg(src + i);
     float xt, yt, zt;
     xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
-    int nb[METHOD == 2 ? 7 : 27];
-    int cnt;
-    if (METHOD == 2) cnt = neighbors_direct7(slots, mask, min_points, leaf, xt, yt, zt, nb);
-    else cnt = find_neighbors(sh.tab, METHOD, xt, yt, zt, nb);
-    if (cnt == 0) continue;
-    npairs += cnt;
     float S = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f;
     float M00 = 0.f, M01 = 0.f, M02 = 0.f, M11 = 0.f, M12 = 0.f, M22 = 0.f;
     float B00 = 0.f, B01 = 0.f, B02 = 0.f, B11 = 0.f, B12 = 0.f, B22 = 0.f;
-    FRec cur = load_frec(recs + nb[0]);
-    for (int k = 0; k < cnt; ++k) {
-      const FRec r = cur;
-      if (k + 1 < cnt) cur = load_frec(recs + nb[k + 1]);
-      // x = T x_src - mean, to the float the reference's double subtraction rounds to
-      const float x0 = (xt - r.a.x) - r.a.w, x1 = (yt - r.a.y) - r.b.x, x2 = (zt - r.a.z) - r.b.y;
-      const float C00 = r.b.z, C01 = r.b.w, C02 = r.c.x, C11 = r.c.y, C12 = r.c.z, C22 = r.c.w;
-      const float w0 = fmaf(x2, C02, fmaf(x1, C01, x0 * C00));
-      const float w1 = fmaf(x2, C12, fmaf(x1, C11, x0 * C01));
-      const float w2 = fmaf(x2, C22, fmaf(x1, C12, x0 * C02));
-      const float q = fmaf(x2, w2, fmaf(x1, w1, x0 * w0));
-      const float es = expf(nhalf_d2f * q);                      // NDT_I:507
-      const float eg = d2f * es;                                 // NDT_I:511
-      if (eg > 1.f || eg < 0.f || eg != eg) continue;            // NDT_I:514-515: the pair adds nothing
-      const float f = d1d2f * es;                                // NDT_I:518
-      S += es;
-      const float t0 = f * w0, t1 = f * w1, t2 = f * w2;
-      a0 += t0; a1 += t1; a2 += t2;
-      if (CH) {
-        M00 = fmaf(f, C00, M00); M01 = fmaf(f, C01, M01); M02 = fmaf(f, C02, M02);
-        M11 = fmaf(f, C11, M11); M12 = fmaf(f, C12, M12); M22 = fmaf(f, C22, M22);
-        B00 = fmaf(t0, w0, B00); B01 = fmaf(t0, w1, B01); B02 = fmaf(t0, w2, B02);
-        B11 = fmaf(t1, w1, B11); B12 = fmaf(t1, w2, B12); B22 = fmaf(t2, w2, B22);
+    // one (point, voxel) pair of updateDerivatives (NDT_I:491-548), accumulated per point
+#define NDTB_PAIR(r)                                                                                         \
+    {                                                                                                        \
+      const float x0 = (xt - (r).a.x) - (r).a.w, x1 = (yt - (r).a.y) - (r).b.x, x2 = (zt - (r).a.z) - (r).b.y; \
+      const float C00 = (r).b.z, C01 = (r).b.w, C02 = (r).c.x, C11 = (r).c.y, C12 = (r).c.z, C22 = (r).c.w;  \
+      const float w0 = fmaf(x2, C02, fmaf(x1, C01, x0 * C00));                                               \
+      const float w1 = fmaf(x2, C12, fmaf(x1, C11, x0 * C01));                                               \
+      const float w2 = fmaf(x2, C22, fmaf(x1, C12, x0 * C02));                                               \
+      const float q = fmaf(x2, w2, fmaf(x1, w1, x0 * w0));                                                   \
+      const float es = expf(nhalf_d2f * q);                      /* NDT_I:507 */                             \
+      const float eg = d2f * es;                                 /* NDT_I:511 */                             \
+      if (!(eg > 1.f || eg < 0.f || eg != eg)) {                 /* NDT_I:514-515: else the pair adds nothing */ \
+        const float f = d1d2f * es;                              /* NDT_I:518 */                             \
+        S += es;                                                                                             \
+        const float t0 = f * w0, t1 = f * w1, t2 = f * w2;                                                   \
+        a0 += t0; a1 += t1; a2 += t2;                                                                        \
+        if (CH) {                                                                                            \
+          M00 = fmaf(f, C00, M00); M01 = fmaf(f, C01, M01); M02 = fmaf(f, C02, M02);                         \
+          M11 = fmaf(f, C11, M11); M12 = fmaf(f, C12, M12); M22 = fmaf(f, C22, M22);                         \
+          B00 = fmaf(t0, w0, B00); B01 = fmaf(t0, w1, B01); B02 = fmaf(t0, w2, B02);                         \
+          B11 = fmaf(t1, w1, B11); B12 = fmaf(t1, w2, B12); B22 = fmaf(t2, w2, B22);                         \
+        }                                                                                                    \
+      }                                                                                                      \
+    }
+    if (METHOD == 2) {
+      // DIRECT7: the seven cells in the reference's order, fully unrolled and predicated (no compaction,
+      // no local memory); the record of cell o+1 is in flight while cell o is being evaluated.
+      int v[7];
+      neighbors7(sh.tab, xt, yt, zt, v);
+      int cnt = 0;
+#pragma unroll
+      for (int o = 0; o < 7; ++o) cnt += v[o] >= 0 ? 1 : 0;
+      if (cnt == 0) continue;
+      npairs += cnt;
+      FRec nxt = {};
+      if (v[0] >= 0) nxt = load_frec(recs + v[0]);
+#pragma unroll
+      for (int o = 0; o < 7; ++o) {
+        const FRec r = nxt;
+        if (o + 1 < 7) { if (v[o + 1] >= 0) nxt = load_frec(recs + v[o + 1]); }
+        if (v[o] >= 0) NDTB_PAIR(r)
+      }
+    } else {
+      int nb[27];
+      const int cnt = find_neighbors(sh.tab, METHOD, xt, yt, zt, nb);
+      if (cnt == 0) continue;
+      npairs += cnt;
+      FRec cur = load_frec(recs + nb[0]);
+      for (int k = 0; k < cnt; ++k) {
+        const FRec r = cur;
+        if (k + 1 < cnt) cur = load_frec(recs + nb[k + 1]);
+        NDTB_PAIR(r)
       }
     }
+#undef NDTB_PAIR
     // ---- once per point: computePointDerivatives (NDT_I:401-445) and the 6x6 algebra ----------
     acc[0] += sh.neg_d1 * (double)S;                             // NDT_I:509
 #define JH(r) fmaf(sh.jh[r].z, p.z, fmaf(sh.jh[r].y, p.y, sh.jh[r].x * p.x))

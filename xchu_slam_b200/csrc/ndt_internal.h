@@ -67,6 +67,13 @@ struct VoxelTable {          // all pointers device
   uint32_t mask;             // capacity - 1 (capacity is a power of two)
   VoxelRec* rec;
   FastRec* frec;             // same voxels, layout of the fast kernel
+  // Dense cell -> voxel index over the target's bounding box padded by 2 cells (nullptr when the box
+  // exceeds dense_max_cells: the hash table is then the only index).  Code per cell: v >= 0 voxel v
+  // usable by the DIRECT searches (nr_points >= min_points); -2 - v: voxel v holds >= min_points
+  // points but is flagged invalid (seen only by the radius search, VGC_H:485-497); -1 otherwise.
+  int* dense;
+  int dlo[3];                // cell coordinate of dense[0] (= min_b - 2)
+  int dn[3];                 // dense dimensions in cells (x fastest)
   double* icov64;            // [v][9] Leaf::icov_ in f64, read only by the FP64 computeHessian / calculateScore kernels
   float4* centroid;          // x, y, z (f32, VGC_I:289), w = bit pattern of inserted point count
   unsigned long long* vkey;  // packed absolute cell of voxel v
@@ -132,6 +139,9 @@ struct TableStorage {
   int min_b[3] = {0, 0, 0}, max_b[3] = {0, 0, 0};
   float mn[3], mx[3];        // float bounding box of all inserted points
   bool have_bbox = false;
+  long long dense_max_cells = 0;   // 0: no dense index
+  size_t dense_cap = 0;            // ints allocated for t.dense
+  int* dense_buf = nullptr;        // the allocation (t.dense is nullptr while the box is too large)
 };
 cudaError_t table_reserve(TableStorage& ts, size_t n_vox_needed, cudaStream_t s, long long* launches);
 void table_free(TableStorage& ts);

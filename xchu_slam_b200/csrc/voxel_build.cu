@@ -85,7 +85,8 @@ static cudaError_t ws_reserve(BuildWorkspace* ws, size_t n) {
 void table_free(TableStorage& ts) {
   VoxelTable& t = ts.t;
   cudaFree(t.slots); cudaFree(t.rec); cudaFree(t.frec); cudaFree(t.icov64); cudaFree(t.centroid); cudaFree(t.vkey); cudaFree(t.vn);
-  cudaFree(t.vsum); cudaFree(t.vsxx); cudaFree(t.vcsum);
+  cudaFree(t.vsum); cudaFree(t.vsxx); cudaFree(t.vcsum); cudaFree(ts.dense_buf);
+  ts.dense_buf = nullptr; ts.dense_cap = 0; t.dense = nullptr;
   t.slots = nullptr; t.rec = nullptr; t.frec = nullptr; t.icov64 = nullptr; t.centroid = nullptr; t.vkey = nullptr; t.vn = nullptr;
   t.vsum = nullptr; t.vsxx = nullptr; t.vcsum = nullptr;
   ts.vox_cap = ts.slot_cap = 0; ts.n_vox = 0; ts.valid = false; ts.have_bbox = false;
@@ -147,6 +148,7 @@ cudaError_t table_reserve(TableStorage& ts, size_t need, cudaStream_t s, long lo
 }
 
 cudaError_t table_clear(TableStorage& ts, cudaStream_t s, long long* launches) {
+  ts.t.dense = nullptr;
   ts.n_vox = 0;
   ts.valid = false;
   ts.have_bbox = false;
@@ -414,6 +416,58 @@ __global__ void k_run_merge(const float4* __restrict__ pts, const unsigned int* 
   finalize_voxel(t, v, n, sum, sxx, cs, slot);
 }
 
+// ---- dense cell index (VoxelTable::dense) -------------------------------------------------
+__global__ void k_dense_fill(int* __restrict__ d, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) d[i] = -1;
+}
+__global__ void k_dense_scatter(VoxelTable t, int n_vox) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_vox) return;
+  int i, j, k;
+  unpack_key(t.vkey[v], i, j, k);
+  const int nr = t.rec[v].nr_points;
+  int code = -1;
+  if (nr >= t.min_points) code = v;
+  else if (nr == -1 && t.vn[v] >= t.min_points) code = -2 - v;
+  t.dense[((size_t)(k - t.dlo[2]) * t.dn[1] + (j - t.dlo[1])) * t.dn[0] + (i - t.dlo[0])] = code;
+}
+// (Re)build the dense index over [min_b - 2, max_b + 2] when that box holds <= dense_max_cells cells.
+// Every voxel is re-scattered (V is small next to the point count); the -1 fill only runs when the box changed.
+static cudaError_t table_build_dense(TableStorage& ts, cudaStream_t s, long long* launches) {
+  VoxelTable& t = ts.t;
+  t.dense = nullptr;
+  if (!ts.valid || ts.n_vox <= 0 || ts.dense_max_cells <= 0) return cudaSuccess;
+  int lo[3], dn[3];
+  long long cells = 1;
+  for (int a = 0; a < 3; ++a) {
+    lo[a] = ts.min_b[a] - 2;
+    dn[a] = ts.max_b[a] - ts.min_b[a] + 5;
+    cells *= dn[a];
+    if (cells > ts.dense_max_cells) return cudaSuccess;
+  }
+  bool refill = false;
+  if ((size_t)cells > ts.dense_cap) {
+    cudaFree(ts.dense_buf);
+    ts.dense_buf = nullptr;
+    ts.dense_cap = 0;
+    const size_t cap = (size_t)cells + (size_t)cells / 8;
+    CK(cudaMalloc(&ts.dense_buf, cap * sizeof(int)));
+    ts.dense_cap = cap;
+    refill = true;
+  }
+  for (int a = 0; a < 3; ++a)
+    if (lo[a] != t.dlo[a] || dn[a] != t.dn[a]) refill = true;
+  for (int a = 0; a < 3; ++a) { t.dlo[a] = lo[a]; t.dn[a] = dn[a]; }
+  t.dense = ts.dense_buf;
+  if (refill) {
+    k_dense_fill<<<148 * 8, 256, 0, s>>>(t.dense, (size_t)cells);
+    if (launches) ++*launches;
+  }
+  k_dense_scatter<<<(ts.n_vox + 255) / 256, 256, 0, s>>>(t, ts.n_vox);
+  if (launches) ++*launches;
+  return cudaGetLastError();
+}
+
 static int bits_for(long long range) {
   int b = 1;
   while ((1ll << b) < range) ++b;
@@ -454,6 +508,7 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
   if (!ok) {  // "Leaf size is too small for the input dataset": the reference leaves an EMPTY grid
     ts.valid = false;
     ts.n_vox = 0;
+    t.dense = nullptr;
     if (ts.slot_cap) { k_fill_slots<<<(unsigned)((ts.slot_cap + 255) / 256), 256, 0, s>>>(t.slots, ts.slot_cap); ++L; }
     return cudaGetLastError();
   }
@@ -486,6 +541,7 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
   CK(cudaMemcpyAsync(ws->h_counts + 1, ws->counts + 1, sizeof(int), cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
   ts.n_vox += ws->h_counts[1];
+  CK(table_build_dense(ts, s, launches));
   return cudaGetLastError();
 }
 

@@ -23,7 +23,7 @@ class NdtError(RuntimeError):
 class Params(C.Structure):
     _fields_ = [("resolution", C.c_float), ("step_size", C.c_double), ("trans_eps", C.c_double), ("max_iter", C.c_int),
                 ("outlier_ratio", C.c_double), ("search_method", C.c_int), ("min_points", C.c_int), ("eig_mult", C.c_double),
-                ("strict_math", C.c_int)]
+                ("strict_math", C.c_int), ("dense_max_cells", C.c_longlong)]
 
 
 class Result(C.Structure):
@@ -184,6 +184,11 @@ class NormalDistributionsTransform:
     def setStrictMath(self, on):
         """1: term-by-term derivative kernel in the reference's float operation order; 0: fast kernel."""
         self._params.strict_math = int(bool(on))
+        self._push()
+
+    def setDenseMaxCells(self, n):
+        """0: hash-table lookups only; otherwise the dense cell index is used when the box fits."""
+        self._params.dense_max_cells = int(n)
         self._push()
 
     def setInputTarget(self, cloud):     # NDT_H:117-122
