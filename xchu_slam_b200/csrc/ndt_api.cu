@@ -92,6 +92,11 @@ struct Engine {
 
   int fail(const std::string& m) { err = m; return 1; }
 
+  // Which derivative kernel runs.  DIRECT26 skips the point's own voxel; Newton on that objective is not
+  // contractive and float-level differences between the factorised and the term-by-term arithmetic grow
+  // from iterate to iterate (centimetres after ~10 iterations), so that mode always gets the strict kernel.
+  bool use_strict() const { return params.strict_math != 0 || params.search_method == NDTB_DIRECT26; }
+
   int init(int dev) {
     device = dev;
     int count = 0;
@@ -298,7 +303,7 @@ struct Engine {
         deriv_events.push_back(a); deriv_events.push_back(b);
       }
       CKE(cudaEventRecord(deriv_events[ev_used], stream));
-      CKE((params.strict_math ? launch_derivatives : launch_derivatives_fast)(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk,
+      CKE((use_strict() ? launch_derivatives : launch_derivatives_fast)(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk,
                                                                                 d_partials, params.search_method, mt_live, stream));
       CKE(cudaEventRecord(deriv_events[ev_used + 1], stream));
       ev_used += 2;
@@ -575,7 +580,7 @@ static int single_eval(Engine& e, const float T[16], const double p[6], int mode
   cudaMemcpyAsync(e.d_active, e.h_active, sizeof(int), cudaMemcpyHostToDevice, e.stream);
   if (launch_prepare_eval(e.d_states, e.d_T16, e.d_p6, mode, e.stream) != cudaSuccess) return e.fail("prepare failed");
   cudaError_t ce;
-  if (mode == 1 || mode == 2) ce = (e.params.strict_math ? launch_derivatives : launch_derivatives_fast)(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.params.search_method, true, e.stream);
+  if (mode == 1 || mode == 2) ce = (e.use_strict() ? launch_derivatives : launch_derivatives_fast)(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.params.search_method, true, e.stream);
   else ce = launch_hessian_f64(e.d_states, e.d_tables, e.src_pool, e.d_blockmap, st.n_blocks, chunk, e.d_partials, e.stream);
   if (ce != cudaSuccess) return e.fail(std::string("eval launch: ") + cudaGetErrorString(ce));
   if (launch_newton(e.d_states, 1, e.d_partials, nullptr, 0, e.d_active, e.stream) != cudaSuccess) return e.fail("reduce failed");
