@@ -1,0 +1,82 @@
+"""CPU checks of the drop-in boundary: libndt_b200.so loads, exports exactly what
+include/ndt_b200/ndt_c_api.h declares, mirrors the reference's constructor defaults, and fails
+loudly (no CPU fallback) when there is no CUDA device.  No compute calls here."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "ndt_b200", "ndt_c_api.h")
+
+
+def _declared():
+    txt = open(HEADER).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(ndtb_[a-z0-9_]+)\s*\(", txt)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from xchu_slam_b200 import build, ndt
+    build.build_cuda()
+    return ndt.load_library()
+
+
+def test_header_symbols_exported(lib):
+    from xchu_slam_b200 import ndt
+    names = _declared()
+    assert len(names) >= 30
+    out = subprocess.run(["nm", "-D", "--defined-only", ndt.LIB_PATH], capture_output=True, text=True).stdout
+    exported = set(re.findall(r" T (ndtb_[a-z0-9_]+)", out))
+    assert set(names) <= exported, sorted(set(names) - exported)
+    assert sorted(ndt.SYMBOLS) == names           # the Python mirror binds every declared entry point
+    for n in names:
+        assert hasattr(lib, n)
+
+
+def test_no_torch_types_in_abi():
+    txt = open(HEADER).read()
+    assert "torch" not in txt and "at::" not in txt and "std::" not in txt
+    assert 'extern "C"' in txt
+
+
+def test_default_params_match_reference_ctor(lib):
+    """ndt_omp_impl.hpp:46-69 + voxel_grid_covariance_omp.h:199-207."""
+    from xchu_slam_b200 import ndt
+    p = ndt.Params()
+    lib.ndtb_default_params(C.byref(p))
+    assert p.resolution == 1.0 and p.step_size == 0.1 and p.trans_eps == 0.1 and p.max_iter == 35
+    assert p.outlier_ratio == 0.55 and p.search_method == ndt.DIRECT7 and p.min_points == 6 and p.eig_mult == 0.01
+    assert p.strict_math == 0 and p.dense_max_cells == 1 << 26
+    assert (ndt.KDTREE, ndt.DIRECT26, ndt.DIRECT7, ndt.DIRECT1) == (0, 1, 2, 3)      # ndt_omp.h:52-57
+
+
+def test_create_fails_loudly_without_gpu(lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from xchu_slam_b200 import ndt
+    h = C.c_void_p()
+    assert lib.ndtb_create(0, C.byref(h)) != 0
+    assert not h.value
+    assert b"no CPU fallback" in lib.ndtb_last_error(None)
+    with pytest.raises(ndt.NdtError):
+        ndt.NormalDistributionsTransform()
+    with pytest.raises(ndt.NdtError):
+        ndt.BatchNDT()
+
+
+def test_product_does_not_import_oracle():
+    """The oracle is test infrastructure: nothing under xchu_slam_b200/ or include/ may reference it."""
+    bad = []
+    for base in ("xchu_slam_b200", "include"):
+        for d, _, files in os.walk(os.path.join(ROOT, base)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")):
+                    t = open(os.path.join(d, f), errors="ignore").read()
+                    if re.search(r"from oracle|import oracle|ndt_oracle|libndt_oracle", t):
+                        bad.append(os.path.join(d, f))
+    assert not bad, bad

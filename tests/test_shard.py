@@ -1,0 +1,116 @@
+"""Host-side sharding of independent registrations (xchu_slam_b200/shard.py): plan properties on one
+process, and the N>1 path with world_size 2 over gloo on CPU.  The local work in the gloo test is
+done by the CPU oracle standing in for the per-rank BatchNDT (a test may use the oracle; the product
+runner is shard.gpu_runner)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_plan_is_a_balanced_partition_grouped_by_target():
+    from xchu_slam_b200 import shard
+    rng = np.random.default_rng(0)
+    it = rng.integers(0, 9, 101)
+    for world in (1, 2, 3, 4, 8):
+        plan = shard.plan_shards(it, world)
+        allidx = np.concatenate(plan)
+        assert sorted(allidx.tolist()) == list(range(101))                 # a partition
+        sizes = [len(p) for p in plan]
+        assert max(sizes) - min(sizes) <= 1                                # balanced
+        # contiguous in target order: a target is split over at most two neighbouring ranks per cut
+        tmax = -1
+        for p in plan:
+            if len(p):
+                assert it[p].min() >= tmax
+                tmax = it[p].max()
+        n_build = sum(len(np.unique(it[p])) for p in plan if len(p))
+        assert n_build <= len(np.unique(it)) + world - 1                   # table builds: at most one extra per cut
+
+
+def test_plan_more_ranks_than_items():
+    from xchu_slam_b200 import shard
+    plan = shard.plan_shards([0, 0, 1], 8)
+    assert sum(len(p) for p in plan) == 3 and all(len(p) <= 1 for p in plan)
+
+
+def test_local_problem_remaps_ids():
+    from xchu_slam_b200 import shard
+    it = np.array([5, 5, 7, 9, 9, 9])
+    isrc = np.array([3, 4, 3, 8, 8, 2])
+    tids, sids, lt, ls = shard.local_problem(np.array([2, 3, 5]), it, isrc)
+    assert tids.tolist() == [7, 9] and sids.tolist() == [2, 3, 8]
+    assert tids[lt].tolist() == [7, 9, 9] and sids[ls].tolist() == [3, 8, 2]
+
+
+def test_pack_unpack_round_trip():
+    from xchu_slam_b200 import shard
+    r = [dict(T=np.arange(16, dtype=np.float32).reshape(4, 4), iterations=7, converged=True, score=1.5, trans_probability=0.25, n_evals=8)]
+    u = shard.unpack_results(shard.pack_results(r))[0]
+    assert np.array_equal(u["T"], r[0]["T"]) and u["iterations"] == 7 and u["converged"] and u["score"] == 1.5 and u["n_evals"] == 8
+
+
+def _oracle_runner(targets, sources, it, isrc, guesses):
+    from oracle import oracle
+    out = []
+    for k in range(len(it)):
+        o = oracle.OracleNDT()
+        o.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, num_threads=1)
+        o.set_target(targets[it[k]])
+        o.set_source(sources[isrc[k]])
+        r = o.align(guesses[k])
+        r["n_evals"] = len(r["trace"])
+        out.append(r)
+    return out
+
+
+def _problem():
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "ndt_tiny.npz"))
+    from xchu_slam_b200 import synth
+    tgt, src, gt = gold["target"], gold["source"], gold["gt"]
+    targets = [tgt, tgt[: len(tgt) * 3 // 4], tgt[len(tgt) // 8:]]
+    sources = [src, src[::2].copy()]
+    it = np.array([0, 1, 2, 0, 1, 2, 0], np.int32)
+    isrc = np.array([0, 1, 0, 1, 0, 1, 0], np.int32)
+    guesses = np.stack([synth.perturbed_guess(gt, 300 + i) for i in range(len(it))])
+    return targets, sources, it, isrc, guesses
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import torch.distributed as dist
+    from xchu_slam_b200 import shard
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    targets, sources, it, isrc, guesses = _problem()
+    res = shard.run_sharded(_oracle_runner, targets, sources, it, isrc, guesses)
+    q.put((rank, shard.pack_results(res)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_run_sharded_world2_gloo_matches_single_rank():
+    import torch.multiprocessing as mp
+    from xchu_slam_b200 import shard
+    targets, sources, it, isrc, guesses = _problem()
+    single = shard.pack_results(shard.run_sharded(_oracle_runner, targets, sources, it, isrc, guesses))
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=240) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for r in range(2):                       # every rank holds the full, identically ordered result list
+        assert np.array_equal(got[r], single)
+    assert np.all(single[:, 16] >= 1)
