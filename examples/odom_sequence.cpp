@@ -1,0 +1,222 @@
+// odom_sequence.cpp -- headless C++ mirror of xchu_slam's scan-to-localmap odometry loop
+// (reference xchu_mapping/src/odom_node.cpp:208-356 LidarOdom::OdomEstimate, :42-83 ParamInitial)
+// driving the drop-in pclomp::NormalDistributionsTransform of include/pclomp/ndt_omp.h.
+//
+// It is the caller side of BASELINE config C2 (a sequence of scans registered against a localmap
+// that is refreshed by the distance-threshold strategy, every refresh going through
+// setInputTarget -> incremental voxel rebuild) and doubles as the compile/run test of the shim:
+// the NDT calls below are the reference's own lines (odom_node.cpp:70-78, 228, 278-283, 349).
+// ROS plumbing, IMU/odometry guesses and publishers are out of scope.
+//
+//   odom_sequence <sequence.bin> <out.txt> [--res R] [--no-incremental] [--max-scans N] [--device D]
+//
+// sequence.bin: "NDTSEQ1\0", int32 n_scans, then per scan: int32 n, double gt[6] (sensor pose
+// x y z roll pitch yaw), float xyzi[n][4] (filter_node output, sensor frame).
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../include/pclomp/ndt_omp.h"
+
+typedef pcl::PointXYZI PointT;
+typedef pcl::PointCloud<PointT> Cloud;
+
+struct Pose6D {   // include/xchu_mapping/common.h
+  double x = 0, y = 0, z = 0, roll = 0, pitch = 0, yaw = 0;
+  Pose6D operator+(const Pose6D& o) const { Pose6D r; r.x = x + o.x; r.y = y + o.y; r.z = z + o.z; r.roll = roll + o.roll; r.pitch = pitch + o.pitch; r.yaw = yaw + o.yaw; return r; }
+  Pose6D operator-(const Pose6D& o) const {
+    Pose6D r; r.x = x - o.x; r.y = y - o.y; r.z = z - o.z; r.roll = roll - o.roll; r.pitch = pitch - o.pitch;
+    double d = yaw - o.yaw;   // calcDiffForRadian
+    if (d >= M_PI) d -= 2 * M_PI; else if (d < -M_PI) d += 2 * M_PI;
+    r.yaw = d;
+    return r;
+  }
+};
+
+// common.h:64-71: Translation * Rz * Ry * Rx (double), cast to float by the caller
+static Eigen::Matrix4f Pose6D2Matrix(const Pose6D& p) {
+  const double cr = cos(p.roll), sr = sin(p.roll), cp = cos(p.pitch), sp = sin(p.pitch), cy = cos(p.yaw), sy = sin(p.yaw);
+  const double R[3][3] = {{cy * cp, cy * sp * sr - sy * cr, cy * sp * cr + sy * sr},
+                          {sy * cp, sy * sp * sr + cy * cr, sy * sp * cr - cy * sr},
+                          {-sp, cp * sr, cp * cr}};
+  Eigen::Matrix4f m = Eigen::Matrix4f::Identity();
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) m(r, c) = (float)R[r][c];
+  m(0, 3) = (float)p.x; m(1, 3) = (float)p.y; m(2, 3) = (float)p.z;
+  return m;
+}
+// common.h:51-63: tf getRPY of the rotation block
+static Pose6D Matrix2Pose6D(const Eigen::Matrix4f& m) {
+  Pose6D p;
+  p.x = m(0, 3); p.y = m(1, 3); p.z = m(2, 3);
+  p.pitch = asin(fmax(-1.0, fmin(1.0, -(double)m(2, 0))));
+  p.roll = atan2((double)m(2, 1), (double)m(2, 2));
+  p.yaw = atan2((double)m(1, 0), (double)m(0, 0));
+  return p;
+}
+// pcl::transformPointCloud (float, left to right)
+static void transformPointCloud(const Cloud& in, Cloud& out, const Eigen::Matrix4f& T) {
+  out.points.resize(in.points.size());
+  for (size_t i = 0; i < in.points.size(); ++i) {
+    const PointT& p = in.points[i];
+    PointT q = p;
+    q.x = ((T(0, 0) * p.x + T(0, 1) * p.y) + T(0, 2) * p.z) + T(0, 3);
+    q.y = ((T(1, 0) * p.x + T(1, 1) * p.y) + T(1, 2) * p.z) + T(1, 3);
+    q.z = ((T(2, 0) * p.x + T(2, 1) * p.y) + T(2, 2) * p.z) + T(2, 3);
+    out.points[i] = q;
+  }
+  out.width = (decltype(out.width))out.points.size();
+  out.height = 1;
+}
+// pcl::VoxelGrid (centroid per occupied leaf, output in ascending leaf index): downSizeFilterLocalmap, odom_node.cpp:98, 334-335
+static void voxelDownsample(const Cloud& in, Cloud& out, float leaf) {
+  struct Acc { double x = 0, y = 0, z = 0, i = 0; int n = 0; };
+  std::map<long long, Acc> cells;
+  const float inv = 1.0f / leaf;
+  for (const PointT& p : in.points) {
+    const long long a = (long long)floorf(p.x * inv), b = (long long)floorf(p.y * inv), c = (long long)floorf(p.z * inv);
+    Acc& s = cells[((c + (1 << 20)) << 42) | ((b + (1 << 20)) << 21) | (a + (1 << 20))];
+    s.x += p.x; s.y += p.y; s.z += p.z; s.i += p.intensity; s.n++;
+  }
+  Cloud r;
+  r.points.reserve(cells.size());
+  for (auto& kv : cells) {
+    PointT q;
+    q.x = (float)(kv.second.x / kv.second.n); q.y = (float)(kv.second.y / kv.second.n); q.z = (float)(kv.second.z / kv.second.n);
+    q.intensity = (float)(kv.second.i / kv.second.n);
+    r.points.push_back(q);
+  }
+  r.width = (decltype(r.width))r.points.size();
+  r.height = 1;
+  out = r;
+}
+
+int main(int argc, char** argv) {
+  if (argc < 3) { fprintf(stderr, "usage: odom_sequence <sequence.bin> <out.txt> [--res R] [--no-incremental] [--max-scans N] [--device D]\n"); return 2; }
+  float ndt_res = 2.0f;              // odom_node.cpp:43 default
+  const double step_size = 0.1, trans_eps = 0.01, min_add_scan_shift = 0.5;   // odom_node.cpp:44-47
+  const int max_iter = 30;
+  double max_localmap_size = 5;      // odom_node.cpp:49
+  bool incremental = true;
+  int max_scans = 1 << 30, device = 0;
+  for (int a = 3; a < argc; ++a) {
+    if (!strcmp(argv[a], "--res") && a + 1 < argc) ndt_res = (float)atof(argv[++a]);
+    else if (!strcmp(argv[a], "--no-incremental")) incremental = false;
+    else if (!strcmp(argv[a], "--max-scans") && a + 1 < argc) max_scans = atoi(argv[++a]);
+    else if (!strcmp(argv[a], "--device") && a + 1 < argc) device = atoi(argv[++a]);
+    else if (!strcmp(argv[a], "--submap") && a + 1 < argc) max_localmap_size = atof(argv[++a]);
+  }
+  FILE* f = fopen(argv[1], "rb");
+  if (!f) { perror(argv[1]); return 2; }
+  char magic[8];
+  int n_scans = 0;
+  if (fread(magic, 1, 8, f) != 8 || memcmp(magic, "NDTSEQ1", 7) != 0 || fread(&n_scans, 4, 1, f) != 1) { fprintf(stderr, "bad sequence file\n"); return 2; }
+  if (n_scans > max_scans) n_scans = max_scans;
+
+  // ---- ParamInitial, odom_node.cpp:67-80 ---------------------------------------------------
+  pclomp::NormalDistributionsTransform<PointT, PointT>::Ptr omp_ndt;
+  try {
+    pclomp::NormalDistributionsTransform<PointT, PointT>::Ptr ndt(new pclomp::NormalDistributionsTransform<PointT, PointT>(device));
+    ndt->setNeighborhoodSearchMethod(pclomp::DIRECT7);
+    ndt->setNumThreads(1);
+    ndt->setTransformationEpsilon(trans_eps);
+    ndt->setStepSize(step_size);
+    ndt->setResolution(ndt_res);
+    ndt->setMaximumIterations(max_iter);
+    omp_ndt = ndt;
+  } catch (const std::exception& e) {
+    fprintf(stderr, "%s\n", e.what());
+    return 3;
+  }
+  FILE* out = fopen(argv[2], "w");
+  if (!out) { perror(argv[2]); return 2; }
+
+  Cloud localmap, tmp_map;
+  Cloud::Ptr pc_target_(new Cloud()), transformed_scan_ptr(new Cloud());
+  Pose6D previous_pose, current_pose, diff_pose, guess_pose;
+  double localmap_size = 0, shift_dis = 0;
+  int initial_scan_loaded = 0, n_incremental = 0, n_target_sets = 0;
+  double total_align_ms = 0, total_target_ms = 0;
+  const auto wall0 = std::chrono::steady_clock::now();
+
+  for (int s = 0; s < n_scans; ++s) {
+    int n = 0;
+    double gt[6];
+    if (fread(&n, 4, 1, f) != 1 || fread(gt, 8, 6, f) != 6) { fprintf(stderr, "truncated sequence\n"); return 2; }
+    Cloud::Ptr filtered_scan_ptr(new Cloud());
+    filtered_scan_ptr->points.resize(n);
+    std::vector<float> buf((size_t)n * 4);
+    if (fread(buf.data(), 16, n, f) != (size_t)n) { fprintf(stderr, "truncated sequence\n"); return 2; }
+    for (int i = 0; i < n; ++i) { PointT& p = filtered_scan_ptr->points[i]; p.x = buf[i * 4]; p.y = buf[i * 4 + 1]; p.z = buf[i * 4 + 2]; p.intensity = buf[i * 4 + 3]; }
+    filtered_scan_ptr->width = n; filtered_scan_ptr->height = 1;
+    if (s == 0) {   // start the odometry at the first scan's pose (the reference starts at init_x.. = 0)
+      previous_pose.x = gt[0]; previous_pose.y = gt[1]; previous_pose.z = gt[2]; previous_pose.roll = gt[3]; previous_pose.pitch = gt[4]; previous_pose.yaw = gt[5];
+      current_pose = previous_pose;
+    }
+    transformed_scan_ptr->clear();
+    // ---- OdomEstimate, odom_node.cpp:218-231 ----------------------------------------------
+    if (initial_scan_loaded == 0) {
+      transformPointCloud(*filtered_scan_ptr, *transformed_scan_ptr, Pose6D2Matrix(previous_pose));
+      localmap += *transformed_scan_ptr;
+      *pc_target_ += *transformed_scan_ptr;
+      omp_ndt->setInputTarget(pc_target_);
+      initial_scan_loaded = 1;
+    }
+    pc_target_.reset(new Cloud(localmap));                               // :233
+    guess_pose = previous_pose + diff_pose;                              // :237-239
+    guess_pose.pitch = previous_pose.pitch;
+    guess_pose.roll = previous_pose.roll;
+    const Eigen::Matrix4f init_guess = Pose6D2Matrix(guess_pose);        // :256
+    Cloud::Ptr output_cloud(new Cloud());
+    const auto t0 = std::chrono::steady_clock::now();
+    omp_ndt->setInputSource(filtered_scan_ptr);                          // :278-283
+    omp_ndt->align(*output_cloud, init_guess);
+    const double fitness_score = omp_ndt->getFitnessScore();
+    const Eigen::Matrix4f t_localizer = omp_ndt->getFinalTransformation();
+    const bool has_converged = omp_ndt->hasConverged();
+    const int final_num_iteration = omp_ndt->getFinalNumIteration();
+    const auto t1 = std::chrono::steady_clock::now();
+    transformPointCloud(*filtered_scan_ptr, *transformed_scan_ptr, t_localizer);   // :290
+    current_pose = Matrix2Pose6D(t_localizer);                           // :291-296 (tf_l2b = identity)
+    diff_pose = current_pose - previous_pose;                            // :309
+    shift_dis = sqrt(pow(current_pose.x - previous_pose.x, 2.0) + pow(current_pose.y - previous_pose.y, 2.0));   // :322
+    previous_pose = current_pose;
+    double target_ms = 0;
+    int was_inc = -1;
+    if (shift_dis >= min_add_scan_shift) {                               // :329-350
+      localmap_size += shift_dis;
+      voxelDownsample(*transformed_scan_ptr, *transformed_scan_ptr, 1.0f);
+      localmap += *transformed_scan_ptr;
+      tmp_map += *transformed_scan_ptr;
+      const auto t2 = std::chrono::steady_clock::now();
+      if (incremental) omp_ndt->setInputTarget(pc_target_);             // prefix-append detection inside
+      else { ndtb_set_target(omp_ndt->handle(), pc_target_->points.data(), pc_target_->points.size(), sizeof(PointT)); }
+      target_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t2).count();
+      was_inc = incremental && omp_ndt->lastTargetUpdateWasIncremental() ? 1 : 0;
+      n_incremental += was_inc;
+      n_target_sets++;
+    }
+    if (localmap_size >= max_localmap_size) {                            // :352-356
+      localmap = tmp_map;
+      tmp_map.clear();
+      localmap_size = 0.0;
+    }
+    const double align_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    total_align_ms += align_ms;
+    total_target_ms += target_ms;
+    fprintf(out, "%d %d %d %.9g %.9f %.9f %.9f %.9f %.9f %.9f %zu %d %.4f %.4f %.6f %.6f %.6f\n", s, final_num_iteration, has_converged ? 1 : 0,
+            fitness_score, current_pose.x, current_pose.y, current_pose.z, current_pose.roll, current_pose.pitch, current_pose.yaw,
+            pc_target_->size(), was_inc, align_ms, target_ms, gt[0], gt[1], gt[2]);
+  }
+  const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
+  fprintf(out, "# scans %d wall_s %.4f scans_per_s %.2f align_ms_mean %.4f target_ms_mean %.4f target_sets %d incremental %d\n", n_scans, wall,
+          n_scans / wall, total_align_ms / n_scans, n_target_sets ? total_target_ms / n_target_sets : 0.0, n_target_sets, n_incremental);
+  fclose(out);
+  fclose(f);
+  return 0;
+}

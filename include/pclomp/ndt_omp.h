@@ -1,0 +1,158 @@
+// include/pclomp/ndt_omp.h -- drop-in for xchu_slam's xchu_mapping/include/pclomp/ndt_omp.h.
+//
+// Same namespace, class template, enum, ::Ptr and public members as the reference
+// (xchu_mapping/include/pclomp/ndt_omp.h:52-57 enum, :70-71 class, :98-99 Ptr, :110-204 setters /
+// getters, plus the pcl::Registration members odom_node uses: setInputSource, setInputTarget,
+// setTransformationEpsilon, setMaximumIterations, align, getFinalTransformation, hasConverged,
+// getFitnessScore -- src/odom_node.cpp:70-83, 278-283, 349), so that odom_node.cpp's matcher
+// selection and localmap refresh compile unchanged.  Everything underneath is the C ABI of
+// libndt_b200.so (include/ndt_b200/ndt_c_api.h): CUDA only, no CPU fallback -- construction throws
+// std::runtime_error when no device is usable, and every failing ABI call throws with
+// ndtb_last_error() (the reference itself never fails: it has no device to lose).
+//
+// Builds with PCL + Eigen when they are installed (the xchu_slam workspace); otherwise against the
+// stand-ins of pcl_compat.h (this repository's tests).
+#pragma once
+
+#if defined(__has_include)
+#if __has_include(<pcl/point_cloud.h>) && __has_include(<Eigen/Core>) && !defined(NDT_B200_NO_PCL)
+#define NDT_B200_WITH_PCL 1
+#endif
+#endif
+
+#ifdef NDT_B200_WITH_PCL
+#include <Eigen/Core>
+#include <boost/shared_ptr.hpp>
+#include <pcl/point_cloud.h>
+#include <pcl/point_types.h>
+#else
+#include "pcl_compat.h"
+#endif
+
+#include <cfloat>
+#include <limits>
+#include <stdexcept>
+#include <string>
+
+#include "../ndt_b200/ndt_c_api.h"
+
+namespace pclomp {
+
+enum NeighborSearchMethod { KDTREE, DIRECT26, DIRECT7, DIRECT1 };   // ndt_omp.h:52-57
+
+template <typename PointSource, typename PointTarget>
+class NormalDistributionsTransform {
+ public:
+  typedef pcl::PointCloud<PointSource> PointCloudSource;
+  typedef typename PointCloudSource::Ptr PointCloudSourcePtr;
+  typedef typename PointCloudSource::ConstPtr PointCloudSourceConstPtr;
+  typedef pcl::PointCloud<PointTarget> PointCloudTarget;
+  typedef typename PointCloudTarget::Ptr PointCloudTargetPtr;
+  typedef typename PointCloudTarget::ConstPtr PointCloudTargetConstPtr;
+  typedef boost::shared_ptr<NormalDistributionsTransform<PointSource, PointTarget>> Ptr;
+  typedef boost::shared_ptr<const NormalDistributionsTransform<PointSource, PointTarget>> ConstPtr;
+  typedef Eigen::Matrix4f Matrix4;
+
+  // ndt_omp_impl.hpp:46-69: resolution 1.0, step 0.1, outlier 0.55, eps 0.1, 35 iterations, DIRECT7
+  explicit NormalDistributionsTransform(int device = 0) : search_method(DIRECT7) {
+    if (ndtb_create(device, &h_) != 0) throw std::runtime_error(std::string("pclomp(B200): ") + ndtb_last_error(nullptr));
+    ndtb_get_params(h_, &p_);
+    final_transformation_.setIdentity();
+  }
+  virtual ~NormalDistributionsTransform() { ndtb_destroy(h_); }
+  NormalDistributionsTransform(const NormalDistributionsTransform&) = delete;
+  NormalDistributionsTransform& operator=(const NormalDistributionsTransform&) = delete;
+
+  void setNumThreads(int) {}   // ndt_omp.h:110-112: OpenMP threads have no meaning on the device
+
+  // ndt_omp.h:117-122: stores the target and rebuilds the whole voxel grid (init()).
+  // Incremental refresh: when `cloud` extends the previous target (odom_node only ever appends
+  // between window resets, src/odom_node.cpp:336, 349) only the appended tail is merged.
+  inline void setInputTarget(const PointCloudTargetConstPtr& cloud) {
+    target_ = cloud;
+    push_search_method();
+    int inc = 0;
+    ck(ndtb_set_target_auto(h_, cloud->points.data(), cloud->points.size(), sizeof(PointTarget), &inc));
+    last_target_incremental_ = inc != 0;
+  }
+  // cpu::NormalDistributionsTransform::updateVoxelGrid (include/ndt_cpu/NormalDistributionsTransform.h:39)
+  inline void updateVoxelGrid(const PointCloudTargetConstPtr& new_points) {
+    ck(ndtb_update_target(h_, new_points->points.data(), new_points->points.size(), sizeof(PointTarget)));
+  }
+  inline void setInputSource(const PointCloudSourceConstPtr& cloud) {
+    input_ = cloud;
+    ck(ndtb_set_source(h_, cloud->points.data(), cloud->points.size(), sizeof(PointSource)));
+  }
+
+  inline void setResolution(float resolution) {           // ndt_omp.h:127-137
+    if (p_.resolution != resolution) { p_.resolution = resolution; push(); }
+  }
+  inline float getResolution() const { return p_.resolution; }
+  inline double getStepSize() const { return p_.step_size; }
+  inline void setStepSize(double step_size) { p_.step_size = step_size; push(); }      // ndt_omp.h:160-164
+  inline double getOulierRatio() const { return p_.outlier_ratio; }                      // (sic) ndt_omp.h:169-173
+  inline void setOulierRatio(double outlier_ratio) { p_.outlier_ratio = outlier_ratio; push(); }
+  inline void setNeighborhoodSearchMethod(NeighborSearchMethod method) { search_method = method; push_search_method(); }
+  inline void setTransformationEpsilon(double epsilon) { p_.trans_eps = epsilon; push(); }
+  inline double getTransformationEpsilon() const { return p_.trans_eps; }
+  inline void setMaximumIterations(int n) { p_.max_iter = n; push(); }
+  inline int getMaximumIterations() const { return p_.max_iter; }
+  inline double getTransformationProbability() const { return result_.trans_probability; }   // ndt_omp.h:191-195
+  inline int getFinalNumIteration() const { return result_.iterations; }                     // ndt_omp.h:200-204
+
+  // pcl::Registration::align: `output` receives the source moved by the final transformation
+  inline void align(PointCloudSource& output) { align(output, Matrix4::Identity()); }
+  inline void align(PointCloudSource& output, const Matrix4& guess) {
+    if (!input_ || !target_) throw std::runtime_error("pclomp(B200): align() needs setInputSource and setInputTarget");
+    push_search_method();
+    ck(ndtb_align(h_, guess.data(), &result_));
+    for (int i = 0; i < 16; ++i) final_transformation_.data()[i] = result_.T[i];
+    if (&output != input_.get()) {
+      output.points = input_->points;   // pcl::Registration::align copies the source fields first
+      output.header = input_->header;
+      output.width = (decltype(output.width))output.points.size();
+      output.height = 1;
+      output.is_dense = input_->is_dense;
+    }
+    if (!output.points.empty()) ck(ndtb_get_output(h_, output.points.data(), sizeof(PointSource)));
+  }
+  inline Matrix4 getFinalTransformation() const { return final_transformation_; }
+  inline bool hasConverged() const { return result_.converged != 0; }
+  inline double getFitnessScore(double max_range = std::numeric_limits<double>::max()) {
+    double out = 0;
+    ck(ndtb_fitness(h_, max_range, nullptr, &out));
+    return out;
+  }
+  // ndt_omp_impl.hpp:919-952 (the reference scores an already transformed cloud: pass its transform)
+  inline double calculateScore(const Matrix4& cloud_transform) {
+    double out = 0;
+    ck(ndtb_calculate_score(h_, cloud_transform.data(), &out));
+    return out;
+  }
+
+  // ---- not in the reference ---------------------------------------------------------------
+  bool lastTargetUpdateWasIncremental() const { return last_target_incremental_; }
+  void setStrictMath(bool on) { p_.strict_math = on ? 1 : 0; push(); }
+  ndtb_handle* handle() { return h_; }
+
+  NeighborSearchMethod search_method;   // public member in the reference too (ndt_omp.h:494)
+
+ protected:
+  void ck(int rc) const {
+    if (rc != 0) throw std::runtime_error(std::string("pclomp(B200): ") + ndtb_last_error(h_));
+  }
+  void push() { ck(ndtb_set_params(h_, &p_)); }
+  void push_search_method() {   // `search_method` may have been assigned directly
+    if (p_.search_method != (int)search_method) { p_.search_method = (int)search_method; push(); }
+  }
+
+  ndtb_handle* h_ = nullptr;
+  ndtb_params p_;
+  ndtb_result result_ = ndtb_result();
+  Matrix4 final_transformation_;
+  PointCloudSourceConstPtr input_;
+  PointCloudTargetConstPtr target_;
+  bool last_target_incremental_ = false;
+};
+
+}  // namespace pclomp

@@ -61,10 +61,27 @@ def _build_cuda(force=False, verbose=False, defines=()):
     return LIB
 
 
+EXAMPLES = os.path.join(HERE, "..", "examples")
+
+
+def build_examples(force=False):
+    """Host C++ above the C ABI: the headless mirror of odom_node's loop over include/pclomp/ndt_omp.h."""
+    src = os.path.join(EXAMPLES, "odom_sequence.cpp")
+    exe = os.path.join(EXAMPLES, "odom_sequence")
+    deps = [src, LIB, os.path.join(HERE, "..", "include", "pclomp", "ndt_omp.h"), os.path.join(HERE, "..", "include", "pclomp", "pcl_compat.h"),
+            os.path.join(HERE, "..", "include", "ndt_b200", "ndt_c_api.h")]
+    if force or _stale(exe, deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", src, "-o", exe, "-L" + HERE, "-lndt_b200",
+                               "-Wl,-rpath,$ORIGIN/../xchu_slam_b200"])
+    return exe
+
+
 def build_all(force=False, verbose=False):
     from . import synth
     synth.build(force)
-    return build_cuda(force, verbose)
+    lib = build_cuda(force, verbose)
+    build_examples(force)
+    return lib
 
 
 if __name__ == "__main__":

@@ -260,3 +260,23 @@ def batch_workload(n_submaps=64, scans_per_submap=8, hyps_per_scan=8, n_target=1
                  item_source=out["item_source"], guesses=out["guesses"], gt=out["gt"])
         os.replace(tmp, path)
     return out
+
+
+def write_sequence(path, n_scans=1000, n_points=20000, seed=BASE_SEED, traj_start=50, step=0.86):
+    """BASELINE configs[1] (C2) input: n_scans consecutive filter_node-style scans along the KITTI-00-like
+    drive with their ground-truth sensor poses, in the flat format examples/odom_sequence.cpp reads:
+    "NDTSEQ1\0", int32 n_scans, then per scan int32 n, float64 gt[6], float32 xyzi[n][4]."""
+    w = World(seed)
+    poses = w.trajectory(traj_start + n_scans + 2, step=step, seed=seed & 0xFFFF)
+    tmp = path + ".tmp%d" % os.getpid()
+    with open(tmp, "wb") as f:
+        f.write(b"NDTSEQ1\0")
+        f.write(np.int32(n_scans).tobytes())
+        for i in range(n_scans):
+            vp = poses[traj_start + i]
+            pts = source_scan(w, vp, seed + 300000 + i, n_points)
+            f.write(np.int32(pts.shape[0]).tobytes())
+            f.write(np.asarray(sensor_pose(vp), dtype=np.float64).tobytes())
+            f.write(np.ascontiguousarray(pts, dtype=np.float32).tobytes())
+    os.replace(tmp, path)
+    return path
