@@ -218,15 +218,15 @@ def main():
         b.clear()
         if resident:
             for t in tg_dev:
-                b.add_target_ptr(t.data_ptr(), t.shape[0], 16, True)
+                b.add_target_ptr(t.data_ptr(), t.shape[0], 16, 2)     # resident in HBM: borrowed in place
             for s in sc_dev:
-                b.add_source_ptr(s.data_ptr(), s.shape[0], 16, True)
+                b.add_source_ptr(s.data_ptr(), s.shape[0], 16, 2)
         else:
             for t in tg_host:
-                b.add_target_ptr(t.data_ptr(), t.shape[0], 16, False)
+                b.add_target_ptr(t.data_ptr(), t.shape[0], 16, 0)     # pinned host memory: H2D inside the call
             for s in sc_host:
-                b.add_source_ptr(s.data_ptr(), s.shape[0], 16, False)
-        res = b.run(it, isrc, G)      # returns after the device finished and results are on the host
+                b.add_source_ptr(s.data_ptr(), s.shape[0], 16, 0)
+        res = b.run_raw(it, isrc, G)  # returns after the device finished and the result records are on the host
         return res, b.stats()
 
     def timed(resident, steps):
@@ -284,7 +284,7 @@ def main():
             traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get("dram_bytes_per_launch")
         except Exception:
             pass
-        conv = sum(1 for r in res if r["converged"])
+        conv = int(np.count_nonzero(res["converged"]))
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32 terms, f64 accumulate", "data": "synthetic", "config": workload_config(a, world),
@@ -301,7 +301,7 @@ def main():
                 "breakdown_ms_per_step": {"voxel_build": agg["build_ms"] / a.steps, "derivatives": agg["deriv_ms"] / a.steps,
                                           "device_total": agg["total_ms"] / a.steps},
                 "clocks": clocks, "converged_frac": conv / len(res),
-                "mean_iterations": float(np.mean([r["iterations"] for r in res]))}
+                "mean_iterations": float(np.mean(res["iterations"]))}
         if not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_sample(a, w, a.cpu_aligns)
         print(json.dumps(line), flush=True)

@@ -121,8 +121,10 @@ int ndtb_last_timing(ndtb_handle* h, double* build_ms, double* align_ms);
 /* ---- batched registration on one device (north_star item 4) ------------------------------
  * A batch holds targets (submaps) and sources (scans) resident in HBM and runs any number of
  * independent registrations {target id, source id, initial guess} concurrently; no collective
- * inside a registration.  `on_device` != 0 means `pts` is a DEVICE pointer on the batch's
- * device (copied device-to-device); otherwise a host pointer. */
+ * inside a registration.  `on_device`: 0 = `pts` is a HOST pointer (uploaded asynchronously on the
+ * batch's copy stream, overlapped with the voxel-table builds of earlier targets: the buffer must stay
+ * valid until ndtb_batch_run returns); 1 = DEVICE pointer on the batch's device, copied device-to-device;
+ * 2 = DEVICE pointer BORROWED in place (16-byte records, no copy; valid until ndtb_batch_clear). */
 int ndtb_batch_create(int device, ndtb_batch** out);
 int ndtb_batch_destroy(ndtb_batch* b);
 const char* ndtb_batch_last_error(const ndtb_batch* b);

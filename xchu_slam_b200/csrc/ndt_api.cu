@@ -25,12 +25,15 @@ thread_local std::string g_create_error;
   } while (0)
 
 struct Target {
-  float4* pts = nullptr;
+  float4* pts = nullptr;       // owned allocation (cap points)
+  const float4* use = nullptr; // what the build reads: pts, or a borrowed device buffer
   size_t n = 0, cap = 0;
   TableStorage ts;
   bool built = false;
+  cudaEvent_t uploaded = nullptr;   // recorded on the copy stream after the H2D of this target
+  bool pending_upload = false;
 };
-struct Source { long long offset; size_t n; };
+struct Source { long long offset; size_t n; const float4* borrowed; };
 
 // Eigen 3.3 MatrixBase::eulerAngles(0,1,2) on the float rotation block (NDT_I:102)
 static void euler_012(const float T[16], float out[3]) {
@@ -50,6 +53,9 @@ struct Engine {
   int device = 0;
   cudaStream_t stream = nullptr;
   bool own_stream = true;
+  cudaStream_t copy_stream = nullptr;      // batch uploads from host memory run here, overlapped with table builds
+  cudaEvent_t sources_uploaded = nullptr;
+  bool sources_pending = false;
   std::string err;
   ndtb_params params;
   BuildWorkspace* ws = nullptr;
@@ -104,6 +110,8 @@ struct Engine {
     if (dev < 0 || dev >= count) return fail("invalid device ordinal");
     CKE(cudaSetDevice(dev));
     CKE(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    CKE(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
+    CKE(cudaEventCreateWithFlags(&sources_uploaded, cudaEventDisableTiming));
     ws = build_ws_create();
     if (!ws) return fail("workspace allocation failed");
     nn = nn_create();
@@ -117,7 +125,9 @@ struct Engine {
   }
   void destroy() {
     cudaSetDevice(device);
-    for (auto& t : targets) { cudaFree(t.pts); table_free(t.ts); }
+    for (auto& t : targets) { cudaFree(t.pts); table_free(t.ts); if (t.uploaded) cudaEventDestroy(t.uploaded); }
+    if (copy_stream) cudaStreamDestroy(copy_stream);
+    if (sources_uploaded) cudaEventDestroy(sources_uploaded);
     targets.clear();
     build_ws_destroy(ws);
     nn_destroy(nn);
@@ -130,7 +140,8 @@ struct Engine {
   }
 
   // copy n records (xyz = first three floats) into a float4 device array
-  int upload_points(float4* dst, const void* pts, size_t n, size_t stride, bool on_device) {
+  int upload_points(float4* dst, const void* pts, size_t n, size_t stride, bool on_device, cudaStream_t stream_) {
+    cudaStream_t stream = stream_;
     if (n == 0) return 0;
     if (stride < 12) return fail("stride_bytes must be >= 12");
     const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
@@ -169,8 +180,9 @@ struct Engine {
   // full (re)build of a target's voxel table from its resident points: init(), NDT_H:271-278
   int build_target(Target& t) {
     table_config(t);
+    if (t.pending_upload) { CKE(cudaStreamWaitEvent(stream, t.uploaded, 0)); t.pending_upload = false; }
     CKE(table_clear(t.ts, stream, &stats.kernel_launches));
-    CKE(table_append(t.ts, ws, t.pts, t.n, stream, &stats.kernel_launches));
+    CKE(table_append(t.ts, ws, t.use ? t.use : t.pts, t.n, stream, &stats.kernel_launches));
     t.built = true;
     return 0;
   }
@@ -189,23 +201,35 @@ struct Engine {
     return 0;
   }
 
-  int add_source(const void* pts, size_t n, size_t stride, bool on_device, int* id) {
+  // where: 0 host memory, 1 device memory (copied), 2 device memory borrowed (float4 records, no copy; the
+  // caller keeps it alive until the batch is cleared).  async: host uploads go to the copy stream.
+  int add_source(const void* pts, size_t n, size_t stride, int where, bool async, int* id) {
+    if (where == 2) {
+      if (stride != 16) return fail("a borrowed device buffer must hold 16-byte records");
+      sources.push_back(Source{-1, n, static_cast<const float4*>(pts)});
+      if (id) *id = (int)sources.size() - 1;
+      return 0;
+    }
     if (src_used + n > src_cap) {
       const size_t nc = (src_used + n) + (src_used + n) / 2 + 4096;
       float4* q = nullptr;
       CKE(cudaMalloc(&q, nc * sizeof(float4)));
+      CKE(cudaStreamSynchronize(copy_stream));
       if (src_pool && src_used) CKE(cudaMemcpyAsync(q, src_pool, src_used * sizeof(float4), cudaMemcpyDeviceToDevice, stream));
       CKE(cudaStreamSynchronize(stream));
       cudaFree(src_pool);
       src_pool = q;
       src_cap = nc;
     }
-    if (upload_points(src_pool + src_used, pts, n, stride, on_device)) return 1;
-    sources.push_back(Source{(long long)src_used, n});
+    const bool on_copy = async && where == 0;
+    if (upload_points(src_pool + src_used, pts, n, stride, where == 1, on_copy ? copy_stream : stream)) return 1;
+    if (on_copy) sources_pending = true;
+    sources.push_back(Source{(long long)src_used, n, nullptr});
     if (id) *id = (int)sources.size() - 1;
     src_used += n;
     return 0;
   }
+  const float4* source_ptr(const Source& s) const { return s.borrowed ? s.borrowed : src_pool + s.offset; }
 
   template <typename T>
   int ensure(T*& p, size_t& cap, size_t need) {
@@ -221,7 +245,7 @@ struct Engine {
     std::memset(&st, 0, sizeof(st));
     st.n_src = (int)src.n;
     st.target = target;
-    st.src_offset = src.offset;
+    st.src = source_ptr(src);
     st.step_size = params.step_size;
     st.trans_eps = params.trans_eps;
     st.max_iter = params.max_iter;
@@ -254,6 +278,7 @@ struct Engine {
     for (auto& t : targets)
       if (!t.built && t.n > 0 && build_target(t)) return 1;
     CKE(cudaEventRecord(ev[1], stream));
+    if (sources_pending) { CKE(cudaStreamWaitEvent(stream, sources_uploaded, 0)); sources_pending = false; }
     if (sync_tables()) return 1;
     // work decomposition: one block per `chunk` source points of one registration
     size_t total_pts = 0;
@@ -411,7 +436,8 @@ int ndtb_set_target(ndtb_handle* h, const void* pts, size_t n, size_t stride_byt
   if (e.reserve_target(t, n)) return 1;
   t.n = 0;
   cudaEventRecord(e.ev[0], e.stream);
-  if (e.upload_points(t.pts, pts, n, stride_bytes, false)) return 1;
+  if (e.upload_points(t.pts, pts, n, stride_bytes, false, e.stream)) return 1;
+  t.use = nullptr;
   t.n = n;
   e.nn_valid = false;
   t.ts.have_bbox = false;
@@ -432,7 +458,7 @@ int ndtb_update_target(ndtb_handle* h, const void* pts, size_t n, size_t stride_
   if (n == 0) return 0;
   if (e.reserve_target(t, t.n + n)) return 1;
   cudaEventRecord(e.ev[0], e.stream);
-  if (e.upload_points(t.pts + t.n, pts, n, stride_bytes, false)) return 1;
+  if (e.upload_points(t.pts + t.n, pts, n, stride_bytes, false, e.stream)) return 1;
   e.table_config(t);
   cudaError_t ce = table_append(t.ts, e.ws, t.pts + t.n, n, e.stream, &e.stats.kernel_launches);
   if (ce != cudaSuccess) return e.fail(std::string("table_append: ") + cudaGetErrorString(ce));
@@ -457,7 +483,7 @@ int ndtb_set_target_auto(ndtb_handle* h, const void* pts, size_t n, size_t strid
   if (e.reserve_target(t, old_n + n)) return 1;
   cudaEventRecord(e.ev[0], e.stream);
   float4* fresh = t.pts + old_n;
-  if (e.upload_points(fresh, pts, n, stride_bytes, false)) return 1;
+  if (e.upload_points(fresh, pts, n, stride_bytes, false, e.stream)) return 1;
   *e.h_active = 1;
   cudaMemcpyAsync(e.d_active, e.h_active, sizeof(int), cudaMemcpyHostToDevice, e.stream);
   cudaError_t ce = launch_prefix_equal(t.pts, fresh, old_n, e.d_active, e.stream);
@@ -498,7 +524,7 @@ int ndtb_set_source(ndtb_handle* h, const void* pts, size_t n, size_t stride_byt
   e.sources.clear();
   e.src_used = 0;
   e.have_result = false;
-  return e.add_source(pts, n, stride_bytes, false, nullptr);
+  return e.add_source(pts, n, stride_bytes, 0, false, nullptr);
 }
 
 int ndtb_align(ndtb_handle* h, const float guess[16], ndtb_result* out) {
@@ -703,8 +729,9 @@ int ndtb_batch_clear(ndtb_batch* b) {
   Engine& e = b->e;
   cudaSetDevice(e.device);
   // keep the allocations (grow-only pools); forget the contents
-  for (auto& t : e.targets) { t.n = 0; t.built = false; t.ts.have_bbox = false; }
+  for (auto& t : e.targets) { t.n = 0; t.built = false; t.ts.have_bbox = false; t.use = nullptr; t.pending_upload = false; }
   e.n_targets_live = 0;
+  e.sources_pending = false;
   e.sources.clear();
   e.src_used = 0;
   return 0;
@@ -714,9 +741,21 @@ int ndtb_batch_add_target(ndtb_batch* b, const void* pts, size_t n, size_t strid
   cudaSetDevice(e.device);
   if (e.n_targets_live == (int)e.targets.size()) e.targets.emplace_back();
   Target& t = e.targets[e.n_targets_live];
-  if (e.reserve_target(t, n)) return 1;
   t.n = 0;
-  if (e.upload_points(t.pts, pts, n, stride_bytes, on_device != 0)) return 1;
+  t.use = nullptr;
+  t.pending_upload = false;
+  if (on_device == 2) {   // borrow: the table build reads the caller's device buffer in place
+    if (stride_bytes != 16) return e.fail("a borrowed device buffer must hold 16-byte records");
+    t.use = static_cast<const float4*>(pts);
+  } else {
+    if (e.reserve_target(t, n)) return 1;
+    if (on_device == 0) {   // host memory: upload on the copy stream; the build of THIS target waits for it
+      if (!t.uploaded && cudaEventCreateWithFlags(&t.uploaded, cudaEventDisableTiming) != cudaSuccess) return e.fail("event creation failed");
+      if (e.upload_points(t.pts, pts, n, stride_bytes, false, e.copy_stream)) return 1;
+      if (cudaEventRecord(t.uploaded, e.copy_stream) != cudaSuccess) return e.fail("event record failed");
+      t.pending_upload = true;
+    } else if (e.upload_points(t.pts, pts, n, stride_bytes, true, e.stream)) return 1;
+  }
   t.n = n;
   t.built = false;
   t.ts.have_bbox = false;
@@ -725,8 +764,11 @@ int ndtb_batch_add_target(ndtb_batch* b, const void* pts, size_t n, size_t strid
   return 0;
 }
 int ndtb_batch_add_source(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int on_device, int* id) {
-  cudaSetDevice(b->e.device);
-  return b->e.add_source(pts, n, stride_bytes, on_device != 0, id);
+  Engine& e = b->e;
+  cudaSetDevice(e.device);
+  if (e.add_source(pts, n, stride_bytes, on_device, true, id)) return 1;
+  if (on_device == 0 && cudaEventRecord(e.sources_uploaded, e.copy_stream) != cudaSuccess) return e.fail("event record failed");
+  return 0;
 }
 int ndtb_batch_run(ndtb_batch* b, int n_items, const int* item_target, const int* item_source, const float* guesses,
                    ndtb_result* results) {

@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const 
 #pragma unroll
   for (int k = 0; k < kAccN; ++k) acc[k] = 0.0;
   int npairs = 0;
-  const float4* __restrict__ src = src_pool + st.src_offset;
+  const float4* __restrict__ src = st.src;
   const int end = min(bm.y + chunk, st.n_src);
   const VoxelRec* __restrict__ recs = sh.tab.rec;
   const float d2f = sh.d2f;
@@ -254,7 +254,7 @@ __global__ void __launch_bounds__(128) k_hessian_f64(const AlignState* __restric
   double acc[kAccN];
   for (int k = 0; k < kAccN; ++k) acc[k] = 0.0;
   int npairs = 0;
-  const float4* __restrict__ src = src_pool + st.src_offset;
+  const float4* __restrict__ src = st.src;
   const int end = min(bm.y + chunk, st.n_src);
   const double d1 = st.req.d1, d2 = st.req.d2, d3 = st.req.d3;
   for (int i = bm.y + tid; i < end; i += 128) {
@@ -698,24 +698,10 @@ __device__ void mt_continue(NewtonCtx& c, double phi_t, double d_phi_t, double p
   post_step(c);
 }
 
-__global__ void __launch_bounds__(64) k_newton(AlignState* __restrict__ states, int n_items, const double* __restrict__ partials,
-                                               double* __restrict__ trace, int trace_cap, int* __restrict__ n_active) {
-  const int item = blockIdx.x;
-  if (item >= n_items) return;
-  AlignState& st = states[item];
-  if (st.done) return;
-  __shared__ double sums[kPartialStride];
-  const int tid = threadIdx.x;
-  const int mode = st.req.mode;
-  if (mode != 0 && tid < kPartialStride) {
-    double v = 0;
-    const double* p = partials + (size_t)st.first_block * kPartialStride + tid;
-    for (int b = 0; b < st.n_blocks; ++b) v += p[(size_t)b * kPartialStride];   // fixed order: deterministic
-    sums[tid] = v;
-  }
-  __syncthreads();
-  if (tid != 0) return;
-  NewtonCtx c{&st, trace ? trace + (size_t)item * trace_cap * kTraceRec : nullptr, trace_cap, n_active};
+// The state machine proper: runs on one thread, on a SHARED-MEMORY copy of the registration's state
+// (global-memory latency on every st.* access made this kernel 15 % of a batched step).
+__device__ void newton_advance(AlignState& st, const double* sums, double* trace, int trace_cap, int* n_active) {
+  NewtonCtx c{&st, trace, trace_cap, n_active};
   const double mu = 1.e-4;
   if (st.phase == PH_START) {
     // first computeDerivatives of computeTransformation (NDT_I:112): cloud already moved by the guess
@@ -779,6 +765,37 @@ __global__ void __launch_bounds__(64) k_newton(AlignState* __restrict__ states, 
       return;
     }
     default: return;
+  }
+}
+
+__global__ void __launch_bounds__(64) k_newton(AlignState* __restrict__ states, int n_items, const double* __restrict__ partials,
+                                               double* __restrict__ trace, int trace_cap, int* __restrict__ n_active) {
+  const int item = blockIdx.x;
+  if (item >= n_items) return;
+  if (states[item].done) return;
+  __shared__ double sums[kPartialStride];
+  __shared__ AlignState st;
+  static_assert(sizeof(AlignState) % 8 == 0, "AlignState is copied as 64-bit words");
+  const int tid = threadIdx.x;
+  {
+    const unsigned long long* src = reinterpret_cast<const unsigned long long*>(states + item);
+    unsigned long long* dst = reinterpret_cast<unsigned long long*>(&st);
+    for (int k = tid; k < (int)(sizeof(AlignState) / 8); k += 64) dst[k] = src[k];
+  }
+  __syncthreads();
+  if (st.req.mode != 0 && tid < kPartialStride) {
+    double v = 0;
+    const double* p = partials + (size_t)st.first_block * kPartialStride + tid;
+    for (int b = 0; b < st.n_blocks; ++b) v += p[(size_t)b * kPartialStride];   // fixed order: deterministic
+    sums[tid] = v;
+  }
+  __syncthreads();
+  if (tid == 0) newton_advance(st, sums, trace ? trace + (size_t)item * trace_cap * kTraceRec : nullptr, trace_cap, n_active);
+  __syncthreads();
+  {
+    const unsigned long long* src = reinterpret_cast<const unsigned long long*>(&st);
+    unsigned long long* dst = reinterpret_cast<unsigned long long*>(states + item);
+    for (int k = tid; k < (int)(sizeof(AlignState) / 8); k += 64) dst[k] = src[k];
   }
 }
 

@@ -121,7 +121,7 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
 #pragma unroll
   for (int k = 0; k < kFAcc; ++k) acc[k] = 0.0;
   int npairs = 0;
-  const float4* __restrict__ src = src_pool + st.src_offset;
+  const float4* __restrict__ src = st.src;
   const int end = min(bm.y + chunk, st.n_src);
   const FastRec* __restrict__ recs = sh.tab.frec;
   const float d2f = sh.d2f, nhalf_d2f = sh.nhalf_d2f, d1d2f = sh.d1d2f;

@@ -106,7 +106,7 @@ struct AlignState {
   EvalReq req;
   // problem
   int n_src, target, first_block, n_blocks;
-  long long src_offset;      // into the batch's source point pool
+  const float4* src;         // this registration's source points (pool slice or a borrowed device buffer)
   double step_size, trans_eps;
   int max_iter;
   float resolution;

@@ -31,6 +31,11 @@ class Result(C.Structure):
                 ("trans_probability", C.c_double), ("n_evals", C.c_int)]
 
 
+RESULT_DTYPE = np.dtype([("T", np.float32, 16), ("iterations", np.int32), ("converged", np.int32), ("score", np.float64),
+                         ("trans_probability", np.float64), ("n_evals", np.int32)], align=True)
+assert RESULT_DTYPE.itemsize == C.sizeof(Result)
+
+
 class BatchStats(C.Structure):
     _fields_ = [("build_ms", C.c_double), ("deriv_ms", C.c_double), ("total_ms", C.c_double),
                 ("kernel_launches", C.c_longlong), ("deriv_launches", C.c_longlong),
@@ -358,6 +363,7 @@ class BatchNDT:
         return i.value
 
     def add_target_ptr(self, ptr, n, stride=16, on_device=True):
+        """on_device: False / 0 host pointer (async upload), True / 1 device pointer (copied), 2 device pointer borrowed."""
         i = C.c_int()
         self._ck(self._L.ndtb_batch_add_target(self._h, C.c_void_p(ptr), n, stride, int(on_device), C.byref(i)))
         return i.value
@@ -367,19 +373,23 @@ class BatchNDT:
         self._ck(self._L.ndtb_batch_add_source(self._h, C.c_void_p(ptr), n, stride, int(on_device), C.byref(i)))
         return i.value
 
-    def run(self, item_target, item_source, guesses):
+    def run_raw(self, item_target, item_source, guesses):
+        """Runs the registrations; returns the ndtb_result records as a numpy structured array
+        (fields T [16, column-major], iterations, converged, score, trans_probability, n_evals)."""
         it = np.ascontiguousarray(item_target, dtype=np.int32)
         isrc = np.ascontiguousarray(item_source, dtype=np.int32)
         n = it.shape[0]
         G = np.ascontiguousarray(np.asarray(guesses, dtype=np.float32).reshape(n, 4, 4).transpose(0, 2, 1)).reshape(n, 16)
-        res = (Result * n)()
-        self._ck(self._L.ndtb_batch_run(self._h, n, _p(it), _p(isrc), _p(G), C.cast(res, C.c_void_p)))
-        out = []
-        for r in res:
-            out.append(dict(T=np.array(r.T, dtype=np.float32).reshape(4, 4).T.copy(), iterations=r.iterations,
-                            converged=bool(r.converged), score=r.score, trans_probability=r.trans_probability,
-                            n_evals=r.n_evals))
-        return out
+        res = np.zeros(n, dtype=RESULT_DTYPE)
+        self._ck(self._L.ndtb_batch_run(self._h, n, _p(it), _p(isrc), _p(G), _p(res)))
+        return res
+
+    def run(self, item_target, item_source, guesses):
+        res = self.run_raw(item_target, item_source, guesses)
+        T = res["T"].reshape(-1, 4, 4).transpose(0, 2, 1)
+        return [dict(T=T[i].copy(), iterations=int(res["iterations"][i]), converged=bool(res["converged"][i]),
+                     score=float(res["score"][i]), trans_probability=float(res["trans_probability"][i]),
+                     n_evals=int(res["n_evals"][i])) for i in range(res.shape[0])]
 
     def stats(self):
         s = BatchStats()
