@@ -347,7 +347,9 @@ __device__ void angle_axis_matrix(float angle, int axis_id, float R[3][3]) {
   // double and rounded (the libm-independent definition shared with the oracle)
   float ax[3] = {0.f, 0.f, 0.f};
   ax[axis_id] = 1.f;
-  const float s = (float)sin((double)angle), c = (float)cos((double)angle);
+  double sd, cd;
+  sincos((double)angle, &sd, &cd);
+  const float s = (float)sd, c = (float)cd;
   const float sa[3] = {s * ax[0], s * ax[1], s * ax[2]};
   const float one_c = 1.f - c;
   const float ca[3] = {one_c * ax[0], one_c * ax[1], one_c * ax[2]};
@@ -379,9 +381,9 @@ __device__ void pose_to_matrix(const double p[6], float T[16]) {
 // computeAngleDerivatives (NDT_I:286-398)
 __device__ void angle_derivatives(const double p[6], EvalReq& rq) {
   double cx, cy, cz, sx, sy, sz;
-  if (fabs(p[3]) < 10e-5) { cx = 1.0; sx = 0.0; } else { cx = cos(p[3]); sx = sin(p[3]); }
-  if (fabs(p[4]) < 10e-5) { cy = 1.0; sy = 0.0; } else { cy = cos(p[4]); sy = sin(p[4]); }
-  if (fabs(p[5]) < 10e-5) { cz = 1.0; sz = 0.0; } else { cz = cos(p[5]); sz = sin(p[5]); }
+  if (fabs(p[3]) < 10e-5) { cx = 1.0; sx = 0.0; } else sincos(p[3], &sx, &cx);
+  if (fabs(p[4]) < 10e-5) { cy = 1.0; sy = 0.0; } else sincos(p[4], &sy, &cy);
+  if (fabs(p[5]) < 10e-5) { cz = 1.0; sz = 0.0; } else sincos(p[5], &sz, &cz);
   const double J[8][3] = {
       {(-sx * sz + cx * sy * cz), (-sx * cz - cx * sy * sz), (-cx * cy)},
       {(cx * sz + sx * sy * cz), (cx * cz - sx * sy * sz), (-sx * cy)},
@@ -463,69 +465,100 @@ __device__ void svd_solve6(const double* H, const double* b, double* x) {
 
 // Newton step H x = b.  Eigen::JacobiSVD::solve is a pseudo-inverse solve; for the full-rank,
 // moderately conditioned Hessians of a registration that is the ordinary solution, which Gaussian
-// elimination with FULL pivoting plus one step of iterative refinement delivers to the same ~1e-15
-// in a few hundred serial FP64 operations instead of the ~10^5 of the Jacobi sweeps (the sweeps were
-// 15 % of a batched step).  Rank-deficient or non-finite systems (empty grid: H = 0) return false
-// and take the SVD path, which keeps the minimum-norm / zero-step behaviour of NDT_I:119-130.
-__device__ bool lu_solve6(const double* H, const double* b, double* x) {
-  double A[6][6], rhs[6];
-  int cperm[6];
+// elimination with row pivoting plus one step of iterative refinement delivers to the same ~1e-15 in a
+// few hundred FP64 operations instead of the ~10^5 of the Jacobi sweeps.  Everything is unrolled with
+// compile-time indices (row swaps are predicated selects), so the factors live in registers: the version
+// with run-time indices went through local memory and made k_newton 15-25 % of a batched step.
+// Rank-deficient or non-finite systems (empty grid: H = 0) return false and take the SVD path, which keeps
+// the minimum-norm / zero-step behaviour of NDT_I:119-130.
+struct LU6 {
+  double a[6][6];   // L (unit diagonal, below) and U (on and above the diagonal) of the row-permuted matrix
+  int piv[6];       // row chosen at step k
+};
+__device__ __forceinline__ bool lu_factor6(const double* H, LU6& f) {
+#pragma unroll
+  for (int i = 0; i < 6; ++i)
+#pragma unroll
+    for (int j = 0; j < 6; ++j) f.a[i][j] = H[i * 6 + j];
   double pmax = 0.0, pmin = DBL_MAX;
-  for (int i = 0; i < 6; ++i) {
-    cperm[i] = i;
-    rhs[i] = b[i];
-    for (int j = 0; j < 6; ++j) A[i][j] = H[i * 6 + j];
-  }
+#pragma unroll
   for (int k = 0; k < 6; ++k) {
-    int pi = k, pj = k;
-    double best = -1.0;
-    for (int i = k; i < 6; ++i)
-      for (int j = k; j < 6; ++j) {
-        const double v = fabs(A[i][j]);
-        if (!(v <= DBL_MAX)) return false;   // NaN / inf
-        if (v > best) { best = v; pi = i; pj = j; }
-      }
-    if (!(best > 0.0)) return false;
-    if (pi != k) {
-      for (int j = 0; j < 6; ++j) { const double t = A[k][j]; A[k][j] = A[pi][j]; A[pi][j] = t; }
-      const double t = rhs[k]; rhs[k] = rhs[pi]; rhs[pi] = t;
+    int pi = k;
+    double best = fabs(f.a[k][k]);
+#pragma unroll
+    for (int i = k + 1; i < 6; ++i) {
+      const double v = fabs(f.a[i][k]);
+      if (v > best) { best = v; pi = i; }
     }
-    if (pj != k) {
-      for (int i = 0; i < 6; ++i) { const double t = A[i][k]; A[i][k] = A[i][pj]; A[i][pj] = t; }
-      const int t = cperm[k]; cperm[k] = cperm[pj]; cperm[pj] = t;
+    if (!(best > 0.0) || !(best <= DBL_MAX)) return false;   // singular column, NaN or inf
+    f.piv[k] = pi;
+#pragma unroll
+    for (int i = k + 1; i < 6; ++i) {       // swap rows k and pi (pi is a run-time value: predicated selects)
+      const bool sw = (i == pi);
+#pragma unroll
+      for (int j = 0; j < 6; ++j) {
+        const double t = f.a[k][j], u = f.a[i][j];
+        f.a[k][j] = sw ? u : t;
+        f.a[i][j] = sw ? t : u;
+      }
     }
     pmax = fmax(pmax, best);
     pmin = fmin(pmin, best);
-    const double inv = 1.0 / A[k][k];
+    const double inv = 1.0 / f.a[k][k];
+#pragma unroll
     for (int i = k + 1; i < 6; ++i) {
-      const double m = A[i][k] * inv;
-      A[i][k] = m;
-      for (int j = k + 1; j < 6; ++j) A[i][j] -= m * A[k][j];
-      rhs[i] -= m * rhs[k];
+      const double m = f.a[i][k] * inv;
+      f.a[i][k] = m;
+#pragma unroll
+      for (int j = k + 1; j < 6; ++j) f.a[i][j] -= m * f.a[k][j];
     }
   }
-  if (!(pmin > 1e-10 * pmax)) return false;
+  return pmin > 1e-10 * pmax;
+}
+__device__ __forceinline__ void lu_apply6(const LU6& f, const double* b, double* x) {
   double y[6];
-  for (int i = 5; i >= 0; --i) {
-    double v = rhs[i];
-    for (int j = i + 1; j < 6; ++j) v -= A[i][j] * y[j];
-    y[i] = v / A[i][i];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) y[i] = b[i];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {             // all row swaps first: the stored L is in fully permuted row order
+#pragma unroll
+    for (int i = k + 1; i < 6; ++i) {
+      const bool sw = (i == f.piv[k]);
+      const double t = y[k], u = y[i];
+      y[k] = sw ? u : t;
+      y[i] = sw ? t : u;
+    }
   }
-  for (int i = 0; i < 6; ++i) x[cperm[i]] = y[i];
-  return true;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {             // forward substitution with unit-diagonal L
+#pragma unroll
+    for (int i = k + 1; i < 6; ++i) y[i] -= f.a[i][k] * y[k];
+  }
+#pragma unroll
+  for (int i = 5; i >= 0; --i) {
+    double v = y[i];
+#pragma unroll
+    for (int j = i + 1; j < 6; ++j) v -= f.a[i][j] * x[j];
+    x[i] = v / f.a[i][i];
+  }
 }
 __device__ void solve6(const double* H, const double* b, double* x) {
-  if (!lu_solve6(H, b, x)) { svd_solve6(H, b, x); return; }
+  LU6 f;
+  if (!lu_factor6(H, f)) { svd_solve6(H, b, x); return; }
+  lu_apply6(f, b, x);
   double r[6], d[6];
+#pragma unroll
   for (int i = 0; i < 6; ++i) {   // one refinement step: r = b - H x
     double v = b[i];
+#pragma unroll
     for (int j = 0; j < 6; ++j) v -= H[i * 6 + j] * x[j];
     r[i] = v;
   }
-  if (lu_solve6(H, r, d))
-    for (int i = 0; i < 6; ++i) x[i] += d[i];
-  for (int i = 0; i < 6; ++i)
-    if (!(fabs(x[i]) <= DBL_MAX)) { svd_solve6(H, b, x); return; }
+  lu_apply6(f, r, d);
+  bool ok = true;
+#pragma unroll
+  for (int i = 0; i < 6; ++i) { x[i] += d[i]; ok = ok && (fabs(x[i]) <= DBL_MAX); }
+  if (!ok) svd_solve6(H, b, x);
 }
 
 // ---------------------------------------------------------------------------------------
