@@ -2,11 +2,13 @@
 // Newton loop driver) and the extern "C" ABI declared in include/ndt_b200/ndt_c_api.h.
 // Host logic mirrors pcl::Registration::align + pclomp::NormalDistributionsTransform
 // (reference xchu_mapping/include/pclomp/ndt_omp.h:110-278, ndt_omp_impl.hpp:73-164).
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/ndt_b200/ndt_c_api.h"
@@ -53,6 +55,13 @@ struct Engine {
   int device = 0;
   cudaStream_t stream = nullptr;
   bool own_stream = true;
+  // Concurrent table builds of a batch: a few host threads, each with its own stream and workspace, so the small
+  // per-target kernels (one thread per voxel, radix-sort passes) of different submaps overlap on the device.
+  static constexpr int kBuildLanes = 4;
+  cudaStream_t bstream[kBuildLanes] = {nullptr, nullptr, nullptr, nullptr};
+  BuildWorkspace* bws[kBuildLanes] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t bdone[kBuildLanes] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t bstart = nullptr;
   cudaStream_t copy_stream = nullptr;      // batch uploads from host memory run here, overlapped with table builds
   cudaEvent_t sources_uploaded = nullptr;
   bool sources_pending = false;
@@ -126,6 +135,12 @@ struct Engine {
   void destroy() {
     cudaSetDevice(device);
     for (auto& t : targets) { cudaFree(t.pts); table_free(t.ts); if (t.uploaded) cudaEventDestroy(t.uploaded); }
+    for (int g = 0; g < kBuildLanes; ++g) {
+      if (bws[g]) build_ws_destroy(bws[g]);
+      if (bstream[g]) cudaStreamDestroy(bstream[g]);
+      if (bdone[g]) cudaEventDestroy(bdone[g]);
+    }
+    if (bstart) cudaEventDestroy(bstart);
     if (copy_stream) cudaStreamDestroy(copy_stream);
     if (sources_uploaded) cudaEventDestroy(sources_uploaded);
     targets.clear();
@@ -184,6 +199,52 @@ struct Engine {
     CKE(table_clear(t.ts, stream, &stats.kernel_launches));
     CKE(table_append(t.ts, ws, t.use ? t.use : t.pts, t.n, stream, &stats.kernel_launches));
     t.built = true;
+    return 0;
+  }
+
+  // Builds every target that needs it.  One target: on the engine's stream.  Several: kBuildLanes host threads, each
+  // driving its own stream / workspace (table_append synchronises its stream three times per target; a thread per
+  // lane keeps those waits from serialising the lanes).  The engine's stream then waits for every lane.
+  int build_pending_targets() {
+    std::vector<Target*> todo;
+    for (auto& t : targets)
+      if (!t.built && t.n > 0) todo.push_back(&t);
+    if (todo.empty()) return 0;
+    if (todo.size() == 1) return build_target(*todo[0]);
+    const int lanes = (int)std::min<size_t>(kBuildLanes, todo.size());
+    if (!bstart) CKE(cudaEventCreateWithFlags(&bstart, cudaEventDisableTiming));
+    for (int g = 0; g < lanes; ++g) {
+      if (!bstream[g]) CKE(cudaStreamCreateWithFlags(&bstream[g], cudaStreamNonBlocking));
+      if (!bdone[g]) CKE(cudaEventCreateWithFlags(&bdone[g], cudaEventDisableTiming));
+      if (!bws[g]) { bws[g] = build_ws_create(); if (!bws[g]) return fail("workspace allocation failed"); }
+    }
+    CKE(cudaEventRecord(bstart, stream));
+    std::string errs[kBuildLanes];
+    long long launches[kBuildLanes] = {0, 0, 0, 0};
+    auto work = [&](int g) {
+      if (cudaSetDevice(device) != cudaSuccess) { errs[g] = "cudaSetDevice failed"; return; }
+      cudaStream_t bs = bstream[g];
+      cudaError_t ce = cudaStreamWaitEvent(bs, bstart, 0);
+      for (size_t k = g; k < todo.size() && ce == cudaSuccess; k += lanes) {
+        Target& t = *todo[k];
+        table_config(t);
+        if (t.pending_upload) { ce = cudaStreamWaitEvent(bs, t.uploaded, 0); t.pending_upload = false; }
+        if (ce == cudaSuccess) ce = table_clear(t.ts, bs, &launches[g]);
+        if (ce == cudaSuccess) ce = table_append(t.ts, bws[g], t.use ? t.use : t.pts, t.n, bs, &launches[g]);
+        t.built = true;
+      }
+      if (ce == cudaSuccess) ce = cudaEventRecord(bdone[g], bs);
+      if (ce != cudaSuccess) errs[g] = std::string("table build: ") + cudaGetErrorString(ce);
+    };
+    std::vector<std::thread> th;
+    for (int g = 1; g < lanes; ++g) th.emplace_back(work, g);
+    work(0);
+    for (auto& x : th) x.join();
+    for (int g = 0; g < lanes; ++g) {
+      if (!errs[g].empty()) return fail(errs[g]);
+      stats.kernel_launches += launches[g];
+      CKE(cudaStreamWaitEvent(stream, bdone[g], 0));
+    }
     return 0;
   }
 
@@ -275,8 +336,7 @@ struct Engine {
     CKE(cudaSetDevice(device));
     stats = ndtb_batch_stats{};
     CKE(cudaEventRecord(ev[0], stream));
-    for (auto& t : targets)
-      if (!t.built && t.n > 0 && build_target(t)) return 1;
+    if (build_pending_targets()) return 1;
     CKE(cudaEventRecord(ev[1], stream));
     if (sources_pending) { CKE(cudaStreamWaitEvent(stream, sources_uploaded, 0)); sources_pending = false; }
     if (sync_tables()) return 1;

@@ -33,6 +33,9 @@ namespace ndtb {
 #ifndef NDTB_FAST_MINBLOCKS
 #define NDTB_FAST_MINBLOCKS 4
 #endif
+#ifndef NDTB_FAST_ACC_SMEM   // 1: the 28 FP64 accumulators of a thread live in shared memory (in the reduction layout)
+#define NDTB_FAST_ACC_SMEM 0
+#endif
 constexpr int kFT = NDTB_FAST_THREADS;
 constexpr int kFAcc = 28;          // score, g[6], H upper triangle [21]
 constexpr int kFCols = kFAcc + 1;  // + pair count
@@ -62,8 +65,10 @@ __device__ __forceinline__ void fast_reduce_store(const double* acc, int npairs,
   extern __shared__ double red_sm[];                 // [warps][kFCols][kFPad] + [warps][kFCols]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = kFT >> 5;
   double* mine = red_sm + (size_t)warp * kFCols * kFPad;
+#if !NDTB_FAST_ACC_SMEM
 #pragma unroll
   for (int k = 0; k < kFAcc; ++k) mine[k * kFPad + lane] = acc[k];
+#endif
   mine[kFAcc * kFPad + lane] = (double)npairs;
   __syncwarp();
   double* wsum = red_sm + (size_t)nwarps * kFCols * kFPad;
@@ -117,9 +122,17 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
     sh.tab = tables[st.target];
   }
   __syncthreads();
+#if NDTB_FAST_ACC_SMEM
+  extern __shared__ double red_sm[];
+  double* const acc_sm = red_sm + (size_t)(tid >> 5) * kFCols * kFPad + (tid & 31);
+  const double* acc = nullptr;
+#define ACC(k) acc_sm[(k) * kFPad]
+#else
   double acc[kFAcc];
+#define ACC(k) acc[k]
+#endif
 #pragma unroll
-  for (int k = 0; k < kFAcc; ++k) acc[k] = 0.0;
+  for (int k = 0; k < kFAcc; ++k) ACC(k) = 0.0;
   int npairs = 0;
   const float4* __restrict__ src = st.src;
   const int end = min(bm.y + chunk, st.n_src);
@@ -188,13 +201,13 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
     }
 #undef NDTB_PAIR
     // ---- once per point: computePointDerivatives (NDT_I:401-445) and the 6x6 algebra ----------
-    acc[0] += sh.neg_d1 * (double)S;                             // NDT_I:509
+    ACC(0) += sh.neg_d1 * (double)S;                             // NDT_I:509
 #define JH(r) fmaf(sh.jh[r].z, p.z, fmaf(sh.jh[r].y, p.y, sh.jh[r].x * p.x))
     const float g13 = JH(0), g23 = JH(1), g04 = JH(2), g14 = JH(3), g24 = JH(4), g05 = JH(5), g15 = JH(6), g25 = JH(7);
-    acc[1] += (double)a0; acc[2] += (double)a1; acc[3] += (double)a2;                         // NDT_I:521-523
-    acc[4] += (double)fmaf(g23, a2, g13 * a1);
-    acc[5] += (double)fmaf(g24, a2, fmaf(g14, a1, g04 * a0));
-    acc[6] += (double)fmaf(g25, a2, fmaf(g15, a1, g05 * a0));
+    ACC(1) += (double)a0; ACC(2) += (double)a1; ACC(3) += (double)a2;                         // NDT_I:521-523
+    ACC(4) += (double)fmaf(g23, a2, g13 * a1);
+    ACC(5) += (double)fmaf(g24, a2, fmaf(g14, a1, g04 * a0));
+    ACC(6) += (double)fmaf(g25, a2, fmaf(g15, a1, g05 * a0));
     if (CH) {
       const float nd2 = -d2f;
       const float N00 = fmaf(nd2, B00, M00), N01 = fmaf(nd2, B01, M01), N02 = fmaf(nd2, B02, M02);
@@ -212,19 +225,19 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
       const float h44 = fmaf(a2, JH(16), fmaf(a1, JH(15), a0 * JH(14)));
       const float h45 = fmaf(a2, JH(19), fmaf(a1, JH(18), a0 * JH(17)));
       const float h55 = fmaf(a2, JH(22), fmaf(a1, JH(21), a0 * JH(20)));
-      double* H = acc + 7;
-      H[0] += (double)N00; H[1] += (double)N01; H[2] += (double)N02; H[3] += (double)P00; H[4] += (double)P01; H[5] += (double)P02;
-      H[6] += (double)N11; H[7] += (double)N12; H[8] += (double)P10; H[9] += (double)P11; H[10] += (double)P12;
-      H[11] += (double)N22; H[12] += (double)P20; H[13] += (double)P21; H[14] += (double)P22;
-      H[15] += (double)(fmaf(g23, P20, g13 * P10) + h33);
-      H[16] += (double)(fmaf(g23, P21, g13 * P11) + h34);
-      H[17] += (double)(fmaf(g23, P22, g13 * P12) + h35);
-      H[18] += (double)(fmaf(g24, P21, fmaf(g14, P11, g04 * P01)) + h44);
-      H[19] += (double)(fmaf(g24, P22, fmaf(g14, P12, g04 * P02)) + h45);
-      H[20] += (double)(fmaf(g25, P22, fmaf(g15, P12, g05 * P02)) + h55);
+      ACC(7) += (double)N00; ACC(8) += (double)N01; ACC(9) += (double)N02; ACC(10) += (double)P00; ACC(11) += (double)P01; ACC(12) += (double)P02;
+      ACC(13) += (double)N11; ACC(14) += (double)N12; ACC(15) += (double)P10; ACC(16) += (double)P11; ACC(17) += (double)P12;
+      ACC(18) += (double)N22; ACC(19) += (double)P20; ACC(20) += (double)P21; ACC(21) += (double)P22;
+      ACC(22) += (double)(fmaf(g23, P20, g13 * P10) + h33);
+      ACC(23) += (double)(fmaf(g23, P21, g13 * P11) + h34);
+      ACC(24) += (double)(fmaf(g23, P22, g13 * P12) + h35);
+      ACC(25) += (double)(fmaf(g24, P21, fmaf(g14, P11, g04 * P01)) + h44);
+      ACC(26) += (double)(fmaf(g24, P22, fmaf(g14, P12, g04 * P02)) + h45);
+      ACC(27) += (double)(fmaf(g25, P22, fmaf(g15, P12, g05 * P02)) + h55);
     }
 #undef JH
   }
+#undef ACC
   fast_reduce_store(acc, npairs, partials + (size_t)blockIdx.x * kPartialStride);
 }
 

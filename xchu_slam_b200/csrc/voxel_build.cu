@@ -482,7 +482,7 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
   long long& L = launches ? *launches : dummy;
   // bounding box of the new points
   k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
-  k_minmax<<<296, 256, 0, s>>>(pts, n, ws->mm, 1);
+  k_minmax<<<148 * 8, 256, 0, s>>>(pts, n, ws->mm, 1);
   k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
   L += 3;
   CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
@@ -613,7 +613,7 @@ cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, si
     g->pts_cap = n + n / 4;
   }
   k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
-  k_minmax<<<296, 256, 0, s>>>(pts, n, ws->mm, 1);
+  k_minmax<<<148 * 8, 256, 0, s>>>(pts, n, ws->mm, 1);
   k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
   CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
