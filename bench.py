@@ -45,6 +45,10 @@ def parse():
     ap.add_argument("--n-source", type=int, default=20000)
     ap.add_argument("--cpu-aligns", type=int, default=24, help="aligns in the bounded CPU sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--inflight", type=int, default=1,
+                    help="batches in flight per GPU for `value` (host threads, one BatchNDT and stream each)")
+    ap.add_argument("--inflight-e2e", type=int, default=2,
+                    help="batches in flight per GPU for `e2e`: the H2D of one step overlaps the compute of another")
     return ap.parse_args()
 
 
@@ -209,12 +213,32 @@ def main():
     d2h_bytes = n_items * C.sizeof(ndt.Result)
     torch.cuda.synchronize()
 
-    b = ndt.BatchNDT(device=local)
-    b.set_stream(torch.cuda.current_stream().cuda_stream)   # torch's events then bracket the library's work
-    b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=ndt.DIRECT7)
+    n_batches = max(1, a.inflight, a.inflight_e2e)
+    batches = []
+    for k in range(n_batches):
+        bk = ndt.BatchNDT(device=local)
+        bk.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=ndt.DIRECT7)
+        batches.append(bk)
+    # batch 0 runs on torch's current stream, so torch's events bracket the library's work directly
+    batches[0].set_stream(torch.cuda.current_stream().cuda_stream)
     it, isrc, G = w["item_target"], w["item_source"], w["guesses"]
 
-    def step(resident):
+    upload_lock, compute_lock = threading.Lock(), threading.Lock()
+
+    def step(resident, b=None, pipelined=False):
+        """pipelined (several batches in flight): a two-stage pipeline -- one batch uploads while another computes."""
+        b = b or batches[0]
+        if pipelined:
+            with upload_lock:
+                b.clear()
+                for t in tg_host:
+                    b.add_target_ptr(t.data_ptr(), t.shape[0], 16, 0)
+                for s in sc_host:
+                    b.add_source_ptr(s.data_ptr(), s.shape[0], 16, 0)
+                b.wait_uploads()
+            with compute_lock:
+                res = b.run_raw(it, isrc, G)
+                return res, b.stats()
         b.clear()
         if resident:
             for t in tg_dev:
@@ -229,42 +253,59 @@ def main():
         res = b.run_raw(it, isrc, G)  # returns after the device finished and the result records are on the host
         return res, b.stats()
 
-    def timed(resident, steps):
+    def timed(resident, steps, inflight):
+        """EXACTLY `steps` steps.  inflight > 1: that many host threads, each driving its own BatchNDT (own streams) and
+        taking steps round-robin; the GPU overlaps one step's uploads / tail iterations with another step's compute."""
         barrier()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
         e0.record()
         agg = dict(deriv_ms=0.0, build_ms=0.0, total_ms=0.0, kernel_launches=0, deriv_launches=0, points=0, pairs=0)
-        res = None
-        for _ in range(steps):
-            res, st = step(resident)
-            agg["deriv_ms"] += st["deriv_ms"]; agg["build_ms"] += st["build_ms"]; agg["total_ms"] += st["total_ms"]
-            agg["kernel_launches"] += st["kernel_launches"]; agg["deriv_launches"] += st["deriv_launches"]
-            agg["points"] += st["points_evaluated"]; agg["pairs"] += st["pairs_evaluated"]
-        e1.record()
+        out = {}
+        lock = threading.Lock()
+
+        def worker(j):
+            torch.cuda.set_device(local)
+            for k in range(j, steps, inflight):
+                res, st = step(resident, batches[j], pipelined=(inflight > 1 and not resident))
+                with lock:
+                    out[k] = res
+                    agg["deriv_ms"] += st["deriv_ms"]; agg["build_ms"] += st["build_ms"]; agg["total_ms"] += st["total_ms"]
+                    agg["kernel_launches"] += st["kernel_launches"]; agg["deriv_launches"] += st["deriv_launches"]
+                    agg["points"] += st["points_evaluated"]; agg["pairs"] += st["pairs_evaluated"]
+        if inflight <= 1:
+            worker(0)
+        else:
+            th = [threading.Thread(target=worker, args=(j,)) for j in range(inflight)]
+            for t in th:
+                t.start()
+            for t in th:
+                t.join()
+        e1.record()          # every run_raw has returned: all of the steps' device work precedes this record
         torch.cuda.synchronize()
         barrier()
         wall = time.perf_counter() - t0
-        # device time: CUDA events on the stream the library launches on (set_stream above)
         ms = e0.elapsed_time(e1)
         agg["wall_ms"] = wall * 1e3
         if dist is not None:
             tt = torch.tensor([ms], device=dev, dtype=torch.float64)
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
             ms = float(tt.item())
-        return ms, agg, res
+        return ms, agg, out[steps - 1]
 
     for _ in range(a.warmup):
-        step(True)
+        for bk in batches[:max(1, a.inflight)]:
+            step(True, bk)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ms, agg, res = timed(True, a.steps)
+    ms, agg, res = timed(True, a.steps, max(1, a.inflight))
     clocks = sampler.stop() if rank == 0 else None
     for _ in range(min(a.warmup, 1)):
-        step(False)
-    ms_e2e, agg_e2e, _ = timed(False, a.steps)
+        for bk in batches[:max(1, a.inflight_e2e)]:
+            step(False, bk)
+    ms_e2e, agg_e2e, _ = timed(False, a.steps, max(1, a.inflight_e2e))
 
     if rank == 0:
         value = world * n_items * a.steps / (ms / 1e3)
@@ -289,7 +330,7 @@ def main():
                 "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f32 terms, f64 accumulate", "data": "synthetic", "config": workload_config(a, world),
                 "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                        "ms_per_step": ms_e2e / a.steps},
+                        "ms_per_step": ms_e2e / a.steps, "batches_in_flight": max(1, a.inflight_e2e)},
                 "gpu_launches": int(agg["kernel_launches"]),
                 "roofline": {"bound": "hbm", "kernel": "k_derivatives", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak if peak else None, "traffic": traffic,

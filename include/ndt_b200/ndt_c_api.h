@@ -132,6 +132,9 @@ int ndtb_batch_set_params(ndtb_batch* b, const ndtb_params* p);
 int ndtb_batch_clear(ndtb_batch* b);
 int ndtb_batch_add_target(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int on_device, int* id);
 int ndtb_batch_add_source(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int on_device, int* id);
+/* Blocks until every host upload enqueued by ndtb_batch_add_* so far has landed in HBM (lets a caller with several
+ * batches in flight stage one batch's uploads behind another batch's compute). */
+int ndtb_batch_wait_uploads(ndtb_batch* b);
 /* Builds every target's voxel table (if not built yet) and runs n_items registrations.
  * guesses: n_items x 16 floats.  results: n_items records (host). */
 int ndtb_batch_run(ndtb_batch* b, int n_items, const int* item_target, const int* item_source,

@@ -37,6 +37,27 @@ struct Target {
 };
 struct Source { long long offset; size_t n; const float4* borrowed; };
 
+// Grow-only pinned + mapped host buffer: the host fills it, a kernel pulls it (ndt_core.cu launch_pull).
+struct PinnedBuf {
+  void* h = nullptr;
+  void* d = nullptr;    // device alias of h
+  size_t cap = 0;
+  cudaError_t reserve(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (h) cudaFreeHost(h);
+    h = d = nullptr;
+    cap = 0;
+    const size_t nc = ((bytes + bytes / 4 + 4095) / 4096) * 4096;
+    cudaError_t e = cudaHostAlloc(&h, nc, cudaHostAllocMapped);
+    if (e != cudaSuccess) return e;
+    e = cudaHostGetDevicePointer(&d, h, 0);
+    if (e != cudaSuccess) return e;
+    cap = nc;
+    return cudaSuccess;
+  }
+  void release() { if (h) cudaFreeHost(h); h = d = nullptr; cap = 0; }
+};
+
 // Eigen 3.3 MatrixBase::eulerAngles(0,1,2) on the float rotation block (NDT_I:102)
 static void euler_012(const float T[16], float out[3]) {
   auto m = [&](int r, int c) { return T[c * 4 + r]; };
@@ -79,7 +100,8 @@ struct Engine {
   std::vector<Source> sources;
   AlignState* d_states = nullptr;
   size_t states_cap = 0;
-  std::vector<AlignState> h_states;
+  PinnedBuf st_states, st_bmap, st_tables;   // staging of the run set-up
+  AlignState* h_states = nullptr;            // = st_states.h
   int2* d_blockmap = nullptr;
   size_t blockmap_cap = 0;
   double* d_partials = nullptr;
@@ -88,7 +110,8 @@ struct Engine {
   size_t trace_doubles = 0;
   int trace_cap = 0;
   int* d_active = nullptr;
-  int* h_active = nullptr;
+  int* h_active = nullptr;       // pinned + mapped: the device publishes the unfinished-registration count into it
+  int* h_active_dev = nullptr;
   float* d_T16 = nullptr;
   double* d_p6 = nullptr;
   float4* d_output = nullptr;
@@ -125,7 +148,8 @@ struct Engine {
     if (!ws) return fail("workspace allocation failed");
     nn = nn_create();
     CKE(cudaMalloc(&d_active, sizeof(int)));
-    CKE(cudaMallocHost(&h_active, sizeof(int)));
+    CKE(cudaHostAlloc(&h_active, sizeof(int), cudaHostAllocMapped));
+    CKE(cudaHostGetDevicePointer(&h_active_dev, h_active, 0));
     CKE(cudaMalloc(&d_T16, 16 * sizeof(float)));
     CKE(cudaMalloc(&d_p6, 6 * sizeof(double)));
     for (auto& e : ev) CKE(cudaEventCreate(&e));
@@ -146,6 +170,7 @@ struct Engine {
     targets.clear();
     build_ws_destroy(ws);
     nn_destroy(nn);
+    st_states.release(); st_bmap.release(); st_tables.release();
     cudaFree(d_tables); cudaFree(src_pool); cudaFree(d_states); cudaFree(d_blockmap); cudaFree(d_partials);
     cudaFree(d_trace); cudaFree(d_active); cudaFreeHost(h_active); cudaFree(d_T16); cudaFree(d_p6);
     cudaFree(d_output); cudaFree(d_d2);
@@ -253,12 +278,14 @@ struct Engine {
       cudaFree(d_tables);
       d_tables = nullptr;
       d_tables_cap = targets.size() + 8;
-      CKE(cudaMalloc(&d_tables, d_tables_cap * sizeof(VoxelTable)));
+      CKE(cudaMalloc(&d_tables, ((d_tables_cap * sizeof(VoxelTable) + 15) / 16) * 16));
     }
-    std::vector<VoxelTable> h(targets.size());
+    if (targets.empty()) return 0;
+    CKE(cudaStreamSynchronize(stream));   // the staging buffer may still be read by the previous pull
+    CKE(st_tables.reserve(targets.size() * sizeof(VoxelTable)));
+    VoxelTable* h = static_cast<VoxelTable*>(st_tables.h);
     for (size_t i = 0; i < targets.size(); ++i) h[i] = targets[i].ts.t;
-    if (!h.empty()) CKE(cudaMemcpyAsync(d_tables, h.data(), h.size() * sizeof(VoxelTable), cudaMemcpyHostToDevice, stream));
-    CKE(cudaStreamSynchronize(stream));
+    CKE(launch_pull(d_tables, st_tables.d, targets.size() * sizeof(VoxelTable), stream));
     return 0;
   }
 
@@ -298,7 +325,7 @@ struct Engine {
     cudaFree(p);
     p = nullptr;
     cap = need + need / 4 + 16;
-    CKE(cudaMalloc(&p, cap * sizeof(T)));
+    CKE(cudaMalloc(&p, ((cap * sizeof(T) + 15) / 16) * 16));
     return 0;
   }
 
@@ -352,29 +379,34 @@ struct Engine {
     if (chunk < 256) chunk = 256;
     if (chunk > 512) chunk = 512;
     if (const char* ev = getenv("NDTB_CHUNK")) { const int c = atoi(ev); if (c >= 128) chunk = c; }   // tuning knob
-    h_states.resize(n_items);
-    std::vector<int2> bmap;
+    size_t total_blocks = 0;
+    for (int i = 0; i < n_items; ++i) total_blocks += (sources[item_source[i]].n + chunk - 1) / chunk;
+    CKE(st_states.reserve((size_t)n_items * sizeof(AlignState)));
+    CKE(st_bmap.reserve(total_blocks * sizeof(int2) + 16));
+    h_states = static_cast<AlignState*>(st_states.h);
+    int2* bmap = static_cast<int2*>(st_bmap.h);
+    size_t nb_fill = 0;
     for (int i = 0; i < n_items; ++i) {
       AlignState& st = h_states[i];
       fill_state(st, item_target[i], sources[item_source[i]], guesses + (size_t)i * 16);
       if (!targets[item_target[i]].ts.valid) st.req.search_method = params.search_method;  // empty grid: no neighbours at all
-      st.first_block = (int)bmap.size();
+      st.first_block = (int)nb_fill;
       st.n_blocks = (st.n_src + chunk - 1) / chunk;
-      for (int b = 0; b < st.n_blocks; ++b) bmap.push_back(make_int2(i, b * chunk));
+      for (int b = 0; b < st.n_blocks; ++b) bmap[nb_fill++] = make_int2(i, b * chunk);
     }
-    const int n_blocks = (int)bmap.size();
+    const int n_blocks = (int)nb_fill;
     if (ensure(d_states, states_cap, (size_t)n_items)) return 1;
-    if (ensure(d_blockmap, blockmap_cap, bmap.size())) return 1;
-    if (ensure(d_partials, partials_cap, bmap.size() * 44)) return 1;
+    if (ensure(d_blockmap, blockmap_cap, nb_fill + 2)) return 1;
+    if (ensure(d_partials, partials_cap, nb_fill * 44 + 2)) return 1;
     const bool mt_live = !((params.step_size - params.trans_eps / 2) > 0);   // NDT_I:807: the inner loop runs only then
     const int evals_per_iter = mt_live ? 12 : 1;
     const int max_evals = 1 + (params.max_iter + 2) * evals_per_iter;
     trace_cap = want_trace ? max_evals + 1 : 0;
     if (want_trace && ensure(d_trace, trace_doubles, (size_t)n_items * trace_cap * kTraceRec)) return 1;
-    CKE(cudaMemcpyAsync(d_states, h_states.data(), (size_t)n_items * sizeof(AlignState), cudaMemcpyHostToDevice, stream));
-    if (!bmap.empty()) CKE(cudaMemcpyAsync(d_blockmap, bmap.data(), bmap.size() * sizeof(int2), cudaMemcpyHostToDevice, stream));
-    *h_active = n_items;
-    CKE(cudaMemcpyAsync(d_active, h_active, sizeof(int), cudaMemcpyHostToDevice, stream));
+    CKE(launch_pull(d_states, st_states.d, (size_t)n_items * sizeof(AlignState), stream));
+    CKE(launch_pull(d_blockmap, st_bmap.d, nb_fill * sizeof(int2), stream));
+    CKE(launch_set_int(d_active, n_items, stream));
+    stats.kernel_launches += 3;
     CKE(cudaEventRecord(ev[2], stream));
     // PH_START: set up the first evaluation request
     CKE(launch_newton(d_states, n_items, d_partials, want_trace ? d_trace : nullptr, trace_cap, d_active, stream));
@@ -400,13 +432,15 @@ struct Engine {
       CKE(launch_newton(d_states, n_items, d_partials, want_trace ? d_trace : nullptr, trace_cap, d_active, stream));
       stats.kernel_launches++;
       if ((it + 1) % poll == 0 || it + 1 == max_evals) {
-        CKE(cudaMemcpyAsync(h_active, d_active, sizeof(int), cudaMemcpyDeviceToHost, stream));
+        // published by a one-thread kernel straight into mapped host memory: a D2H memcpy would queue on a copy engine
+        // behind another batch's multi-megabyte uploads and stall this loop for their whole duration
+        CKE(launch_publish(d_active, h_active_dev, stream));
         CKE(cudaStreamSynchronize(stream));
-        if (*h_active <= 0) break;
+        if (*(volatile int*)h_active <= 0) break;
       }
     }
     CKE(cudaEventRecord(ev[3], stream));
-    CKE(cudaMemcpyAsync(h_states.data(), d_states, (size_t)n_items * sizeof(AlignState), cudaMemcpyDeviceToHost, stream));
+    CKE(cudaMemcpyAsync(h_states, d_states, (size_t)n_items * sizeof(AlignState), cudaMemcpyDeviceToHost, stream));
     if (want_trace) {
       h_trace.resize((size_t)n_items * trace_cap * kTraceRec);
       CKE(cudaMemcpyAsync(h_trace.data(), d_trace, h_trace.size() * sizeof(double), cudaMemcpyDeviceToHost, stream));
@@ -828,6 +862,12 @@ int ndtb_batch_add_source(ndtb_batch* b, const void* pts, size_t n, size_t strid
   cudaSetDevice(e.device);
   if (e.add_source(pts, n, stride_bytes, on_device, true, id)) return 1;
   if (on_device == 0 && cudaEventRecord(e.sources_uploaded, e.copy_stream) != cudaSuccess) return e.fail("event record failed");
+  return 0;
+}
+int ndtb_batch_wait_uploads(ndtb_batch* b) {
+  Engine& e = b->e;
+  cudaSetDevice(e.device);
+  if (cudaStreamSynchronize(e.copy_stream) != cudaSuccess) return e.fail("upload failed");
   return 0;
 }
 int ndtb_batch_run(ndtb_batch* b, int n_items, const int* item_target, const int* item_source, const float* guesses,

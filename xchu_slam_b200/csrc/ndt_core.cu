@@ -931,6 +931,29 @@ cudaError_t launch_prepare_eval(AlignState* st, const float* T16, const double* 
   k_prepare_eval<<<1, 32, 0, s>>>(st, T16, p6, mode);
   return cudaGetLastError();
 }
+// Small host -> device transfers of the run set-up (registration states, block map, table descriptors) are PULLED by
+// a kernel out of mapped pinned host memory instead of being pushed with cudaMemcpyAsync: an H2D memcpy queues on the
+// copy engine behind any other batch's multi-megabyte cloud uploads and would stall this batch for their duration.
+__global__ void k_pull(uint4* __restrict__ dst, const uint4* __restrict__ src, size_t n16) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+cudaError_t launch_pull(void* dst_dev, const void* src_mapped_dev, size_t bytes, cudaStream_t s) {
+  if (bytes == 0) return cudaSuccess;
+  const size_t n16 = (bytes + 15) / 16;   // both buffers are allocated in multiples of 16 bytes
+  const unsigned blocks = (unsigned)((n16 + 255) / 256 < 1184 ? (n16 + 255) / 256 : 1184);
+  k_pull<<<blocks, 256, 0, s>>>(static_cast<uint4*>(dst_dev), static_cast<const uint4*>(src_mapped_dev), n16);
+  return cudaGetLastError();
+}
+__global__ void k_set_int(int* dst, int v) { *dst = v; }
+cudaError_t launch_set_int(int* dst, int v, cudaStream_t s) {
+  k_set_int<<<1, 1, 0, s>>>(dst, v);
+  return cudaGetLastError();
+}
+__global__ void k_publish(const int* __restrict__ src, int* __restrict__ dst) { *dst = *src; __threadfence_system(); }
+cudaError_t launch_publish(const int* src_dev, int* dst_mapped_host, cudaStream_t s) {
+  k_publish<<<1, 1, 0, s>>>(src_dev, dst_mapped_host);
+  return cudaGetLastError();
+}
 cudaError_t launch_prefix_equal(const float4* a, const float4* b, size_t n, int* flag, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
   k_prefix_equal<<<296, 256, 0, s>>>(reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b), n, flag);

@@ -167,6 +167,9 @@ cudaError_t launch_neighbors(const VoxelTable* table, const float* xyz, size_t n
                              cudaStream_t s);
 cudaError_t launch_transform(const float4* src, size_t n, const float* T16_colmajor_dev, float4* out, cudaStream_t s);
 cudaError_t launch_prepare_eval(AlignState* st, const float* T16_dev, const double* p6_dev, int mode, cudaStream_t s);
+cudaError_t launch_pull(void* dst_dev, const void* src_mapped_dev, size_t bytes, cudaStream_t s);
+cudaError_t launch_set_int(int* dst, int v, cudaStream_t s);
+cudaError_t launch_publish(const int* src_dev, int* dst_mapped_host, cudaStream_t s);
 cudaError_t launch_prefix_equal(const float4* a, const float4* b, size_t n, int* flag, cudaStream_t s);
 
 // fitness (exact 1-NN over the raw target, grid of key-sorted points)

@@ -48,7 +48,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_neighbors",
            "ndtb_eval_derivatives", "ndtb_compute_hessian", "ndtb_get_trace", "ndtb_last_timing", "ndtb_batch_create",
            "ndtb_batch_destroy", "ndtb_batch_last_error", "ndtb_batch_set_params", "ndtb_batch_clear", "ndtb_batch_add_target",
-           "ndtb_batch_add_source", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream"]
+           "ndtb_batch_add_source", "ndtb_batch_wait_uploads", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream"]
 
 _lib = None
 
@@ -94,6 +94,7 @@ def load_library():
     L.ndtb_batch_clear.argtypes = [vp]
     L.ndtb_batch_add_target.argtypes = [vp, vp, sz, sz, C.c_int, C.POINTER(C.c_int)]
     L.ndtb_batch_add_source.argtypes = [vp, vp, sz, sz, C.c_int, C.POINTER(C.c_int)]
+    L.ndtb_batch_wait_uploads.argtypes = [vp]
     L.ndtb_batch_run.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
     L.ndtb_batch_set_stream.argtypes = [vp, vp]
@@ -372,6 +373,9 @@ class BatchNDT:
         i = C.c_int()
         self._ck(self._L.ndtb_batch_add_source(self._h, C.c_void_p(ptr), n, stride, int(on_device), C.byref(i)))
         return i.value
+
+    def wait_uploads(self):
+        self._ck(self._L.ndtb_batch_wait_uploads(self._h))
 
     def run_raw(self, item_target, item_source, guesses):
         """Runs the registrations; returns the ndtb_result records as a numpy structured array
