@@ -27,6 +27,10 @@ def get_case(name):
         c = synth.make_case(n_source=20000, n_target=300000, seed=synth.BASE_SEED)
     elif name == "tiny":
         c = synth.make_case(n_source=1500, n_target=20000, seed=synth.BASE_SEED + 2)
+    elif name == "c3":       # BASELINE configs[2]: 20k-pt scan vs 5M-pt localmap, res 0.5
+        c = synth.make_case(n_source=20000, n_target=5000000, seed=synth.BASE_SEED + 3, keyframe_leaf=0.25)
+    elif name == "c4":       # BASELINE configs[3]: undownsampled 120k-pt scan vs 1M-pt map, res 2.0
+        c = synth.make_case(n_source=120000, n_target=1000000, seed=synth.BASE_SEED + 4, dense=True)
     else:
         raise KeyError(name)
     _CASES[name] = c
@@ -41,6 +45,16 @@ def case_small():
 @pytest.fixture(scope="session")
 def case_c1():
     return get_case("c1")
+
+
+@pytest.fixture(scope="session")
+def case_c3():
+    return get_case("c3")
+
+
+@pytest.fixture(scope="session")
+def case_c4():
+    return get_case("c4")
 
 
 @pytest.fixture(scope="session")
