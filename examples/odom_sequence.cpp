@@ -8,7 +8,7 @@
 // the NDT calls below are the reference's own lines (odom_node.cpp:70-78, 228, 278-283, 349).
 // ROS plumbing, IMU/odometry guesses and publishers are out of scope.
 //
-//   odom_sequence <sequence.bin> <out.txt> [--res R] [--no-incremental] [--max-scans N] [--device D]
+//   odom_sequence <sequence.bin> <out.txt> [--res R] [--no-incremental] [--device-localmap] [--strict|--fast] [--threads N] [--max-scans N] [--device D]
 //
 // sequence.bin: "NDTSEQ1\0", int32 n_scans, then per scan: int32 n, double gt[6] (sensor pose
 // x y z roll pitch yaw), float xyzi[n][4] (filter_node output, sensor frame).
@@ -17,11 +17,24 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <map>
 #include <string>
 #include <vector>
 
+#ifdef ODOM_USE_REFERENCE
+// The SAME caller compiled against the reference's own pclomp::NormalDistributionsTransform
+// (/root/reference/xchu_mapping/include/pclomp/*, over the stand-in Eigen/PCL headers of oracle/ref_stubs/):
+// the CPU arm of config C2 and the trajectory oracle for the drop-in.  Test infrastructure; built as
+// examples/odom_sequence_ref only where /root/reference exists.
+#include <pcl/point_types.h>
+#include <pcl/registration/registration.h>
+#include <pclomp/ndt_omp.h>
+#include <pclomp/ndt_omp_impl.hpp>
+#include <pclomp/voxel_grid_covariance_omp_impl.hpp>
+#else
 #include "../include/pclomp/ndt_omp.h"
+#endif
 
 typedef pcl::PointXYZI PointT;
 typedef pcl::PointCloud<PointT> Cloud;
@@ -73,23 +86,44 @@ static void transformPointCloud(const Cloud& in, Cloud& out, const Eigen::Matrix
   out.width = (decltype(out.width))out.points.size();
   out.height = 1;
 }
-// pcl::VoxelGrid (centroid per occupied leaf, output in ascending leaf index): downSizeFilterLocalmap, odom_node.cpp:98, 334-335
+// downSizeFilterLocalmap (odom_node.cpp:98, 334-335): pcl::VoxelGrid<PointXYZI>, downsample_all_data_ = true -- one point
+// per occupied leaf in ascending leaf index (k, j, i), float centroids of x, y, z, intensity over the leaf's points in
+// input order, divided by float(count) (the restatement of oracle/thirdparty_math.h; PCL is not in this image).
 static void voxelDownsample(const Cloud& in, Cloud& out, float leaf) {
-  struct Acc { double x = 0, y = 0, z = 0, i = 0; int n = 0; };
-  std::map<long long, Acc> cells;
-  const float inv = 1.0f / leaf;
-  for (const PointT& p : in.points) {
-    const long long a = (long long)floorf(p.x * inv), b = (long long)floorf(p.y * inv), c = (long long)floorf(p.z * inv);
-    Acc& s = cells[((c + (1 << 20)) << 42) | ((b + (1 << 20)) << 21) | (a + (1 << 20))];
-    s.x += p.x; s.y += p.y; s.z += p.z; s.i += p.intensity; s.n++;
-  }
+  const size_t n = in.points.size();
   Cloud r;
-  r.points.reserve(cells.size());
-  for (auto& kv : cells) {
-    PointT q;
-    q.x = (float)(kv.second.x / kv.second.n); q.y = (float)(kv.second.y / kv.second.n); q.z = (float)(kv.second.z / kv.second.n);
-    q.intensity = (float)(kv.second.i / kv.second.n);
-    r.points.push_back(q);
+  if (n) {
+    const float inv = 1.0f / leaf;
+    float mn[3] = {3.402823466e38f, 3.402823466e38f, 3.402823466e38f}, mx[3] = {-3.402823466e38f, -3.402823466e38f, -3.402823466e38f};
+    for (const PointT& p : in.points) {
+      const float v[3] = {p.x, p.y, p.z};
+      for (int a = 0; a < 3; ++a) { mn[a] = v[a] < mn[a] ? v[a] : mn[a]; mx[a] = v[a] > mx[a] ? v[a] : mx[a]; }
+    }
+    int min_b[3], max_b[3];
+    for (int a = 0; a < 3; ++a) { min_b[a] = (int)floorf(mn[a] * inv); max_b[a] = (int)floorf(mx[a] * inv); }
+    const int d0 = max_b[0] - min_b[0] + 1, d1 = max_b[1] - min_b[1] + 1;
+    std::vector<std::pair<unsigned, unsigned>> iv(n);
+    for (size_t i = 0; i < n; ++i) {
+      const PointT& p = in.points[i];
+      const int a = (int)(floorf(p.x * inv) - (float)min_b[0]), b = (int)(floorf(p.y * inv) - (float)min_b[1]), c = (int)(floorf(p.z * inv) - (float)min_b[2]);
+      iv[i] = std::make_pair((unsigned)(a + b * d0 + c * d0 * d1), (unsigned)i);
+    }
+    std::stable_sort(iv.begin(), iv.end(), [](const std::pair<unsigned, unsigned>& x, const std::pair<unsigned, unsigned>& y) { return x.first < y.first; });
+    for (size_t b = 0; b < n;) {
+      size_t e = b + 1;
+      while (e < n && iv[e].first == iv[b].first) ++e;
+      const PointT& p0 = in.points[iv[b].second];
+      float c[4] = {p0.x, p0.y, p0.z, p0.intensity};
+      for (size_t q = b + 1; q < e; ++q) {
+        const PointT& p = in.points[iv[q].second];
+        c[0] += p.x; c[1] += p.y; c[2] += p.z; c[3] += p.intensity;
+      }
+      const float cnt = (float)(e - b);
+      PointT o;
+      o.x = c[0] / cnt; o.y = c[1] / cnt; o.z = c[2] / cnt; o.intensity = c[3] / cnt;
+      r.points.push_back(o);
+      b = e;
+    }
   }
   r.width = (decltype(r.width))r.points.size();
   r.height = 1;
@@ -97,18 +131,23 @@ static void voxelDownsample(const Cloud& in, Cloud& out, float leaf) {
 }
 
 int main(int argc, char** argv) {
-  if (argc < 3) { fprintf(stderr, "usage: odom_sequence <sequence.bin> <out.txt> [--res R] [--no-incremental] [--max-scans N] [--device D]\n"); return 2; }
+  if (argc < 3) { fprintf(stderr, "usage: odom_sequence <sequence.bin> <out.txt> [--res R] [--no-incremental] [--device-localmap] [--strict|--fast] [--threads N] [--max-scans N] [--device D]\n"); return 2; }
   float ndt_res = 2.0f;              // odom_node.cpp:43 default
   const double step_size = 0.1, trans_eps = 0.01, min_add_scan_shift = 0.5;   // odom_node.cpp:44-47
   const int max_iter = 30;
   double max_localmap_size = 5;      // odom_node.cpp:49
-  bool incremental = true;
-  int max_scans = 1 << 30, device = 0;
+  bool incremental = true, device_localmap = false;
+  int strict = -1;   // library default: a handle runs the term-by-term kernel
+  int max_scans = 1 << 30, device = 0, threads = 1;   // odom_node.cpp:74 runs ndt_omp with one thread
   for (int a = 3; a < argc; ++a) {
     if (!strcmp(argv[a], "--res") && a + 1 < argc) ndt_res = (float)atof(argv[++a]);
     else if (!strcmp(argv[a], "--no-incremental")) incremental = false;
+    else if (!strcmp(argv[a], "--device-localmap")) device_localmap = true;   // localmap kept in HBM (ndtb_localmap_*)
+    else if (!strcmp(argv[a], "--strict")) strict = 1;                         // term-by-term derivative kernel (the default for a handle)
+    else if (!strcmp(argv[a], "--fast")) strict = 0;                           // factorised derivative kernel
     else if (!strcmp(argv[a], "--max-scans") && a + 1 < argc) max_scans = atoi(argv[++a]);
     else if (!strcmp(argv[a], "--device") && a + 1 < argc) device = atoi(argv[++a]);
+    else if (!strcmp(argv[a], "--threads") && a + 1 < argc) threads = atoi(argv[++a]);
     else if (!strcmp(argv[a], "--submap") && a + 1 < argc) max_localmap_size = atof(argv[++a]);
   }
   FILE* f = fopen(argv[1], "rb");
@@ -121,9 +160,17 @@ int main(int argc, char** argv) {
   // ---- ParamInitial, odom_node.cpp:67-80 ---------------------------------------------------
   pclomp::NormalDistributionsTransform<PointT, PointT>::Ptr omp_ndt;
   try {
+#ifdef ODOM_USE_REFERENCE
+    (void)device;
+    pclomp::NormalDistributionsTransform<PointT, PointT>::Ptr ndt(new pclomp::NormalDistributionsTransform<PointT, PointT>());
+#else
     pclomp::NormalDistributionsTransform<PointT, PointT>::Ptr ndt(new pclomp::NormalDistributionsTransform<PointT, PointT>(device));
+#endif
+#ifndef ODOM_USE_REFERENCE
+    if (strict >= 0) ndt->setStrictMath(strict != 0);
+#endif
     ndt->setNeighborhoodSearchMethod(pclomp::DIRECT7);
-    ndt->setNumThreads(1);
+    ndt->setNumThreads(threads);
     ndt->setTransformationEpsilon(trans_eps);
     ndt->setStepSize(step_size);
     ndt->setResolution(ndt_res);
@@ -141,7 +188,7 @@ int main(int argc, char** argv) {
   Pose6D previous_pose, current_pose, diff_pose, guess_pose;
   double localmap_size = 0, shift_dis = 0;
   int initial_scan_loaded = 0, n_incremental = 0, n_target_sets = 0;
-  double total_align_ms = 0, total_target_ms = 0;
+  double total_align_ms = 0, total_target_ms = 0, total_fitness_ms = 0, total_source_ms = 0;
   const auto wall0 = std::chrono::steady_clock::now();
 
   for (int s = 0; s < n_scans; ++s) {
@@ -160,28 +207,55 @@ int main(int argc, char** argv) {
     }
     transformed_scan_ptr->clear();
     // ---- OdomEstimate, odom_node.cpp:218-231 ----------------------------------------------
+#ifndef ODOM_USE_REFERENCE
+    if (device_localmap) {   // the scan is the only cloud that crosses the bus
+      const auto ts0 = std::chrono::steady_clock::now();
+      omp_ndt->setInputSource(filtered_scan_ptr);
+      total_source_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - ts0).count();
+    }
+#endif
     if (initial_scan_loaded == 0) {
-      transformPointCloud(*filtered_scan_ptr, *transformed_scan_ptr, Pose6D2Matrix(previous_pose));
-      localmap += *transformed_scan_ptr;
-      *pc_target_ += *transformed_scan_ptr;
-      omp_ndt->setInputTarget(pc_target_);
+#ifndef ODOM_USE_REFERENCE
+      if (device_localmap) {
+        omp_ndt->localmapAppendSource(Pose6D2Matrix(previous_pose), 0.f, false);
+        omp_ndt->localmapSnapshot();
+        omp_ndt->localmapSetTarget();
+      } else
+#endif
+      {
+        transformPointCloud(*filtered_scan_ptr, *transformed_scan_ptr, Pose6D2Matrix(previous_pose));
+        localmap += *transformed_scan_ptr;
+        *pc_target_ += *transformed_scan_ptr;
+        omp_ndt->setInputTarget(pc_target_);
+      }
       initial_scan_loaded = 1;
     }
-    pc_target_.reset(new Cloud(localmap));                               // :233
+    size_t target_points = 0;
+#ifndef ODOM_USE_REFERENCE
+    if (device_localmap) { omp_ndt->localmapSnapshot(); target_points = omp_ndt->localmapSize(2); } else
+#endif
+    { pc_target_.reset(new Cloud(localmap)); target_points = pc_target_->size(); }   // :233
     guess_pose = previous_pose + diff_pose;                              // :237-239
     guess_pose.pitch = previous_pose.pitch;
     guess_pose.roll = previous_pose.roll;
     const Eigen::Matrix4f init_guess = Pose6D2Matrix(guess_pose);        // :256
     Cloud::Ptr output_cloud(new Cloud());
     const auto t0 = std::chrono::steady_clock::now();
-    omp_ndt->setInputSource(filtered_scan_ptr);                          // :278-283
-    omp_ndt->align(*output_cloud, init_guess);
+#ifndef ODOM_USE_REFERENCE
+    if (device_localmap) omp_ndt->alignNoOutput(init_guess); else
+#endif
+    {
+      omp_ndt->setInputSource(filtered_scan_ptr);                        // :278-283
+      omp_ndt->align(*output_cloud, init_guess);
+    }
+    const auto tf0 = std::chrono::steady_clock::now();
     const double fitness_score = omp_ndt->getFitnessScore();
+    total_fitness_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tf0).count();
     const Eigen::Matrix4f t_localizer = omp_ndt->getFinalTransformation();
     const bool has_converged = omp_ndt->hasConverged();
     const int final_num_iteration = omp_ndt->getFinalNumIteration();
     const auto t1 = std::chrono::steady_clock::now();
-    transformPointCloud(*filtered_scan_ptr, *transformed_scan_ptr, t_localizer);   // :290
+    if (!device_localmap) transformPointCloud(*filtered_scan_ptr, *transformed_scan_ptr, t_localizer);   // :290
     current_pose = Matrix2Pose6D(t_localizer);                           // :291-296 (tf_l2b = identity)
     diff_pose = current_pose - previous_pose;                            // :309
     shift_dis = sqrt(pow(current_pose.x - previous_pose.x, 2.0) + pow(current_pose.y - previous_pose.y, 2.0));   // :322
@@ -190,20 +264,37 @@ int main(int argc, char** argv) {
     int was_inc = -1;
     if (shift_dis >= min_add_scan_shift) {                               // :329-350
       localmap_size += shift_dis;
+      auto t2 = std::chrono::steady_clock::now();
+#ifndef ODOM_USE_REFERENCE
+      if (device_localmap) {
+        omp_ndt->localmapAppendSource(t_localizer, 1.0f, true);          // :290, 334-337 on the device
+        omp_ndt->localmapSetTarget(!incremental);                        // :349
+        was_inc = omp_ndt->lastTargetUpdateWasIncremental() ? 1 : 0;
+      } else
+#endif
+      {
       voxelDownsample(*transformed_scan_ptr, *transformed_scan_ptr, 1.0f);
       localmap += *transformed_scan_ptr;
       tmp_map += *transformed_scan_ptr;
-      const auto t2 = std::chrono::steady_clock::now();
+      t2 = std::chrono::steady_clock::now();
+#ifdef ODOM_USE_REFERENCE
+      omp_ndt->setInputTarget(pc_target_);                               // :349, full rebuild
+      was_inc = 0;
+#else
       if (incremental) omp_ndt->setInputTarget(pc_target_);             // prefix-append detection inside
       else { ndtb_set_target(omp_ndt->handle(), pc_target_->points.data(), pc_target_->points.size(), sizeof(PointT)); }
-      target_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t2).count();
       was_inc = incremental && omp_ndt->lastTargetUpdateWasIncremental() ? 1 : 0;
+#endif
+      }
+      target_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t2).count();
       n_incremental += was_inc;
       n_target_sets++;
     }
     if (localmap_size >= max_localmap_size) {                            // :352-356
-      localmap = tmp_map;
-      tmp_map.clear();
+#ifndef ODOM_USE_REFERENCE
+      if (device_localmap) omp_ndt->localmapRoll(); else
+#endif
+      { localmap = tmp_map; tmp_map.clear(); }
       localmap_size = 0.0;
     }
     const double align_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
@@ -211,11 +302,12 @@ int main(int argc, char** argv) {
     total_target_ms += target_ms;
     fprintf(out, "%d %d %d %.9g %.9f %.9f %.9f %.9f %.9f %.9f %zu %d %.4f %.4f %.6f %.6f %.6f\n", s, final_num_iteration, has_converged ? 1 : 0,
             fitness_score, current_pose.x, current_pose.y, current_pose.z, current_pose.roll, current_pose.pitch, current_pose.yaw,
-            pc_target_->size(), was_inc, align_ms, target_ms, gt[0], gt[1], gt[2]);
+            target_points, was_inc, align_ms, target_ms, gt[0], gt[1], gt[2]);
   }
   const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
-  fprintf(out, "# scans %d wall_s %.4f scans_per_s %.2f align_ms_mean %.4f target_ms_mean %.4f target_sets %d incremental %d\n", n_scans, wall,
-          n_scans / wall, total_align_ms / n_scans, n_target_sets ? total_target_ms / n_target_sets : 0.0, n_target_sets, n_incremental);
+  fprintf(out, "# scans %d wall_s %.4f scans_per_s %.2f align_ms_mean %.4f target_ms_mean %.4f target_sets %d incremental %d fitness_ms_mean %.4f source_ms_mean %.4f\n",
+          n_scans, wall, n_scans / wall, total_align_ms / n_scans, n_target_sets ? total_target_ms / n_target_sets : 0.0, n_target_sets, n_incremental,
+          total_fitness_ms / n_scans, total_source_ms / n_scans);
   fclose(out);
   fclose(f);
   return 0;

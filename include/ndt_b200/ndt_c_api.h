@@ -43,9 +43,12 @@ typedef struct ndtb_params {
   int search_method;     /* setNeighborhoodSearchMethod, NDT_H:184-186 default DIRECT7 */
   int min_points;        /* min_points_per_voxel_,    VGC_H:204       default 6    */
   double eig_mult;       /* min_covar_eigvalue_mult_, VGC_H:205       default 0.01 */
-  int strict_math;       /* 0 (default): per-point factorised derivative kernel (results within the 1e-6
-                            parity tolerance of the reference arithmetic); 1: term-by-term kernel that
-                            reproduces every float operation of NDT_I:491-548 in the reference's order */
+  int strict_math;       /* which derivative kernel runs.  1: the term-by-term kernel that reproduces every float
+                            operation of NDT_I:491-548 in the reference's order (bit-identical per-pair terms: a whole
+                            odometry sequence then replays the reference's trajectory exactly); 0: the per-point factorised
+                            kernel (3.5x faster per evaluation; score / gradient / Hessian within 1e-6 relative of the
+                            reference arithmetic); -1 (default): 1 for an ndtb_handle (single registrations are
+                            latency-bound, the strict kernel costs nothing measurable), 0 for an ndtb_batch */
   long long dense_max_cells; /* cell -> voxel lookups go through a dense int32 index over the target's bounding box
                             when that box (padded by 2 cells) holds at most this many cells, else through the
                             hash table; 0 = hash only.  default 2^26 (256 MB of index per target at most) */
@@ -117,6 +120,35 @@ int ndtb_compute_hessian(ndtb_handle* h, const float T[16], const double p[6], d
 int ndtb_get_trace(ndtb_handle* h, double* out, int max_recs, int* n);
 /* Device time (ms, CUDA events on the handle's stream) of the last set_target / update / align. */
 int ndtb_last_timing(ndtb_handle* h, double* build_ms, double* align_ms);
+
+/* ---- odom_node's localmap kept on the device ------------------
+ * What LidarOdom::OdomEstimate does to its clouds either side of align() (reference
+ * xchu_mapping/src/odom_node.cpp, ODOM below), with the clouds resident in HBM: the only per-scan
+ * host<->device traffic left is the scan itself (ndtb_set_source) and the 4x4 result.
+ *   localmap / tmp_map : pcl::PointCloud<PointXYZI> localmap, tmp_map        (ODOM members)
+ *   snapshot           : pc_target_.reset(new PointCloud(localmap))           (ODOM:233)
+ * Points carry intensity (ndtb_set_source keeps the float at byte offset 16 of 32-byte records). */
+/* localmap.clear(); tmp_map.clear(); snapshot = empty. */
+int ndtb_localmap_clear(ndtb_handle* h);
+/* transformed = T * current source (pcl::transformPointCloud, ODOM:220 / :290); when leaf > 0 it is then
+ * voxel-centroid downsampled like downSizeFilterLocalmap (pcl::VoxelGrid, leaf^3 cells, ODOM:98, 334-335);
+ * localmap += transformed (ODOM:221 / :336) and, when also_tmp != 0, tmp_map += transformed (ODOM:337).
+ * *n_added (may be NULL) = points appended. */
+int ndtb_localmap_append_source(ndtb_handle* h, const float T[16], float leaf, int also_tmp, size_t* n_added);
+/* pc_target_.reset(new PointCloud(localmap)) (ODOM:233): remembers the localmap as it is now. */
+int ndtb_localmap_snapshot(ndtb_handle* h);
+/* setInputTarget(pc_target_) (ODOM:228 / :349) with pc_target_ = the last snapshot.  Only the points the
+ * snapshot gained since the previous call are merged into the voxel table (result identical to a full
+ * rebuild); after ndtb_localmap_roll, or when `force_full` != 0, the table is rebuilt.  No host traffic. */
+int ndtb_localmap_set_target(ndtb_handle* h, int force_full, int* was_incremental);
+/* localmap = tmp_map; tmp_map.clear() (ODOM:352-356). */
+int ndtb_localmap_roll(ndtb_handle* h);
+/* sizes[0..2] = points in localmap, tmp_map, snapshot. */
+int ndtb_localmap_sizes(ndtb_handle* h, size_t sizes[3]);
+/* Copies a cloud to the host: which = 0 localmap, 1 tmp_map, 2 the cloud appended by the last
+ * ndtb_localmap_append_source.  Records of stride_bytes: x, y, z at offset 0 and, when stride_bytes >= 20,
+ * intensity at offset 16.  `cap` = records `pts` can hold; *n = records written. */
+int ndtb_localmap_download(ndtb_handle* h, int which, void* pts, size_t cap, size_t stride_bytes, size_t* n);
 
 /* ---- batched registration on one device (north_star item 4) ------------------------------
  * A batch holds targets (submaps) and sources (scans) resident in HBM and runs any number of

@@ -74,6 +74,7 @@ class NormalDistributionsTransform {
     int inc = 0;
     ck(ndtb_set_target_auto(h_, cloud->points.data(), cloud->points.size(), sizeof(PointTarget), &inc));
     last_target_incremental_ = inc != 0;
+    target_set_ = true;
   }
   // cpu::NormalDistributionsTransform::updateVoxelGrid (include/ndt_cpu/NormalDistributionsTransform.h:39)
   inline void updateVoxelGrid(const PointCloudTargetConstPtr& new_points) {
@@ -103,7 +104,7 @@ class NormalDistributionsTransform {
   // pcl::Registration::align: `output` receives the source moved by the final transformation
   inline void align(PointCloudSource& output) { align(output, Matrix4::Identity()); }
   inline void align(PointCloudSource& output, const Matrix4& guess) {
-    if (!input_ || !target_) throw std::runtime_error("pclomp(B200): align() needs setInputSource and setInputTarget");
+    if (!input_ || !target_set_) throw std::runtime_error("pclomp(B200): align() needs setInputSource and setInputTarget");
     push_search_method();
     ck(ndtb_align(h_, guess.data(), &result_));
     for (int i = 0; i < 16; ++i) final_transformation_.data()[i] = result_.T[i];
@@ -132,6 +133,31 @@ class NormalDistributionsTransform {
 
   // ---- not in the reference ---------------------------------------------------------------
   bool lastTargetUpdateWasIncremental() const { return last_target_incremental_; }
+  // align() without the copy of the moved source back to the host (odom_node never reads output_cloud, ODOM:262-279)
+  inline void alignNoOutput(const Matrix4& guess) {
+    if (!input_ || !target_set_) throw std::runtime_error("pclomp(B200): align() needs setInputSource and a target");
+    push_search_method();
+    ck(ndtb_align(h_, guess.data(), &result_));
+    for (int i = 0; i < 16; ++i) final_transformation_.data()[i] = result_.T[i];
+  }
+  // odom_node's localmap kept in HBM (ndt_c_api.h "localmap" section; reference src/odom_node.cpp:218-233, 289-290, 329-356)
+  inline void localmapClear() { ck(ndtb_localmap_clear(h_)); }
+  // localmap (+ tmp_map) += [voxel-downsampled at `leaf` if > 0] T * current source; returns the points appended
+  inline size_t localmapAppendSource(const Matrix4& T, float leaf, bool also_tmp) {
+    size_t n = 0;
+    ck(ndtb_localmap_append_source(h_, T.data(), leaf, also_tmp ? 1 : 0, &n));
+    return n;
+  }
+  inline void localmapSnapshot() { ck(ndtb_localmap_snapshot(h_)); }                 // pc_target_.reset(new Cloud(localmap))
+  inline void localmapSetTarget(bool force_full = false) {                          // setInputTarget(pc_target_)
+    push_search_method();
+    int inc = 0;
+    ck(ndtb_localmap_set_target(h_, force_full ? 1 : 0, &inc));
+    last_target_incremental_ = inc != 0;
+    target_set_ = true;
+  }
+  inline void localmapRoll() { ck(ndtb_localmap_roll(h_)); }                         // localmap = tmp_map; tmp_map.clear()
+  inline size_t localmapSize(int which = 0) { size_t s[3]; ck(ndtb_localmap_sizes(h_, s)); return s[which]; }
   void setStrictMath(bool on) { p_.strict_math = on ? 1 : 0; push(); }
   ndtb_handle* handle() { return h_; }
 
@@ -153,6 +179,7 @@ class NormalDistributionsTransform {
   PointCloudSourceConstPtr input_;
   PointCloudTargetConstPtr target_;
   bool last_target_incremental_ = false;
+  bool target_set_ = false;
 };
 
 }  // namespace pclomp

@@ -927,6 +927,14 @@ double oracle_mt_trial(double a_l, double f_l, double g_l, double a_u, double f_
 int oracle_mt_update(double* s /*a_l f_l g_l a_u f_u g_u*/, double a_t, double f_t, double g_t) {
   return Ndt::update_interval_mt(s[0], s[1], s[2], s[3], s[4], s[5], a_t, f_t, g_t) ? 1 : 0;
 }
+// pcl::VoxelGrid centroid downsample as odom_node applies it to every keyframe (ODOM:334-335); the restatement lives
+// in thirdparty_math.h.  in: n x stride floats (x y z, intensity at ioff); out: up to n x 4 floats; returns the count.
+size_t oracle_voxelgrid_downsample(const float* in, size_t n, size_t stride, size_t ioff, float leaf, float* out) {
+  std::vector<float> o;
+  voxelgrid_centroids(in, n, stride, ioff, leaf, o);
+  std::memcpy(out, o.data(), o.size() * sizeof(float));
+  return o.size() / 4;
+}
 int oracle_max_threads() {
 #ifdef _OPENMP
   return omp_get_max_threads();

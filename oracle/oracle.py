@@ -69,6 +69,8 @@ def lib():
         L.oracle_mt_trial.restype = C.c_double
         L.oracle_mt_update.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double]
         L.oracle_max_threads.restype = C.c_int
+        L.oracle_voxelgrid_downsample.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_float, C.c_void_p]
+        L.oracle_voxelgrid_downsample.restype = C.c_size_t
         _lib = L
     return _lib
 
@@ -114,6 +116,26 @@ def mt_update(state, a_t, f_t, g_t):
     s = np.ascontiguousarray(state, dtype=np.float64).copy()
     conv = lib().oracle_mt_update(_p(s), a_t, f_t, g_t)
     return bool(conv), s
+
+
+def voxelgrid_downsample(pts, leaf):
+    """pcl::VoxelGrid<PointXYZI> centroid downsample (odom_node's downSizeFilterLocalmap, ODOM:98, 334-335).
+    pts: (n, 4) float32 x y z intensity -> (m, 4), leaves in ascending index order."""
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    assert pts.ndim == 2 and pts.shape[1] == 4
+    out = np.zeros_like(pts)
+    m = lib().oracle_voxelgrid_downsample(_p(pts), pts.shape[0], 4, 3, float(leaf), _p(out))
+    return out[:m].copy()
+
+
+def transform_cloud(pts, T):
+    """pcl::transformPointCloud: x' = ((m00 x + m01 y) + m02 z) + m03 in float32, other fields copied."""
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    T = np.asarray(T, dtype=np.float32)
+    out = pts.copy()
+    for r in range(3):
+        out[:, r] = ((T[r, 0] * pts[:, 0] + T[r, 1] * pts[:, 1]) + T[r, 2] * pts[:, 2]) + T[r, 3]
+    return out
 
 
 def max_threads():

@@ -87,6 +87,12 @@ class PointCloud {
   const PointT& back() const { return points.back(); }
   PointT& operator[](size_t i) { return points[i]; }
   const PointT& operator[](size_t i) const { return points[i]; }
+  PointCloud& operator+=(const PointCloud& o) {
+    points.insert(points.end(), o.points.begin(), o.points.end());
+    width = (uint32_t)points.size();
+    height = 1;
+    return *this;
+  }
 };
 
 // neither PointXYZ nor PointXYZI carries an rgb/rgba field

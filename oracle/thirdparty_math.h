@@ -10,7 +10,9 @@
 #pragma once
 #include <algorithm>
 #include <cmath>
+#include <cstdint>
 #include <limits>
+#include <vector>
 
 namespace tpm {
 
@@ -199,4 +201,57 @@ inline void euler_012(const float T[16], float out[3]) {
   const float r2 = std::atan2(s1 * m(2, 0) - c1 * m(1, 0), c1 * m(1, 1) - s1 * m(2, 1));
   out[0] = -r0; out[1] = -r1; out[2] = -r2;
 }
+// pcl::VoxelGrid<PointXYZI>::applyFilter (PCL 1.7 filters/impl/voxel_grid.hpp) with downsample_all_data_ = true
+// (the default), as odom_node uses it for downSizeFilterLocalmap (src/odom_node.cpp:98, 334-335):
+//   min/max over the cloud; min_b = floor(min * inv_leaf), max_b likewise, inv_leaf = 1.0f / leaf;
+//   if dx*dy*dz (from (max - min) * inv_leaf + 1) overflows int32: warn and return the input unchanged;
+//   leaf index of a point: (floor(x*inv) - min_b.x) + (floor(y*inv) - min_b.y) * dx + (floor(z*inv) - min_b.z) * dx * dy;
+//   points sorted by leaf index (std::sort on the index alone; DECISION: input order among equals, i.e. a stable sort);
+//   one output point per occupied leaf in ascending index: float sums of x, y, z, intensity in that order, each divided by
+//   float(count) (DECISION: true division, Eigen >= 3.3 `/=`).
+// in: n records of `stride` floats (x y z at 0..2, intensity at `ioff`); out: packed x y z intensity.
+inline void voxelgrid_centroids(const float* in, size_t n, size_t stride, size_t ioff, float leaf, std::vector<float>& out) {
+  out.clear();
+  if (n == 0) return;
+  const float inv = 1.0f / leaf;
+  float mn[3] = {3.402823466e38f, 3.402823466e38f, 3.402823466e38f}, mx[3] = {-3.402823466e38f, -3.402823466e38f, -3.402823466e38f};
+  for (size_t i = 0; i < n; ++i)
+    for (int a = 0; a < 3; ++a) {
+      const float v = in[i * stride + a];
+      mn[a] = v < mn[a] ? v : mn[a];
+      mx[a] = v > mx[a] ? v : mx[a];
+    }
+  const int64_t dx = (int64_t)((mx[0] - mn[0]) * inv) + 1, dy = (int64_t)((mx[1] - mn[1]) * inv) + 1, dz = (int64_t)((mx[2] - mn[2]) * inv) + 1;
+  if (dx * dy * dz > (int64_t)std::numeric_limits<int32_t>::max()) {
+    for (size_t i = 0; i < n; ++i) { out.push_back(in[i * stride]); out.push_back(in[i * stride + 1]); out.push_back(in[i * stride + 2]); out.push_back(in[i * stride + ioff]); }
+    return;
+  }
+  int min_b[3], max_b[3];
+  for (int a = 0; a < 3; ++a) { min_b[a] = (int)std::floor(mn[a] * inv); max_b[a] = (int)std::floor(mx[a] * inv); }
+  const int div0 = max_b[0] - min_b[0] + 1, div1 = max_b[1] - min_b[1] + 1;
+  const int mul[3] = {1, div0, div0 * div1};
+  std::vector<std::pair<unsigned, unsigned>> iv(n);   // (leaf index, point index)
+  for (size_t i = 0; i < n; ++i) {
+    const int ijk0 = (int)(std::floor(in[i * stride] * inv) - (float)min_b[0]);
+    const int ijk1 = (int)(std::floor(in[i * stride + 1] * inv) - (float)min_b[1]);
+    const int ijk2 = (int)(std::floor(in[i * stride + 2] * inv) - (float)min_b[2]);
+    iv[i] = std::make_pair((unsigned)(ijk0 * mul[0] + ijk1 * mul[1] + ijk2 * mul[2]), (unsigned)i);
+  }
+  std::stable_sort(iv.begin(), iv.end(), [](const std::pair<unsigned, unsigned>& a, const std::pair<unsigned, unsigned>& b) { return a.first < b.first; });
+  size_t b = 0;
+  while (b < n) {
+    size_t e = b + 1;
+    while (e < n && iv[e].first == iv[b].first) ++e;
+    const float* p0 = in + (size_t)iv[b].second * stride;
+    float c[4] = {p0[0], p0[1], p0[2], p0[ioff]};
+    for (size_t q = b + 1; q < e; ++q) {
+      const float* p = in + (size_t)iv[q].second * stride;
+      c[0] += p[0]; c[1] += p[1]; c[2] += p[2]; c[3] += p[ioff];
+    }
+    const float cnt = (float)(e - b);
+    for (int a = 0; a < 4; ++a) out.push_back(c[a] / cnt);
+    b = e;
+  }
+}
+
 }  // namespace tpm

@@ -53,3 +53,51 @@ def test_odometry_sequence_tracks_ground_truth_and_refreshes_incrementally(exe, 
     # incremental voxel rebuild == full rebuild: identical tables -> identical trajectories
     assert np.array_equal(a[:, 1:3], b[:, 1:3])
     assert np.array_equal(a[:, 4:10], b[:, 4:10])
+
+
+@pytest.mark.gpu
+def test_same_caller_two_backends_same_trajectory(exe, tmp_path):
+    """Drop-in check at the caller level: examples/odom_sequence.cpp (the mirror of odom_node's loop) compiled twice --
+    against include/pclomp/ndt_omp.h (libndt_b200.so, GPU) and against the reference's own pclomp headers
+    (examples/odom_sequence_ref, CPU, over the stand-in Eigen/PCL headers) -- must produce the SAME odometry on the same
+    sequence.  A handle runs the term-by-term derivative kernel by default (strict_math -1), whose per-pair float terms
+    are the reference's bit for bit; each pose feeds the next guess and the localmap, so the trajectories can only stay
+    identical if every align is: iteration counts, convergence flags, localmap sizes and poses are required to be EQUAL,
+    fitness scores within 1e-9 relative (exact 1-NN on both sides, f64 mean).
+    The factorised kernel (--fast, 1e-6 per evaluation) is held to the north-star gate per align instead: it tracks the
+    reference within 1e-4 m / 1e-5 rad until the first voxel-membership flip of the localmap feedback loop."""
+    from xchu_slam_b200 import build, synth
+    ref_exe = build.build_example_reference()
+    if ref_exe is None:
+        pytest.skip("examples/odom_sequence_ref not built (needs /root/reference)")
+    seq = synth.write_sequence(str(tmp_path / "seq.bin"), n_scans=60, n_points=20000)
+    b, sb = _run(ref_exe, seq, str(tmp_path / "ref.txt"), "--res", "1.0", "--threads", str(os.cpu_count() or 1))
+    for flags in ([], ["--device-localmap"]):
+        a, sa = _run(exe, seq, str(tmp_path / "gpu.txt"), "--res", "1.0", *flags)
+        assert a.shape == b.shape and a.shape[0] == 60
+        assert np.array_equal(a[:, 1:3], b[:, 1:3])                       # iterations, converged
+        assert np.array_equal(a[:, 10], b[:, 10])                         # localmap sizes
+        assert np.array_equal(a[:, 4:10], b[:, 4:10])                     # poses: identical
+        assert np.max(np.abs(a[:, 3] - b[:, 3]) / b[:, 3]) < 1e-9
+    f, sf = _run(exe, seq, str(tmp_path / "fast.txt"), "--res", "1.0", "--fast")
+    same = np.flatnonzero(f[:, 10] != b[:, 10])
+    upto = int(same[0]) if len(same) else 60                              # scans before the localmaps first differ
+    assert upto >= 10
+    assert np.array_equal(f[:upto, 1:3], b[:upto, 1:3])
+    assert np.max(np.abs(f[:upto, 4:7] - b[:upto, 4:7])) < 1e-4 and np.max(np.abs(f[:upto, 7:10] - b[:upto, 7:10])) < 1e-5
+    assert np.max(np.linalg.norm(f[:, 4:6] - b[:, 4:6], axis=1)) < 0.05   # and stays a good odometry afterwards
+
+
+@pytest.mark.gpu
+def test_device_localmap_mode_gives_the_same_odometry(exe, tmp_path):
+    """--device-localmap keeps localmap / tmp_map / the pc_target_ snapshot in HBM (ndtb_localmap_*): same clouds bit for bit,
+    hence the same voxel tables and the same trajectory as the host-side localmap, with or without incremental refresh."""
+    from xchu_slam_b200 import synth
+    seq = synth.write_sequence(str(tmp_path / "seq.bin"), n_scans=40, n_points=20000)
+    a, sa = _run(exe, seq, str(tmp_path / "host.txt"), "--res", "1.0")
+    b, sb = _run(exe, seq, str(tmp_path / "dev.txt"), "--res", "1.0", "--device-localmap")
+    c, sc = _run(exe, seq, str(tmp_path / "devfull.txt"), "--res", "1.0", "--device-localmap", "--no-incremental")
+    for x, sx in ((b, sb), (c, sc)):
+        assert np.array_equal(a[:, 1:3], x[:, 1:3])          # iterations, converged
+        assert np.array_equal(a[:, 3:11], x[:, 3:11])        # fitness, pose, target size
+    assert int(sb["incremental"]) >= int(sb["target_sets"]) - 8 and int(sc["incremental"]) == 0

@@ -127,13 +127,30 @@ struct Engine {
   bool have_result = false;
   std::vector<double> h_trace;
   int h_trace_n = 0;
+  // odom_node's localmap on the device (ndtb_localmap_*): localmap, tmp_map, the cloud appended last
+  struct DevCloud { float4* p = nullptr; size_t n = 0, cap = 0; };
+  DevCloud lm, lm_tmp, lm_last;
+  float4* lm_scratch = nullptr;
+  size_t lm_scratch_cap = 0;
+  size_t lm_snapshot = 0;
+  bool lm_snapshot_valid = false;
+  unsigned long long lm_gen = 1;     // bumped whenever the localmap's contents stop being an extension of what they were
+  unsigned long long tgt_gen = 0;    // localmap generation the target's points were taken from (0: not from the localmap)
+  size_t tgt_from_lm = 0;            // leading localmap points already merged into the target
+  PinnedBuf st_src;                  // host staging of strided sources (x y z intensity packed to 16 B)
 
   int fail(const std::string& m) { err = m; return 1; }
 
   // Which derivative kernel runs.  DIRECT26 skips the point's own voxel; Newton on that objective is not
   // contractive and float-level differences between the factorised and the term-by-term arithmetic grow
   // from iterate to iterate (centimetres after ~10 iterations), so that mode always gets the strict kernel.
-  bool use_strict() const { return params.strict_math != 0 || params.search_method == NDTB_DIRECT26; }
+  // strict_math < 0 (default): a single handle (sequential odometry, latency-bound: the term-by-term kernel costs nothing
+  // measurable there and replays the reference's float arithmetic bit for bit) gets the strict kernel, a batch the
+  // factorised one.
+  bool single = false;
+  bool use_strict() const {
+    return params.strict_math > 0 || (params.strict_math < 0 && single) || params.search_method == NDTB_DIRECT26;
+  }
 
   int init(int dev) {
     device = dev;
@@ -174,6 +191,8 @@ struct Engine {
     cudaFree(d_tables); cudaFree(src_pool); cudaFree(d_states); cudaFree(d_blockmap); cudaFree(d_partials);
     cudaFree(d_trace); cudaFree(d_active); cudaFreeHost(h_active); cudaFree(d_T16); cudaFree(d_p6);
     cudaFree(d_output); cudaFree(d_d2);
+    cudaFree(lm.p); cudaFree(lm_tmp.p); cudaFree(lm_last.p); cudaFree(lm_scratch);
+    st_src.release();
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     for (auto& e : deriv_events) cudaEventDestroy(e);
     if (stream && own_stream) cudaStreamDestroy(stream);
@@ -478,7 +497,7 @@ extern "C" {
 
 void ndtb_default_params(ndtb_params* p) {
   p->resolution = 1.0f; p->step_size = 0.1; p->trans_eps = 0.1; p->max_iter = 35; p->outlier_ratio = 0.55;
-  p->search_method = NDTB_DIRECT7; p->min_points = 6; p->eig_mult = 0.01; p->strict_math = 0; p->dense_max_cells = 1ll << 26;
+  p->search_method = NDTB_DIRECT7; p->min_points = 6; p->eig_mult = 0.01; p->strict_math = -1; p->dense_max_cells = 1ll << 26;
 }
 
 static int create_engine(int device, Engine& e) { return e.init(device); }
@@ -488,6 +507,7 @@ int ndtb_create(int device, ndtb_handle** out) {
   ndtb_handle* h = new ndtb_handle();
   if (create_engine(device, h->e)) { g_create_error = h->e.err; delete h; *out = nullptr; return 1; }
   h->e.targets.resize(1);
+  h->e.single = true;
   *out = h;
   return 0;
 }
@@ -534,6 +554,7 @@ int ndtb_set_target(ndtb_handle* h, const void* pts, size_t n, size_t stride_byt
   t.use = nullptr;
   t.n = n;
   e.nn_valid = false;
+  e.tgt_gen = 0;
   t.ts.have_bbox = false;
   if (e.build_target(t)) return 1;
   cudaEventRecord(e.ev[1], e.stream);
@@ -558,6 +579,7 @@ int ndtb_update_target(ndtb_handle* h, const void* pts, size_t n, size_t stride_
   if (ce != cudaSuccess) return e.fail(std::string("table_append: ") + cudaGetErrorString(ce));
   t.n += n;
   e.nn_valid = false;
+  e.tgt_gen = 0;
   cudaEventRecord(e.ev[1], e.stream);
   if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
   float ms = 0;
@@ -595,12 +617,14 @@ int ndtb_set_target_auto(ndtb_handle* h, const void* pts, size_t n, size_t strid
       if (ce != cudaSuccess) return e.fail(std::string("table_append: ") + cudaGetErrorString(ce));
       t.n = n;
       e.nn_valid = false;
+      e.tgt_gen = 0;
     }
     if (was_incremental) *was_incremental = 1;
   } else {
     cudaMemcpyAsync(t.pts, fresh, n * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
     t.n = n;
     e.nn_valid = false;
+    e.tgt_gen = 0;
     t.ts.have_bbox = false;
     if (e.build_target(t)) return 1;
   }
@@ -618,6 +642,20 @@ int ndtb_set_source(ndtb_handle* h, const void* pts, size_t n, size_t stride_byt
   e.sources.clear();
   e.src_used = 0;
   e.have_result = false;
+  if (stride_bytes >= 20 && n > 0) {
+    // pcl::PointXYZI-like records: pack x y z intensity into the pinned staging buffer on the host (one pass over
+    // 32-byte records) and upload 16 B / point in one copy -- cheaper than a strided pageable copy, and the
+    // intensity travels in .w for the localmap entry points (no kernel of the NDT path reads .w)
+    if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");   // staging may still be in flight
+    if (e.st_src.reserve(n * sizeof(float4)) != cudaSuccess) return e.fail("pinned staging allocation failed");
+    float4* dst = static_cast<float4*>(e.st_src.h);
+    const char* src = static_cast<const char*>(pts);
+    for (size_t i = 0; i < n; ++i) {
+      const float* f = reinterpret_cast<const float*>(src + i * stride_bytes);
+      dst[i] = make_float4(f[0], f[1], f[2], f[4]);
+    }
+    return e.add_source(e.st_src.h, n, 16, 0, false, nullptr);
+  }
   return e.add_source(pts, n, stride_bytes, 0, false, nullptr);
 }
 
@@ -795,6 +833,148 @@ int ndtb_get_trace(ndtb_handle* h, double* out, int max_recs, int* n) {
 int ndtb_last_timing(ndtb_handle* h, double* build_ms, double* align_ms) {
   if (build_ms) *build_ms = h->e.last_build_ms;
   if (align_ms) *align_ms = h->e.last_align_ms;
+  return 0;
+}
+
+// ---- odom_node's localmap on the device (reference src/odom_node.cpp:218-233, 289-290, 329-356) ---------
+static int lm_reserve(Engine& e, Engine::DevCloud& c, size_t need) {
+  if (need <= c.cap) return 0;
+  const size_t nc = need + need / 2 + 4096;
+  float4* q = nullptr;
+  if (cudaMalloc(&q, nc * sizeof(float4)) != cudaSuccess) return e.fail("localmap allocation failed");
+  if (c.p && c.n) cudaMemcpyAsync(q, c.p, c.n * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  cudaFree(c.p);
+  c.p = q;
+  c.cap = nc;
+  return 0;
+}
+
+int ndtb_localmap_clear(ndtb_handle* h) {
+  Engine& e = h->e;
+  e.lm.n = e.lm_tmp.n = e.lm_last.n = 0;
+  e.lm_snapshot = 0;
+  e.lm_snapshot_valid = false;
+  ++e.lm_gen;
+  return 0;
+}
+
+int ndtb_localmap_append_source(ndtb_handle* h, const float T[16], float leaf, int also_tmp, size_t* n_added) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  if (n_added) *n_added = 0;
+  if (e.sources.empty()) return e.fail("ndtb_localmap_append_source needs a source (ndtb_set_source)");
+  const size_t n = e.sources[0].n;
+  if (n == 0) return 0;
+  if (lm_reserve(e, e.lm_last, n)) return 1;
+  if (n > e.lm_scratch_cap) {
+    cudaFree(e.lm_scratch);
+    e.lm_scratch = nullptr;
+    if (cudaMalloc(&e.lm_scratch, (n + n / 4) * sizeof(float4)) != cudaSuccess) return e.fail("alloc");
+    e.lm_scratch_cap = n + n / 4;
+  }
+  cudaMemcpyAsync(e.d_T16, T, 64, cudaMemcpyHostToDevice, e.stream);
+  const bool ds = leaf > 0.f;
+  if (launch_transform(e.source_ptr(e.sources[0]), n, e.d_T16, ds ? e.lm_scratch : e.lm_last.p, e.stream) != cudaSuccess)
+    return e.fail("transform failed");
+  ++e.stats.kernel_launches;
+  size_t m = n;
+  if (ds) {
+    cudaError_t ce = voxelgrid_downsample(e.ws, e.lm_scratch, n, leaf, e.lm_last.p, &m, e.stream, &e.stats.kernel_launches);
+    if (ce != cudaSuccess) return e.fail(std::string("voxelgrid_downsample: ") + cudaGetErrorString(ce));
+  }
+  e.lm_last.n = m;
+  if (lm_reserve(e, e.lm, e.lm.n + m)) return 1;
+  cudaMemcpyAsync(e.lm.p + e.lm.n, e.lm_last.p, m * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+  e.lm.n += m;
+  if (also_tmp) {
+    if (lm_reserve(e, e.lm_tmp, e.lm_tmp.n + m)) return 1;
+    cudaMemcpyAsync(e.lm_tmp.p + e.lm_tmp.n, e.lm_last.p, m * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+    e.lm_tmp.n += m;
+  }
+  if (n_added) *n_added = m;
+  return cudaGetLastError() == cudaSuccess ? 0 : e.fail("localmap append failed");
+}
+
+int ndtb_localmap_snapshot(ndtb_handle* h) {
+  h->e.lm_snapshot = h->e.lm.n;
+  h->e.lm_snapshot_valid = true;
+  return 0;
+}
+
+int ndtb_localmap_set_target(ndtb_handle* h, int force_full, int* was_incremental) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  if (was_incremental) *was_incremental = 0;
+  if (!e.lm_snapshot_valid) return e.fail("ndtb_localmap_set_target needs a snapshot taken after the last roll / clear");
+  Target& t = e.targets[0];
+  const size_t n = e.lm_snapshot;
+  const bool inc = !force_full && t.built && t.ts.valid && e.tgt_gen == e.lm_gen && e.tgt_from_lm <= n && t.n == e.tgt_from_lm && t.n > 0;
+  cudaEventRecord(e.ev[0], e.stream);
+  if (inc) {
+    const size_t tail = n - e.tgt_from_lm;
+    if (tail > 0) {
+      if (e.reserve_target(t, n)) return 1;
+      cudaMemcpyAsync(t.pts + t.n, e.lm.p + e.tgt_from_lm, tail * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+      e.table_config(t);
+      cudaError_t ce = table_append(t.ts, e.ws, t.pts + t.n, tail, e.stream, &e.stats.kernel_launches);
+      if (ce != cudaSuccess) return e.fail(std::string("table_append: ") + cudaGetErrorString(ce));
+      t.n = n;
+      e.nn_valid = false;
+    }
+    if (was_incremental) *was_incremental = 1;
+  } else {
+    if (e.reserve_target(t, n)) return 1;
+    t.n = 0;
+    if (n) cudaMemcpyAsync(t.pts, e.lm.p, n * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+    t.use = nullptr;
+    t.n = n;
+    e.nn_valid = false;
+    t.ts.have_bbox = false;
+    if (e.build_target(t)) return 1;
+  }
+  e.tgt_gen = e.lm_gen;
+  e.tgt_from_lm = n;
+  cudaEventRecord(e.ev[1], e.stream);
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e.ev[0], e.ev[1]);
+  e.last_build_ms = ms;
+  return 0;
+}
+
+int ndtb_localmap_roll(ndtb_handle* h) {
+  Engine& e = h->e;
+  std::swap(e.lm, e.lm_tmp);
+  e.lm_tmp.n = 0;
+  ++e.lm_gen;
+  e.lm_snapshot = 0;
+  e.lm_snapshot_valid = false;
+  return 0;
+}
+
+int ndtb_localmap_sizes(ndtb_handle* h, size_t sizes[3]) {
+  sizes[0] = h->e.lm.n; sizes[1] = h->e.lm_tmp.n; sizes[2] = h->e.lm_snapshot_valid ? h->e.lm_snapshot : 0;
+  return 0;
+}
+
+int ndtb_localmap_download(ndtb_handle* h, int which, void* pts, size_t cap, size_t stride_bytes, size_t* n) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  const Engine::DevCloud* c = which == 0 ? &e.lm : which == 1 ? &e.lm_tmp : which == 2 ? &e.lm_last : nullptr;
+  if (!c) return e.fail("which must be 0 (localmap), 1 (tmp_map) or 2 (last appended cloud)");
+  if (stride_bytes < 12) return e.fail("stride_bytes must be >= 12");
+  const size_t m = c->n < cap ? c->n : cap;
+  if (n) *n = m;
+  if (m == 0) return 0;
+  if (stride_bytes == 16) {
+    cudaMemcpyAsync(pts, c->p, m * 16, cudaMemcpyDeviceToHost, e.stream);
+  } else {
+    cudaMemcpy2DAsync(pts, stride_bytes, c->p, 16, 12, m, cudaMemcpyDeviceToHost, e.stream);
+    if (stride_bytes >= 20)
+      cudaMemcpy2DAsync(static_cast<char*>(pts) + 16, stride_bytes, reinterpret_cast<const char*>(c->p) + 12, 16, 4, m, cudaMemcpyDeviceToHost, e.stream);
+  }
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
   return 0;
 }
 

@@ -172,6 +172,10 @@ cudaError_t launch_set_int(int* dst, int v, cudaStream_t s);
 cudaError_t launch_publish(const int* src_dev, int* dst_mapped_host, cudaStream_t s);
 cudaError_t launch_prefix_equal(const float4* a, const float4* b, size_t n, int* flag, cudaStream_t s);
 
+// pcl::VoxelGrid centroid downsample (odom_node's downSizeFilterLocalmap); out needs room for n points
+cudaError_t voxelgrid_downsample(BuildWorkspace* ws, const float4* in, size_t n, float leaf, float4* out, size_t* n_out,
+                                 cudaStream_t s, long long* launches);
+
 // fitness (exact 1-NN over the raw target, grid of key-sorted points)
 struct NNGridStorage;
 NNGridStorage* nn_create();

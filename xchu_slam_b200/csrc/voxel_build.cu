@@ -547,6 +547,79 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
 
 
 // ---------------------------------------------------------------------------------------
+// pcl::VoxelGrid<PointXYZI>::applyFilter with downsample_all_data_ = true (the default), as odom_node uses it for
+// downSizeFilterLocalmap (reference src/odom_node.cpp:98, 334-335; PCL itself is not vendored -- SURVEY.md appendix B):
+// one output point per occupied leaf = the centroid of x, y, z AND intensity over the leaf's points, float sums divided
+// by float(count); output in ascending leaf index i + j*dx + k*dx*dy, i.e. ascending (k, j, i).  PCL orders the points
+// of a leaf with std::sort on the leaf index alone (unspecified among equals); here, as in the oracle, they are summed
+// in INPUT order (what a stable sort gives).  Leaf of a point: floor(x * inverse_leaf_size) - min_b, the same
+// expression the target build uses.  Overflow guard (dx*dy*dz > INT_MAX): PCL warns and returns the input unchanged.
+// in.w carries the intensity.  Blocks the stream twice (bounding box, leaf count).
+// ---------------------------------------------------------------------------------------
+__global__ void k_vg_centroid(const float4* __restrict__ pts, const unsigned int* __restrict__ sorted_idx, const int* __restrict__ run_start,
+                              int n_runs, float4* __restrict__ out) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_runs) return;
+  const int b = run_start[r], e = run_start[r + 1];
+  float4 s = pts[sorted_idx[b]];
+  for (int q = b + 1; q < e; ++q) {
+    const float4 p = pts[sorted_idx[q]];
+    s.x = __fadd_rn(s.x, p.x); s.y = __fadd_rn(s.y, p.y); s.z = __fadd_rn(s.z, p.z); s.w = __fadd_rn(s.w, p.w);
+  }
+  const float cnt = (float)(e - b);
+  out[r] = make_float4(__fdiv_rn(s.x, cnt), __fdiv_rn(s.y, cnt), __fdiv_rn(s.z, cnt), __fdiv_rn(s.w, cnt));
+}
+
+cudaError_t voxelgrid_downsample(BuildWorkspace* ws, const float4* in, size_t n, float leaf, float4* out, size_t* n_out, cudaStream_t s,
+                                 long long* launches) {
+  *n_out = 0;
+  if (n == 0) return cudaSuccess;
+  CK(ws_reserve(ws, n));
+  long long dummy = 0;
+  long long& L = launches ? *launches : dummy;
+  k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
+  k_minmax<<<148 * 2, 256, 0, s>>>(in, n, ws->mm, 1);
+  k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
+  L += 3;
+  CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  const float inv = 1.0f / leaf;     // pcl::VoxelGrid::setLeafSize
+  const float* mn = ws->h_mm;
+  const float* mx = ws->h_mm + 3;
+  const long long dx = (long long)((mx[0] - mn[0]) * inv) + 1, dy = (long long)((mx[1] - mn[1]) * inv) + 1, dz = (long long)((mx[2] - mn[2]) * inv) + 1;
+  int c0[3], c1[3];
+  bool ok = dx * dy * dz <= 2147483647ll;
+  for (int a = 0; a < 3; ++a) {
+    c0[a] = (int)floorf(mn[a] * inv);
+    c1[a] = (int)floorf(mx[a] * inv);
+    if (!coord_ok(c0[a]) || !coord_ok(c1[a]) || !(mn[a] == mn[a]) || !(mx[a] == mx[a])) ok = false;
+  }
+  if (!ok) {   // "Leaf size is too small for the input dataset. Integer indices would overflow.": output = input
+    CK(cudaMemcpyAsync(out, in, n * sizeof(float4), cudaMemcpyDeviceToDevice, s));
+    *n_out = n;
+    return cudaSuccess;
+  }
+  const int bi = bits_for((long long)c1[0] - c0[0] + 1), bj = bits_for((long long)c1[1] - c0[1] + 1), bk = bits_for((long long)c1[2] - c0[2] + 1);
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  k_keys<<<nb, 256, 0, s>>>(in, n, inv, c0[0], c0[1], c0[2], bi, bj, ws->keys_in, ws->idx_in);
+  size_t tb = ws->cub_bytes;
+  CK(cub::DeviceRadixSort::SortPairs(ws->cub_temp, tb, ws->keys_in, ws->keys_out, ws->idx_in, ws->idx_out, (int)n, 0, bi + bj + bk, s));
+  k_flags<<<nb, 256, 0, s>>>(ws->keys_out, n, ws->flags);
+  tb = ws->cub_bytes;
+  CK(cub::DeviceScan::InclusiveSum(ws->cub_temp, tb, ws->flags, ws->scan, (int)n, s));
+  k_run_starts<<<nb, 256, 0, s>>>(ws->flags, ws->scan, n, ws->run_start, ws->counts);
+  L += 5 + (bi + bj + bk + 7) / 8 + 2;
+  CK(cudaMemcpyAsync(ws->h_counts, ws->counts, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  const int n_runs = ws->h_counts[0];
+  k_vg_centroid<<<(unsigned)((n_runs + 127) / 128), 128, 0, s>>>(in, ws->idx_out, ws->run_start, n_runs, out);
+  ++L;
+  *n_out = (size_t)n_runs;
+  return cudaGetLastError();
+}
+
+
+// ---------------------------------------------------------------------------------------
 // Exact 1-NN over the raw target for pcl::Registration::getFitnessScore (K6): target points
 // sorted by cell, cell -> [start, end) in a hash table, ring search with the same stopping rule
 // as a kd-tree search would give (exact minimum of the float squared distances).

@@ -48,7 +48,9 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_neighbors",
            "ndtb_eval_derivatives", "ndtb_compute_hessian", "ndtb_get_trace", "ndtb_last_timing", "ndtb_batch_create",
            "ndtb_batch_destroy", "ndtb_batch_last_error", "ndtb_batch_set_params", "ndtb_batch_clear", "ndtb_batch_add_target",
-           "ndtb_batch_add_source", "ndtb_batch_wait_uploads", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream"]
+           "ndtb_batch_add_source", "ndtb_batch_wait_uploads", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream",
+           "ndtb_localmap_clear", "ndtb_localmap_append_source", "ndtb_localmap_snapshot", "ndtb_localmap_set_target",
+           "ndtb_localmap_roll", "ndtb_localmap_sizes", "ndtb_localmap_download"]
 
 _lib = None
 
@@ -98,6 +100,13 @@ def load_library():
     L.ndtb_batch_run.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
     L.ndtb_batch_set_stream.argtypes = [vp, vp]
+    L.ndtb_localmap_clear.argtypes = [vp]
+    L.ndtb_localmap_append_source.argtypes = [vp, vp, C.c_float, C.c_int, C.POINTER(sz)]
+    L.ndtb_localmap_snapshot.argtypes = [vp]
+    L.ndtb_localmap_set_target.argtypes = [vp, C.c_int, C.POINTER(C.c_int)]
+    L.ndtb_localmap_roll.argtypes = [vp]
+    L.ndtb_localmap_sizes.argtypes = [vp, vp]
+    L.ndtb_localmap_download.argtypes = [vp, C.c_int, vp, sz, sz, C.POINTER(sz)]
     _lib = L
     return L
 
@@ -306,6 +315,41 @@ class NormalDistributionsTransform:
         H = np.zeros((6, 6))
         self._ck(self._L.ndtb_compute_hessian(self._h, _p(Tc), _p(p), _p(H)))
         return H
+
+    # ---- odom_node's localmap on the device (reference src/odom_node.cpp:218-233, 289-290, 329-356) ----
+    def localmapClear(self):
+        self._ck(self._L.ndtb_localmap_clear(self._h))
+
+    def localmapAppendSource(self, T, leaf=0.0, also_tmp=True):
+        """localmap (+ tmp_map) += voxel-downsampled (leaf > 0) T * source.  Returns the number of points appended."""
+        n = C.c_size_t()
+        Tc = _colmajor(T)
+        self._ck(self._L.ndtb_localmap_append_source(self._h, _p(Tc), float(leaf), int(also_tmp), C.byref(n)))
+        return n.value
+
+    def localmapSnapshot(self):
+        self._ck(self._L.ndtb_localmap_snapshot(self._h))
+
+    def localmapSetTarget(self, force_full=False):
+        inc = C.c_int()
+        self._ck(self._L.ndtb_localmap_set_target(self._h, int(force_full), C.byref(inc)))
+        return bool(inc.value)
+
+    def localmapRoll(self):
+        self._ck(self._L.ndtb_localmap_roll(self._h))
+
+    def localmapSizes(self):
+        a = np.zeros(3, dtype=np.uint64)
+        self._ck(self._L.ndtb_localmap_sizes(self._h, _p(a)))
+        return tuple(int(x) for x in a)
+
+    def localmapDownload(self, which=0):
+        """which: 0 localmap, 1 tmp_map, 2 the cloud appended last.  Returns (n, 4) float32 x y z intensity."""
+        cap = max(1, self.localmapSizes()[0] if which == 0 else self.localmapSizes()[1] if which == 1 else self._n_source)
+        out = np.zeros((cap, 4), np.float32)
+        n = C.c_size_t()
+        self._ck(self._L.ndtb_localmap_download(self._h, int(which), _p(out), cap, 16, C.byref(n)))
+        return out[:n.value].copy()
 
     def lastTiming(self):
         b, a = C.c_double(), C.c_double()
