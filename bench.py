@@ -119,7 +119,7 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_sample(a, w, n_aligns):
+def cpu_sample(a, w, n_aligns, gpu_res=None):
     """Oracle (CPU restatement of ndt_omp, OpenMP on all host cores) on a bounded sample of the workload: up to
     scans*hyps registrations against each of the first submaps (each submap's grid built once, serially, as the
     reference does), n_aligns registrations in total; aligns/s = registrations / (build + align time)."""
@@ -129,6 +129,7 @@ def cpu_sample(a, w, n_aligns):
     o.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=oracle.DIRECT7, num_threads=nthreads)
     per_submap = a.scans * a.hyps
     t_build, t_align, evals, n, n_built = 0.0, 0.0, 0, 0, 0
+    par = dict(n=0, iterations_equal=0, within_gate=0, max_dt=0.0, max_dr=0.0, dt=[])
     it = np.asarray(w["item_target"])
     for sub in range(len(w["targets"])):
         if n >= n_aligns:
@@ -144,6 +145,12 @@ def cpu_sample(a, w, n_aligns):
             t_align += time.perf_counter() - t0
             evals += len(r["trace"])
             n += 1
+            if gpu_res is not None:      # the SAME registration as run on the device in the last timed step
+                Tg = np.asarray(gpu_res["T"][i], dtype=np.float32).reshape(4, 4).T
+                dt = float(np.max(np.abs(Tg[:3, 3] - r["T"][:3, 3]))); dr = float(np.max(np.abs(Tg[:3, :3] - r["T"][:3, :3])))
+                eq = int(gpu_res["iterations"][i]) == r["iterations"] and bool(gpu_res["converged"][i]) == r["converged"]
+                par["n"] += 1; par["iterations_equal"] += int(eq); par["within_gate"] += int(eq and dt < 1e-4 and dr < 1e-5)
+                par["dt"].append(dt); par["max_dt"] = max(par["max_dt"], dt); par["max_dr"] = max(par["max_dr"], dr)
     # a partly used last submap still pays its whole build: charge builds at the workload's 1 build : per_submap aligns
     total = t_align + (t_build / n_built) * (n / per_submap)
     return {"value": n / total, "unit": UNIT, "cores": nthreads, "kind": "port",
@@ -151,7 +158,13 @@ def cpu_sample(a, w, n_aligns):
                       "%.1f ms/align, %.1f evaluations/align; %.1f s of CPU wall time); oracle = dependency-free restatement of "
                       "ndt_omp, g++ -O2 -fopenmp, %d threads" % (n, n_built, t_build / n_built, per_submap, 1e3 * t_align / n,
                                                                   evals / n, t_align + t_build, nthreads),
-            "build_s": t_build / n_built, "align_ms": 1e3 * t_align / n}
+            "build_s": t_build / n_built, "align_ms": 1e3 * t_align / n,
+            "parity": None if gpu_res is None else {
+                "registrations_compared": par["n"], "iterations_and_convergence_equal": par["iterations_equal"],
+                "also_final_transform_within_1e-4m_1e-5rad": par["within_gate"],
+                "translation_diff_m": {"median": float(np.median(par["dt"])), "p99": float(np.percentile(par["dt"], 99)), "max": par["max_dt"]},
+                "note": "GPU (factorised kernel, strict_math 0) vs the CPU oracle on the same items; the registrations outside the "
+                        "gate are ones whose fixed-step Newton iteration does not settle (DESIGN.md section 5); strict_math 1 replays them too"}}
 
 
 def run_reference(a):
@@ -174,10 +187,33 @@ def run_reference(a):
         cpu_sample(a, w, 2)
     t0 = time.perf_counter()
     vals = [cpu_sample(a, w, per_step) for _ in range(a.steps)]
+    for x in vals:
+        x.pop("parity", None)
     dt = time.perf_counter() - t0
     v = float(np.mean([x["value"] for x in vals]))
-    cb = dict(vals[-1]); cb["value"] = v
-    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+    cb = dict(vals[-1]); cb["value"] = v; cb.pop("parity", None)
+    rb = None
+    try:
+        from oracle import ref
+        if ref.available():      # the reference's own NDT sources over the stand-in Eigen/PCL headers, same items, a smaller sample
+            nthreads = len(os.sched_getaffinity(0))
+            r = ref.RefNDT()
+            r.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2, num_threads=nthreads)
+            t0 = time.perf_counter(); r.set_target(w["targets"][0]); tb = time.perf_counter() - t0
+            ids = np.flatnonzero(np.asarray(w["item_target"]) == 0)[:24]
+            t0 = time.perf_counter()
+            for i in ids:
+                r.set_source(w["sources"][w["item_source"][i]])
+                r.align(w["guesses"][i])
+            ta = time.perf_counter() - t0
+            per = a.scans * a.hyps
+            rb = {"value": len(ids) / (ta + tb * len(ids) / per), "unit": UNIT, "cores": nthreads, "aligns": int(len(ids)), "build_s": tb,
+                  "align_ms": 1e3 * ta / len(ids),
+                  "note": "oracle/_ref: the reference's ndt_omp sources compiled against stand-in Eigen/PCL headers whose eager, "
+                          "unvectorised evaluation is slower than Eigen's; reported beside the (faster) port, which stays the baseline"}
+    except Exception as ex:      # the reference build is optional evidence, never a reason to fail the arm
+        rb = {"unavailable": str(ex)[:200]}
+    line = {"impl": "reference", "reference_build": rb, "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 terms, f64 accumulate",
             "data": "synthetic", "config": workload_config(a, a.gpus), "cpu_baseline": cb,
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
@@ -350,7 +386,9 @@ def main():
                 "clocks": clocks, "converged_frac": conv / len(res),
                 "mean_iterations": float(np.mean(res["iterations"]))}
         if not a.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_sample(a, w, a.cpu_aligns)
+            cb = cpu_sample(a, w, a.cpu_aligns, gpu_res=res)
+            line["parity_vs_cpu_sample"] = cb.pop("parity")
+            line["cpu_baseline"] = cb
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()

@@ -728,6 +728,17 @@ struct Ndt {
         const float lim = (float)(ring - 1) * nn.cell;
         if (best <= lim * lim) break;
       }
+      if (ring > 4) {
+        // a query far outside the target (a 60 m scan against odom_node's 5 m localmap window): walking ever larger empty
+        // shells costs ring^2 cells each; the minimum over ALL target points is the same number
+        const size_t m = target.size() / 3;
+        for (size_t i = 0; i < m; ++i) {
+          const float ex = q[0] - target[i * 3], ey = q[1] - target[i * 3 + 1], ez = q[2] - target[i * 3 + 2];
+          const float d = (ex * ex + ey * ey) + ez * ez;
+          if (d < best) best = d;
+        }
+        break;
+      }
       for (int dz = -ring; dz <= ring; ++dz)
         for (int dy = -ring; dy <= ring; ++dy)
           for (int dx = -ring; dx <= ring; ++dx) {

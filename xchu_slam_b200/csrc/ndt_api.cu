@@ -137,6 +137,7 @@ struct Engine {
   unsigned long long lm_gen = 1;     // bumped whenever the localmap's contents stop being an extension of what they were
   unsigned long long tgt_gen = 0;    // localmap generation the target's points were taken from (0: not from the localmap)
   size_t tgt_from_lm = 0;            // leading localmap points already merged into the target
+  PinnedBuf st_d2;                   // host landing zone of the per-point squared NN distances (getFitnessScore)
   PinnedBuf st_src;                  // host staging of strided sources (x y z intensity packed to 16 B)
 
   int fail(const std::string& m) { err = m; return 1; }
@@ -192,7 +193,7 @@ struct Engine {
     cudaFree(d_trace); cudaFree(d_active); cudaFreeHost(h_active); cudaFree(d_T16); cudaFree(d_p6);
     cudaFree(d_output); cudaFree(d_d2);
     cudaFree(lm.p); cudaFree(lm_tmp.p); cudaFree(lm_last.p); cudaFree(lm_scratch);
-    st_src.release();
+    st_src.release(); st_d2.release();
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     for (auto& e : deriv_events) cudaEventDestroy(e);
     if (stream && own_stream) cudaStreamDestroy(stream);
@@ -692,7 +693,11 @@ int ndtb_fitness(ndtb_handle* h, double max_range, const float* T, double* out) 
   if (!T && !e.have_result) return e.fail("no align result");
   if (!e.nn_valid) {
     const float cell = e.params.resolution > 0.25f ? e.params.resolution : 0.25f;
-    cudaError_t ce = nn_build(e.nn, e.ws, t.pts, t.n, cell, e.stream, &e.stats.kernel_launches);
+    // the voxel table already holds the float bounding box of the target's points: the NN grid build never blocks
+    float bb[6];
+    for (int a = 0; a < 3; ++a) { bb[a] = t.ts.mn[a]; bb[3 + a] = t.ts.mx[a]; }
+    cudaError_t ce = nn_build(e.nn, e.ws, t.use ? t.use : t.pts, t.n, cell, t.built && t.ts.have_bbox ? bb : nullptr, e.stream,
+                              &e.stats.kernel_launches);
     if (ce != cudaSuccess) return e.fail(std::string("nn_build: ") + cudaGetErrorString(ce));
     e.nn_valid = true;
   }
@@ -700,8 +705,9 @@ int ndtb_fitness(ndtb_handle* h, double max_range, const float* T, double* out) 
   if (n > e.d2_cap) { cudaFree(e.d_d2); e.d_d2 = nullptr; if (cudaMalloc(&e.d_d2, n * sizeof(float)) != cudaSuccess) return e.fail("alloc"); e.d2_cap = n; }
   cudaMemcpyAsync(e.d_T16, T ? T : e.last.T, 64, cudaMemcpyHostToDevice, e.stream);
   if (nn_query(e.nn, e.src_pool + e.sources[0].offset, n, e.d_T16, e.d_d2, e.stream) != cudaSuccess) return e.fail("nn_query failed");
-  std::vector<float> d(n);
-  cudaMemcpyAsync(d.data(), e.d_d2, n * sizeof(float), cudaMemcpyDeviceToHost, e.stream);
+  if (e.st_d2.reserve(n * sizeof(float)) != cudaSuccess) return e.fail("pinned staging allocation failed");
+  const float* d = static_cast<const float*>(e.st_d2.h);
+  cudaMemcpyAsync(e.st_d2.h, e.d_d2, n * sizeof(float), cudaMemcpyDeviceToHost, e.stream);
   if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
   // pcl::Registration::getFitnessScore: double accumulation in point order over d <= max_range
   double s = 0;

@@ -36,6 +36,9 @@ namespace ndtb {
 #ifndef NDTB_FAST_ACC_SMEM   // 1: the 28 FP64 accumulators of a thread live in shared memory (in the reduction layout)
 #define NDTB_FAST_ACC_SMEM 0
 #endif
+#ifndef NDTB_FAST_PREFETCH   // 1 (DIRECT7): the NEXT point's source record and its seven cell codes are fetched while this point's
+#define NDTB_FAST_PREFETCH 0  //    pairs are evaluated (two of the three dependent global loads of a point leave the critical path)
+#endif
 constexpr int kFT = NDTB_FAST_THREADS;
 constexpr int kFAcc = 28;          // score, g[6], H upper triangle [21]
 constexpr int kFCols = kFAcc + 1;  // + pair count
@@ -138,10 +141,39 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
   const int end = min(bm.y + chunk, st.n_src);
   const FastRec* __restrict__ recs = sh.tab.frec;
   const float d2f = sh.d2f, nhalf_d2f = sh.nhalf_d2f, d1d2f = sh.d1d2f;
+#if NDTB_FAST_PREFETCH
+  float4 p_nx = make_float4(0.f, 0.f, 0.f, 0.f);
+  float xt_nx = 0.f, yt_nx = 0.f, zt_nx = 0.f;
+  int v_nx[7];
+  if (METHOD == 2 && bm.y + tid < end) {
+    p_nx = __ldg(src + bm.y + tid);
+    xform(sh.T, p_nx.x, p_nx.y, p_nx.z, xt_nx, yt_nx, zt_nx);
+    neighbors7(sh.tab, xt_nx, yt_nx, zt_nx, v_nx);
+  }
+#endif
   for (int i = bm.y + tid; i < end; i += kFT) {
+#if NDTB_FAST_PREFETCH
+    float4 p;
+    float xt, yt, zt;
+    int v[7];
+    if (METHOD == 2) {
+      p = p_nx; xt = xt_nx; yt = yt_nx; zt = zt_nx;
+#pragma unroll
+      for (int o = 0; o < 7; ++o) v[o] = v_nx[o];
+      if (i + kFT < end) {
+        p_nx = __ldg(src + i + kFT);
+        xform(sh.T, p_nx.x, p_nx.y, p_nx.z, xt_nx, yt_nx, zt_nx);
+        neighbors7(sh.tab, xt_nx, yt_nx, zt_nx, v_nx);
+      }
+    } else {
+      p = __ldg(src + i);
+      xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
+    }
+#else
     const float4 p = __ldg(src + i);
     float xt, yt, zt;
     xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
+#endif
     float S = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f;
     float M00 = 0.f, M01 = 0.f, M02 = 0.f, M11 = 0.f, M12 = 0.f, M22 = 0.f;
     float B00 = 0.f, B01 = 0.f, B02 = 0.f, B11 = 0.f, B12 = 0.f, B22 = 0.f;
@@ -172,8 +204,10 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
     if (METHOD == 2) {
       // DIRECT7: the seven cells in the reference's order, fully unrolled and predicated (no compaction,
       // no local memory); the record of cell o+1 is in flight while cell o is being evaluated.
+#if !NDTB_FAST_PREFETCH
       int v[7];
       neighbors7(sh.tab, xt, yt, zt, v);
+#endif
       int cnt = 0;
 #pragma unroll
       for (int o = 0; o < 7; ++o) cnt += v[o] >= 0 ? 1 : 0;

@@ -180,8 +180,8 @@ cudaError_t voxelgrid_downsample(BuildWorkspace* ws, const float4* in, size_t n,
 struct NNGridStorage;
 NNGridStorage* nn_create();
 void nn_destroy(NNGridStorage* g);
-cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, size_t n, float cell, cudaStream_t s,
-                     long long* launches);
+cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, size_t n, float cell, const float* bbox,
+                     cudaStream_t s, long long* launches);
 cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float* T16_dev, float* d2_out,
                      cudaStream_t s);
 constexpr int kPhaseStart = 10, kPhaseEvalOnly = 11;   // AlignState::phase values used by the host

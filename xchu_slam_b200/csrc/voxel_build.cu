@@ -632,11 +632,14 @@ struct NNGridStorage {
   size_t slot_cap = 0;
   uint32_t mask = 0;
   float cell = 1.f;
+  int* far_idx = nullptr;      // queries the ring search could not settle ...
+  size_t far_cap = 0;
+  int* far_count = nullptr;    // ... and how many there are
 };
 NNGridStorage* nn_create() { return new NNGridStorage(); }
 void nn_destroy(NNGridStorage* g) {
   if (!g) return;
-  cudaFree(g->sorted); cudaFree(g->slots);
+  cudaFree(g->sorted); cudaFree(g->slots); cudaFree(g->far_idx); cudaFree(g->far_count);
   delete g;
 }
 __global__ void k_nn_keys(const float4* __restrict__ pts, size_t n, float cell, int i0, int j0, int k0, int bi, int bj,
@@ -657,10 +660,10 @@ __global__ void k_nn_fill(CellSlot* slots, size_t n) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) { CellSlot s; s.key = kEmptyKey; s.start = 0; s.end = 0; slots[i] = s; }
 }
-__global__ void k_nn_insert(const float4* __restrict__ sorted, const int* __restrict__ run_start, int n_runs, float cell,
+__global__ void k_nn_insert(const float4* __restrict__ sorted, const int* __restrict__ run_start, const int* __restrict__ n_runs_dev, float cell,
                             CellSlot* __restrict__ slots, uint32_t mask) {
   int r = blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= n_runs) return;
+  if (r >= *n_runs_dev) return;
   const float4 p = sorted[run_start[r]];
   const unsigned long long key = pack_key((int)floorf(p.x / cell), (int)floorf(p.y / cell), (int)floorf(p.z / cell));
   uint32_t h = hash_key(key) & mask;
@@ -672,7 +675,10 @@ __global__ void k_nn_insert(const float4* __restrict__ sorted, const int* __rest
   slots[h].start = run_start[r];
   slots[h].end = run_start[r + 1];
 }
-cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, size_t n, float cell, cudaStream_t s, long long* launches) {
+// bbox: the float bounding box of pts when the caller has it (min xyz, max xyz; the voxel table keeps it) -- the build
+// then never blocks the stream; nullptr: computed here (one synchronisation).
+cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, size_t n, float cell, const float* bbox, cudaStream_t s,
+                     long long* launches) {
   long long dummy = 0;
   long long& L = launches ? *launches : dummy;
   g->n = n;
@@ -682,17 +688,24 @@ cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, si
   if (n > g->pts_cap) {
     cudaFree(g->sorted);
     g->sorted = nullptr;
-    CK(cudaMalloc(&g->sorted, (n + n / 4) * sizeof(float4)));
-    g->pts_cap = n + n / 4;
+    CK(cudaMalloc(&g->sorted, (n + n / 2) * sizeof(float4)));
+    g->pts_cap = n + n / 2;
   }
-  k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
-  k_minmax<<<148 * 8, 256, 0, s>>>(pts, n, ws->mm, 1);
-  k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
-  CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
-  CK(cudaStreamSynchronize(s));
+  float bb[6];
+  if (bbox) {
+    for (int a = 0; a < 6; ++a) bb[a] = bbox[a];
+  } else {
+    k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
+    k_minmax<<<148 * 8, 256, 0, s>>>(pts, n, ws->mm, 1);
+    k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
+    L += 3;
+    CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    for (int a = 0; a < 6; ++a) bb[a] = ws->h_mm[a];
+  }
   int c0[3], c1[3];
   for (int a = 0; a < 3; ++a) {
-    c0[a] = (int)floorf(ws->h_mm[a] / cell); c1[a] = (int)floorf(ws->h_mm[3 + a] / cell);
+    c0[a] = (int)floorf(bb[a] / cell); c1[a] = (int)floorf(bb[3 + a] / cell);
     if (!coord_ok(c0[a]) || !coord_ok(c1[a])) return cudaErrorInvalidValue;
   }
   const int bi = bits_for((long long)c1[0] - c0[0] + 1), bj = bits_for((long long)c1[1] - c0[1] + 1), bk = bits_for((long long)c1[2] - c0[2] + 1);
@@ -705,26 +718,28 @@ cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, si
   tb = ws->cub_bytes;
   CK(cub::DeviceScan::InclusiveSum(ws->cub_temp, tb, ws->flags, ws->scan, (int)n, s));
   k_run_starts<<<nb, 256, 0, s>>>(ws->flags, ws->scan, n, ws->run_start, ws->counts);
-  CK(cudaMemcpyAsync(ws->h_counts, ws->counts, sizeof(int), cudaMemcpyDeviceToHost, s));
-  CK(cudaStreamSynchronize(s));
-  const int n_runs = ws->h_counts[0];
+  // occupied cells <= points: a table of >= 2n slots keeps the load factor <= 0.5 without asking the device how many there are
   size_t want = 1024;
-  while (want < (size_t)n_runs * 4) want <<= 1;
+  while (want < n * 2) want <<= 1;
   if (want > g->slot_cap) {
     cudaFree(g->slots);
     g->slots = nullptr;
     CK(cudaMalloc(&g->slots, want * sizeof(CellSlot)));
     g->slot_cap = want;
   }
-  g->mask = (uint32_t)(g->slot_cap - 1);
-  k_nn_fill<<<(unsigned)((g->slot_cap + 255) / 256), 256, 0, s>>>(g->slots, g->slot_cap);
-  k_nn_insert<<<(n_runs + 127) / 128, 128, 0, s>>>(g->sorted, ws->run_start, n_runs, cell, g->slots, g->mask);
-  L += 11 + (bi + bj + bk + 7) / 8;
+  g->mask = (uint32_t)(want - 1);
+  k_nn_fill<<<(unsigned)((want + 255) / 256), 256, 0, s>>>(g->slots, want);
+  k_nn_insert<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(g->sorted, ws->run_start, ws->counts, cell, g->slots, g->mask);
+  L += 8 + (bi + bj + bk + 7) / 8;
   return cudaGetLastError();
 }
 
+// Ring search over the cell grid.  A query is settled once its best squared distance is <= ((ring-1)*cell)^2, the least
+// any point of a farther ring can be away.  Queries still open after `max_ring` rings (the scan reaches far beyond a
+// small localmap) go to k_nn_far instead of walking ever larger, empty shells.
 __global__ void k_nn_query(const float4* __restrict__ sorted, size_t n_tgt, const CellSlot* __restrict__ slots, uint32_t mask, float cell,
-                           const float4* __restrict__ src, size_t n, const float* __restrict__ T16, float* __restrict__ d2_out) {
+                           const float4* __restrict__ src, size_t n, const float* __restrict__ T16, int max_ring, float* __restrict__ d2_out,
+                           int* __restrict__ far_idx, int* __restrict__ far_count) {
   size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float4 p = src[i];
@@ -735,11 +750,12 @@ __global__ void k_nn_query(const float4* __restrict__ sorted, size_t n_tgt, cons
   const int ci = (int)floorf(qx / cell), cj = (int)floorf(qy / cell), ck = (int)floorf(qz / cell);
   float best = FLT_MAX;
   bool certain = false;
-  for (int ring = 0; ring <= 8; ++ring) {
+  for (int ring = 0; ring <= max_ring + 1; ++ring) {
     if (ring >= 1) {
       const float lim = (float)(ring - 1) * cell;   // every point in rings >= `ring` is at least this far
       if (best <= lim * lim) { certain = true; break; }
     }
+    if (ring > max_ring) break;
     for (int dz = -ring; dz <= ring; ++dz)
       for (int dy = -ring; dy <= ring; ++dy)
         for (int dx = -ring; dx <= ring; ++dx) {
@@ -763,22 +779,68 @@ __global__ void k_nn_query(const float4* __restrict__ sorted, size_t n_tgt, cons
           }
         }
   }
-  if (!certain) {
-    const float lim = 8.f * cell;
-    if (!(best <= lim * lim)) {   // far-away query: exhaustive scan (rare)
-      for (size_t t = 0; t < n_tgt; ++t) {
-        const float4 tp = sorted[t];
-        const float ex = qx - tp.x, ey = qy - tp.y, ez = qz - tp.z;
-        const float d = (ex * ex + ey * ey) + ez * ez;
-        if (d < best) best = d;
-      }
+  d2_out[i] = best;
+  if (!certain) far_idx[atomicAdd(far_count, 1)] = (int)i;
+}
+// The open queries against EVERY target point: one thread per query, the target streamed through shared memory in
+// tiles (the minimum of the same float expression, so the result is the exact 1-NN distance whatever the order).
+constexpr int kFarThreads = 128, kFarTile = 1024;
+__global__ void __launch_bounds__(kFarThreads)
+k_nn_far(const float4* __restrict__ sorted, size_t n_tgt, const float4* __restrict__ src, const float* __restrict__ T16,
+         const int* __restrict__ far_idx, const int* __restrict__ far_count, float* __restrict__ d2_out) {
+  __shared__ float4 tile[kFarTile];
+  const int n_far = *far_count;
+  if ((int)(blockIdx.x * kFarThreads) >= n_far) return;
+  const int f = blockIdx.x * kFarThreads + threadIdx.x;
+  const bool live = f < n_far;
+  const int i = live ? far_idx[f] : 0;
+  float qx = 0.f, qy = 0.f, qz = 0.f;
+  if (live) {
+    const float4 p = src[i];
+    qx = ((T16[0] * p.x + T16[4] * p.y) + T16[8] * p.z) + T16[12];
+    qy = ((T16[1] * p.x + T16[5] * p.y) + T16[9] * p.z) + T16[13];
+    qz = ((T16[2] * p.x + T16[6] * p.y) + T16[10] * p.z) + T16[14];
+  }
+  float best = FLT_MAX;
+  // blockIdx.y takes one slice of the target, so that no thread walks the whole of it
+  const size_t slice = (n_tgt + gridDim.y - 1) / gridDim.y;
+  const size_t lo = (size_t)blockIdx.y * slice, hi = min(n_tgt, lo + slice);
+  for (size_t base = lo; base < hi; base += kFarTile) {
+    const int m = (int)min((size_t)kFarTile, hi - base);
+    __syncthreads();
+    for (int t = threadIdx.x; t < m; t += kFarThreads) tile[t] = sorted[base + t];
+    __syncthreads();
+#pragma unroll 8
+    for (int t = 0; t < m; ++t) {
+      const float4 tp = tile[t];
+      const float ex = qx - tp.x, ey = qy - tp.y, ez = qz - tp.z;
+      const float d = (ex * ex + ey * ey) + ez * ez;
+      best = fminf(best, d);
     }
   }
-  d2_out[i] = best;
+  // squared distances are >= 0: their bit patterns order like the floats, so the slices combine with an integer atomicMin
+  // (the entry already holds the ring search's best, itself a distance to a real target point)
+  if (live) atomicMin(reinterpret_cast<int*>(d2_out) + i, __float_as_int(best));
 }
 cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float* T16_dev, float* d2_out, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
-  k_nn_query<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(g->sorted, g->n, g->slots, g->mask, g->cell, src, n, T16_dev, d2_out);
+  if (n > g->far_cap) {
+    cudaFree(g->far_idx);
+    g->far_idx = nullptr;
+    CK(cudaMalloc(&g->far_idx, (n + n / 4) * sizeof(int)));
+    g->far_cap = n + n / 4;
+  }
+  if (!g->far_count) CK(cudaMalloc(&g->far_count, sizeof(int)));
+  CK(cudaMemsetAsync(g->far_count, 0, sizeof(int), s));
+  // small target: hand a query to the exhaustive pass early (its cost is n_far * n_tgt); large target: keep walking rings
+  const int max_ring = g->n <= (size_t)1 << 17 ? 2 : 8;
+  k_nn_query<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(g->sorted, g->n, g->slots, g->mask, g->cell, src, n, T16_dev, max_ring, d2_out,
+                                                         g->far_idx, g->far_count);
+  unsigned slices = (unsigned)((g->n + 2047) / 2048);
+  if (slices > 64) slices = 64;
+  if (slices < 1) slices = 1;
+  k_nn_far<<<dim3((unsigned)((n + kFarThreads - 1) / kFarThreads), slices), kFarThreads, 0, s>>>(g->sorted, g->n, src, T16_dev, g->far_idx,
+                                                                                                 g->far_count, d2_out);
   return cudaGetLastError();
 }
 
