@@ -243,6 +243,20 @@ def main():
 
     from xchu_slam_b200 import ndt
     w = get_workload(a, rank, barrier)
+    order = os.environ.get("NDT_BENCH_SOURCE_ORDER", "")     # experiment: point order inside each scan (results are order-independent)
+    if order:
+        def reorder(s):
+            if order == "random":
+                return s[np.random.default_rng(1).permutation(s.shape[0])]
+            cell = float(order.split(":")[1]) if ":" in order else 1.0
+            c = np.floor(s[:, :3] / cell).astype(np.int64)
+            c -= c.min(0)
+            key = np.zeros(len(c), np.int64)
+            for b in range(10):                                  # Morton code of the cell
+                for ax in range(3):
+                    key |= ((c[:, ax] >> b) & 1) << (3 * b + ax)
+            return np.ascontiguousarray(s[np.argsort(key, kind="stable")])
+        w["sources"] = [reorder(s) for s in w["sources"]]
     n_items = len(w["item_target"])
     dev = torch.device("cuda", local)
 

@@ -150,6 +150,24 @@ int ndtb_localmap_sizes(ndtb_handle* h, size_t sizes[3]);
  * intensity at offset 16.  `cap` = records `pts` can hold; *n = records written. */
 int ndtb_localmap_download(ndtb_handle* h, int which, void* pts, size_t cap, size_t stride_bytes, size_t* n);
 
+/* ---- filter_node's front end on the device ---------------------
+ * What CloudFilter::PcCB does to a raw scan before odom_node sees it (reference xchu_mapping/src/filter_node.cpp:236-262):
+ * pcl::removeNaNFromPointCloud, the range gate r_min < sqrt(x^2 + y^2) < r_max (:242-247), downSizeFilterKeyFrames
+ * (pcl::VoxelGrid, leaf 0.5 m, :33-34, 249-251) and pcl::StatisticalOutlierRemoval (mean_k 30, stddev_mul 1.0, :254-262).
+ * The filtered scan becomes the handle's source (as if passed to ndtb_set_source) and stays in HBM. */
+typedef struct ndtb_filter_params {
+  double r_min, r_max;   /* 1.0, 60.0 */
+  float leaf;            /* 0.5; <= 0 skips the downsample */
+  int mean_k;            /* 30; <= 0 skips the outlier removal; at most 63 */
+  double stddev_mul;     /* 1.0 */
+} ndtb_filter_params;
+void ndtb_default_filter_params(ndtb_filter_params* p);
+/* pts: n raw records (x y z at offset 0; intensity at byte offset 16 when stride_bytes >= 20, else the 4th float of
+ * 16-byte records).  counts[0..2] (may be NULL) = points after the gate, after the downsample, after the outlier removal. */
+int ndtb_filter_scan(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes, const ndtb_filter_params* p, size_t counts[3]);
+/* Copies the handle's current source to the host (records as in ndtb_localmap_download). */
+int ndtb_get_source(ndtb_handle* h, void* pts, size_t cap, size_t stride_bytes, size_t* n);
+
 /* ---- batched registration on one device (north_star item 4) ------------------------------
  * A batch holds targets (submaps) and sources (scans) resident in HBM and runs any number of
  * independent registrations {target id, source id, initial guess} concurrently; no collective

@@ -946,6 +946,27 @@ size_t oracle_voxelgrid_downsample(const float* in, size_t n, size_t stride, siz
   std::memcpy(out, o.data(), o.size() * sizeof(float));
   return o.size() / 4;
 }
+// filter_node's front end (src/filter_node.cpp:236-273): NaN removal + range gate, 0.5 m pcl::VoxelGrid, statistical outlier
+// removal -- the restatements of thirdparty_math.h chained.  in: n x 4 floats (x y z intensity); out: up to n x 4;
+// counts[0..2] = points after the gate, after the downsample, after the outlier removal; dist (may be null): the per-point
+// mean neighbour distances of the downsampled cloud.  Returns counts[2].
+size_t oracle_filter_scan(const float* in, size_t n, double r_min, double r_max, float leaf, int mean_k, double std_mul, float* out,
+                          size_t* counts, float* dist) {
+  std::vector<uint32_t> keep;
+  range_gate(in, n, 4, r_min, r_max, keep);
+  std::vector<float> gated(keep.size() * 4);
+  for (size_t i = 0; i < keep.size(); ++i) std::memcpy(&gated[i * 4], in + (size_t)keep[i] * 4, 16);
+  counts[0] = keep.size();
+  std::vector<float> ds;
+  voxelgrid_centroids(gated.data(), keep.size(), 4, 3, leaf, ds);
+  counts[1] = ds.size() / 4;
+  std::vector<float> d;
+  sor_filter(ds.data(), ds.size() / 4, 4, mean_k, std_mul, keep, &d);
+  if (dist && !d.empty()) std::memcpy(dist, d.data(), d.size() * sizeof(float));
+  for (size_t i = 0; i < keep.size(); ++i) std::memcpy(out + i * 4, &ds[(size_t)keep[i] * 4], 16);
+  counts[2] = keep.size();
+  return keep.size();
+}
 int oracle_max_threads() {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -71,6 +71,9 @@ def lib():
         L.oracle_max_threads.restype = C.c_int
         L.oracle_voxelgrid_downsample.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_float, C.c_void_p]
         L.oracle_voxelgrid_downsample.restype = C.c_size_t
+        L.oracle_filter_scan.argtypes = [C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_float, C.c_int, C.c_double, C.c_void_p,
+                                         C.c_void_p, C.c_void_p]
+        L.oracle_filter_scan.restype = C.c_size_t
         _lib = L
     return _lib
 
@@ -126,6 +129,18 @@ def voxelgrid_downsample(pts, leaf):
     out = np.zeros_like(pts)
     m = lib().oracle_voxelgrid_downsample(_p(pts), pts.shape[0], 4, 3, float(leaf), _p(out))
     return out[:m].copy()
+
+
+def filter_scan(pts, r_min=1.0, r_max=60.0, leaf=0.5, mean_k=30, std_mul=1.0):
+    """filter_node's front end (reference src/filter_node.cpp:236-273): NaN removal, range gate, pcl::VoxelGrid, statistical
+    outlier removal.  pts (n, 4) float32 -> dict(cloud (m, 4), counts (after gate, after downsample, after SOR), distances)."""
+    pts = np.ascontiguousarray(pts, dtype=np.float32)
+    assert pts.ndim == 2 and pts.shape[1] == 4
+    out = np.zeros_like(pts)
+    counts = np.zeros(3, dtype=np.uint64)
+    dist = np.zeros(pts.shape[0], dtype=np.float32)
+    m = lib().oracle_filter_scan(_p(pts), pts.shape[0], r_min, r_max, leaf, mean_k, std_mul, _p(out), _p(counts), _p(dist))
+    return dict(cloud=out[:m].copy(), counts=tuple(int(c) for c in counts), distances=dist[:int(counts[1])].copy())
 
 
 def transform_cloud(pts, T):

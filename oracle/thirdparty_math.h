@@ -254,4 +254,73 @@ inline void voxelgrid_centroids(const float* in, size_t n, size_t stride, size_t
   }
 }
 
+// ---- filter_node front end (reference src/filter_node.cpp:236-273) --------------------------------------------------
+// pcl::removeNaNFromPointCloud + the range gate of filter_node.cpp:242-247:
+//   r = std::sqrt(pow(point.x, 2.0) + pow(point.y, 2.0)) in double; keep iff 1.0 < r && r < 60 (bounds passed in).
+inline void range_gate(const float* in, size_t n, size_t stride, double r_min, double r_max, std::vector<uint32_t>& keep) {
+  keep.clear();
+  for (size_t i = 0; i < n; ++i) {
+    const float x = in[i * stride], y = in[i * stride + 1], z = in[i * stride + 2];
+    if (!std::isfinite(x) || !std::isfinite(y) || !std::isfinite(z)) continue;
+    const double r = std::sqrt((double)x * (double)x + (double)y * (double)y);
+    if (r_min < r && r < r_max) keep.push_back((uint32_t)i);
+  }
+}
+// pcl::StatisticalOutlierRemoval<PointXYZI>::applyFilterIndices (PCL 1.7 filters/impl/statistical_outlier_removal.hpp),
+// setMeanK(mean_k), setStddevMulThresh(std_mul), negative_ = false (filter_node.cpp:254-262):
+//   per point: the mean_k + 1 nearest neighbours (the point itself is neighbour 0), squared float distances
+//   ((dx^2 + dy^2) + dz^2) ascending; dist_sum (double) += sqrt(nn_dists[k]) for k = 1..mean_k
+//   (DECISION: the unqualified sqrt binds ::sqrt(double), like the exp of NDT_I:507); distances[i] = float(dist_sum / mean_k);
+//   sum += distances[i]; sq_sum += distances[i] * distances[i] (a FLOAT product added to a double), in point order;
+//   mean = sum / n; variance = (sq_sum - sum * sum / n) / (n - 1); threshold = mean + std_mul * sqrt(variance);
+//   a point is removed iff distances[i] > threshold.
+// DECISION: a cloud with fewer than mean_k + 1 points is returned unchanged (PCL reads stale distances there).
+// xyz: n records of `stride` floats.  Exact k-NN by exhaustive search (test sizes only).
+inline void sor_mean_distances(const float* xyz, size_t n, size_t stride, int mean_k, std::vector<float>& distances) {
+  distances.assign(n, 0.f);
+  if (n < (size_t)mean_k + 1) return;
+  const long nn = (long)n;
+#pragma omp parallel
+  {
+    std::vector<float> d2(n);
+#pragma omp for schedule(static)
+    for (long i = 0; i < nn; ++i) {
+      const float qx = xyz[i * stride], qy = xyz[i * stride + 1], qz = xyz[i * stride + 2];
+      for (size_t j = 0; j < n; ++j) {
+        const float ex = qx - xyz[j * stride], ey = qy - xyz[j * stride + 1], ez = qz - xyz[j * stride + 2];
+        d2[j] = (ex * ex + ey * ey) + ez * ez;
+      }
+      std::partial_sort(d2.begin(), d2.begin() + mean_k + 1, d2.end());
+      double dist_sum = 0.0;
+      for (int k = 1; k < mean_k + 1; ++k) dist_sum += std::sqrt((double)d2[k]);
+      distances[i] = (float)(dist_sum / mean_k);
+    }
+  }
+}
+inline double sor_threshold(const std::vector<float>& distances, double std_mul) {
+  double sum = 0, sq_sum = 0;
+  for (size_t i = 0; i < distances.size(); ++i) {
+    sum += distances[i];
+    sq_sum += distances[i] * distances[i];
+  }
+  const double nv = (double)distances.size();
+  const double mean = sum / nv;
+  const double variance = (sq_sum - sum * sum / nv) / (nv - 1);
+  return mean + std_mul * std::sqrt(variance);
+}
+inline void sor_filter(const float* xyz, size_t n, size_t stride, int mean_k, double std_mul, std::vector<uint32_t>& keep,
+                       std::vector<float>* distances_out = nullptr) {
+  keep.clear();
+  if (n < (size_t)mean_k + 1) {
+    for (size_t i = 0; i < n; ++i) keep.push_back((uint32_t)i);
+    return;
+  }
+  std::vector<float> dist;
+  sor_mean_distances(xyz, n, stride, mean_k, dist);
+  const double thr = sor_threshold(dist, std_mul);
+  for (size_t i = 0; i < n; ++i)
+    if (!(dist[i] > thr)) keep.push_back((uint32_t)i);
+  if (distances_out) *distances_out = dist;
+}
+
 }  // namespace tpm

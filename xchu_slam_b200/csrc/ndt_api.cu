@@ -137,6 +137,9 @@ struct Engine {
   unsigned long long lm_gen = 1;     // bumped whenever the localmap's contents stop being an extension of what they were
   unsigned long long tgt_gen = 0;    // localmap generation the target's points were taken from (0: not from the localmap)
   size_t tgt_from_lm = 0;            // leading localmap points already merged into the target
+  FilterWorkspace* flt = nullptr;    // filter_node front end (ndtb_filter_scan)
+  float4* flt_raw = nullptr;
+  size_t flt_raw_cap = 0;
   PinnedBuf st_d2;                   // host landing zone of the per-point squared NN distances (getFitnessScore)
   PinnedBuf st_src;                  // host staging of strided sources (x y z intensity packed to 16 B)
 
@@ -194,6 +197,7 @@ struct Engine {
     cudaFree(d_output); cudaFree(d_d2);
     cudaFree(lm.p); cudaFree(lm_tmp.p); cudaFree(lm_last.p); cudaFree(lm_scratch);
     st_src.release(); st_d2.release();
+    filter_ws_destroy(flt); cudaFree(flt_raw);
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     for (auto& e : deriv_events) cudaEventDestroy(e);
     if (stream && own_stream) cudaStreamDestroy(stream);
@@ -980,6 +984,61 @@ int ndtb_localmap_download(ndtb_handle* h, int which, void* pts, size_t cap, siz
     if (stride_bytes >= 20)
       cudaMemcpy2DAsync(static_cast<char*>(pts) + 16, stride_bytes, reinterpret_cast<const char*>(c->p) + 12, 16, 4, m, cudaMemcpyDeviceToHost, e.stream);
   }
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  return 0;
+}
+
+// ---- filter_node's front end (reference src/filter_node.cpp:236-262) -----------------------------------
+void ndtb_default_filter_params(ndtb_filter_params* p) { p->r_min = 1.0; p->r_max = 60.0; p->leaf = 0.5f; p->mean_k = 30; p->stddev_mul = 1.0; }
+
+static void copy_cloud_to_host(Engine& e, const float4* d, size_t m, void* pts, size_t stride_bytes) {
+  if (stride_bytes == 16) {
+    cudaMemcpyAsync(pts, d, m * 16, cudaMemcpyDeviceToHost, e.stream);
+  } else {
+    cudaMemcpy2DAsync(pts, stride_bytes, d, 16, 12, m, cudaMemcpyDeviceToHost, e.stream);
+    if (stride_bytes >= 20)
+      cudaMemcpy2DAsync(static_cast<char*>(pts) + 16, stride_bytes, reinterpret_cast<const char*>(d) + 12, 16, 4, m, cudaMemcpyDeviceToHost, e.stream);
+  }
+}
+
+int ndtb_filter_scan(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes, const ndtb_filter_params* p, size_t counts[3]) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  ndtb_filter_params fp;
+  if (p) fp = *p; else ndtb_default_filter_params(&fp);
+  if (fp.mean_k > 63) return e.fail("mean_k must be <= 63");
+  size_t c[3] = {0, 0, 0};
+  // the raw scan goes through the same upload path as a source, then is filtered in place of it
+  if (ndtb_set_source(h, pts, n, stride_bytes)) return 1;
+  if (n > 0) {
+    if (!e.flt) { e.flt = filter_ws_create(); if (!e.flt) return e.fail("filter workspace allocation failed"); }
+    if (n > e.flt_raw_cap) {
+      cudaFree(e.flt_raw);
+      e.flt_raw = nullptr;
+      if (cudaMalloc(&e.flt_raw, (n + n / 4) * sizeof(float4)) != cudaSuccess) return e.fail("alloc");
+      e.flt_raw_cap = n + n / 4;
+    }
+    float4* src = e.src_pool + e.sources[0].offset;
+    cudaMemcpyAsync(e.flt_raw, src, n * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+    cudaError_t ce = filter_scan(e.flt, e.ws, e.flt_raw, n, fp.r_min, fp.r_max, fp.leaf, fp.mean_k, fp.stddev_mul, src, c, e.stream,
+                                 &e.stats.kernel_launches);
+    if (ce != cudaSuccess) return e.fail(std::string("filter_scan: ") + cudaGetErrorString(ce));
+    e.sources[0].n = c[2];
+    e.src_used = c[2];
+  }
+  if (counts) { counts[0] = c[0]; counts[1] = c[1]; counts[2] = c[2]; }
+  return 0;
+}
+
+int ndtb_get_source(ndtb_handle* h, void* pts, size_t cap, size_t stride_bytes, size_t* n) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  if (e.sources.empty()) return e.fail("no source");
+  if (stride_bytes < 12) return e.fail("stride_bytes must be >= 12");
+  const size_t m = e.sources[0].n < cap ? e.sources[0].n : cap;
+  if (n) *n = m;
+  if (m == 0) return 0;
+  copy_cloud_to_host(e, e.source_ptr(e.sources[0]), m, pts, stride_bytes);
   if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
   return 0;
 }

@@ -176,6 +176,13 @@ cudaError_t launch_prefix_equal(const float4* a, const float4* b, size_t n, int*
 cudaError_t voxelgrid_downsample(BuildWorkspace* ws, const float4* in, size_t n, float leaf, float4* out, size_t* n_out,
                                  cudaStream_t s, long long* launches);
 
+// filter_node's front end (range gate, pcl::VoxelGrid, pcl::StatisticalOutlierRemoval) on device records
+struct FilterWorkspace;
+FilterWorkspace* filter_ws_create();
+void filter_ws_destroy(FilterWorkspace* f);
+cudaError_t filter_scan(FilterWorkspace* f, BuildWorkspace* ws, const float4* raw, size_t n, double r_min, double r_max, float leaf,
+                        int mean_k, double std_mul, float4* out, size_t counts[3], cudaStream_t s, long long* launches);
+
 // fitness (exact 1-NN over the raw target, grid of key-sorted points)
 struct NNGridStorage;
 NNGridStorage* nn_create();

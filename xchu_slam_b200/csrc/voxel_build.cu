@@ -844,4 +844,222 @@ cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float*
   return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------
+// filter_node's front end on the device (reference src/filter_node.cpp:236-273):
+// pcl::removeNaNFromPointCloud + range gate 1 < r_xy < 60 (:236-247), pcl::VoxelGrid 0.5 m (:249-251, the kernels of
+// voxelgrid_downsample above), pcl::StatisticalOutlierRemoval k = 30, 1 sigma (:254-262).  The third-party pieces are
+// restated in oracle/thirdparty_math.h; everything here is float / double arithmetic in that order, so the result
+// is the same cloud bit for bit.
+// ---------------------------------------------------------------------------------------
+__global__ void k_gate_flags(const float4* __restrict__ pts, size_t n, double r_min, double r_max, int* __restrict__ flags) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 p = pts[i];
+  const bool finite = isfinite(p.x) && isfinite(p.y) && isfinite(p.z);
+  const double r = sqrt((double)p.x * (double)p.x + (double)p.y * (double)p.y);   // std::sqrt(pow(x, 2.0) + pow(y, 2.0))
+  flags[i] = (finite && r_min < r && r < r_max) ? 1 : 0;
+}
+__global__ void k_sor_flags(const float* __restrict__ dist, size_t n, double threshold, int* __restrict__ flags) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) flags[i] = ((double)dist[i] > threshold) ? 0 : 1;
+}
+
+constexpr int kKnnMax = 64;   // mean_k + 1 <= kKnnMax
+// ascending array of the k smallest squared distances seen so far
+__device__ __forceinline__ void knn_insert(float* best, int& cnt, int k, float d) {
+  if (cnt == k && !(d < best[k - 1])) return;
+  int pos = cnt < k ? cnt : k - 1;
+  while (pos > 0 && best[pos - 1] > d) { best[pos] = best[pos - 1]; --pos; }
+  best[pos] = d;
+  if (cnt < k) ++cnt;
+}
+// dist_sum (double) += sqrt(nn_dists[k]), k = 1..mean_k; distances[i] = float(dist_sum / mean_k)
+__device__ __forceinline__ float knn_mean(const float* best, int mean_k) {
+  double s = 0.0;
+  for (int k = 1; k < mean_k + 1; ++k) s += sqrt((double)best[k]);
+  return (float)(s / (double)mean_k);
+}
+// One thread per point of the cloud (original order); neighbours are searched in the cell-sorted copy.  Settled once the
+// k-th best is <= ((ring-1)*cell)^2; points still open after max_ring rings (isolated returns) go to k_knn_far.
+__global__ void k_knn_mean(const float4* __restrict__ pts, size_t n, const float4* __restrict__ sorted, const CellSlot* __restrict__ slots,
+                           uint32_t mask, float cell, int mean_k, int max_ring, float* __restrict__ dist, int* __restrict__ far_idx,
+                           int* __restrict__ far_count) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 q = pts[i];
+  const int ci = (int)floorf(q.x / cell), cj = (int)floorf(q.y / cell), ck = (int)floorf(q.z / cell);
+  float best[kKnnMax];
+  int cnt = 0;
+  const int k = mean_k + 1;
+  bool certain = false;
+  for (int ring = 0; ring <= max_ring + 1; ++ring) {
+    if (ring >= 1 && cnt == k) {
+      const float lim = (float)(ring - 1) * cell;
+      if (best[k - 1] <= lim * lim) { certain = true; break; }
+    }
+    if (ring > max_ring) break;
+    for (int dz = -ring; dz <= ring; ++dz)
+      for (int dy = -ring; dy <= ring; ++dy)
+        for (int dx = -ring; dx <= ring; ++dx) {
+          if (max(abs(dx), max(abs(dy), abs(dz))) != ring) continue;
+          const int a = ci + dx, b = cj + dy, c = ck + dz;
+          if (!coord_ok(a) || !coord_ok(b) || !coord_ok(c)) continue;
+          const unsigned long long key = pack_key(a, b, c);
+          uint32_t h = hash_key(key) & mask;
+          int s0 = 0, s1 = 0;
+          while (true) {
+            const CellSlot sl = slots[h];
+            if (sl.key == key) { s0 = sl.start; s1 = sl.end; break; }
+            if (sl.key == kEmptyKey) break;
+            h = (h + 1) & mask;
+          }
+          for (int t = s0; t < s1; ++t) {
+            const float4 tp = sorted[t];
+            const float ex = q.x - tp.x, ey = q.y - tp.y, ez = q.z - tp.z;
+            knn_insert(best, cnt, k, (ex * ex + ey * ey) + ez * ez);
+          }
+        }
+  }
+  if (certain) dist[i] = knn_mean(best, mean_k);
+  else far_idx[atomicAdd(far_count, 1)] = (int)i;
+}
+__global__ void __launch_bounds__(kFarThreads)
+k_knn_far(const float4* __restrict__ pts, const float4* __restrict__ sorted, size_t n, int mean_k, const int* __restrict__ far_idx,
+          const int* __restrict__ far_count, float* __restrict__ dist) {
+  __shared__ float4 tile[kFarTile];
+  const int n_far = *far_count;
+  if ((int)(blockIdx.x * kFarThreads) >= n_far) return;
+  const int f = blockIdx.x * kFarThreads + threadIdx.x;
+  const bool live = f < n_far;
+  const int i = live ? far_idx[f] : 0;
+  const float4 q = pts[i];
+  float best[kKnnMax];
+  int cnt = 0;
+  const int k = mean_k + 1;
+  for (size_t base = 0; base < n; base += kFarTile) {
+    const int m = (int)min((size_t)kFarTile, n - base);
+    __syncthreads();
+    for (int t = threadIdx.x; t < m; t += kFarThreads) tile[t] = sorted[base + t];
+    __syncthreads();
+    if (live)
+      for (int t = 0; t < m; ++t) {
+        const float4 tp = tile[t];
+        const float ex = q.x - tp.x, ey = q.y - tp.y, ez = q.z - tp.z;
+        knn_insert(best, cnt, k, (ex * ex + ey * ey) + ez * ez);
+      }
+  }
+  if (live) dist[i] = knn_mean(best, mean_k);
+}
+
+struct FilterWorkspace {
+  float4 *a = nullptr, *b = nullptr;   // gated cloud, downsampled cloud
+  int* flags = nullptr;
+  float* dist = nullptr;
+  size_t cap = 0;
+  int* d_count = nullptr;
+  int* h_count = nullptr;               // pinned
+  float* h_dist = nullptr;              // pinned, cap floats
+  NNGridStorage* nn = nullptr;
+};
+FilterWorkspace* filter_ws_create() {
+  FilterWorkspace* f = new FilterWorkspace();
+  f->nn = nn_create();
+  if (cudaMalloc(&f->d_count, sizeof(int)) != cudaSuccess || cudaMallocHost(&f->h_count, sizeof(int)) != cudaSuccess) { delete f; return nullptr; }
+  return f;
+}
+void filter_ws_destroy(FilterWorkspace* f) {
+  if (!f) return;
+  cudaFree(f->a); cudaFree(f->b); cudaFree(f->flags); cudaFree(f->dist); cudaFree(f->d_count);
+  cudaFreeHost(f->h_count); cudaFreeHost(f->h_dist);
+  nn_destroy(f->nn);
+  delete f;
+}
+static cudaError_t filter_ws_reserve(FilterWorkspace* f, size_t n) {
+  if (n <= f->cap) return cudaSuccess;
+  cudaFree(f->a); cudaFree(f->b); cudaFree(f->flags); cudaFree(f->dist); cudaFreeHost(f->h_dist);
+  f->a = f->b = nullptr; f->flags = nullptr; f->dist = nullptr; f->h_dist = nullptr; f->cap = 0;
+  const size_t cap = n + n / 4 + 1024;
+  CK(cudaMalloc(&f->a, cap * sizeof(float4))); CK(cudaMalloc(&f->b, cap * sizeof(float4)));
+  CK(cudaMalloc(&f->flags, cap * sizeof(int))); CK(cudaMalloc(&f->dist, cap * sizeof(float)));
+  CK(cudaMallocHost(&f->h_dist, cap * sizeof(float)));
+  f->cap = cap;
+  return cudaSuccess;
+}
+// order-preserving compaction of the flagged records; *n_out on the host (blocks the stream once)
+static cudaError_t compact_flagged(FilterWorkspace* f, BuildWorkspace* ws, const float4* in, size_t n, float4* out, size_t* n_out,
+                                   cudaStream_t s) {
+  size_t need = 0;
+  CK(cub::DeviceSelect::Flagged(nullptr, need, in, f->flags, out, f->d_count, (int)n, s));
+  if (need > ws->cub_bytes) return cudaErrorMemoryAllocation;   // ws_reserve(n) sized the scratch for a 64-bit pair sort of n: always larger
+  size_t tb = ws->cub_bytes;
+  CK(cub::DeviceSelect::Flagged(ws->cub_temp, tb, in, f->flags, out, f->d_count, (int)n, s));
+  CK(cudaMemcpyAsync(f->h_count, f->d_count, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  *n_out = (size_t)*f->h_count;
+  return cudaSuccess;
+}
+
+// raw: n device records (x y z intensity).  out: room for n records.  counts[0..2] = points after the gate, after the
+// voxel downsample, after the outlier removal (= records written to out).
+cudaError_t filter_scan(FilterWorkspace* f, BuildWorkspace* ws, const float4* raw, size_t n, double r_min, double r_max, float leaf, int mean_k,
+                        double std_mul, float4* out, size_t counts[3], cudaStream_t s, long long* launches) {
+  counts[0] = counts[1] = counts[2] = 0;
+  if (n == 0) return cudaSuccess;
+  if (mean_k + 1 > kKnnMax) return cudaErrorInvalidValue;   // mean_k <= 0: no outlier removal
+  long long dummy = 0;
+  long long& L = launches ? *launches : dummy;
+  CK(filter_ws_reserve(f, n));
+  CK(ws_reserve(ws, n));
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  k_gate_flags<<<nb, 256, 0, s>>>(raw, n, r_min, r_max, f->flags);
+  size_t n_gate = 0;
+  CK(compact_flagged(f, ws, raw, n, f->a, &n_gate, s));
+  L += 4;
+  counts[0] = n_gate;
+  if (n_gate == 0) return cudaSuccess;
+  size_t n_ds = 0;
+  if (leaf > 0.f) CK(voxelgrid_downsample(ws, f->a, n_gate, leaf, f->b, &n_ds, s, launches));
+  else { CK(cudaMemcpyAsync(f->b, f->a, n_gate * sizeof(float4), cudaMemcpyDeviceToDevice, s)); n_ds = n_gate; }
+  counts[1] = n_ds;
+  if (mean_k <= 0 || n_ds < (size_t)mean_k + 1) {   // no outlier removal asked for, or too few points for the neighbour statistics: returned unchanged (thirdparty_math.h DECISION)
+    CK(cudaMemcpyAsync(out, f->b, n_ds * sizeof(float4), cudaMemcpyDeviceToDevice, s));
+    counts[2] = n_ds;
+    return cudaSuccess;
+  }
+  // exact k-NN over a cell grid of the downsampled cloud (cells of two leaves: a handful of points each)
+  const float cell = leaf > 0.f ? 2.f * leaf : 1.f;
+  CK(nn_build(f->nn, ws, f->b, n_ds, cell, nullptr, s, launches));
+  NNGridStorage* g = f->nn;
+  if (n_ds > g->far_cap) {
+    cudaFree(g->far_idx);
+    g->far_idx = nullptr;
+    CK(cudaMalloc(&g->far_idx, (n_ds + n_ds / 4) * sizeof(int)));
+    g->far_cap = n_ds + n_ds / 4;
+  }
+  if (!g->far_count) CK(cudaMalloc(&g->far_count, sizeof(int)));
+  CK(cudaMemsetAsync(g->far_count, 0, sizeof(int), s));
+  const unsigned qb = (unsigned)((n_ds + 127) / 128);
+  k_knn_mean<<<qb, 128, 0, s>>>(f->b, n_ds, g->sorted, g->slots, g->mask, cell, mean_k, 6, f->dist, g->far_idx, g->far_count);
+  k_knn_far<<<(unsigned)((n_ds + kFarThreads - 1) / kFarThreads), kFarThreads, 0, s>>>(f->b, g->sorted, n_ds, mean_k, g->far_idx, g->far_count, f->dist);
+  L += 2;
+  CK(cudaMemcpyAsync(f->h_dist, f->dist, n_ds * sizeof(float), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  // mean and standard deviation of the distance vector, sequential in point order (statistical_outlier_removal.hpp)
+  double sum = 0, sq_sum = 0;
+  for (size_t i = 0; i < n_ds; ++i) {
+    sum += f->h_dist[i];
+    sq_sum += f->h_dist[i] * f->h_dist[i];   // a FLOAT product added to a double, as in PCL
+  }
+  const double nv = (double)n_ds;
+  const double mean = sum / nv;
+  const double variance = (sq_sum - sum * sum / nv) / (nv - 1);
+  const double threshold = mean + std_mul * sqrt(variance);
+  k_sor_flags<<<(unsigned)((n_ds + 255) / 256), 256, 0, s>>>(f->dist, n_ds, threshold, f->flags);
+  size_t n_keep = 0;
+  CK(compact_flagged(f, ws, f->b, n_ds, out, &n_keep, s));
+  L += 4;
+  counts[2] = n_keep;
+  return cudaGetLastError();
+}
+
 }  // namespace ndtb

@@ -31,6 +31,10 @@ class Result(C.Structure):
                 ("trans_probability", C.c_double), ("n_evals", C.c_int)]
 
 
+class FilterParams(C.Structure):
+    _fields_ = [("r_min", C.c_double), ("r_max", C.c_double), ("leaf", C.c_float), ("mean_k", C.c_int), ("stddev_mul", C.c_double)]
+
+
 RESULT_DTYPE = np.dtype([("T", np.float32, 16), ("iterations", np.int32), ("converged", np.int32), ("score", np.float64),
                          ("trans_probability", np.float64), ("n_evals", np.int32)], align=True)
 assert RESULT_DTYPE.itemsize == C.sizeof(Result)
@@ -50,7 +54,8 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_batch_destroy", "ndtb_batch_last_error", "ndtb_batch_set_params", "ndtb_batch_clear", "ndtb_batch_add_target",
            "ndtb_batch_add_source", "ndtb_batch_wait_uploads", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream",
            "ndtb_localmap_clear", "ndtb_localmap_append_source", "ndtb_localmap_snapshot", "ndtb_localmap_set_target",
-           "ndtb_localmap_roll", "ndtb_localmap_sizes", "ndtb_localmap_download"]
+           "ndtb_localmap_roll", "ndtb_localmap_sizes", "ndtb_localmap_download", "ndtb_default_filter_params", "ndtb_filter_scan",
+           "ndtb_get_source"]
 
 _lib = None
 
@@ -100,6 +105,9 @@ def load_library():
     L.ndtb_batch_run.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
     L.ndtb_batch_set_stream.argtypes = [vp, vp]
+    L.ndtb_default_filter_params.argtypes = [C.POINTER(FilterParams)]
+    L.ndtb_filter_scan.argtypes = [vp, vp, sz, sz, C.POINTER(FilterParams), vp]
+    L.ndtb_get_source.argtypes = [vp, vp, sz, sz, C.POINTER(sz)]
     L.ndtb_localmap_clear.argtypes = [vp]
     L.ndtb_localmap_append_source.argtypes = [vp, vp, C.c_float, C.c_int, C.POINTER(sz)]
     L.ndtb_localmap_snapshot.argtypes = [vp]
@@ -315,6 +323,23 @@ class NormalDistributionsTransform:
         H = np.zeros((6, 6))
         self._ck(self._L.ndtb_compute_hessian(self._h, _p(Tc), _p(p), _p(H)))
         return H
+
+    # ---- filter_node's front end on the device (reference src/filter_node.cpp:236-262) ----
+    def filterScan(self, raw, r_min=1.0, r_max=60.0, leaf=0.5, mean_k=30, stddev_mul=1.0):
+        """NaN removal, range gate, pcl::VoxelGrid, pcl::StatisticalOutlierRemoval; the result becomes the source.
+        Returns (points after the gate, after the downsample, after the outlier removal)."""
+        raw = _cloud(raw)
+        fp = FilterParams(r_min, r_max, leaf, mean_k, stddev_mul)
+        counts = np.zeros(3, dtype=np.uint64)
+        self._ck(self._L.ndtb_filter_scan(self._h, _p(raw), raw.shape[0], raw.strides[0], C.byref(fp), _p(counts)))
+        self._n_source = int(counts[2])
+        return tuple(int(c) for c in counts)
+
+    def getSource(self):
+        out = np.zeros((max(1, self._n_source), 4), np.float32)
+        n = C.c_size_t()
+        self._ck(self._L.ndtb_get_source(self._h, _p(out), out.shape[0], 16, C.byref(n)))
+        return out[:n.value].copy()
 
     # ---- odom_node's localmap on the device (reference src/odom_node.cpp:218-233, 289-290, 329-356) ----
     def localmapClear(self):
