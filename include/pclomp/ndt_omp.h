@@ -140,6 +140,17 @@ class NormalDistributionsTransform {
     ck(ndtb_align(h_, guess.data(), &result_));
     for (int i = 0; i < 16; ++i) final_transformation_.data()[i] = result_.T[i];
   }
+  // filter_node's front end on the device (ndt_c_api.h "filter_node" section; reference src/filter_node.cpp:236-262): the
+  // filtered scan becomes the source, as if setInputSource had been called with it; returns its size
+  inline size_t filterScan(const PointCloudSource& raw, double r_min = 1.0, double r_max = 60.0, float leaf = 0.5f, int mean_k = 30,
+                           double stddev_mul = 1.0) {
+    ndtb_filter_params fp;
+    fp.r_min = r_min; fp.r_max = r_max; fp.leaf = leaf; fp.mean_k = mean_k; fp.stddev_mul = stddev_mul;
+    size_t c[3] = {0, 0, 0};
+    ck(ndtb_filter_scan(h_, raw.points.data(), raw.points.size(), sizeof(PointSource), &fp, c));
+    input_.reset(new PointCloudSource());          // a placeholder: the source lives on the device
+    return c[2];
+  }
   // odom_node's localmap kept in HBM (ndt_c_api.h "localmap" section; reference src/odom_node.cpp:218-233, 289-290, 329-356)
   inline void localmapClear() { ck(ndtb_localmap_clear(h_)); }
   // localmap (+ tmp_map) += [voxel-downsampled at `leaf` if > 0] T * current source; returns the points appended

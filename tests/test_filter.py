@@ -84,7 +84,8 @@ def test_device_filter_scan_edges():
     g = ndt.NormalDistributionsTransform()
     raw = _raw_scan()
     # gate only / gate + downsample / different k and sigma / isolated far points (the exhaustive k-NN pass)
-    for kw in (dict(leaf=0.0, mean_k=0), dict(leaf=1.0, mean_k=0), dict(leaf=0.5, mean_k=10, stddev_mul=0.5), dict(leaf=2.0, mean_k=30)):
+    for kw in (dict(leaf=0.0, mean_k=0), dict(leaf=1.0, mean_k=0), dict(leaf=0.5, mean_k=10, stddev_mul=0.5), dict(leaf=2.0, mean_k=30),
+               dict(leaf=0.1, mean_k=8)):      # > 32768 points after the downsample: cell-grid ring search + sweep for the leftovers
         ro = oracle.filter_scan(raw, r_min=1.0, r_max=60.0, leaf=kw["leaf"] if kw["leaf"] > 0 else 1e-4, mean_k=kw["mean_k"] if kw["mean_k"] > 0 else 100000,
                                 std_mul=kw.get("stddev_mul", 1.0)) if kw["leaf"] > 0 else None
         counts = g.filterScan(raw, **kw)

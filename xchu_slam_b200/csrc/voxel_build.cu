@@ -183,6 +183,11 @@ __global__ void k_minmax(const float4* __restrict__ pts, size_t n, float* __rest
     for (int a = 0; a < 3; ++a) { atomicMin(&o[a], enc(mn[a])); atomicMax(&o[3 + a], enc(mx[a])); }
   }
 }
+// grid for k_minmax: enough blocks for the points, at most 8 per SM (every warp ends in six atomics)
+static inline unsigned minmax_grid(size_t n) {
+  const size_t b = (n + 1023) / 1024;   // 4 points per thread
+  return (unsigned)(b < 1 ? 1 : (b > 148 * 8 ? 148 * 8 : b));
+}
 __global__ void k_minmax_init(float* out6) {
   int* o = reinterpret_cast<int*>(out6);
   if (threadIdx.x < 3) o[threadIdx.x] = 0x7FFFFFFF;
@@ -482,7 +487,7 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
   long long& L = launches ? *launches : dummy;
   // bounding box of the new points
   k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
-  k_minmax<<<148 * 8, 256, 0, s>>>(pts, n, ws->mm, 1);
+  k_minmax<<<minmax_grid(n), 256, 0, s>>>(pts, n, ws->mm, 1);
   k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
   L += 3;
   CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
@@ -578,7 +583,7 @@ cudaError_t voxelgrid_downsample(BuildWorkspace* ws, const float4* in, size_t n,
   long long dummy = 0;
   long long& L = launches ? *launches : dummy;
   k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
-  k_minmax<<<148 * 2, 256, 0, s>>>(in, n, ws->mm, 1);
+  k_minmax<<<minmax_grid(n), 256, 0, s>>>(in, n, ws->mm, 1);
   k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
   L += 3;
   CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
@@ -696,7 +701,7 @@ cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, si
     for (int a = 0; a < 6; ++a) bb[a] = bbox[a];
   } else {
     k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
-    k_minmax<<<148 * 8, 256, 0, s>>>(pts, n, ws->mm, 1);
+    k_minmax<<<minmax_grid(n), 256, 0, s>>>(pts, n, ws->mm, 1);
     k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
     L += 3;
     CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
@@ -879,14 +884,14 @@ __device__ __forceinline__ float knn_mean(const float* best, int mean_k) {
   for (int k = 1; k < mean_k + 1; ++k) s += sqrt((double)best[k]);
   return (float)(s / (double)mean_k);
 }
-// One thread per point of the cloud (original order); neighbours are searched in the cell-sorted copy.  Settled once the
-// k-th best is <= ((ring-1)*cell)^2; points still open after max_ring rings (isolated returns) go to k_knn_far.
-__global__ void k_knn_mean(const float4* __restrict__ pts, size_t n, const float4* __restrict__ sorted, const CellSlot* __restrict__ slots,
+// Ring search over the cell grid, one thread per point of the CELL-SORTED copy (position s; its index in the cloud is
+// order[s]).  Settled once the k-th best is <= ((ring-1)*cell)^2; points still open after max_ring rings go to k_knn_sweep.
+__global__ void k_knn_mean(const float4* __restrict__ sorted, const unsigned int* __restrict__ order, size_t n, const CellSlot* __restrict__ slots,
                            uint32_t mask, float cell, int mean_k, int max_ring, float* __restrict__ dist, int* __restrict__ far_idx,
                            int* __restrict__ far_count) {
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const float4 q = pts[i];
+  const size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const float4 q = sorted[s];
   const int ci = (int)floorf(q.x / cell), cj = (int)floorf(q.y / cell), ck = (int)floorf(q.z / cell);
   float best[kKnnMax];
   int cnt = 0;
@@ -920,35 +925,51 @@ __global__ void k_knn_mean(const float4* __restrict__ pts, size_t n, const float
           }
         }
   }
-  if (certain) dist[i] = knn_mean(best, mean_k);
-  else far_idx[atomicAdd(far_count, 1)] = (int)i;
+  if (certain) dist[order[s]] = knn_mean(best, mean_k);
+  else far_idx[atomicAdd(far_count, 1)] = (int)s;
 }
-__global__ void __launch_bounds__(kFarThreads)
-k_knn_far(const float4* __restrict__ pts, const float4* __restrict__ sorted, size_t n, int mean_k, const int* __restrict__ far_idx,
-          const int* __restrict__ far_count, float* __restrict__ dist) {
-  __shared__ float4 tile[kFarTile];
-  const int n_far = *far_count;
-  if ((int)(blockIdx.x * kFarThreads) >= n_far) return;
-  const int f = blockIdx.x * kFarThreads + threadIdx.x;
-  const bool live = f < n_far;
-  const int i = live ? far_idx[f] : 0;
-  const float4 q = pts[i];
+// Exhaustive k-NN for the listed positions (far_idx == nullptr: every position): the cell-sorted copy is swept OUTWARD from
+// the query's own position, so that its spatial neighbours come first, the k-th best tightens within a few dozen
+// candidates and almost every later candidate is rejected by one comparison.  Exact: every point is visited.
+__global__ void __launch_bounds__(128)
+k_knn_sweep(const float4* __restrict__ sorted, const unsigned int* __restrict__ order, size_t n, int mean_k, const int* __restrict__ far_idx,
+            const int* __restrict__ far_count, float* __restrict__ dist) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n_list = far_idx ? *far_count : (int)n;
+  if (f >= n_list) return;
+  const int s = far_idx ? far_idx[f] : f;
+  const float4 q = sorted[s];
   float best[kKnnMax];
   int cnt = 0;
   const int k = mean_k + 1;
-  for (size_t base = 0; base < n; base += kFarTile) {
-    const int m = (int)min((size_t)kFarTile, n - base);
-    __syncthreads();
-    for (int t = threadIdx.x; t < m; t += kFarThreads) tile[t] = sorted[base + t];
-    __syncthreads();
-    if (live)
-      for (int t = 0; t < m; ++t) {
-        const float4 tp = tile[t];
+  const int nn = (int)n;
+  float kth = FLT_MAX;            // register copy of best[k-1] once k candidates are held: the common case is one compare
+  // four candidates from each side per round, loads first: the sweep is bound by the latency of its loads otherwise
+  for (int o = 0; o < nn; o += 4) {
+    float dh[4], dl[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int jh = s + o + u, jl = s - 1 - o - u;
+      dh[u] = FLT_MAX; dl[u] = FLT_MAX;
+      if (jh < nn) {
+        const float4 tp = __ldg(sorted + jh);
         const float ex = q.x - tp.x, ey = q.y - tp.y, ez = q.z - tp.z;
-        knn_insert(best, cnt, k, (ex * ex + ey * ey) + ez * ez);
+        dh[u] = (ex * ex + ey * ey) + ez * ez;
       }
+      if (jl >= 0) {
+        const float4 tp = __ldg(sorted + jl);
+        const float ex = q.x - tp.x, ey = q.y - tp.y, ez = q.z - tp.z;
+        dl[u] = (ex * ex + ey * ey) + ez * ez;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (s + o + u < nn && (cnt < k || dh[u] < kth)) { knn_insert(best, cnt, k, dh[u]); if (cnt == k) kth = best[k - 1]; }
+      if (s - 1 - o - u >= 0 && (cnt < k || dl[u] < kth)) { knn_insert(best, cnt, k, dl[u]); if (cnt == k) kth = best[k - 1]; }
+    }
+    if (s + o + 4 >= nn && s - 1 - o - 4 < 0) break;
   }
-  if (live) dist[i] = knn_mean(best, mean_k);
+  dist[order[s]] = knn_mean(best, mean_k);
 }
 
 struct FilterWorkspace {
@@ -1039,9 +1060,17 @@ cudaError_t filter_scan(FilterWorkspace* f, BuildWorkspace* ws, const float4* ra
   if (!g->far_count) CK(cudaMalloc(&g->far_count, sizeof(int)));
   CK(cudaMemsetAsync(g->far_count, 0, sizeof(int), s));
   const unsigned qb = (unsigned)((n_ds + 127) / 128);
-  k_knn_mean<<<qb, 128, 0, s>>>(f->b, n_ds, g->sorted, g->slots, g->mask, cell, mean_k, 6, f->dist, g->far_idx, g->far_count);
-  k_knn_far<<<(unsigned)((n_ds + kFarThreads - 1) / kFarThreads), kFarThreads, 0, s>>>(f->b, g->sorted, n_ds, mean_k, g->far_idx, g->far_count, f->dist);
-  L += 2;
+  // ws->idx_out still holds the permutation of nn_build's sort: position in the cell-sorted copy -> index in the cloud
+  if (n_ds <= 32768) {
+    // a downsampled 64-beam scan is sparse (the 31st neighbour of most points lies several cells away): sweeping the whole
+    // cloud per point beats walking mostly empty shells of cells
+    k_knn_sweep<<<qb, 128, 0, s>>>(g->sorted, ws->idx_out, n_ds, mean_k, nullptr, nullptr, f->dist);
+    L += 1;
+  } else {
+    k_knn_mean<<<qb, 128, 0, s>>>(g->sorted, ws->idx_out, n_ds, g->slots, g->mask, cell, mean_k, 2, f->dist, g->far_idx, g->far_count);
+    k_knn_sweep<<<qb, 128, 0, s>>>(g->sorted, ws->idx_out, n_ds, mean_k, g->far_idx, g->far_count, f->dist);
+    L += 2;
+  }
   CK(cudaMemcpyAsync(f->h_dist, f->dist, n_ds * sizeof(float), cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
   // mean and standard deviation of the distance vector, sequential in point order (statistical_outlier_removal.hpp)
