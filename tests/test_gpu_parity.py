@@ -443,3 +443,28 @@ def test_batch_c5_shape_against_oracle():
         # the registrations recover the ground truth (the batch is not trivially wrong everywhere)
         gt_err = [np.max(np.abs(r["T"][:3, 3] - synth.pose6_to_matrix(g6)[:3, 3])) for r, g6 in zip(res, w["gt"])]
         assert np.median(gt_err) < 0.05
+
+
+@pytest.mark.parametrize("strict", [False, True])
+@pytest.mark.parametrize("name", ["empty source", "source outside the grid", "one-point source", "no voxel reaches 6 points"])
+def test_edge_cases(case_tiny, name, strict):
+    """Degenerate inputs the reference handles by value (no exceptions, no error codes): empty source (score 0/0 -> NaN
+    probability, `converged` true by the NaN test of NDT_I:126-130), a source with no neighbour voxel at all (H = 0, zero
+    Newton step), a single point, a target none of whose voxels reaches min_points."""
+    from test_reference_build import _edge_cases
+    from oracle import oracle
+    from xchu_slam_b200 import ndt
+    s, t, G = _edge_cases(case_tiny)[name]
+    o = oracle.OracleNDT()
+    o.set_params(resolution=1.0, trans_eps=0.01, max_iter=30, search_method=2, num_threads=1)
+    o.set_target(t); o.set_source(s)
+    ro = o.align(G)
+    g = ndt.NormalDistributionsTransform()
+    g.setTransformationEpsilon(0.01); g.setMaximumIterations(30); g.setStrictMath(strict)
+    g.setInputTarget(t); g.setInputSource(s)
+    g.align(G)
+    rg = g.result()
+    assert rg["iterations"] == ro["iterations"] and rg["converged"] == ro["converged"]
+    assert np.max(np.abs(rg["T"] - ro["T"])) < 1e-4
+    tp = rg["trans_probability"]
+    assert (np.isnan(tp) and np.isnan(ro["trans_probability"])) or abs(tp - ro["trans_probability"]) <= 1e-6 * max(1.0, abs(ro["trans_probability"]))

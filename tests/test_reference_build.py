@@ -224,3 +224,24 @@ def test_golden_fixture_is_what_the_reference_sources_produce():
         assert a["iterations"] == gold[name + "_iterations"] and int(a["converged"]) == gold[name + "_converged"]
         assert np.max(np.abs(a["T"] - gold[name + "_T"])) < 1e-6
         assert abs(r.fitness() - gold[name + "_fitness"]) <= 1e-9 * gold[name + "_fitness"]
+
+
+def _edge_cases(case):
+    src, tgt, gt, guess = case
+    far = src.copy()
+    far[:, :3] += 5000.0
+    eye = np.eye(4, dtype=np.float32)
+    return {"empty source": (np.zeros((0, 4), np.float32), tgt, guess),          # score 0/0: trans_probability NaN, converged (NDT_I:126-130)
+            "source outside the grid": (far, tgt, eye),                          # no neighbour anywhere: H = 0, zero step
+            "one-point source": (src[:1], tgt, guess),
+            "no voxel reaches 6 points": (src, tgt[::40], guess)}
+
+
+@pytest.mark.parametrize("name", ["empty source", "source outside the grid", "one-point source", "no voxel reaches 6 points"])
+def test_edge_cases_bit_exact(case_tiny, name):
+    s, t, G = _edge_cases(case_tiny)[name]
+    o, r = _pair((s, t))
+    ro, rr = o.align(G), r.align(G)
+    assert ro["iterations"] == rr["iterations"] and ro["converged"] == rr["converged"]
+    assert np.array_equal(ro["T"], rr["T"])
+    assert ro["trans_probability"] == rr["trans_probability"] or (np.isnan(ro["trans_probability"]) and np.isnan(rr["trans_probability"]))
