@@ -189,6 +189,10 @@ int ndtb_batch_wait_uploads(ndtb_batch* b);
  * guesses: n_items x 16 floats.  results: n_items records (host). */
 int ndtb_batch_run(ndtb_batch* b, int n_items, const int* item_target, const int* item_source,
                    const float* guesses, ndtb_result* results);
+/* pcl::Registration::getFitnessScore(max_range) of every registration of the last ndtb_batch_run, at its final
+ * transform: loop-closure candidates are accepted on it (reference xchu_mapping/src/pgo_node.cpp:460-476, fitness <= 0.3).
+ * out: one double per item of that run (host).  Exact 1-NN over each target; one launch per distinct target. */
+int ndtb_batch_fitness(ndtb_batch* b, double max_range, double* out);
 /* Device times (ms) of the last run: voxel-table builds, derivative kernels, whole run; number of
  * kernels launched; derivative-kernel launches; (point, voxel) pairs and points evaluated. */
 typedef struct ndtb_batch_stats {

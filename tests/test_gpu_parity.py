@@ -423,6 +423,8 @@ def test_batch_c5_shape_against_oracle():
         for i in np.flatnonzero(np.asarray(w["item_target"]) == t):
             o.set_source(w["sources"][w["item_source"][i]])
             ref_res[i] = o.align(w["guesses"][i])
+            ref_res[i]["fitness"] = o.fitness()
+            ref_res[i]["fitness_1m"] = o.fitness(1.0)
     for strict in (1, 0):
         b = ndt.BatchNDT()
         b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2, strict_math=strict)
@@ -431,13 +433,17 @@ def test_batch_c5_shape_against_oracle():
         for s in w["sources"]:
             b.add_source(s)
         res = b.run(w["item_target"], w["item_source"], w["guesses"])
+        # getFitnessScore of every registration of the batch (the loop-closure gate, pgo_node.cpp:460-476)
+        fit, fit1 = b.fitness(len(res)), b.fitness(len(res), 1.0)
         n_off = 0
-        for r, q in zip(res, ref_res):
+        for k, (r, q) in enumerate(zip(res, ref_res)):
             dT = np.max(np.abs(r["T"][:3, 3] - q["T"][:3, 3]))
             dR = np.max(np.abs(r["T"][:3, :3] - q["T"][:3, :3]))
             ok = r["iterations"] == q["iterations"] and r["converged"] == q["converged"] and dT < 1e-4 and dR < 1e-5
             if strict or q["iterations"] <= 14:
                 assert ok, (strict, r["iterations"], q["iterations"], dT, dR)
+            if ok:
+                assert abs(fit[k] - q["fitness"]) <= 1e-5 * q["fitness"] and abs(fit1[k] - q["fitness_1m"]) <= 1e-5 * q["fitness_1m"]
             n_off += 0 if ok else 1
         assert n_off <= 2
         # the registrations recover the ground truth (the batch is not trivially wrong everywhere)

@@ -137,6 +137,13 @@ struct Engine {
   unsigned long long lm_gen = 1;     // bumped whenever the localmap's contents stop being an extension of what they were
   unsigned long long tgt_gen = 0;    // localmap generation the target's points were taken from (0: not from the localmap)
   size_t tgt_from_lm = 0;            // leading localmap points already merged into the target
+  std::vector<int> last_item_target;   // targets of the items of the last run (ndtb_batch_fitness)
+  double* d_fit_partial = nullptr;
+  size_t fit_partial_cap = 0;
+  double* d_fit_out = nullptr;
+  size_t fit_out_cap = 0;
+  int* d_fit_items = nullptr;
+  size_t fit_items_cap = 0;
   FilterWorkspace* flt = nullptr;    // filter_node front end (ndtb_filter_scan)
   float4* flt_raw = nullptr;
   size_t flt_raw_cap = 0;
@@ -198,6 +205,7 @@ struct Engine {
     cudaFree(lm.p); cudaFree(lm_tmp.p); cudaFree(lm_last.p); cudaFree(lm_scratch);
     st_src.release(); st_d2.release();
     filter_ws_destroy(flt); cudaFree(flt_raw);
+    cudaFree(d_fit_partial); cudaFree(d_fit_out); cudaFree(d_fit_items);
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     for (auto& e : deriv_events) cudaEventDestroy(e);
     if (stream && own_stream) cudaStreamDestroy(stream);
@@ -383,8 +391,10 @@ struct Engine {
   // Run n_items registrations to completion on the device.  want_trace: per-evaluation records.
   int run_items(int n_items, const int* item_target, const int* item_source, const float* guesses, ndtb_result* results,
                 bool want_trace) {
+    last_item_target.clear();
     if (n_items <= 0) return 0;
     CKE(cudaSetDevice(device));
+    last_item_target.assign(item_target, item_target + n_items);
     stats = ndtb_batch_stats{};
     CKE(cudaEventRecord(ev[0], stream));
     if (build_pending_targets()) return 1;
@@ -1121,6 +1131,43 @@ int ndtb_batch_run(ndtb_batch* b, int n_items, const int* item_target, const int
   for (int i = 0; i < n_items; ++i)
     if (item_target[i] < 0 || item_target[i] >= e.n_targets_live) return e.fail("item target id out of range");
   return e.run_items(n_items, item_target, item_source, guesses, results, false);
+}
+int ndtb_batch_fitness(ndtb_batch* b, double max_range, double* out) {
+  Engine& e = b->e;
+  const int n = (int)e.last_item_target.size();
+  if (n == 0) return e.fail("ndtb_batch_fitness needs a completed ndtb_batch_run");
+  if (cudaSetDevice(e.device) != cudaSuccess) return e.fail("cudaSetDevice failed");
+  const int bpi = 8;   // blocks per registration
+  if (e.ensure(e.d_fit_partial, e.fit_partial_cap, (size_t)n * bpi * 2)) return 1;
+  if (e.ensure(e.d_fit_out, e.fit_out_cap, (size_t)n)) return 1;
+  if (e.ensure(e.d_fit_items, e.fit_items_cap, (size_t)n)) return 1;
+  // registrations grouped by target: one NN grid build and one launch per target
+  std::vector<int> order(n);
+  for (int i = 0; i < n; ++i) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int c) { return e.last_item_target[a] < e.last_item_target[c]; });
+  if (cudaMemcpyAsync(e.d_fit_items, order.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, e.stream) != cudaSuccess)
+    return e.fail("upload failed");
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");   // `order` is pageable: landed before it goes away
+  for (int g0 = 0; g0 < n;) {
+    const int tid = e.last_item_target[order[g0]];
+    int g1 = g0;
+    while (g1 < n && e.last_item_target[order[g1]] == tid) ++g1;
+    Target& t = e.targets[tid];
+    if (t.n == 0 || !t.built) return e.fail("ndtb_batch_fitness: a target of the last run is gone (ndtb_batch_clear was called)");
+    const float cell = e.params.resolution > 0.25f ? e.params.resolution : 0.25f;
+    float bb[6];
+    for (int a = 0; a < 3; ++a) { bb[a] = t.ts.mn[a]; bb[3 + a] = t.ts.mx[a]; }
+    cudaError_t ce = nn_build(e.nn, e.ws, t.use ? t.use : t.pts, t.n, cell, t.ts.have_bbox ? bb : nullptr, e.stream, &e.stats.kernel_launches);
+    if (ce == cudaSuccess) ce = nn_fitness_batch(e.nn, e.d_states, e.d_fit_items + g0, g1 - g0, max_range, bpi, e.d_fit_partial, e.stream);
+    if (ce != cudaSuccess) return e.fail(std::string("batch fitness: ") + cudaGetErrorString(ce));
+    ++e.stats.kernel_launches;
+    g0 = g1;
+  }
+  e.nn_valid = false;
+  if (fitness_finish(e.d_fit_partial, n, bpi, e.d_fit_out, e.stream) != cudaSuccess) return e.fail("fitness_finish failed");
+  if (cudaMemcpyAsync(out, e.d_fit_out, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, e.stream) != cudaSuccess) return e.fail("copy failed");
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  return 0;
 }
 int ndtb_batch_get_stats(ndtb_batch* b, ndtb_batch_stats* s) { *s = b->e.stats; return 0; }
 int ndtb_batch_set_stream(ndtb_batch* b, void* cuda_stream) {

@@ -191,6 +191,10 @@ cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, si
                      cudaStream_t s, long long* launches);
 cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float* T16_dev, float* d2_out,
                      cudaStream_t s);
+// getFitnessScore of every registration of a batch that shares the grid's target (items_dev: ids into states)
+cudaError_t nn_fitness_batch(NNGridStorage* g, const AlignState* states, const int* items_dev, int n_group, double max_range,
+                             int blocks_per_item, double* partial, cudaStream_t s);
+cudaError_t fitness_finish(const double* partial, int n_items, int blocks_per_item, double* out, cudaStream_t s);
 constexpr int kPhaseStart = 10, kPhaseEvalOnly = 11;   // AlignState::phase values used by the host
 
 }  // namespace ndtb

@@ -849,6 +849,95 @@ cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float*
   return cudaGetLastError();
 }
 
+// Batched getFitnessScore (loop-closure candidates are accepted on it, reference src/pgo_node.cpp:460-476): every
+// registration of a batch that shares one target, in one launch.  blockIdx.y walks `items` (ids into `states`); the
+// transform is the registration's final one.  A query the ring search cannot settle scans the whole target itself (a scan
+// registered against a submap lies inside it, so this is rare).  Per item: sum and count of the squared distances
+// <= max_range, reduced in a fixed order (lane, then warp, then block partials added by k_fitness_finish).
+__global__ void __launch_bounds__(128)
+k_nn_fitness_batch(const float4* __restrict__ sorted, size_t n_tgt, const CellSlot* __restrict__ slots, uint32_t mask, float cell,
+                   const AlignState* __restrict__ states, const int* __restrict__ items, double max_range, int blocks_per_item,
+                   double* __restrict__ partial /* [n_items_total][blocks_per_item][2] */) {
+  const int item = items[blockIdx.y];
+  const AlignState& st = states[item];
+  const float* T16 = st.final_T;
+  const int n = st.n_src;
+  double s = 0.0, c = 0.0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += blocks_per_item * blockDim.x) {
+    const float4 p = st.src[i];
+    const float qx = ((T16[0] * p.x + T16[4] * p.y) + T16[8] * p.z) + T16[12];
+    const float qy = ((T16[1] * p.x + T16[5] * p.y) + T16[9] * p.z) + T16[13];
+    const float qz = ((T16[2] * p.x + T16[6] * p.y) + T16[10] * p.z) + T16[14];
+    const int ci = (int)floorf(qx / cell), cj = (int)floorf(qy / cell), ck = (int)floorf(qz / cell);
+    float best = FLT_MAX;
+    bool certain = false;
+    for (int ring = 0; ring <= 9; ++ring) {
+      if (ring >= 1) {
+        const float lim = (float)(ring - 1) * cell;
+        if (best <= lim * lim) { certain = true; break; }
+      }
+      if (ring > 8) break;
+      for (int dz = -ring; dz <= ring; ++dz)
+        for (int dy = -ring; dy <= ring; ++dy)
+          for (int dx = -ring; dx <= ring; ++dx) {
+            if (max(abs(dx), max(abs(dy), abs(dz))) != ring) continue;
+            const int a = ci + dx, b = cj + dy, cc = ck + dz;
+            if (!coord_ok(a) || !coord_ok(b) || !coord_ok(cc)) continue;
+            const unsigned long long key = pack_key(a, b, cc);
+            uint32_t h = hash_key(key) & mask;
+            int s0 = 0, s1 = 0;
+            while (true) {
+              const CellSlot sl = slots[h];
+              if (sl.key == key) { s0 = sl.start; s1 = sl.end; break; }
+              if (sl.key == kEmptyKey) break;
+              h = (h + 1) & mask;
+            }
+            for (int t = s0; t < s1; ++t) {
+              const float4 tp = sorted[t];
+              const float ex = qx - tp.x, ey = qy - tp.y, ez = qz - tp.z;
+              const float d = (ex * ex + ey * ey) + ez * ez;
+              if (d < best) best = d;
+            }
+          }
+    }
+    if (!certain)
+      for (size_t t = 0; t < n_tgt; ++t) {
+        const float4 tp = sorted[t];
+        const float ex = qx - tp.x, ey = qy - tp.y, ez = qz - tp.z;
+        const float d = (ex * ex + ey * ey) + ez * ez;
+        if (d < best) best = d;
+      }
+    if ((double)best <= max_range) { s += (double)best; c += 1.0; }
+  }
+  __shared__ double sh[2][4];
+  for (int o = 16; o > 0; o >>= 1) { s += __shfl_down_sync(0xffffffffu, s, o); c += __shfl_down_sync(0xffffffffu, c, o); }
+  if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = s; sh[1][threadIdx.x >> 5] = c; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double* o = partial + ((size_t)item * blocks_per_item + blockIdx.x) * 2;
+    o[0] = ((sh[0][0] + sh[0][1]) + sh[0][2]) + sh[0][3];
+    o[1] = ((sh[1][0] + sh[1][1]) + sh[1][2]) + sh[1][3];
+  }
+}
+__global__ void k_fitness_finish(const double* __restrict__ partial, int n_items, int blocks_per_item, double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_items) return;
+  double s = 0.0, c = 0.0;
+  for (int b = 0; b < blocks_per_item; ++b) { s += partial[((size_t)i * blocks_per_item + b) * 2]; c += partial[((size_t)i * blocks_per_item + b) * 2 + 1]; }
+  out[i] = c > 0.0 ? s / c : 1.7976931348623157e308;   // std::numeric_limits<double>::max () when no point is in range
+}
+cudaError_t nn_fitness_batch(NNGridStorage* g, const AlignState* states, const int* items_dev, int n_group, double max_range,
+                             int blocks_per_item, double* partial, cudaStream_t s) {
+  if (n_group <= 0) return cudaSuccess;
+  k_nn_fitness_batch<<<dim3((unsigned)blocks_per_item, (unsigned)n_group), 128, 0, s>>>(g->sorted, g->n, g->slots, g->mask, g->cell, states,
+                                                                                    items_dev, max_range, blocks_per_item, partial);
+  return cudaGetLastError();
+}
+cudaError_t fitness_finish(const double* partial, int n_items, int blocks_per_item, double* out, cudaStream_t s) {
+  k_fitness_finish<<<(n_items + 127) / 128, 128, 0, s>>>(partial, n_items, blocks_per_item, out);
+  return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------------------------------
 // filter_node's front end on the device (reference src/filter_node.cpp:236-273):
 // pcl::removeNaNFromPointCloud + range gate 1 < r_xy < 60 (:236-247), pcl::VoxelGrid 0.5 m (:249-251, the kernels of

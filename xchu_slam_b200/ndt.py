@@ -52,7 +52,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_neighbors",
            "ndtb_eval_derivatives", "ndtb_compute_hessian", "ndtb_get_trace", "ndtb_last_timing", "ndtb_batch_create",
            "ndtb_batch_destroy", "ndtb_batch_last_error", "ndtb_batch_set_params", "ndtb_batch_clear", "ndtb_batch_add_target",
-           "ndtb_batch_add_source", "ndtb_batch_wait_uploads", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream",
+           "ndtb_batch_add_source", "ndtb_batch_wait_uploads", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream", "ndtb_batch_fitness",
            "ndtb_localmap_clear", "ndtb_localmap_append_source", "ndtb_localmap_snapshot", "ndtb_localmap_set_target",
            "ndtb_localmap_roll", "ndtb_localmap_sizes", "ndtb_localmap_download", "ndtb_default_filter_params", "ndtb_filter_scan",
            "ndtb_get_source"]
@@ -105,6 +105,7 @@ def load_library():
     L.ndtb_batch_run.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
     L.ndtb_batch_set_stream.argtypes = [vp, vp]
+    L.ndtb_batch_fitness.argtypes = [vp, C.c_double, vp]
     L.ndtb_default_filter_params.argtypes = [C.POINTER(FilterParams)]
     L.ndtb_filter_scan.argtypes = [vp, vp, sz, sz, C.POINTER(FilterParams), vp]
     L.ndtb_get_source.argtypes = [vp, vp, sz, sz, C.POINTER(sz)]
@@ -463,6 +464,12 @@ class BatchNDT:
         return [dict(T=T[i].copy(), iterations=int(res["iterations"][i]), converged=bool(res["converged"][i]),
                      score=float(res["score"][i]), trans_probability=float(res["trans_probability"][i]),
                      n_evals=int(res["n_evals"][i])) for i in range(res.shape[0])]
+
+    def fitness(self, n_items, max_range=float(np.finfo(np.float64).max)):
+        """getFitnessScore of every registration of the last run (loop-closure gate, pgo_node.cpp:460-476)."""
+        out = np.zeros(n_items, dtype=np.float64)
+        self._ck(self._L.ndtb_batch_fitness(self._h, float(max_range), _p(out)))
+        return out
 
     def stats(self):
         s = BatchStats()
