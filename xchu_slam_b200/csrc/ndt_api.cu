@@ -893,7 +893,7 @@ int ndtb_localmap_append_source(ndtb_handle* h, const float T[16], float leaf, i
     if (cudaMalloc(&e.lm_scratch, (n + n / 4) * sizeof(float4)) != cudaSuccess) return e.fail("alloc");
     e.lm_scratch_cap = n + n / 4;
   }
-  cudaMemcpyAsync(e.d_T16, T, 64, cudaMemcpyHostToDevice, e.stream);
+  if (cudaMemcpyAsync(e.d_T16, T, 64, cudaMemcpyHostToDevice, e.stream) != cudaSuccess) return e.fail("device copy failed");
   const bool ds = leaf > 0.f;
   if (launch_transform(e.source_ptr(e.sources[0]), n, e.d_T16, ds ? e.lm_scratch : e.lm_last.p, e.stream) != cudaSuccess)
     return e.fail("transform failed");
@@ -905,11 +905,11 @@ int ndtb_localmap_append_source(ndtb_handle* h, const float T[16], float leaf, i
   }
   e.lm_last.n = m;
   if (lm_reserve(e, e.lm, e.lm.n + m)) return 1;
-  cudaMemcpyAsync(e.lm.p + e.lm.n, e.lm_last.p, m * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+  if (cudaMemcpyAsync(e.lm.p + e.lm.n, e.lm_last.p, m * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream) != cudaSuccess) return e.fail("device copy failed");
   e.lm.n += m;
   if (also_tmp) {
     if (lm_reserve(e, e.lm_tmp, e.lm_tmp.n + m)) return 1;
-    cudaMemcpyAsync(e.lm_tmp.p + e.lm_tmp.n, e.lm_last.p, m * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+    if (cudaMemcpyAsync(e.lm_tmp.p + e.lm_tmp.n, e.lm_last.p, m * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream) != cudaSuccess) return e.fail("device copy failed");
     e.lm_tmp.n += m;
   }
   if (n_added) *n_added = m;
@@ -935,7 +935,7 @@ int ndtb_localmap_set_target(ndtb_handle* h, int force_full, int* was_incrementa
     const size_t tail = n - e.tgt_from_lm;
     if (tail > 0) {
       if (e.reserve_target(t, n)) return 1;
-      cudaMemcpyAsync(t.pts + t.n, e.lm.p + e.tgt_from_lm, tail * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+      if (cudaMemcpyAsync(t.pts + t.n, e.lm.p + e.tgt_from_lm, tail * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream) != cudaSuccess) return e.fail("device copy failed");
       e.table_config(t);
       cudaError_t ce = table_append(t.ts, e.ws, t.pts + t.n, tail, e.stream, &e.stats.kernel_launches);
       if (ce != cudaSuccess) return e.fail(std::string("table_append: ") + cudaGetErrorString(ce));
@@ -988,11 +988,11 @@ int ndtb_localmap_download(ndtb_handle* h, int which, void* pts, size_t cap, siz
   if (n) *n = m;
   if (m == 0) return 0;
   if (stride_bytes == 16) {
-    cudaMemcpyAsync(pts, c->p, m * 16, cudaMemcpyDeviceToHost, e.stream);
+    if (cudaMemcpyAsync(pts, c->p, m * 16, cudaMemcpyDeviceToHost, e.stream) != cudaSuccess) return e.fail("device copy failed");
   } else {
-    cudaMemcpy2DAsync(pts, stride_bytes, c->p, 16, 12, m, cudaMemcpyDeviceToHost, e.stream);
+    if (cudaMemcpy2DAsync(pts, stride_bytes, c->p, 16, 12, m, cudaMemcpyDeviceToHost, e.stream) != cudaSuccess) return e.fail("device copy failed");
     if (stride_bytes >= 20)
-      cudaMemcpy2DAsync(static_cast<char*>(pts) + 16, stride_bytes, reinterpret_cast<const char*>(c->p) + 12, 16, 4, m, cudaMemcpyDeviceToHost, e.stream);
+      if (cudaMemcpy2DAsync(static_cast<char*>(pts) + 16, stride_bytes, reinterpret_cast<const char*>(c->p) + 12, 16, 4, m, cudaMemcpyDeviceToHost, e.stream) != cudaSuccess) return e.fail("device copy failed");
   }
   if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
   return 0;
@@ -1001,14 +1001,15 @@ int ndtb_localmap_download(ndtb_handle* h, int which, void* pts, size_t cap, siz
 // ---- filter_node's front end (reference src/filter_node.cpp:236-262) -----------------------------------
 void ndtb_default_filter_params(ndtb_filter_params* p) { p->r_min = 1.0; p->r_max = 60.0; p->leaf = 0.5f; p->mean_k = 30; p->stddev_mul = 1.0; }
 
-static void copy_cloud_to_host(Engine& e, const float4* d, size_t m, void* pts, size_t stride_bytes) {
+static int copy_cloud_to_host(Engine& e, const float4* d, size_t m, void* pts, size_t stride_bytes) {
   if (stride_bytes == 16) {
-    cudaMemcpyAsync(pts, d, m * 16, cudaMemcpyDeviceToHost, e.stream);
+    if (cudaMemcpyAsync(pts, d, m * 16, cudaMemcpyDeviceToHost, e.stream) != cudaSuccess) return e.fail("device copy failed");
   } else {
-    cudaMemcpy2DAsync(pts, stride_bytes, d, 16, 12, m, cudaMemcpyDeviceToHost, e.stream);
+    if (cudaMemcpy2DAsync(pts, stride_bytes, d, 16, 12, m, cudaMemcpyDeviceToHost, e.stream) != cudaSuccess) return e.fail("device copy failed");
     if (stride_bytes >= 20)
-      cudaMemcpy2DAsync(static_cast<char*>(pts) + 16, stride_bytes, reinterpret_cast<const char*>(d) + 12, 16, 4, m, cudaMemcpyDeviceToHost, e.stream);
+      if (cudaMemcpy2DAsync(static_cast<char*>(pts) + 16, stride_bytes, reinterpret_cast<const char*>(d) + 12, 16, 4, m, cudaMemcpyDeviceToHost, e.stream) != cudaSuccess) return e.fail("device copy failed");
   }
+  return 0;
 }
 
 int ndtb_filter_scan(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes, const ndtb_filter_params* p, size_t counts[3]) {
@@ -1029,7 +1030,7 @@ int ndtb_filter_scan(ndtb_handle* h, const void* pts, size_t n, size_t stride_by
       e.flt_raw_cap = n + n / 4;
     }
     float4* src = e.src_pool + e.sources[0].offset;
-    cudaMemcpyAsync(e.flt_raw, src, n * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+    if (cudaMemcpyAsync(e.flt_raw, src, n * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream) != cudaSuccess) return e.fail("device copy failed");
     cudaError_t ce = filter_scan(e.flt, e.ws, e.flt_raw, n, fp.r_min, fp.r_max, fp.leaf, fp.mean_k, fp.stddev_mul, src, c, e.stream,
                                  &e.stats.kernel_launches);
     if (ce != cudaSuccess) return e.fail(std::string("filter_scan: ") + cudaGetErrorString(ce));
@@ -1048,7 +1049,7 @@ int ndtb_get_source(ndtb_handle* h, void* pts, size_t cap, size_t stride_bytes, 
   const size_t m = e.sources[0].n < cap ? e.sources[0].n : cap;
   if (n) *n = m;
   if (m == 0) return 0;
-  copy_cloud_to_host(e, e.source_ptr(e.sources[0]), m, pts, stride_bytes);
+  if (copy_cloud_to_host(e, e.source_ptr(e.sources[0]), m, pts, stride_bytes)) return 1;
   if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
   return 0;
 }
