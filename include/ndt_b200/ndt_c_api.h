@@ -193,6 +193,27 @@ int ndtb_batch_run(ndtb_batch* b, int n_items, const int* item_target, const int
  * transform: loop-closure candidates are accepted on it (reference xchu_mapping/src/pgo_node.cpp:460-476, fitness <= 0.3).
  * out: one double per item of that run (host).  Exact 1-NN over each target; one launch per distinct target. */
 int ndtb_batch_fitness(ndtb_batch* b, double max_range, double* out);
+/* ---- loop-closure submaps on the device --------------------
+ * Replaces PGO::LoopFindNearKeyframesCloud (reference xchu_mapping/src/pgo_node.cpp:530-554) and feeds the batch the
+ * clouds PGO::ICPRefine (pgo_node.cpp:404-476) registers: keyframe clouds (sensor frame) stay resident in HBM
+ * (keyframeLaserClouds, pgo_node.cpp:216); a submap is the concatenation, in ascending keyframe order, of the keyframes
+ * root - half_window .. root + half_window that exist, each moved into the map frame by its pose as
+ * PGO::TransformCloud2Map does (pgo_node.cpp:568-590: x' = ((m00 x + m01 y) + m02 z) + m03 in float, intensity kept),
+ * then pcl::VoxelGrid-downsampled at `leaf` (downSizeFilterICP, pgo_node.cpp:75, 551-552; leaf <= 0: no downsample).
+ * Keyframes survive ndtb_batch_clear; ids count from 0 in the order added. */
+int ndtb_batch_add_keyframe(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int* kf_id);
+int ndtb_batch_clear_keyframes(ndtb_batch* b);
+int ndtb_batch_num_keyframes(const ndtb_batch* b);
+/* poses: one column-major 4x4 float matrix per keyframe id (what pcl::getTransformation makes of keyframePosesUpdated[id]),
+ * n_poses of them; keyframes with id >= n_poses or id >= the number stored are skipped like the reference's range test
+ * (pgo_node.cpp:538-539).  as_target != 0: the submap becomes a batch target (id = target id), else a batch source.
+ * n_points (may be NULL) = points of the submap; an empty submap (no keyframe in range) still gets an id and holds 0 points. */
+int ndtb_batch_add_submap(ndtb_batch* b, int as_target, int root, int half_window, const float* poses, int n_poses, float leaf,
+                          int* id, size_t* n_points);
+/* Copies target / source `id` of the batch to the host (x y z at offset 0, intensity at byte 12 for 16-byte records, at
+ * byte 16 for stride_bytes >= 20): test hook, and what a caller publishing the submap needs. */
+int ndtb_batch_download(ndtb_batch* b, int is_target, int id, void* pts, size_t cap, size_t stride_bytes, size_t* n);
+
 /* Device times (ms) of the last run: voxel-table builds, derivative kernels, whole run; number of
  * kernels launched; derivative-kernel launches; (point, voxel) pairs and points evaluated. */
 typedef struct ndtb_batch_stats {

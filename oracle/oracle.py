@@ -153,6 +153,46 @@ def transform_cloud(pts, T):
     return out
 
 
+def get_transformation(x, y, z, roll, pitch, yaw):
+    """pcl::getTransformation (float overload; PCL common/eigen.h, not in /root/reference -- restated from the published
+    formula): R = Rz(yaw) Ry(pitch) Rx(roll) written out entry by entry in float, sinf/cosf per thirdparty_math.h's convention
+    ((float) of the double function).  Used by PGO::TransformCloud2Map (pgo_node.cpp:574)."""
+    import struct
+
+    def f32(v):
+        return struct.unpack("f", struct.pack("f", float(v)))[0]
+    import math
+    x, y, z, roll, pitch, yaw = (f32(v) for v in (x, y, z, roll, pitch, yaw))
+    A, B = f32(math.cos(yaw)), f32(math.sin(yaw))
+    Cc, D = f32(math.cos(pitch)), f32(math.sin(pitch))
+    E, F = f32(math.cos(roll)), f32(math.sin(roll))
+    DE, DF = f32(D * E), f32(D * F)
+    rows = [[f32(A * Cc), f32(f32(A * DF) - f32(B * E)), f32(f32(B * F) + f32(A * DE)), x],
+            [f32(B * Cc), f32(f32(A * E) + f32(B * DF)), f32(f32(B * DE) - f32(A * F)), y],
+            [f32(-D), f32(Cc * F), f32(Cc * E), z],
+            [0.0, 0.0, 0.0, 1.0]]
+    return np.array(rows, dtype=np.float32)
+
+
+def loop_find_near_keyframes_cloud(keyframes, pose_mats, key, submap_size, root_idx, leaf):
+    """PGO::LoopFindNearKeyframesCloud (pgo_node.cpp:530-554): keyframes root_idx - submap_size .. root_idx + submap_size that
+    exist, each through TransformCloud2Map with its own pose (pgo_node.cpp:542, 568-590), stacked, then downSizeFilterICP.
+    `key` is accepted and ignored exactly as the reference ignores it (pgo_node.cpp:537).  keyframes: list of (n, 4) float32;
+    pose_mats: list of 4x4 float32 (get_transformation of keyframePosesUpdated[i]).  An empty stack is returned as is
+    (pgo_node.cpp:547-548)."""
+    del key
+    parts = []
+    for i in range(-submap_size, submap_size + 1):
+        k = root_idx + i
+        if k < 0 or k >= len(keyframes):
+            continue
+        parts.append(transform_cloud(keyframes[k], pose_mats[k]))
+    if not parts or sum(p.shape[0] for p in parts) == 0:
+        return np.zeros((0, 4), dtype=np.float32)
+    near = np.ascontiguousarray(np.concatenate(parts, axis=0))
+    return voxelgrid_downsample(near, leaf) if leaf > 0 else near
+
+
 def max_threads():
     return lib().oracle_max_threads()
 

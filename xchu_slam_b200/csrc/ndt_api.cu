@@ -147,6 +147,13 @@ struct Engine {
   FilterWorkspace* flt = nullptr;    // filter_node front end (ndtb_filter_scan)
   float4* flt_raw = nullptr;
   size_t flt_raw_cap = 0;
+  // loop-closure keyframe store (ndtb_batch_add_keyframe / ndtb_batch_add_submap)
+  struct KeyFrame { float4* p = nullptr; size_t n = 0; };
+  std::vector<KeyFrame> kfs;
+  SubmapSeg* d_segs = nullptr;
+  size_t segs_cap = 0;
+  float4* kf_cat = nullptr;          // stacked, not yet downsampled submap
+  size_t kf_cat_cap = 0;
   PinnedBuf st_d2;                   // host landing zone of the per-point squared NN distances (getFitnessScore)
   PinnedBuf st_src;                  // host staging of strided sources (x y z intensity packed to 16 B)
 
@@ -206,6 +213,9 @@ struct Engine {
     st_src.release(); st_d2.release();
     filter_ws_destroy(flt); cudaFree(flt_raw);
     cudaFree(d_fit_partial); cudaFree(d_fit_out); cudaFree(d_fit_items);
+    for (auto& k : kfs) cudaFree(k.p);
+    kfs.clear();
+    cudaFree(d_segs); cudaFree(kf_cat);
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     for (auto& e : deriv_events) cudaEventDestroy(e);
     if (stream && own_stream) cudaStreamDestroy(stream);
@@ -323,6 +333,20 @@ struct Engine {
 
   // where: 0 host memory, 1 device memory (copied), 2 device memory borrowed (float4 records, no copy; the
   // caller keeps it alive until the batch is cleared).  async: host uploads go to the copy stream.
+  // room for n more points behind src_used in the source pool
+  int reserve_sources(size_t n) {
+    if (src_used + n <= src_cap) return 0;
+    const size_t nc = (src_used + n) + (src_used + n) / 2 + 4096;
+    float4* q = nullptr;
+    CKE(cudaMalloc(&q, nc * sizeof(float4)));
+    CKE(cudaStreamSynchronize(copy_stream));
+    if (src_pool && src_used) CKE(cudaMemcpyAsync(q, src_pool, src_used * sizeof(float4), cudaMemcpyDeviceToDevice, stream));
+    CKE(cudaStreamSynchronize(stream));
+    cudaFree(src_pool);
+    src_pool = q;
+    src_cap = nc;
+    return 0;
+  }
   int add_source(const void* pts, size_t n, size_t stride, int where, bool async, int* id) {
     if (where == 2) {
       if (stride != 16) return fail("a borrowed device buffer must hold 16-byte records");
@@ -330,17 +354,7 @@ struct Engine {
       if (id) *id = (int)sources.size() - 1;
       return 0;
     }
-    if (src_used + n > src_cap) {
-      const size_t nc = (src_used + n) + (src_used + n) / 2 + 4096;
-      float4* q = nullptr;
-      CKE(cudaMalloc(&q, nc * sizeof(float4)));
-      CKE(cudaStreamSynchronize(copy_stream));
-      if (src_pool && src_used) CKE(cudaMemcpyAsync(q, src_pool, src_used * sizeof(float4), cudaMemcpyDeviceToDevice, stream));
-      CKE(cudaStreamSynchronize(stream));
-      cudaFree(src_pool);
-      src_pool = q;
-      src_cap = nc;
-    }
+    if (reserve_sources(n)) return 1;
     const bool on_copy = async && where == 0;
     if (upload_points(src_pool + src_used, pts, n, stride, where == 1, on_copy ? copy_stream : stream)) return 1;
     if (on_copy) sources_pending = true;
@@ -411,7 +425,7 @@ struct Engine {
     // small blocks keep the tail iterations (few registrations still active) balanced over the 148 SMs
     int chunk = (int)((total_pts / (148 * 8) + 255) / 256 * 256);
     if (chunk < 256) chunk = 256;
-    if (chunk > 512) chunk = 512;
+    if (chunk > 1024) chunk = 1024;   // 1024 amortises the per-block set-up and reduction best (profiles/r01_v9_kernel_variants.txt)
     if (const char* ev = getenv("NDTB_CHUNK")) { const int c = atoi(ev); if (c >= 128) chunk = c; }   // tuning knob
     size_t total_blocks = 0;
     for (int i = 0; i < n_items; ++i) total_blocks += (sources[item_source[i]].n + chunk - 1) / chunk;
@@ -1170,6 +1184,140 @@ int ndtb_batch_fitness(ndtb_batch* b, double max_range, double* out) {
   if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
   return 0;
 }
+// ---- loop-closure submaps (reference src/pgo_node.cpp:404-476, 530-554, 568-590) -------------------------
+int ndtb_batch_add_keyframe(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int* kf_id) {
+  Engine& e = b->e;
+  if (cudaSetDevice(e.device) != cudaSuccess) return e.fail("cudaSetDevice failed");
+  if (n > 0 && stride_bytes < 12) return e.fail("stride_bytes must be >= 12");
+  Engine::KeyFrame k;
+  k.n = n;
+  if (n > 0) {
+    if (cudaMalloc(&k.p, n * sizeof(float4)) != cudaSuccess) return e.fail("keyframe allocation failed");
+    // x y z intensity packed on the host as ndtb_set_source does, one 16 B / point upload
+    if (cudaStreamSynchronize(e.stream) != cudaSuccess) { cudaFree(k.p); return e.fail("sync failed"); }
+    if (e.st_src.reserve(n * sizeof(float4)) != cudaSuccess) { cudaFree(k.p); return e.fail("pinned staging allocation failed"); }
+    float4* dst = static_cast<float4*>(e.st_src.h);
+    const char* src = static_cast<const char*>(pts);
+    for (size_t i = 0; i < n; ++i) {
+      const float* f = reinterpret_cast<const float*>(src + i * stride_bytes);
+      dst[i] = make_float4(f[0], f[1], f[2], stride_bytes >= 20 ? f[4] : (stride_bytes >= 16 ? f[3] : 0.f));
+    }
+    if (cudaMemcpyAsync(k.p, dst, n * sizeof(float4), cudaMemcpyHostToDevice, e.stream) != cudaSuccess ||
+        cudaStreamSynchronize(e.stream) != cudaSuccess) {
+      cudaFree(k.p);
+      return e.fail("keyframe upload failed");
+    }
+  }
+  e.kfs.push_back(k);
+  if (kf_id) *kf_id = (int)e.kfs.size() - 1;
+  return 0;
+}
+int ndtb_batch_clear_keyframes(ndtb_batch* b) {
+  Engine& e = b->e;
+  cudaSetDevice(e.device);
+  cudaStreamSynchronize(e.stream);
+  for (auto& k : e.kfs) cudaFree(k.p);
+  e.kfs.clear();
+  return 0;
+}
+int ndtb_batch_num_keyframes(const ndtb_batch* b) { return (int)b->e.kfs.size(); }
+
+int ndtb_batch_add_submap(ndtb_batch* b, int as_target, int root, int half_window, const float* poses, int n_poses, float leaf,
+                          int* id, size_t* n_points) {
+  Engine& e = b->e;
+  if (cudaSetDevice(e.device) != cudaSuccess) return e.fail("cudaSetDevice failed");
+  if (n_points) *n_points = 0;
+  if (half_window < 0) return e.fail("half_window must be >= 0");
+  std::vector<SubmapSeg> segs;
+  size_t total = 0, max_n = 0;
+  for (long long i = -(long long)half_window; i <= (long long)half_window; ++i) {
+    const long long k = (long long)root + i;
+    if (k < 0 || k >= (long long)e.kfs.size() || k >= (long long)n_poses) continue;   // pgo_node.cpp:538-539
+    const Engine::KeyFrame& kf = e.kfs[(size_t)k];
+    if (kf.n == 0) continue;
+    SubmapSeg sg;
+    sg.src = kf.p;
+    sg.offset = (long long)total;
+    sg.n = kf.n;
+    const float* T = poses + (size_t)k * 16;
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 4; ++c) sg.T[r * 4 + c] = T[c * 4 + r];
+    segs.push_back(sg);
+    total += kf.n;
+    if (kf.n > max_n) max_n = kf.n;
+  }
+  // destination: a fresh batch target, or the tail of the source pool
+  Target* t = nullptr;
+  float4* dst = nullptr;
+  if (as_target) {
+    if (e.n_targets_live == (int)e.targets.size()) e.targets.emplace_back();
+    t = &e.targets[e.n_targets_live];
+    t->n = 0;
+    t->use = nullptr;
+    t->pending_upload = false;
+    t->built = false;
+    t->ts.have_bbox = false;
+    if (e.reserve_target(*t, total)) return 1;
+    dst = t->pts;
+  } else {
+    if (e.reserve_sources(total)) return 1;
+    dst = e.src_pool + e.src_used;
+  }
+  size_t m = 0;
+  if (total > 0) {
+    const bool ds = leaf > 0.f;
+    if (ds && e.ensure(e.kf_cat, e.kf_cat_cap, total)) return 1;
+    if (e.ensure(e.d_segs, e.segs_cap, segs.size())) return 1;
+    // `segs` is pageable: the copy is staged before cudaMemcpyAsync returns
+    if (cudaMemcpyAsync(e.d_segs, segs.data(), segs.size() * sizeof(SubmapSeg), cudaMemcpyHostToDevice, e.stream) != cudaSuccess)
+      return e.fail("upload failed");
+    if (launch_submap_gather(e.d_segs, (int)segs.size(), max_n, ds ? e.kf_cat : dst, e.stream) != cudaSuccess) return e.fail("submap gather failed");
+    ++e.stats.kernel_launches;
+    m = total;
+    if (ds) {
+      cudaError_t ce = voxelgrid_downsample(e.ws, e.kf_cat, total, leaf, dst, &m, e.stream, &e.stats.kernel_launches);
+      if (ce != cudaSuccess) return e.fail(std::string("voxelgrid_downsample: ") + cudaGetErrorString(ce));
+    } else if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  }
+  if (as_target) {
+    t->n = m;
+    if (id) *id = e.n_targets_live;
+    e.n_targets_live++;
+  } else {
+    e.sources.push_back(Source{(long long)e.src_used, m, nullptr});
+    if (id) *id = (int)e.sources.size() - 1;
+    e.src_used += m;
+  }
+  if (n_points) *n_points = m;
+  return 0;
+}
+
+int ndtb_batch_download(ndtb_batch* b, int is_target, int id, void* pts, size_t cap, size_t stride_bytes, size_t* n) {
+  Engine& e = b->e;
+  if (cudaSetDevice(e.device) != cudaSuccess) return e.fail("cudaSetDevice failed");
+  if (stride_bytes < 12) return e.fail("stride_bytes must be >= 12");
+  const float4* d = nullptr;
+  size_t have = 0;
+  if (is_target) {
+    if (id < 0 || id >= e.n_targets_live) return e.fail("target id out of range");
+    const Target& t = e.targets[id];
+    if (t.pending_upload && cudaStreamSynchronize(e.copy_stream) != cudaSuccess) return e.fail("upload failed");
+    d = t.use ? t.use : t.pts;
+    have = t.n;
+  } else {
+    if (id < 0 || id >= (int)e.sources.size()) return e.fail("source id out of range");
+    if (e.sources_pending && cudaStreamSynchronize(e.copy_stream) != cudaSuccess) return e.fail("upload failed");
+    d = e.source_ptr(e.sources[id]);
+    have = e.sources[id].n;
+  }
+  const size_t m = have < cap ? have : cap;
+  if (n) *n = m;
+  if (m == 0) return 0;
+  if (copy_cloud_to_host(e, d, m, pts, stride_bytes)) return 1;
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  return 0;
+}
+
 int ndtb_batch_get_stats(ndtb_batch* b, ndtb_batch_stats* s) { *s = b->e.stats; return 0; }
 int ndtb_batch_set_stream(ndtb_batch* b, void* cuda_stream) {
   Engine& e = b->e;

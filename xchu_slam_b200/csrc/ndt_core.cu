@@ -938,6 +938,26 @@ cudaError_t launch_transform(const float4* src, size_t n, const float* T16, floa
   k_transform<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(src, n, T16, out);
   return cudaGetLastError();
 }
+// PGO::LoopFindNearKeyframesCloud (reference src/pgo_node.cpp:530-546): every keyframe of the window moved into the map
+// frame by its own pose (TransformCloud2Map, pgo_node.cpp:568-590) and stacked; one launch, blockIdx.y = keyframe.
+__global__ void k_submap_gather(const SubmapSeg* __restrict__ segs, float4* __restrict__ out) {
+  const SubmapSeg& sg = segs[blockIdx.y];
+  const float4* __restrict__ src = sg.src;
+  float4* __restrict__ dst = out + sg.offset;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < sg.n; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 p = src[i];
+    float4 o;
+    xform(sg.T, p.x, p.y, p.z, o.x, o.y, o.z);
+    o.w = p.w;
+    dst[i] = o;
+  }
+}
+cudaError_t launch_submap_gather(const SubmapSeg* segs_dev, int n_seg, size_t max_n, float4* out, cudaStream_t s) {
+  if (n_seg <= 0 || max_n == 0) return cudaSuccess;
+  const unsigned bx = (unsigned)((max_n + 255) / 256 < 64 ? (max_n + 255) / 256 : 64);
+  k_submap_gather<<<dim3(bx, (unsigned)n_seg), 256, 0, s>>>(segs_dev, out);
+  return cudaGetLastError();
+}
 cudaError_t launch_prepare_eval(AlignState* st, const float* T16, const double* p6, int mode, cudaStream_t s) {
   k_prepare_eval<<<1, 32, 0, s>>>(st, T16, p6, mode);
   return cudaGetLastError();

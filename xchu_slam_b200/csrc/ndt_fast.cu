@@ -39,6 +39,12 @@ namespace ndtb {
 #ifndef NDTB_FAST_PREFETCH   // 1 (DIRECT7): the NEXT point's source record and its seven cell codes are fetched while this point's
 #define NDTB_FAST_PREFETCH 0  //    pairs are evaluated (two of the three dependent global loads of a point leave the critical path)
 #endif
+#ifndef NDTB_FAST_AB         // 1 (DIRECT7): voxel records alternate between two register sets instead of being copied
+#define NDTB_FAST_AB 0       //    (measured 6 % slower on B200: profiles/r01_v9_kernel_variants.txt)
+#endif
+#ifndef NDTB_FAST_DENSE32    // 1 (DIRECT7): dense-index lookup with block-uniform set-up hoisted and 32-bit index arithmetic
+#define NDTB_FAST_DENSE32 1
+#endif
 constexpr int kFT = NDTB_FAST_THREADS;
 constexpr int kFAcc = 28;          // score, g[6], H upper triangle [21]
 constexpr int kFCols = kFAcc + 1;  // + pair count
@@ -141,6 +147,17 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
   const int end = min(bm.y + chunk, st.n_src);
   const FastRec* __restrict__ recs = sh.tab.frec;
   const float d2f = sh.d2f, nhalf_d2f = sh.nhalf_d2f, d1d2f = sh.d1d2f;
+  // DIRECT7 over the dense cell index, block-uniform set-up.  x / leaf == x * (1 / leaf) bit for bit when leaf is a power
+  // of two (1 / leaf is exact, both are the correctly rounded value of the same real number).
+  const int* __restrict__ dense = sh.tab.dense;
+  const int dlo0 = sh.tab.dlo[0], dlo1 = sh.tab.dlo[1], dlo2 = sh.tab.dlo[2], dn0 = sh.tab.dn[0], dn1 = sh.tab.dn[1], dn2 = sh.tab.dn[2];
+  const int sxy = dn0 * dn1;
+  const bool dense32 = NDTB_FAST_DENSE32 && METHOD == 2 && dense != nullptr && sh.tab.slots != nullptr && (long long)sxy * dn2 < (1ll << 31) &&
+                       (long long)dn0 * dn1 < (1ll << 31);
+  const float leaf = sh.tab.leaf;
+  const unsigned leaf_bits = __float_as_uint(leaf);
+  const bool pow2 = (leaf_bits & 0x807fffffu) == 0u && (leaf_bits >> 23) >= 64u && (leaf_bits >> 23) <= 190u;
+  const float inv_leaf = __fdiv_rn(1.0f, leaf);
 #if NDTB_FAST_PREFETCH
   float4 p_nx = make_float4(0.f, 0.f, 0.f, 0.f);
   float xt_nx = 0.f, yt_nx = 0.f, zt_nx = 0.f;
@@ -206,13 +223,41 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
       // no local memory); the record of cell o+1 is in flight while cell o is being evaluated.
 #if !NDTB_FAST_PREFETCH
       int v[7];
-      neighbors7(sh.tab, xt, yt, zt, v);
+      if (dense32) {
+        // neighbors7()'s dense branch with the block-uniform quantities in registers and 32-bit index arithmetic
+        const int ci = (int)floorf(pow2 ? xt * inv_leaf : __fdiv_rn(xt, leaf)), cj = (int)floorf(pow2 ? yt * inv_leaf : __fdiv_rn(yt, leaf)),
+                  ck = (int)floorf(pow2 ? zt * inv_leaf : __fdiv_rn(zt, leaf));
+        const unsigned ui = (unsigned)(ci - dlo0) - 1u, uj = (unsigned)(cj - dlo1) - 1u, uk = (unsigned)(ck - dlo2) - 1u;
+        if (ui >= (unsigned)(dn0 - 2) || uj >= (unsigned)(dn1 - 2) || uk >= (unsigned)(dn2 - 2)) continue;
+        const int* __restrict__ c = dense + (((ck - dlo2) * dn1 + (cj - dlo1)) * dn0 + (ci - dlo0));
+        v[0] = __ldg(c); v[1] = __ldg(c + 1); v[2] = __ldg(c - 1); v[3] = __ldg(c + dn0); v[4] = __ldg(c - dn0);
+        v[5] = __ldg(c + sxy); v[6] = __ldg(c - sxy);
+      } else {
+        neighbors7(sh.tab, xt, yt, zt, v);
+      }
 #endif
       int cnt = 0;
 #pragma unroll
       for (int o = 0; o < 7; ++o) cnt += v[o] >= 0 ? 1 : 0;
       if (cnt == 0) continue;
       npairs += cnt;
+#if NDTB_FAST_AB
+      // two register sets used alternately: the record of cell o+1 is already in flight when cell o is evaluated, and no
+      // register copies are needed between cells (a predicated load writes its set in place)
+      FRec rA = {}, rB = {};
+      if (v[0] >= 0) rA = load_frec(recs + v[0]);
+      if (v[1] >= 0) rB = load_frec(recs + v[1]);
+#pragma unroll
+      for (int o = 0; o < 7; ++o) {
+        if ((o & 1) == 0) {
+          if (v[o] >= 0) NDTB_PAIR(rA)
+          if (o + 2 < 7) { if (v[o + 2] >= 0) rA = load_frec(recs + v[o + 2]); }
+        } else {
+          if (v[o] >= 0) NDTB_PAIR(rB)
+          if (o + 2 < 7) { if (v[o + 2] >= 0) rB = load_frec(recs + v[o + 2]); }
+        }
+      }
+#else
       FRec nxt = {};
       if (v[0] >= 0) nxt = load_frec(recs + v[0]);
 #pragma unroll
@@ -221,6 +266,7 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
         if (o + 1 < 7) { if (v[o + 1] >= 0) nxt = load_frec(recs + v[o + 1]); }
         if (v[o] >= 0) NDTB_PAIR(r)
       }
+#endif
     } else {
       int nb[27];
       const int cnt = find_neighbors(sh.tab, METHOD, xt, yt, zt, nb);

@@ -166,6 +166,9 @@ cudaError_t launch_newton(AlignState* states, int n_items, const double* partial
 cudaError_t launch_neighbors(const VoxelTable* table, const float* xyz, size_t n, int method, int* cnt, int* ijk,
                              cudaStream_t s);
 cudaError_t launch_transform(const float4* src, size_t n, const float* T16_colmajor_dev, float4* out, cudaStream_t s);
+// One keyframe of a loop-closure submap: n points at src go to out[offset ..) through the row-major 3x4 float transform T.
+struct SubmapSeg { const float4* src; long long offset; size_t n; float T[12]; };
+cudaError_t launch_submap_gather(const SubmapSeg* segs_dev, int n_seg, size_t max_n, float4* out, cudaStream_t s);
 cudaError_t launch_prepare_eval(AlignState* st, const float* T16_dev, const double* p6_dev, int mode, cudaStream_t s);
 cudaError_t launch_pull(void* dst_dev, const void* src_mapped_dev, size_t bytes, cudaStream_t s);
 cudaError_t launch_set_int(int* dst, int v, cudaStream_t s);

@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.environ.get("NDTB_LIB", os.path.join(_HERE, "libndt_b200.so"))   # NDTB_LIB: kernel-variant experiments
+LIB_PATH = os.environ.get("NDTB_LIB") or os.path.join(_HERE, "libndt_b200.so")   # NDTB_LIB: kernel-variant experiments
 
 KDTREE, DIRECT26, DIRECT7, DIRECT1 = 0, 1, 2, 3
 
@@ -55,7 +55,8 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_batch_add_source", "ndtb_batch_wait_uploads", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream", "ndtb_batch_fitness",
            "ndtb_localmap_clear", "ndtb_localmap_append_source", "ndtb_localmap_snapshot", "ndtb_localmap_set_target",
            "ndtb_localmap_roll", "ndtb_localmap_sizes", "ndtb_localmap_download", "ndtb_default_filter_params", "ndtb_filter_scan",
-           "ndtb_get_source"]
+           "ndtb_get_source", "ndtb_batch_add_keyframe", "ndtb_batch_clear_keyframes", "ndtb_batch_num_keyframes",
+           "ndtb_batch_add_submap", "ndtb_batch_download"]
 
 _lib = None
 
@@ -106,6 +107,11 @@ def load_library():
     L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
     L.ndtb_batch_set_stream.argtypes = [vp, vp]
     L.ndtb_batch_fitness.argtypes = [vp, C.c_double, vp]
+    L.ndtb_batch_add_keyframe.argtypes = [vp, vp, sz, sz, C.POINTER(C.c_int)]
+    L.ndtb_batch_clear_keyframes.argtypes = [vp]
+    L.ndtb_batch_num_keyframes.argtypes = [vp]
+    L.ndtb_batch_add_submap.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_float, C.POINTER(C.c_int), C.POINTER(sz)]
+    L.ndtb_batch_download.argtypes = [vp, C.c_int, C.c_int, vp, sz, sz, C.POINTER(sz)]
     L.ndtb_default_filter_params.argtypes = [C.POINTER(FilterParams)]
     L.ndtb_filter_scan.argtypes = [vp, vp, sz, sz, C.POINTER(FilterParams), vp]
     L.ndtb_get_source.argtypes = [vp, vp, sz, sz, C.POINTER(sz)]
@@ -470,6 +476,36 @@ class BatchNDT:
         out = np.zeros(n_items, dtype=np.float64)
         self._ck(self._L.ndtb_batch_fitness(self._h, float(max_range), _p(out)))
         return out
+
+    # ---- loop-closure submaps on the device (pgo_node.cpp:530-554) ----
+    def add_keyframe(self, cloud):
+        """Stores a keyframe cloud (sensor frame; column 3 = intensity when present) in HBM; returns its id."""
+        cloud = _cloud(cloud)
+        i = C.c_int()
+        self._ck(self._L.ndtb_batch_add_keyframe(self._h, _p(cloud), cloud.shape[0], cloud.strides[0], C.byref(i)))
+        return i.value
+
+    def clear_keyframes(self):
+        self._ck(self._L.ndtb_batch_clear_keyframes(self._h))
+
+    def num_keyframes(self):
+        return self._L.ndtb_batch_num_keyframes(self._h)
+
+    def add_submap(self, root, half_window, poses, leaf, as_target=True):
+        """LoopFindNearKeyframesCloud: keyframes root - half_window .. root + half_window through their poses ((n, 4, 4)
+        float32, one per keyframe id), stacked, VoxelGrid(leaf).  Returns (target or source id, points)."""
+        P = np.ascontiguousarray(np.asarray(poses, dtype=np.float32).reshape(-1, 4, 4).transpose(0, 2, 1)).reshape(-1, 16)
+        i, n = C.c_int(), C.c_size_t()
+        self._ck(self._L.ndtb_batch_add_submap(self._h, int(bool(as_target)), int(root), int(half_window), _p(P), P.shape[0], float(leaf),
+                                               C.byref(i), C.byref(n)))
+        return i.value, n.value
+
+    def download(self, id, n, is_target=True):
+        """(n, 4) float32 x y z intensity of a batch target / source."""
+        out = np.zeros((n, 4), dtype=np.float32)
+        m = C.c_size_t()
+        self._ck(self._L.ndtb_batch_download(self._h, int(bool(is_target)), int(id), _p(out), n, 16, C.byref(m)))
+        return out[:m.value]
 
     def stats(self):
         s = BatchStats()
