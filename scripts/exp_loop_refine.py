@@ -38,13 +38,17 @@ def main():
             r.add_keyframe(c, p)
         t_store = time.perf_counter() - t0
         r.refine(pairs[:4])
-        ts = []
+        ts, stages = [], []
         for _ in range(5):
+            tm = {}
             t0 = time.perf_counter()
-            res = r.refine(pairs)
+            res = r.refine(pairs, timing=tm)
             ts.append(time.perf_counter() - t0)
+            stages.append(tm)
         ms = float(np.median(ts) * 1e3)
         out[mode] = {"gpu_ms_per_call": ms, "gpu_candidates_per_s": n_pairs / (ms * 1e-3), "keyframe_store_upload_s": t_store,
+                     "stage_ms": {k: float(np.median([st[k] for st in stages]) * 1e3) for k in stages[0]},
+                     "distinct_targets": len({p[0] for p in pairs}),
                      "accepted": int(sum(x["accepted"] for x in res)), "mean_iterations": float(np.mean([x["iterations"] for x in res])),
                      "mean_target_points": float(np.mean([x["n_target"] for x in res])),
                      "mean_source_points": float(np.mean([x["n_source"] for x in res]))}

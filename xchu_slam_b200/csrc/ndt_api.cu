@@ -78,10 +78,20 @@ struct Engine {
   bool own_stream = true;
   // Concurrent table builds of a batch: a few host threads, each with its own stream and workspace, so the small
   // per-target kernels (one thread per voxel, radix-sort passes) of different submaps overlap on the device.
-  static constexpr int kBuildLanes = 4;
-  cudaStream_t bstream[kBuildLanes] = {nullptr, nullptr, nullptr, nullptr};
-  BuildWorkspace* bws[kBuildLanes] = {nullptr, nullptr, nullptr, nullptr};
-  cudaEvent_t bdone[kBuildLanes] = {nullptr, nullptr, nullptr, nullptr};
+  static constexpr int kBuildLanes = 16;    // upper bound; build_lanes() of them are used
+  cudaStream_t bstream[kBuildLanes] = {};
+  BuildWorkspace* bws[kBuildLanes] = {};
+  cudaEvent_t bdone[kBuildLanes] = {};
+  // A table build is ~25 short launches and two blocking reads (bounding box, voxel count): one lane leaves the GPU idle most
+  // of the time, so several host threads build different targets on their own streams.
+  static int build_lanes() {
+    static const int n = [] {
+      int v = 12;   // 4: 8.3 ms, 8: 6.9 ms, 12: 6.5 ms, 16: 6.6 ms per 64 one-million-point submaps (B200)
+      if (const char* ev = getenv("NDTB_BUILD_LANES")) v = atoi(ev);   // tuning knob
+      return v < 1 ? 1 : (v > kBuildLanes ? kBuildLanes : v);
+    }();
+    return n;
+  }
   cudaEvent_t bstart = nullptr;
   cudaStream_t copy_stream = nullptr;      // batch uploads from host memory run here, overlapped with table builds
   cudaEvent_t sources_uploaded = nullptr;
@@ -183,7 +193,7 @@ struct Engine {
     if (!ws) return fail("workspace allocation failed");
     nn = nn_create();
     CKE(cudaMalloc(&d_active, sizeof(int)));
-    CKE(cudaHostAlloc(&h_active, sizeof(int), cudaHostAllocMapped));
+    CKE(cudaHostAlloc(&h_active, 4 * sizeof(int), cudaHostAllocMapped));   // [0] unfinished registrations, [1..2] k_replan's plan
     CKE(cudaHostGetDevicePointer(&h_active_dev, h_active, 0));
     CKE(cudaMalloc(&d_T16, 16 * sizeof(float)));
     CKE(cudaMalloc(&d_p6, 6 * sizeof(double)));
@@ -278,7 +288,7 @@ struct Engine {
       if (!t.built && t.n > 0) todo.push_back(&t);
     if (todo.empty()) return 0;
     if (todo.size() == 1) return build_target(*todo[0]);
-    const int lanes = (int)std::min<size_t>(kBuildLanes, todo.size());
+    const int lanes = (int)std::min<size_t>((size_t)build_lanes(), todo.size());
     if (!bstart) CKE(cudaEventCreateWithFlags(&bstart, cudaEventDisableTiming));
     for (int g = 0; g < lanes; ++g) {
       if (!bstream[g]) CKE(cudaStreamCreateWithFlags(&bstream[g], cudaStreamNonBlocking));
@@ -287,7 +297,7 @@ struct Engine {
     }
     CKE(cudaEventRecord(bstart, stream));
     std::string errs[kBuildLanes];
-    long long launches[kBuildLanes] = {0, 0, 0, 0};
+    long long launches[kBuildLanes] = {};
     auto work = [&](int g) {
       if (cudaSetDevice(device) != cudaSuccess) { errs[g] = "cudaSetDevice failed"; return; }
       cudaStream_t bs = bstream[g];
@@ -442,10 +452,13 @@ struct Engine {
       st.n_blocks = (st.n_src + chunk - 1) / chunk;
       for (int b = 0; b < st.n_blocks; ++b) bmap[nb_fill++] = make_int2(i, b * chunk);
     }
-    const int n_blocks = (int)nb_fill;
+    int n_blocks = (int)nb_fill;
+    // k_replan never needs more blocks than the start (chunk at its cap) or 148 * 8 + one per registration (smaller chunks)
+    const size_t blocks_cap = std::max(nb_fill, (size_t)(148 * 8 + n_items)) + 16;
+    const bool replan = n_items > 1 && !getenv("NDTB_NO_REPLAN");
     if (ensure(d_states, states_cap, (size_t)n_items)) return 1;
-    if (ensure(d_blockmap, blockmap_cap, nb_fill + 2)) return 1;
-    if (ensure(d_partials, partials_cap, nb_fill * 44 + 2)) return 1;
+    if (ensure(d_blockmap, blockmap_cap, blocks_cap)) return 1;
+    if (ensure(d_partials, partials_cap, blocks_cap * 44)) return 1;
     const bool mt_live = !((params.step_size - params.trans_eps / 2) > 0);   // NDT_I:807: the inner loop runs only then
     const int evals_per_iter = mt_live ? 12 : 1;
     const int max_evals = 1 + (params.max_iter + 2) * evals_per_iter;
@@ -482,9 +495,11 @@ struct Engine {
       if ((it + 1) % poll == 0 || it + 1 == max_evals) {
         // published by a one-thread kernel straight into mapped host memory: a D2H memcpy would queue on a copy engine
         // behind another batch's multi-megabyte uploads and stall this loop for their whole duration
+        if (replan) { CKE(launch_replan(d_states, n_items, d_blockmap, h_active_dev + 1, stream)); stats.kernel_launches++; }
         CKE(launch_publish(d_active, h_active_dev, stream));
         CKE(cudaStreamSynchronize(stream));
         if (*(volatile int*)h_active <= 0) break;
+        if (replan) { n_blocks = ((volatile int*)h_active)[1]; chunk = ((volatile int*)h_active)[2]; }
       }
     }
     CKE(cudaEventRecord(ev[3], stream));

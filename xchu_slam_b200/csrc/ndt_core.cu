@@ -975,6 +975,65 @@ cudaError_t launch_pull(void* dst_dev, const void* src_mapped_dev, size_t bytes,
   k_pull<<<blocks, 256, 0, s>>>(static_cast<uint4*>(dst_dev), static_cast<const uint4*>(src_mapped_dev), n16);
   return cudaGetLastError();
 }
+// Work decomposition of the NEXT evaluations, redone on the device whenever the host polls: only registrations still
+// running get blocks, and the block size follows the live point count (the same rule the host applies to the whole batch
+// at the start), so the tail iterations -- a few stragglers of a batch of thousands -- neither walk a grid of finished
+// blocks nor serialise 1024 points behind one block.  One block; plan = {blocks, chunk} in mapped host memory.
+__global__ void __launch_bounds__(1024) k_replan(AlignState* __restrict__ states, int n_items, int2* __restrict__ blockmap,
+                                                 int* __restrict__ plan_mapped) {
+  __shared__ unsigned long long s_pts[32];
+  __shared__ int s_scan[32];
+  __shared__ int s_base, s_chunk;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  unsigned long long pts = 0;
+  for (int i = tid; i < n_items; i += 1024)
+    if (!states[i].done) pts += (unsigned long long)states[i].n_src;
+  for (int o = 16; o; o >>= 1) pts += __shfl_down_sync(0xffffffffu, pts, o);
+  if (lane == 0) s_pts[warp] = pts;
+  __syncthreads();
+  if (tid == 0) {
+    unsigned long long tot = 0;
+    for (int w = 0; w < 32; ++w) tot += s_pts[w];
+    long long c = (long long)((tot / (148 * 8) + 255) / 256 * 256);
+    s_chunk = (int)(c < 256 ? 256 : (c > 1024 ? 1024 : c));
+    s_base = 0;
+  }
+  __syncthreads();
+  const int chunk = s_chunk;
+  for (int i0 = 0; i0 < n_items; i0 += 1024) {
+    const int i = i0 + tid;
+    int nb = 0, n_src = 0;
+    if (i < n_items && !states[i].done) { n_src = states[i].n_src; nb = (n_src + chunk - 1) / chunk; }
+    int incl = nb;
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) s_scan[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int w = s_scan[lane];
+      for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += t; }
+      s_scan[lane] = w;   // inclusive over warps
+    }
+    __syncthreads();
+    const int first = s_base + (warp ? s_scan[warp - 1] : 0) + incl - nb;
+    if (i < n_items && nb > 0) {
+      states[i].first_block = first;
+      states[i].n_blocks = nb;
+      for (int b = 0; b < nb; ++b) blockmap[first + b] = make_int2(i, b * chunk);
+    }
+    __syncthreads();
+    if (tid == 0) s_base += s_scan[31];
+    __syncthreads();
+  }
+  if (tid == 0) {
+    plan_mapped[0] = s_base;
+    plan_mapped[1] = chunk;
+    __threadfence_system();
+  }
+}
+cudaError_t launch_replan(AlignState* states, int n_items, int2* blockmap, int* plan_mapped, cudaStream_t s) {
+  k_replan<<<1, 1024, 0, s>>>(states, n_items, blockmap, plan_mapped);
+  return cudaGetLastError();
+}
 __global__ void k_set_int(int* dst, int v) { *dst = v; }
 cudaError_t launch_set_int(int* dst, int v, cudaStream_t s) {
   k_set_int<<<1, 1, 0, s>>>(dst, v);

@@ -36,8 +36,8 @@ namespace ndtb {
 #ifndef NDTB_FAST_ACC_SMEM   // 1: the 28 FP64 accumulators of a thread live in shared memory (in the reduction layout)
 #define NDTB_FAST_ACC_SMEM 0
 #endif
-#ifndef NDTB_FAST_PREFETCH   // 1 (DIRECT7): the NEXT point's source record and its seven cell codes are fetched while this point's
-#define NDTB_FAST_PREFETCH 0  //    pairs are evaluated (two of the three dependent global loads of a point leave the critical path)
+#ifndef NDTB_FAST_PFP        // 1: the thread's NEXT source record is fetched one iteration ahead; 2 (DIRECT7): and its seven cell codes
+#define NDTB_FAST_PFP 1       //    (1: -3 % kernel time, 2: +2 %, register spills; profiles/r01_v9_kernel_variants.txt)
 #endif
 #ifndef NDTB_FAST_AB         // 1 (DIRECT7): voxel records alternate between two register sets instead of being copied
 #define NDTB_FAST_AB 0       //    (measured 6 % slower on B200: profiles/r01_v9_kernel_variants.txt)
@@ -106,6 +106,47 @@ static size_t fast_smem_bytes() {
   return ((size_t)nw * kFCols * kFPad + (size_t)nw * kFCols) * sizeof(double);
 }
 
+// DIRECT7 over the dense cell index, block-uniform set-up held in registers.  x / leaf == x * (1 / leaf) bit for bit when leaf
+// is a power of two (1 / leaf is exact, both are the correctly rounded value of the same real number).
+struct Dense7 {
+  const int* dense;
+  int dlo0, dlo1, dlo2, dn0, dn1, dn2, sxy;
+  float leaf, inv_leaf;
+  bool dense32, pow2;
+};
+__device__ __forceinline__ Dense7 make_dense7(const VoxelTable& t, bool direct7) {
+  Dense7 d;
+  d.dense = t.dense;
+  d.dlo0 = t.dlo[0]; d.dlo1 = t.dlo[1]; d.dlo2 = t.dlo[2];
+  d.dn0 = t.dn[0]; d.dn1 = t.dn[1]; d.dn2 = t.dn[2];
+  d.sxy = d.dn0 * d.dn1;
+  d.dense32 = NDTB_FAST_DENSE32 && direct7 && t.dense != nullptr && t.slots != nullptr && (long long)d.dn0 * d.dn1 < (1ll << 31) &&
+              (long long)d.sxy * d.dn2 < (1ll << 31);
+  d.leaf = t.leaf;
+  const unsigned leaf_bits = __float_as_uint(d.leaf);
+  d.pow2 = (leaf_bits & 0x807fffffu) == 0u && (leaf_bits >> 23) >= 64u && (leaf_bits >> 23) <= 190u;
+  d.inv_leaf = __fdiv_rn(1.0f, d.leaf);
+  return d;
+}
+// neighbors7() (ndt_device.cuh) with the dense branch on the hoisted quantities and 32-bit index arithmetic
+__device__ __forceinline__ void lookup7(const Dense7& d, const VoxelTable& t, float xt, float yt, float zt, int* v) {
+  if (d.dense32) {
+    const int ci = (int)floorf(d.pow2 ? xt * d.inv_leaf : __fdiv_rn(xt, d.leaf)), cj = (int)floorf(d.pow2 ? yt * d.inv_leaf : __fdiv_rn(yt, d.leaf)),
+              ck = (int)floorf(d.pow2 ? zt * d.inv_leaf : __fdiv_rn(zt, d.leaf));
+    const unsigned ui = (unsigned)(ci - d.dlo0) - 1u, uj = (unsigned)(cj - d.dlo1) - 1u, uk = (unsigned)(ck - d.dlo2) - 1u;
+    if (ui >= (unsigned)(d.dn0 - 2) || uj >= (unsigned)(d.dn1 - 2) || uk >= (unsigned)(d.dn2 - 2)) {
+#pragma unroll
+      for (int o = 0; o < 7; ++o) v[o] = -1;
+      return;
+    }
+    const int* __restrict__ c = d.dense + (((ck - d.dlo2) * d.dn1 + (cj - d.dlo1)) * d.dn0 + (ci - d.dlo0));
+    v[0] = __ldg(c); v[1] = __ldg(c + 1); v[2] = __ldg(c - 1); v[3] = __ldg(c + d.dn0); v[4] = __ldg(c - d.dn0);
+    v[5] = __ldg(c + d.sxy); v[6] = __ldg(c - d.sxy);
+  } else {
+    neighbors7(t, xt, yt, zt, v);
+  }
+}
+
 template <int METHOD, bool CH>
 __global__ void __launch_bounds__(kFT, NDTB_FAST_MINBLOCKS)
 k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __restrict__ tables, const float4* __restrict__ src_pool,
@@ -147,44 +188,49 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
   const int end = min(bm.y + chunk, st.n_src);
   const FastRec* __restrict__ recs = sh.tab.frec;
   const float d2f = sh.d2f, nhalf_d2f = sh.nhalf_d2f, d1d2f = sh.d1d2f;
-  // DIRECT7 over the dense cell index, block-uniform set-up.  x / leaf == x * (1 / leaf) bit for bit when leaf is a power
-  // of two (1 / leaf is exact, both are the correctly rounded value of the same real number).
-  const int* __restrict__ dense = sh.tab.dense;
-  const int dlo0 = sh.tab.dlo[0], dlo1 = sh.tab.dlo[1], dlo2 = sh.tab.dlo[2], dn0 = sh.tab.dn[0], dn1 = sh.tab.dn[1], dn2 = sh.tab.dn[2];
-  const int sxy = dn0 * dn1;
-  const bool dense32 = NDTB_FAST_DENSE32 && METHOD == 2 && dense != nullptr && sh.tab.slots != nullptr && (long long)sxy * dn2 < (1ll << 31) &&
-                       (long long)dn0 * dn1 < (1ll << 31);
-  const float leaf = sh.tab.leaf;
-  const unsigned leaf_bits = __float_as_uint(leaf);
-  const bool pow2 = (leaf_bits & 0x807fffffu) == 0u && (leaf_bits >> 23) >= 64u && (leaf_bits >> 23) <= 190u;
-  const float inv_leaf = __fdiv_rn(1.0f, leaf);
-#if NDTB_FAST_PREFETCH
+  const Dense7 d7 = make_dense7(sh.tab, METHOD == 2);
+#if NDTB_FAST_PFP
+  // the source record (PFP >= 1) and the seven cell codes (PFP == 2) of the thread's NEXT point are fetched before this point's
+  // pairs are evaluated: one / two of the three dependent global loads of a point leave the critical path
   float4 p_nx = make_float4(0.f, 0.f, 0.f, 0.f);
+#if NDTB_FAST_PFP >= 2
   float xt_nx = 0.f, yt_nx = 0.f, zt_nx = 0.f;
   int v_nx[7];
-  if (METHOD == 2 && bm.y + tid < end) {
+#endif
+  if (bm.y + tid < end) {
     p_nx = __ldg(src + bm.y + tid);
-    xform(sh.T, p_nx.x, p_nx.y, p_nx.z, xt_nx, yt_nx, zt_nx);
-    neighbors7(sh.tab, xt_nx, yt_nx, zt_nx, v_nx);
+#if NDTB_FAST_PFP >= 2
+    if (METHOD == 2) {
+      xform(sh.T, p_nx.x, p_nx.y, p_nx.z, xt_nx, yt_nx, zt_nx);
+      lookup7(d7, sh.tab, xt_nx, yt_nx, zt_nx, v_nx);
+    }
+#endif
   }
 #endif
   for (int i = bm.y + tid; i < end; i += kFT) {
-#if NDTB_FAST_PREFETCH
-    float4 p;
+#if NDTB_FAST_PFP
+    const float4 p = p_nx;
     float xt, yt, zt;
+#if NDTB_FAST_PFP >= 2
     int v[7];
     if (METHOD == 2) {
-      p = p_nx; xt = xt_nx; yt = yt_nx; zt = zt_nx;
+      xt = xt_nx; yt = yt_nx; zt = zt_nx;
 #pragma unroll
       for (int o = 0; o < 7; ++o) v[o] = v_nx[o];
-      if (i + kFT < end) {
-        p_nx = __ldg(src + i + kFT);
-        xform(sh.T, p_nx.x, p_nx.y, p_nx.z, xt_nx, yt_nx, zt_nx);
-        neighbors7(sh.tab, xt_nx, yt_nx, zt_nx, v_nx);
-      }
     } else {
-      p = __ldg(src + i);
       xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
+    }
+#else
+    xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
+#endif
+    if (i + kFT < end) {
+      p_nx = __ldg(src + i + kFT);
+#if NDTB_FAST_PFP >= 2
+      if (METHOD == 2) {
+        xform(sh.T, p_nx.x, p_nx.y, p_nx.z, xt_nx, yt_nx, zt_nx);
+        lookup7(d7, sh.tab, xt_nx, yt_nx, zt_nx, v_nx);
+      }
+#endif
     }
 #else
     const float4 p = __ldg(src + i);
@@ -221,20 +267,9 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
     if (METHOD == 2) {
       // DIRECT7: the seven cells in the reference's order, fully unrolled and predicated (no compaction,
       // no local memory); the record of cell o+1 is in flight while cell o is being evaluated.
-#if !NDTB_FAST_PREFETCH
+#if NDTB_FAST_PFP < 2
       int v[7];
-      if (dense32) {
-        // neighbors7()'s dense branch with the block-uniform quantities in registers and 32-bit index arithmetic
-        const int ci = (int)floorf(pow2 ? xt * inv_leaf : __fdiv_rn(xt, leaf)), cj = (int)floorf(pow2 ? yt * inv_leaf : __fdiv_rn(yt, leaf)),
-                  ck = (int)floorf(pow2 ? zt * inv_leaf : __fdiv_rn(zt, leaf));
-        const unsigned ui = (unsigned)(ci - dlo0) - 1u, uj = (unsigned)(cj - dlo1) - 1u, uk = (unsigned)(ck - dlo2) - 1u;
-        if (ui >= (unsigned)(dn0 - 2) || uj >= (unsigned)(dn1 - 2) || uk >= (unsigned)(dn2 - 2)) continue;
-        const int* __restrict__ c = dense + (((ck - dlo2) * dn1 + (cj - dlo1)) * dn0 + (ci - dlo0));
-        v[0] = __ldg(c); v[1] = __ldg(c + 1); v[2] = __ldg(c - 1); v[3] = __ldg(c + dn0); v[4] = __ldg(c - dn0);
-        v[5] = __ldg(c + sxy); v[6] = __ldg(c - sxy);
-      } else {
-        neighbors7(sh.tab, xt, yt, zt, v);
-      }
+      lookup7(d7, sh.tab, xt, yt, zt, v);
 #endif
       int cnt = 0;
 #pragma unroll

@@ -171,6 +171,7 @@ struct SubmapSeg { const float4* src; long long offset; size_t n; float T[12]; }
 cudaError_t launch_submap_gather(const SubmapSeg* segs_dev, int n_seg, size_t max_n, float4* out, cudaStream_t s);
 cudaError_t launch_prepare_eval(AlignState* st, const float* T16_dev, const double* p6_dev, int mode, cudaStream_t s);
 cudaError_t launch_pull(void* dst_dev, const void* src_mapped_dev, size_t bytes, cudaStream_t s);
+cudaError_t launch_replan(AlignState* states, int n_items, int2* blockmap, int* plan_mapped_host, cudaStream_t s);
 cudaError_t launch_set_int(int* dst, int v, cudaStream_t s);
 cudaError_t launch_publish(const int* src_dev, int* dst_mapped_host, cudaStream_t s);
 cudaError_t launch_prefix_equal(const float4* a, const float4* b, size_t n, int* flag, cudaStream_t s);

@@ -85,9 +85,12 @@ class LoopRefiner:
                 P[k] = T
         return P
 
-    def refine(self, loop_pairs, download_clouds=False):
+    def refine(self, loop_pairs, download_clouds=False, timing=None):
         """loop_pairs: [(loop_kf_idx, curr_kf_idx), ...].  One batched run; per pair a dict(loop, curr, accepted, converged,
-        fitness, T (4x4 float32, the correction in the map frame), iterations, n_source, n_target [, source, target])."""
+        fitness, T (4x4 float32, the correction in the map frame), iterations, n_source, n_target [, source, target]).
+        timing: a dict that receives the host wall time (s) of the three stages (assemble, register, fitness)."""
+        import time
+        t0 = time.perf_counter()
         b = self.batch
         b.clear()
         n_kf = len(self.poses)
@@ -120,14 +123,19 @@ class LoopRefiner:
         live = [i for i, m in enumerate(meta) if m["n_source"] > 0 and m["n_target"] > 0]
         out = [dict(m, accepted=False, converged=False, fitness=float(np.finfo(np.float64).max), T=np.eye(4, dtype=np.float32),
                     iterations=0) for m in meta]
+        t1 = t2 = t3 = time.perf_counter()
         if live:
             guesses = np.tile(np.eye(4, dtype=np.float32), (len(live), 1, 1))
             res = b.run([item_t[i] for i in live], [item_s[i] for i in live], guesses)
+            t2 = time.perf_counter()
             fit = b.fitness(len(live))
+            t3 = time.perf_counter()
             for j, i in enumerate(live):
                 r = res[j]
                 out[i].update(converged=r["converged"], fitness=float(fit[j]), T=r["T"], iterations=r["iterations"],
                               accepted=bool(r["converged"] and fit[j] <= self.threshold))      # pgo_node.cpp:443
+        if timing is not None:
+            timing.update(assemble_s=t1 - t0, register_s=t2 - t1, fitness_s=t3 - t2)
         if download_clouds:
             for o in out:
                 o["source"] = b.download(o["source_id"], o["n_source"], is_target=False)
