@@ -241,6 +241,9 @@ def main():
         if dist is not None:
             dist.barrier()
 
+    # host threads building voxel tables per rank (the library's default is 12): share the host's cores between the ranks
+    if "NDTB_BUILD_LANES" not in os.environ:
+        os.environ["NDTB_BUILD_LANES"] = str(max(4, min(12, (os.cpu_count() or 16) // max(1, world))))
     from xchu_slam_b200 import ndt
     w = get_workload(a, rank, barrier)
     order = os.environ.get("NDT_BENCH_SOURCE_ORDER", "")     # experiment: point order inside each scan (results are order-independent)
@@ -394,7 +397,11 @@ def main():
                              "algorithmic_bytes_per_launch": alg_bytes / max(1, agg["deriv_launches"]),
                              "launches": int(agg["deriv_launches"]), "kernel_ms_per_launch": agg["deriv_ms"] / max(1, agg["deriv_launches"]),
                              "mean_neighbours_per_point": agg["pairs"] / max(1, agg["points"]),
-                             "kernel_share_of_step": agg["deriv_ms"] / ms},
+                             "kernel_share_of_step": agg["deriv_ms"] / ms,
+                             "note": "achieved = algorithmic bytes (16 + 8*7 + 48*neighbours per evaluated point, counted by the kernel) / "
+                                     "kernel time; the voxel records and the cell index of the submaps in flight are L2-resident, so the "
+                                     "DRAM bytes of a launch (`traffic`, one ncu capture of the 4-submap launch) are ~1 % of the algorithmic "
+                                     "bytes and frac can exceed 1: the kernel is bound by L2 gather latency and instruction issue, not HBM"},
                 "breakdown_ms_per_step": {"voxel_build": agg["build_ms"] / a.steps, "derivatives": agg["deriv_ms"] / a.steps,
                                           "device_total": agg["total_ms"] / a.steps},
                 "clocks": clocks, "converged_frac": conv / len(res),

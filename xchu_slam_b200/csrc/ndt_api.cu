@@ -473,7 +473,8 @@ struct Engine {
     CKE(launch_newton(d_states, n_items, d_partials, want_trace ? d_trace : nullptr, trace_cap, d_active, stream));
     stats.kernel_launches++;
     size_t ev_used = 0;
-    const int poll = 4;
+    int poll = 4;
+    if (const char* ev = getenv("NDTB_POLL")) { const int v = atoi(ev); if (v >= 1) poll = v; }   // tuning knob
     for (int it = 0; it < max_evals; ++it) {
       if (deriv_events.size() < ev_used + 2) {
         cudaEvent_t a, b;
