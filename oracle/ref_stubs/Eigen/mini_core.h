@@ -131,6 +131,14 @@ class DenseBase {
     return s;
   }
   Scalar norm() const { return std::sqrt(squaredNorm()); }
+  Scalar sum() const {
+    const int n = size();
+    if (n == 0) return Scalar(0);
+    Scalar s = coeffLin(0);
+    for (int k = 1; k < n; ++k) s += coeffLin(k);
+    return s;
+  }
+  Scalar mean() const { return sum() / Scalar(size()); }   // Eigen: sum() / size()
   void normalize() {
     const Scalar z = squaredNorm();
     if (z > Scalar(0)) *this /= std::sqrt(z);

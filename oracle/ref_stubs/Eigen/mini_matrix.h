@@ -115,6 +115,7 @@ class Matrix : public PlainBase<Matrix<T, R, C>, T, R, C> {
   static Matrix Zero(int n) { Matrix m; m.resize(n); m.setZero(); return m; }
   static Matrix Zero(int r, int c) { Matrix m; m.resize(r, c); m.setZero(); return m; }
   static Matrix Ones() { Matrix m; m.setOnes(); return m; }
+  static Matrix Ones(int r, int c) { Matrix m; m.resize(r, c); m.setOnes(); return m; }
   static Matrix Identity() { Matrix m; m.setIdentity(); return m; }
   static Matrix Constant(const T& v) { Matrix m; for (int k = 0; k < m.size(); ++k) m.data()[k] = v; return m; }
   static Matrix Unit(int k) { Matrix m; m.setZero(); m.data()[k] = T(1); return m; }

@@ -12,8 +12,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "ndt_b200", "ndt_c_api.h")
 
 
-def _declared():
-    txt = open(HEADER).read()
+SC_HEADER = os.path.join(ROOT, "include", "ndt_b200", "sc_c_api.h")
+
+
+def _declared(header=HEADER):
+    txt = open(header).read()
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
     return sorted(set(re.findall(r"\b(ndtb_[a-z0-9_]+)\s*\(", txt)))
 
@@ -35,12 +38,19 @@ def test_header_symbols_exported(lib):
     assert sorted(ndt.SYMBOLS) == names           # the Python mirror binds every declared entry point
     for n in names:
         assert hasattr(lib, n)
+    # ScanContext path (include/ndt_b200/sc_c_api.h), same library
+    from xchu_slam_b200 import scancontext
+    sc_names = _declared(SC_HEADER)
+    assert len(sc_names) >= 10 and set(sc_names) <= exported, sorted(set(sc_names) - exported)
+    assert sorted(scancontext.SYMBOLS) == sc_names
+    assert set(sc_names).isdisjoint(names)
 
 
 def test_no_torch_types_in_abi():
-    txt = open(HEADER).read()
-    assert "torch" not in txt and "at::" not in txt and "std::" not in txt
-    assert 'extern "C"' in txt
+    for h in (HEADER, SC_HEADER):
+        txt = open(h).read()
+        assert "torch" not in txt and "at::" not in txt and "std::" not in txt
+        assert 'extern "C"' in txt
 
 
 def test_default_params_match_reference_ctor(lib):

@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libndt_b200.so")
-SOURCES = ["voxel_build.cu", "ndt_core.cu", "ndt_fast.cu", "ndt_api.cu"]
+SOURCES = ["voxel_build.cu", "ndt_core.cu", "ndt_fast.cu", "ndt_api.cu", "scancontext.cu"]
 # ndt_fast.cu carries explicit round-to-nearest intrinsics where bits matter and wants FMA contraction elsewhere
 NO_FMAD_FALSE = {"ndt_fast.cu"}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
@@ -37,7 +37,8 @@ def build_cuda(force=False, verbose=False, defines=(), lib=None):
 
 
 def _build_cuda(force=False, verbose=False, defines=()):
-    hdrs = [os.path.join(CSRC, "ndt_internal.h"), os.path.join(CSRC, "ndt_device.cuh"), os.path.join(HERE, "..", "include", "ndt_b200", "ndt_c_api.h")]
+    hdrs = [os.path.join(CSRC, "ndt_internal.h"), os.path.join(CSRC, "ndt_device.cuh"), os.path.join(HERE, "..", "include", "ndt_b200", "ndt_c_api.h"),
+            os.path.join(HERE, "..", "include", "ndt_b200", "sc_c_api.h")]
     objs = []
     procs = []
     for src in SOURCES:
