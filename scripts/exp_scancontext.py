@@ -35,6 +35,8 @@ def main():
 
     g = scancontext.SCManager(0)
     g.add_scans(scans[:8]); g.clear()
+    t0 = time.perf_counter(); g.add_scans(scans); t_first = time.perf_counter() - t0      # includes growing the store and the buffers
+    g.clear()
     t0 = time.perf_counter(); g.add_scans(scans); t_make = time.perf_counter() - t0
     n_pairs = 65536
     i1, i2 = rng.integers(0, n_scans, n_pairs), rng.integers(0, n_scans, n_pairs)
@@ -44,7 +46,7 @@ def main():
     ts = q - 30
     g.detect(q[:8], ts[:8])
     t0 = time.perf_counter(); det = g.detect(q, ts); t_det = time.perf_counter() - t0
-    out["gpu"] = {"descriptors_per_s": n_scans / t_make, "make_ms_total": t_make * 1e3, "pair_distances_per_s": n_pairs / t_dist,
+    out["gpu"] = {"descriptors_per_s": n_scans / t_make, "make_ms_total": t_make * 1e3, "make_ms_first_call": t_first * 1e3, "pair_distances_per_s": n_pairs / t_dist,
                   "distance_ms_total": t_dist * 1e3, "detect_queries_per_s": len(q) / t_det, "detect_ms_total": t_det * 1e3,
                   "note": "host wall time of one C-ABI call each, host buffers in, results out (uploads and downloads included)"}
 

@@ -359,7 +359,8 @@ int ndtb_sc_add_scans(ndtb_sc* s, int n_scans, const void* const* pts, const siz
   offs[n_scans] = (long long)total;
   if (s->reserve(s->n + n_scans)) return 1;
   if (cudaStreamSynchronize(s->stream) != cudaSuccess) return s->fail("sync failed");     // staging may still be in flight
-  if (total > s->h_pts_cap) {
+  const bool direct = stride_bytes == 16;     // 16-byte records go up as they are (the kernel reads x y z only)
+  if (!direct && total > s->h_pts_cap) {
     cudaFreeHost(s->h_pts);
     s->h_pts = nullptr;
     s->h_pts_cap = total + total / 4 + 1024;
@@ -377,15 +378,21 @@ int ndtb_sc_add_scans(ndtb_sc* s, int n_scans, const void* const* pts, const siz
     s->offs_cap = (size_t)n_scans + 65;
     if (cudaMalloc(&s->offs, s->offs_cap * sizeof(long long)) != cudaSuccess) { s->offs_cap = 0; return s->fail("offset buffer allocation failed"); }
   }
-  for (int i = 0; i < n_scans; ++i) {
-    const char* src = static_cast<const char*>(pts[i]);
-    float4* dst = s->h_pts + offs[i];
-    for (size_t j = 0; j < n_points[i]; ++j) {
-      const float* f = reinterpret_cast<const float*>(src + j * stride_bytes);
-      dst[j] = make_float4(f[0], f[1], f[2], 0.f);
+  if (direct) {
+    for (int i = 0; i < n_scans; ++i)
+      if (n_points[i] && cudaMemcpyAsync(s->pts + offs[i], pts[i], n_points[i] * sizeof(float4), cudaMemcpyHostToDevice, s->stream) != cudaSuccess)
+        return s->fail("upload failed");
+  } else {
+    for (int i = 0; i < n_scans; ++i) {
+      const char* src = static_cast<const char*>(pts[i]);
+      float4* dst = s->h_pts + offs[i];
+      for (size_t j = 0; j < n_points[i]; ++j) {
+        const float* f = reinterpret_cast<const float*>(src + j * stride_bytes);
+        dst[j] = make_float4(f[0], f[1], f[2], 0.f);
+      }
     }
+    if (total && cudaMemcpyAsync(s->pts, s->h_pts, total * sizeof(float4), cudaMemcpyHostToDevice, s->stream) != cudaSuccess) return s->fail("upload failed");
   }
-  if (total && cudaMemcpyAsync(s->pts, s->h_pts, total * sizeof(float4), cudaMemcpyHostToDevice, s->stream) != cudaSuccess) return s->fail("upload failed");
   if (cudaMemcpyAsync(s->offs, offs.data(), offs.size() * sizeof(long long), cudaMemcpyHostToDevice, s->stream) != cudaSuccess) return s->fail("upload failed");
   const size_t RS = (size_t)s->p.num_ring * s->p.num_sector;
   const size_t smem = RS * sizeof(double) + RS * sizeof(int);
