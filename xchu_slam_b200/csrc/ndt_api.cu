@@ -1168,7 +1168,14 @@ int ndtb_batch_fitness(ndtb_batch* b, double max_range, double* out) {
   const int n = (int)e.last_item_target.size();
   if (n == 0) return e.fail("ndtb_batch_fitness needs a completed ndtb_batch_run");
   if (cudaSetDevice(e.device) != cudaSuccess) return e.fail("cudaSetDevice failed");
-  const int bpi = 8;   // blocks per registration
+  // blocks per registration: 8 when many registrations share a target (the C5 batch), up to 160 when each target has one
+  // (loop-closure candidates), so that a launch always fills the device
+  int g_max = 1;
+  {
+    std::vector<int> cnt(e.targets.size(), 0);
+    for (int i = 0; i < n; ++i) g_max = std::max(g_max, ++cnt[e.last_item_target[i]]);
+  }
+  const int bpi = std::min(160, std::max(8, (148 * 8 + g_max - 1) / g_max));
   if (e.ensure(e.d_fit_partial, e.fit_partial_cap, (size_t)n * bpi * 2)) return 1;
   if (e.ensure(e.d_fit_out, e.fit_out_cap, (size_t)n)) return 1;
   if (e.ensure(e.d_fit_items, e.fit_items_cap, (size_t)n)) return 1;

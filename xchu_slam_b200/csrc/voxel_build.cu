@@ -177,16 +177,27 @@ __global__ void k_minmax(const float4* __restrict__ pts, size_t n, float* __rest
       mn[a] = fminf(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
       mx[a] = fmaxf(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
     }
-  if ((threadIdx.x & 31) == 0) {
+  // warps of the block through shared memory, then ONE set of six atomics per block (a million-point cloud used to end in
+  // ~47k atomics on six addresses, which took longer than reading the points)
+  __shared__ float s_mn[8][3], s_mx[8][3];
+  const int warp = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0)
+    for (int a = 0; a < 3; ++a) { s_mn[warp][a] = mn[a]; s_mx[warp][a] = mx[a]; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    const int a = threadIdx.x, nw = (blockDim.x + 31) >> 5;
+    float lo = s_mn[0][a], hi = s_mx[0][a];
+    for (int w = 1; w < nw; ++w) { lo = fminf(lo, s_mn[w][a]); hi = fmaxf(hi, s_mx[w][a]); }
     auto enc = [](float f) { int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7FFFFFFF; };
     int* o = reinterpret_cast<int*>(out6);
-    for (int a = 0; a < 3; ++a) { atomicMin(&o[a], enc(mn[a])); atomicMax(&o[3 + a], enc(mx[a])); }
+    atomicMin(&o[a], enc(lo));
+    atomicMax(&o[3 + a], enc(hi));
   }
 }
-// grid for k_minmax: enough blocks for the points, at most 8 per SM (every warp ends in six atomics)
+// grid for k_minmax (256 threads): enough blocks for the points, at most 4 per SM
 static inline unsigned minmax_grid(size_t n) {
-  const size_t b = (n + 1023) / 1024;   // 4 points per thread
-  return (unsigned)(b < 1 ? 1 : (b > 148 * 8 ? 148 * 8 : b));
+  const size_t b = (n + 1023) / 1024;   // >= 4 points per thread
+  return (unsigned)(b < 1 ? 1 : (b > 148 * 4 ? 148 * 4 : b));
 }
 __global__ void k_minmax_init(float* out6) {
   int* o = reinterpret_cast<int*>(out6);
