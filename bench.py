@@ -283,6 +283,12 @@ def main():
     it, isrc, G = w["item_target"], w["item_source"], w["guesses"]
 
     upload_lock, compute_lock = threading.Lock(), threading.Lock()
+    # the clouds stay where they are between steps: their pointer tables are built once, a step hands them over in two calls
+    PT = ndt.BatchNDT.pointer_table
+    tab_tg_host = PT([t.data_ptr() for t in tg_host], [t.shape[0] for t in tg_host])
+    tab_sc_host = PT([s.data_ptr() for s in sc_host], [s.shape[0] for s in sc_host])
+    tab_tg_dev = PT([t.data_ptr() for t in tg_dev], [t.shape[0] for t in tg_dev])
+    tab_sc_dev = PT([s.data_ptr() for s in sc_dev], [s.shape[0] for s in sc_dev])
 
     def step(resident, b=None, pipelined=False):
         """pipelined (several batches in flight): a two-stage pipeline -- one batch uploads while another computes."""
@@ -290,25 +296,19 @@ def main():
         if pipelined:
             with upload_lock:
                 b.clear()
-                for t in tg_host:
-                    b.add_target_ptr(t.data_ptr(), t.shape[0], 16, 0)
-                for s in sc_host:
-                    b.add_source_ptr(s.data_ptr(), s.shape[0], 16, 0)
+                b.add_targets_ptr(tab_tg_host, 16, 0)
+                b.add_sources_ptr(tab_sc_host, 16, 0)
                 b.wait_uploads()
             with compute_lock:
                 res = b.run_raw(it, isrc, G)
                 return res, b.stats()
         b.clear()
         if resident:
-            for t in tg_dev:
-                b.add_target_ptr(t.data_ptr(), t.shape[0], 16, 2)     # resident in HBM: borrowed in place
-            for s in sc_dev:
-                b.add_source_ptr(s.data_ptr(), s.shape[0], 16, 2)
+            b.add_targets_ptr(tab_tg_dev, 16, 2)      # resident in HBM: borrowed in place
+            b.add_sources_ptr(tab_sc_dev, 16, 2)
         else:
-            for t in tg_host:
-                b.add_target_ptr(t.data_ptr(), t.shape[0], 16, 0)     # pinned host memory: H2D inside the call
-            for s in sc_host:
-                b.add_source_ptr(s.data_ptr(), s.shape[0], 16, 0)
+            b.add_targets_ptr(tab_tg_host, 16, 0)     # pinned host memory: H2D inside the call
+            b.add_sources_ptr(tab_sc_host, 16, 0)
         res = b.run_raw(it, isrc, G)  # returns after the device finished and the result records are on the host
         return res, b.stats()
 

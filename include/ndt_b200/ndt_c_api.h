@@ -182,6 +182,10 @@ int ndtb_batch_set_params(ndtb_batch* b, const ndtb_params* p);
 int ndtb_batch_clear(ndtb_batch* b);
 int ndtb_batch_add_target(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int on_device, int* id);
 int ndtb_batch_add_source(ndtb_batch* b, const void* pts, size_t n, size_t stride_bytes, int on_device, int* id);
+/* The same for n clouds in one call (pts[i]: ns[i] records of stride_bytes): ids first_id .. first_id + n - 1.  A batch of
+ * thousands of scans is registered with two calls instead of thousands. */
+int ndtb_batch_add_targets(ndtb_batch* b, int n, const void* const* pts, const size_t* ns, size_t stride_bytes, int on_device, int* first_id);
+int ndtb_batch_add_sources(ndtb_batch* b, int n, const void* const* pts, const size_t* ns, size_t stride_bytes, int on_device, int* first_id);
 /* Blocks until every host upload enqueued by ndtb_batch_add_* so far has landed in HBM (lets a caller with several
  * batches in flight stage one batch's uploads behind another batch's compute). */
 int ndtb_batch_wait_uploads(ndtb_batch* b);

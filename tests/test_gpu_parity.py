@@ -334,6 +334,16 @@ def test_batch_matches_single(case_small):
         assert r["score"] == s["score"]
     st = b.stats()
     assert st["deriv_launches"] > 0 and st["pairs_evaluated"] > 0
+    # the same clouds registered through the many-clouds-per-call entry points (ndtb_batch_add_targets / _sources)
+    b2 = ndt.BatchNDT()
+    b2.set_params(trans_eps=0.01, max_iter=30)
+    tg = [np.ascontiguousarray(tgt, dtype=np.float32), np.ascontiguousarray(tgt[:50000], dtype=np.float32)]
+    sc = [np.ascontiguousarray(src, dtype=np.float32), np.ascontiguousarray(src[:3000], dtype=np.float32)]
+    assert b2.add_targets_ptr(ndt.BatchNDT.pointer_table([a.ctypes.data for a in tg], [a.shape[0] for a in tg]), 16, 0) == 0
+    assert b2.add_sources_ptr(ndt.BatchNDT.pointer_table([a.ctypes.data for a in sc], [a.shape[0] for a in sc]), 16, 0) == 0
+    res2 = b2.run(items_t, items_s, guesses + guesses[:2])
+    for r, q in zip(res, res2):
+        assert r["iterations"] == q["iterations"] and np.array_equal(r["T"], q["T"]) and r["score"] == q["score"]
 
 
 @pytest.mark.parametrize("method", [2, 3, 0])

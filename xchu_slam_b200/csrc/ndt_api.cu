@@ -3,6 +3,8 @@
 // Host logic mirrors pcl::Registration::align + pclomp::NormalDistributionsTransform
 // (reference xchu_mapping/include/pclomp/ndt_omp.h:110-278, ndt_omp_impl.hpp:73-164).
 #include <algorithm>
+#include <atomic>
+#include <functional>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -282,12 +284,16 @@ struct Engine {
   // Builds every target that needs it.  One target: on the engine's stream.  Several: kBuildLanes host threads, each
   // driving its own stream / workspace (table_append synchronises its stream three times per target; a thread per
   // lane keeps those waits from serialising the lanes).  The engine's stream then waits for every lane.
-  int build_pending_targets() {
+  // `overlap` (host-only work of the caller, e.g. filling the registration states) runs on the calling thread while the other
+  // lanes are already building; targets are handed out dynamically, so the calling thread joins in late at no cost.
+  int build_pending_targets(const std::function<void()>& overlap = std::function<void()>()) {
     std::vector<Target*> todo;
     for (auto& t : targets)
       if (!t.built && t.n > 0) todo.push_back(&t);
-    if (todo.empty()) return 0;
-    if (todo.size() == 1) return build_target(*todo[0]);
+    if (todo.size() <= 1) {
+      if (overlap) overlap();
+      return todo.empty() ? 0 : build_target(*todo[0]);
+    }
     const int lanes = (int)std::min<size_t>((size_t)build_lanes(), todo.size());
     if (!bstart) CKE(cudaEventCreateWithFlags(&bstart, cudaEventDisableTiming));
     for (int g = 0; g < lanes; ++g) {
@@ -298,11 +304,12 @@ struct Engine {
     CKE(cudaEventRecord(bstart, stream));
     std::string errs[kBuildLanes];
     long long launches[kBuildLanes] = {};
+    std::atomic<size_t> next{0};
     auto work = [&](int g) {
       if (cudaSetDevice(device) != cudaSuccess) { errs[g] = "cudaSetDevice failed"; return; }
       cudaStream_t bs = bstream[g];
       cudaError_t ce = cudaStreamWaitEvent(bs, bstart, 0);
-      for (size_t k = g; k < todo.size() && ce == cudaSuccess; k += lanes) {
+      for (size_t k = next.fetch_add(1); k < todo.size() && ce == cudaSuccess; k = next.fetch_add(1)) {
         Target& t = *todo[k];
         table_config(t);
         if (t.pending_upload) { ce = cudaStreamWaitEvent(bs, t.uploaded, 0); t.pending_upload = false; }
@@ -315,6 +322,7 @@ struct Engine {
     };
     std::vector<std::thread> th;
     for (int g = 1; g < lanes; ++g) th.emplace_back(work, g);
+    if (overlap) overlap();
     work(0);
     for (auto& x : th) x.join();
     for (int g = 0; g < lanes; ++g) {
@@ -420,11 +428,6 @@ struct Engine {
     CKE(cudaSetDevice(device));
     last_item_target.assign(item_target, item_target + n_items);
     stats = ndtb_batch_stats{};
-    CKE(cudaEventRecord(ev[0], stream));
-    if (build_pending_targets()) return 1;
-    CKE(cudaEventRecord(ev[1], stream));
-    if (sources_pending) { CKE(cudaStreamWaitEvent(stream, sources_uploaded, 0)); sources_pending = false; }
-    if (sync_tables()) return 1;
     // work decomposition: one block per `chunk` source points of one registration
     size_t total_pts = 0;
     for (int i = 0; i < n_items; ++i) {
@@ -439,33 +442,45 @@ struct Engine {
     if (const char* ev = getenv("NDTB_CHUNK")) { const int c = atoi(ev); if (c >= 128) chunk = c; }   // tuning knob
     size_t total_blocks = 0;
     for (int i = 0; i < n_items; ++i) total_blocks += (sources[item_source[i]].n + chunk - 1) / chunk;
+    CKE(cudaStreamSynchronize(stream));     // the staging buffers may still be read by the previous run's pulls
     CKE(st_states.reserve((size_t)n_items * sizeof(AlignState)));
     CKE(st_bmap.reserve(total_blocks * sizeof(int2) + 16));
     h_states = static_cast<AlignState*>(st_states.h);
     int2* bmap = static_cast<int2*>(st_bmap.h);
     size_t nb_fill = 0;
-    for (int i = 0; i < n_items; ++i) {
-      AlignState& st = h_states[i];
-      fill_state(st, item_target[i], sources[item_source[i]], guesses + (size_t)i * 16);
-      if (!targets[item_target[i]].ts.valid) st.req.search_method = params.search_method;  // empty grid: no neighbours at all
-      st.first_block = (int)nb_fill;
-      st.n_blocks = (st.n_src + chunk - 1) / chunk;
-      for (int b = 0; b < st.n_blocks; ++b) bmap[nb_fill++] = make_int2(i, b * chunk);
-    }
-    int n_blocks = (int)nb_fill;
+    // the registration states and the block map are filled on this thread WHILE the other lanes build the voxel tables
     // k_replan never needs more blocks than the start (chunk at its cap) or 148 * 8 + one per registration (smaller chunks)
-    const size_t blocks_cap = std::max(nb_fill, (size_t)(148 * 8 + n_items)) + 16;
-    const bool replan = n_items > 1 && !getenv("NDTB_NO_REPLAN");
+    const size_t blocks_cap = std::max(total_blocks, (size_t)(148 * 8 + n_items)) + 16;
+    // (a block size forced through NDTB_CHUNK may exceed the planner's cap, which is what blocks_cap assumes: no re-planning then)
+    const bool replan = n_items > 1 && !getenv("NDTB_NO_REPLAN") && !getenv("NDTB_CHUNK");
     if (ensure(d_states, states_cap, (size_t)n_items)) return 1;
     if (ensure(d_blockmap, blockmap_cap, blocks_cap)) return 1;
     if (ensure(d_partials, partials_cap, blocks_cap * 44)) return 1;
+    cudaError_t pull_err = cudaSuccess;
+    auto fill = [&]() {
+      for (int i = 0; i < n_items; ++i) {
+        AlignState& st = h_states[i];
+        fill_state(st, item_target[i], sources[item_source[i]], guesses + (size_t)i * 16);
+        st.first_block = (int)nb_fill;
+        st.n_blocks = (st.n_src + chunk - 1) / chunk;
+        for (int b = 0; b < st.n_blocks; ++b) bmap[nb_fill++] = make_int2(i, b * chunk);
+      }
+      // ... and pulled into HBM on the engine's stream, also under the builds (which run on the lanes' own streams)
+      pull_err = launch_pull(d_states, st_states.d, (size_t)n_items * sizeof(AlignState), stream);
+      if (pull_err == cudaSuccess) pull_err = launch_pull(d_blockmap, st_bmap.d, nb_fill * sizeof(int2), stream);
+    };
+    CKE(cudaEventRecord(ev[0], stream));
+    if (build_pending_targets(fill)) return 1;
+    CKE(pull_err);
+    CKE(cudaEventRecord(ev[1], stream));
+    if (sources_pending) { CKE(cudaStreamWaitEvent(stream, sources_uploaded, 0)); sources_pending = false; }
+    if (sync_tables()) return 1;
+    int n_blocks = (int)nb_fill;
     const bool mt_live = !((params.step_size - params.trans_eps / 2) > 0);   // NDT_I:807: the inner loop runs only then
     const int evals_per_iter = mt_live ? 12 : 1;
     const int max_evals = 1 + (params.max_iter + 2) * evals_per_iter;
     trace_cap = want_trace ? max_evals + 1 : 0;
     if (want_trace && ensure(d_trace, trace_doubles, (size_t)n_items * trace_cap * kTraceRec)) return 1;
-    CKE(launch_pull(d_states, st_states.d, (size_t)n_items * sizeof(AlignState), stream));
-    CKE(launch_pull(d_blockmap, st_bmap.d, nb_fill * sizeof(int2), stream));
     CKE(launch_set_int(d_active, n_items, stream));
     stats.kernel_launches += 3;
     CKE(cudaEventRecord(ev[2], stream));
@@ -1148,6 +1163,18 @@ int ndtb_batch_add_source(ndtb_batch* b, const void* pts, size_t n, size_t strid
   cudaSetDevice(e.device);
   if (e.add_source(pts, n, stride_bytes, on_device, true, id)) return 1;
   if (on_device == 0 && cudaEventRecord(e.sources_uploaded, e.copy_stream) != cudaSuccess) return e.fail("event record failed");
+  return 0;
+}
+int ndtb_batch_add_targets(ndtb_batch* b, int n, const void* const* pts, const size_t* ns, size_t stride_bytes, int on_device, int* first_id) {
+  if (first_id) *first_id = b->e.n_targets_live;
+  for (int i = 0; i < n; ++i)
+    if (ndtb_batch_add_target(b, pts[i], ns[i], stride_bytes, on_device, nullptr)) return 1;
+  return 0;
+}
+int ndtb_batch_add_sources(ndtb_batch* b, int n, const void* const* pts, const size_t* ns, size_t stride_bytes, int on_device, int* first_id) {
+  if (first_id) *first_id = (int)b->e.sources.size();
+  for (int i = 0; i < n; ++i)
+    if (ndtb_batch_add_source(b, pts[i], ns[i], stride_bytes, on_device, nullptr)) return 1;
   return 0;
 }
 int ndtb_batch_wait_uploads(ndtb_batch* b) {

@@ -56,7 +56,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_localmap_clear", "ndtb_localmap_append_source", "ndtb_localmap_snapshot", "ndtb_localmap_set_target",
            "ndtb_localmap_roll", "ndtb_localmap_sizes", "ndtb_localmap_download", "ndtb_default_filter_params", "ndtb_filter_scan",
            "ndtb_get_source", "ndtb_batch_add_keyframe", "ndtb_batch_clear_keyframes", "ndtb_batch_num_keyframes",
-           "ndtb_batch_add_submap", "ndtb_batch_download"]
+           "ndtb_batch_add_submap", "ndtb_batch_download", "ndtb_batch_add_targets", "ndtb_batch_add_sources"]
 
 _lib = None
 
@@ -102,6 +102,8 @@ def load_library():
     L.ndtb_batch_clear.argtypes = [vp]
     L.ndtb_batch_add_target.argtypes = [vp, vp, sz, sz, C.c_int, C.POINTER(C.c_int)]
     L.ndtb_batch_add_source.argtypes = [vp, vp, sz, sz, C.c_int, C.POINTER(C.c_int)]
+    L.ndtb_batch_add_targets.argtypes = [vp, C.c_int, vp, vp, sz, C.c_int, C.POINTER(C.c_int)]
+    L.ndtb_batch_add_sources.argtypes = [vp, C.c_int, vp, vp, sz, C.c_int, C.POINTER(C.c_int)]
     L.ndtb_batch_wait_uploads.argtypes = [vp]
     L.ndtb_batch_run.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
@@ -448,6 +450,23 @@ class BatchNDT:
     def add_source_ptr(self, ptr, n, stride=16, on_device=True):
         i = C.c_int()
         self._ck(self._L.ndtb_batch_add_source(self._h, C.c_void_p(ptr), n, stride, int(on_device), C.byref(i)))
+        return i.value
+
+    @staticmethod
+    def pointer_table(ptrs, ns):
+        """(void*[n], size_t[n]) for add_targets_ptr / add_sources_ptr; build it once for clouds that stay where they are."""
+        n = len(ptrs)
+        return (C.c_void_p * n)(*ptrs), (C.c_size_t * n)(*ns), n
+
+    def add_targets_ptr(self, table, stride=16, on_device=True):
+        """Many clouds in one C-ABI call; table = BatchNDT.pointer_table(pointers, sizes).  Returns the first id."""
+        i = C.c_int()
+        self._ck(self._L.ndtb_batch_add_targets(self._h, table[2], table[0], table[1], stride, int(on_device), C.byref(i)))
+        return i.value
+
+    def add_sources_ptr(self, table, stride=16, on_device=True):
+        i = C.c_int()
+        self._ck(self._L.ndtb_batch_add_sources(self._h, table[2], table[0], table[1], stride, int(on_device), C.byref(i)))
         return i.value
 
     def wait_uploads(self):
