@@ -214,6 +214,10 @@ int ndtb_batch_num_keyframes(const ndtb_batch* b);
  * n_points (may be NULL) = points of the submap; an empty submap (no keyframe in range) still gets an id and holds 0 points. */
 int ndtb_batch_add_submap(ndtb_batch* b, int as_target, int root, int half_window, const float* poses, int n_poses, float leaf,
                           int* id, size_t* n_points);
+/* n submaps in one call (arrays of n; poses / n_poses / leaf shared): the batch's build lanes assemble them concurrently.
+ * ids[j] / n_points[j] as ndtb_batch_add_submap returns them. */
+int ndtb_batch_add_submaps(ndtb_batch* b, int n, const int* as_target, const int* root, const int* half_window, const float* poses,
+                           int n_poses, float leaf, int* ids, size_t* n_points);
 /* Copies target / source `id` of the batch to the host (x y z at offset 0, intensity at byte 12 for 16-byte records, at
  * byte 16 for stride_bytes >= 20): test hook, and what a caller publishing the submap needs. */
 int ndtb_batch_download(ndtb_batch* b, int is_target, int id, void* pts, size_t cap, size_t stride_bytes, size_t* n);

@@ -166,6 +166,10 @@ struct Engine {
   size_t segs_cap = 0;
   float4* kf_cat = nullptr;          // stacked, not yet downsampled submap
   size_t kf_cat_cap = 0;
+  float4* lane_cat[16] = {};         // the same per build lane (ndtb_batch_add_submaps)
+  size_t lane_cat_cap[16] = {};
+  SubmapSeg* lane_segs[16] = {};
+  size_t lane_segs_cap[16] = {};
   PinnedBuf st_d2;                   // host landing zone of the per-point squared NN distances (getFitnessScore)
   PinnedBuf st_src;                  // host staging of strided sources (x y z intensity packed to 16 B)
 
@@ -228,6 +232,7 @@ struct Engine {
     for (auto& k : kfs) cudaFree(k.p);
     kfs.clear();
     cudaFree(d_segs); cudaFree(kf_cat);
+    for (int g = 0; g < 16; ++g) { cudaFree(lane_cat[g]); cudaFree(lane_segs[g]); }
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     for (auto& e : deriv_events) cudaEventDestroy(e);
     if (stream && own_stream) cudaStreamDestroy(stream);
@@ -284,6 +289,15 @@ struct Engine {
   // Builds every target that needs it.  One target: on the engine's stream.  Several: kBuildLanes host threads, each
   // driving its own stream / workspace (table_append synchronises its stream three times per target; a thread per
   // lane keeps those waits from serialising the lanes).  The engine's stream then waits for every lane.
+  int ensure_lanes(int lanes) {
+    if (!bstart) CKE(cudaEventCreateWithFlags(&bstart, cudaEventDisableTiming));
+    for (int g = 0; g < lanes; ++g) {
+      if (!bstream[g]) CKE(cudaStreamCreateWithFlags(&bstream[g], cudaStreamNonBlocking));
+      if (!bdone[g]) CKE(cudaEventCreateWithFlags(&bdone[g], cudaEventDisableTiming));
+      if (!bws[g]) { bws[g] = build_ws_create(); if (!bws[g]) return fail("workspace allocation failed"); }
+    }
+    return 0;
+  }
   // `overlap` (host-only work of the caller, e.g. filling the registration states) runs on the calling thread while the other
   // lanes are already building; targets are handed out dynamically, so the calling thread joins in late at no cost.
   int build_pending_targets(const std::function<void()>& overlap = std::function<void()>()) {
@@ -295,12 +309,7 @@ struct Engine {
       return todo.empty() ? 0 : build_target(*todo[0]);
     }
     const int lanes = (int)std::min<size_t>((size_t)build_lanes(), todo.size());
-    if (!bstart) CKE(cudaEventCreateWithFlags(&bstart, cudaEventDisableTiming));
-    for (int g = 0; g < lanes; ++g) {
-      if (!bstream[g]) CKE(cudaStreamCreateWithFlags(&bstream[g], cudaStreamNonBlocking));
-      if (!bdone[g]) CKE(cudaEventCreateWithFlags(&bdone[g], cudaEventDisableTiming));
-      if (!bws[g]) { bws[g] = build_ws_create(); if (!bws[g]) return fail("workspace allocation failed"); }
-    }
+    if (ensure_lanes(lanes)) return 1;
     CKE(cudaEventRecord(bstart, stream));
     std::string errs[kBuildLanes];
     long long launches[kBuildLanes] = {};
@@ -1339,6 +1348,115 @@ int ndtb_batch_add_submap(ndtb_batch* b, int as_target, int root, int half_windo
     e.src_used += m;
   }
   if (n_points) *n_points = m;
+  return 0;
+}
+
+// Many submaps in one call: destinations are reserved up front, then the build lanes (host threads with their own streams
+// and sort workspaces) assemble different submaps concurrently -- a submap is ~15 short launches and two blocking reads.
+int ndtb_batch_add_submaps(ndtb_batch* b, int n, const int* as_target, const int* root, const int* half_window, const float* poses,
+                           int n_poses, float leaf, int* ids, size_t* n_points) {
+  Engine& e = b->e;
+  if (cudaSetDevice(e.device) != cudaSuccess) return e.fail("cudaSetDevice failed");
+  if (n <= 0) return 0;
+  struct Job { std::vector<SubmapSeg> segs; size_t total = 0, max_n = 0, m = 0; float4* dst = nullptr; int tslot = -1; long long soff = -1; };
+  std::vector<Job> jobs((size_t)n);
+  size_t src_total = 0;
+  for (int j = 0; j < n; ++j) {
+    if (half_window[j] < 0) return e.fail("half_window must be >= 0");
+    Job& jb = jobs[j];
+    for (long long i = -(long long)half_window[j]; i <= (long long)half_window[j]; ++i) {
+      const long long k = (long long)root[j] + i;
+      if (k < 0 || k >= (long long)e.kfs.size() || k >= (long long)n_poses) continue;   // pgo_node.cpp:538-539
+      const Engine::KeyFrame& kf = e.kfs[(size_t)k];
+      if (kf.n == 0) continue;
+      SubmapSeg sg;
+      sg.src = kf.p;
+      sg.offset = (long long)jb.total;
+      sg.n = kf.n;
+      const float* T = poses + (size_t)k * 16;
+      for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) sg.T[r * 4 + c] = T[c * 4 + r];
+      jb.segs.push_back(sg);
+      jb.total += kf.n;
+      if (kf.n > jb.max_n) jb.max_n = kf.n;
+    }
+    if (!as_target[j]) src_total += jb.total;
+  }
+  // destinations: target slots first (the vector may grow), one reservation of the source pool for all source submaps
+  for (int j = 0; j < n; ++j) {
+    if (!as_target[j]) continue;
+    if (e.n_targets_live == (int)e.targets.size()) e.targets.emplace_back();
+    jobs[j].tslot = e.n_targets_live++;
+    if (ids) ids[j] = jobs[j].tslot;
+  }
+  for (int j = 0; j < n; ++j) {
+    if (jobs[j].tslot < 0) continue;
+    Target& t = e.targets[jobs[j].tslot];
+    t.n = 0; t.use = nullptr; t.pending_upload = false; t.built = false; t.ts.have_bbox = false;
+    if (e.reserve_target(t, jobs[j].total)) return 1;
+    jobs[j].dst = t.pts;
+  }
+  if (e.reserve_sources(src_total)) return 1;
+  for (int j = 0; j < n; ++j) {
+    if (as_target[j]) continue;
+    jobs[j].soff = (long long)e.src_used;
+    jobs[j].dst = e.src_pool + e.src_used;
+    e.src_used += jobs[j].total;                 // a source keeps the room of its undownsampled stack
+  }
+  const int lanes = (int)std::min<size_t>((size_t)Engine::build_lanes(), (size_t)n);
+  if (e.ensure_lanes(lanes)) return 1;
+  if (cudaEventRecord(e.bstart, e.stream) != cudaSuccess) return e.fail("event record failed");
+  std::string errs[Engine::kBuildLanes];
+  long long launches[Engine::kBuildLanes] = {};
+  std::atomic<int> next{0};
+  const bool ds = leaf > 0.f;
+  auto work = [&](int g) {
+    if (cudaSetDevice(e.device) != cudaSuccess) { errs[g] = "cudaSetDevice failed"; return; }
+    cudaStream_t bs = e.bstream[g];
+    if (cudaStreamWaitEvent(bs, e.bstart, 0) != cudaSuccess) { errs[g] = "stream wait failed"; return; }
+    for (int j = next.fetch_add(1); j < n; j = next.fetch_add(1)) {
+      Job& jb = jobs[j];
+      if (jb.total == 0) continue;
+      if (ds && jb.total > e.lane_cat_cap[g]) {
+        cudaFree(e.lane_cat[g]);
+        e.lane_cat[g] = nullptr;
+        e.lane_cat_cap[g] = jb.total + jb.total / 4 + 1024;
+        if (cudaMalloc(&e.lane_cat[g], e.lane_cat_cap[g] * sizeof(float4)) != cudaSuccess) { e.lane_cat_cap[g] = 0; errs[g] = "submap buffer allocation failed"; return; }
+      }
+      if (jb.segs.size() > e.lane_segs_cap[g]) {
+        cudaFree(e.lane_segs[g]);
+        e.lane_segs[g] = nullptr;
+        e.lane_segs_cap[g] = jb.segs.size() + 64;
+        if (cudaMalloc(&e.lane_segs[g], e.lane_segs_cap[g] * sizeof(SubmapSeg)) != cudaSuccess) { e.lane_segs_cap[g] = 0; errs[g] = "segment table allocation failed"; return; }
+      }
+      cudaError_t ce = cudaMemcpyAsync(e.lane_segs[g], jb.segs.data(), jb.segs.size() * sizeof(SubmapSeg), cudaMemcpyHostToDevice, bs);
+      if (ce == cudaSuccess) ce = launch_submap_gather(e.lane_segs[g], (int)jb.segs.size(), jb.max_n, ds ? e.lane_cat[g] : jb.dst, bs);
+      ++launches[g];
+      jb.m = jb.total;
+      if (ce == cudaSuccess && ds) ce = voxelgrid_downsample(e.bws[g], e.lane_cat[g], jb.total, leaf, jb.dst, &jb.m, bs, &launches[g]);
+      if (ce == cudaSuccess) ce = cudaStreamSynchronize(bs);     // jb.segs and the lane's buffers are reused by the next job
+      if (ce != cudaSuccess) { errs[g] = std::string("submap assembly: ") + cudaGetErrorString(ce); return; }
+    }
+    if (cudaEventRecord(e.bdone[g], bs) != cudaSuccess) errs[g] = "event record failed";
+  };
+  std::vector<std::thread> th;
+  for (int g = 1; g < lanes; ++g) th.emplace_back(work, g);
+  work(0);
+  for (auto& x : th) x.join();
+  for (int g = 0; g < lanes; ++g) {
+    if (!errs[g].empty()) return e.fail(errs[g]);
+    e.stats.kernel_launches += launches[g];
+    if (cudaStreamWaitEvent(e.stream, e.bdone[g], 0) != cudaSuccess) return e.fail("stream wait failed");
+  }
+  for (int j = 0; j < n; ++j) {
+    if (jobs[j].tslot >= 0) {
+      e.targets[jobs[j].tslot].n = jobs[j].m;
+    } else {
+      e.sources.push_back(Source{jobs[j].soff, jobs[j].m, nullptr});
+      if (ids) ids[j] = (int)e.sources.size() - 1;
+    }
+    if (n_points) n_points[j] = jobs[j].m;
+  }
   return 0;
 }
 

@@ -95,26 +95,42 @@ class LoopRefiner:
         b.clear()
         n_kf = len(self.poses)
         P = self._pose_array()
-        tgt_cache, src_cache = {}, {}
-        item_t, item_s, meta = [], [], []
+        # the distinct submaps of the call: targets keyed by the loop keyframe, sources by (keyframe, whose pose places it)
+        tkeys, skeys, pair_keys = [], [], []
         for loop_idx, curr_idx in loop_pairs:
             loop_idx, curr_idx = int(loop_idx), int(curr_idx)
-            if loop_idx not in tgt_cache:
-                tgt_cache[loop_idx] = b.add_submap(loop_idx, self.half_window, P, self.filter_size, as_target=True)
             if self.source_mode == "reference":
                 skey = (loop_idx, loop_idx)
             elif self.source_mode == "current":
                 skey = (curr_idx, curr_idx)
             else:
                 skey = (curr_idx, loop_idx)
+            if loop_idx not in tkeys:
+                tkeys.append(loop_idx)
+            if skey not in skeys:
+                skeys.append(skey)
+            pair_keys.append((loop_idx, curr_idx, skey))
+        # everything placed by the stored poses goes to the device in ONE call (assembled concurrently on the build lanes) ...
+        roots, hws, ast, slot = list(tkeys), [self.half_window] * len(tkeys), [True] * len(tkeys), {}
+        for skey in skeys:
+            kf, pose_of = skey
+            in_range = 0 <= kf < n_kf and 0 <= pose_of < n_kf
+            if in_range and kf != pose_of:
+                continue
+            slot[skey] = len(roots)
+            roots.append(kf if in_range else -1)        # no such keyframe: empty cloud
+            hws.append(0)
+            ast.append(False)
+        ids, npts = b.add_submaps(roots, hws, P, self.filter_size, ast) if roots else ([], [])
+        tgt_cache = {k: (int(ids[i]), int(npts[i])) for i, k in enumerate(tkeys)}
+        src_cache = {k: (int(ids[i]), int(npts[i])) for k, i in slot.items()}
+        # ... a keyframe placed by ANOTHER keyframe's pose (current_at_loop_pose) needs its own pose table
+        for skey in skeys:
             if skey not in src_cache:
                 kf, pose_of = skey
-                if not (0 <= kf < n_kf and 0 <= pose_of < n_kf):
-                    src_cache[skey] = b.add_submap(-1, 0, P, self.filter_size, as_target=False)     # no such keyframe: empty cloud
-                elif kf == pose_of:
-                    src_cache[skey] = b.add_submap(kf, 0, P, self.filter_size, as_target=False)
-                else:
-                    src_cache[skey] = b.add_submap(kf, 0, self._pose_array({kf: P[pose_of]}), self.filter_size, as_target=False)
+                src_cache[skey] = b.add_submap(kf, 0, self._pose_array({kf: P[pose_of]}), self.filter_size, as_target=False)
+        item_t, item_s, meta = [], [], []
+        for loop_idx, curr_idx, skey in pair_keys:
             (tid, tn), (sid, sn) = tgt_cache[loop_idx], src_cache[skey]
             meta.append(dict(loop=loop_idx, curr=curr_idx, n_source=sn, n_target=tn, target_id=tid, source_id=sid))
             item_t.append(tid)

@@ -56,7 +56,8 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_localmap_clear", "ndtb_localmap_append_source", "ndtb_localmap_snapshot", "ndtb_localmap_set_target",
            "ndtb_localmap_roll", "ndtb_localmap_sizes", "ndtb_localmap_download", "ndtb_default_filter_params", "ndtb_filter_scan",
            "ndtb_get_source", "ndtb_batch_add_keyframe", "ndtb_batch_clear_keyframes", "ndtb_batch_num_keyframes",
-           "ndtb_batch_add_submap", "ndtb_batch_download", "ndtb_batch_add_targets", "ndtb_batch_add_sources"]
+           "ndtb_batch_add_submap", "ndtb_batch_download", "ndtb_batch_add_targets", "ndtb_batch_add_sources",
+           "ndtb_batch_add_submaps"]
 
 _lib = None
 
@@ -113,6 +114,7 @@ def load_library():
     L.ndtb_batch_clear_keyframes.argtypes = [vp]
     L.ndtb_batch_num_keyframes.argtypes = [vp]
     L.ndtb_batch_add_submap.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_float, C.POINTER(C.c_int), C.POINTER(sz)]
+    L.ndtb_batch_add_submaps.argtypes = [vp, C.c_int, vp, vp, vp, vp, C.c_int, C.c_float, vp, vp]
     L.ndtb_batch_download.argtypes = [vp, C.c_int, C.c_int, vp, sz, sz, C.POINTER(sz)]
     L.ndtb_default_filter_params.argtypes = [C.POINTER(FilterParams)]
     L.ndtb_filter_scan.argtypes = [vp, vp, sz, sz, C.POINTER(FilterParams), vp]
@@ -518,6 +520,18 @@ class BatchNDT:
         self._ck(self._L.ndtb_batch_add_submap(self._h, int(bool(as_target)), int(root), int(half_window), _p(P), P.shape[0], float(leaf),
                                                C.byref(i), C.byref(n)))
         return i.value, n.value
+
+    def add_submaps(self, roots, half_windows, poses, leaf, as_target):
+        """Many submaps in one call, assembled concurrently on the batch's build lanes.  roots / half_windows / as_target:
+        sequences of equal length.  Returns (ids, points) as int arrays."""
+        P = np.ascontiguousarray(np.asarray(poses, dtype=np.float32).reshape(-1, 4, 4).transpose(0, 2, 1)).reshape(-1, 16)
+        r = np.ascontiguousarray(roots, dtype=np.int32)
+        hw = np.ascontiguousarray(half_windows, dtype=np.int32)
+        at = np.ascontiguousarray([1 if a else 0 for a in as_target], dtype=np.int32)
+        ids = np.zeros(r.shape[0], dtype=np.int32)
+        n = np.zeros(r.shape[0], dtype=np.uint64)
+        self._ck(self._L.ndtb_batch_add_submaps(self._h, r.shape[0], _p(at), _p(r), _p(hw), _p(P), P.shape[0], float(leaf), _p(ids), _p(n)))
+        return ids, n.astype(np.int64)
 
     def download(self, id, n, is_target=True):
         """(n, 4) float32 x y z intensity of a batch target / source."""
