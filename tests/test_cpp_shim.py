@@ -101,3 +101,66 @@ def test_device_localmap_mode_gives_the_same_odometry(exe, tmp_path):
         assert np.array_equal(a[:, 1:3], x[:, 1:3])          # iterations, converged
         assert np.array_equal(a[:, 3:11], x[:, 3:11])        # fitness, pose, target size
     assert int(sb["incremental"]) >= int(sb["target_sets"]) - 8 and int(sc["incremental"]) == 0
+
+
+# ---- include/scancontext/Scancontext.h: the SCManager drop-in ------------------------------------
+def _sc_exes():
+    from xchu_slam_b200 import build
+    build.build_cuda()
+    return build.build_sc_example(), build.build_sc_example_reference()
+
+
+def test_sc_shim_compiles_and_fails_loudly_without_gpu(tmp_path):
+    import torch
+    exe_dev, _ = _sc_exes()
+    assert os.path.exists(exe_dev)
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from xchu_slam_b200 import synth
+    seq = synth.write_sequence(str(tmp_path / "s.bin"), n_scans=2, n_points=2000)
+    r = subprocess.run([exe_dev, seq, str(tmp_path / "o.txt")], capture_output=True, text=True)
+    assert r.returncode == 3 and "no CPU fallback" in r.stderr
+
+
+def test_sc_reference_binary_agrees_with_the_oracle(tmp_path):
+    """The reference-compiled caller (examples/sc_sequence_ref) against the oracle port driven from Python on the same file:
+    same loop ids, same yaw bits -- what the device binary is held to on the GPU box."""
+    _, exe_ref = _sc_exes()
+    if exe_ref is None:
+        pytest.skip("examples/sc_sequence_ref not built (needs /root/reference)")
+    from oracle import sc
+    from xchu_slam_b200 import synth
+    seq = synth.write_sequence(str(tmp_path / "seq.bin"), n_scans=70, n_points=6000)
+    out = str(tmp_path / "ref.txt")
+    r = subprocess.run([exe_ref, seq, out, "--revisit", "3,10"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    rows = [l.split() for l in open(out) if not l.startswith("#")]
+    scans = synth.read_sequence(seq)[0]
+    scans = scans + [scans[3], scans[10]]
+    o = sc.OracleSC()
+    assert len(rows) == len(scans)
+    for k, s in enumerate(scans):
+        o.add(s)
+        lid, yaw = o.detect()
+        assert int(rows[k][1]) == lid, k
+        assert np.float32(float(rows[k][2])).tobytes() == np.float32(yaw).tobytes(), k
+    assert [int(x[1]) for x in rows[-2:]] == [3, 10]
+
+
+@pytest.mark.gpu
+def test_sc_same_caller_two_backends_same_loops(tmp_path):
+    """examples/sc_sequence.cpp (pgo_node's three SCManager calls) compiled over include/scancontext/Scancontext.h (device) and over
+    the reference's own Scancontext.cpp (CPU): identical loop ids and identical yaw differences for every keyframe."""
+    exe_dev, exe_ref = _sc_exes()
+    if exe_ref is None:
+        pytest.skip("examples/sc_sequence_ref not built (needs /root/reference)")
+    from xchu_slam_b200 import synth
+    seq = synth.write_sequence(str(tmp_path / "seq.bin"), n_scans=70, n_points=6000)
+    outs = []
+    for exe, name in ((exe_dev, "dev.txt"), (exe_ref, "ref.txt")):
+        r = subprocess.run([exe, seq, str(tmp_path / name), "--revisit", "3,10,20"], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        outs.append([l for l in open(str(tmp_path / name)) if not l.startswith("#")])
+    assert len(outs[0]) == 73
+    assert outs[0] == outs[1]
+    assert [int(l.split()[1]) for l in outs[0][-3:]] == [3, 10, 20]

@@ -74,6 +74,20 @@ def build_examples(force=False):
     if force or _stale(exe, deps):
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", src, "-o", exe, "-L" + HERE, "-lndt_b200",
                                "-Wl,-rpath,$ORIGIN/../xchu_slam_b200"])
+    build_sc_example(force)
+    return exe
+
+
+def build_sc_example(force=False):
+    """examples/sc_sequence.cpp over include/scancontext/Scancontext.h (drop-in for the reference's SCManager)."""
+    inc = os.path.join(HERE, "..", "include")
+    src = os.path.join(EXAMPLES, "sc_sequence.cpp")
+    exe = os.path.join(EXAMPLES, "sc_sequence")
+    deps = [src, LIB, os.path.join(inc, "scancontext", "Scancontext.h"), os.path.join(inc, "pclomp", "pcl_compat.h"),
+            os.path.join(inc, "ndt_b200", "sc_c_api.h")]
+    if force or _stale(exe, deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I" + inc, src, "-o", exe, "-L" + HERE, "-lndt_b200",
+                               "-Wl,-rpath,$ORIGIN/../xchu_slam_b200"])
     return exe
 
 
@@ -92,6 +106,21 @@ def build_example_reference(force=False):
         deps = [src] + [os.path.join(d, f) for d, _, fs in os.walk(stubs) for f in fs] + [os.path.join(HERE, "..", "oracle", "thirdparty_math.h")]
         if force or _stale(exe, deps):
             subprocess.check_call(["g++", "-std=c++17", "-O2", "-fopenmp", "-ffp-contract=off", "-w", "-DODOM_USE_REFERENCE", "-I" + stubs,
+                                   "-I" + REFERENCE_INCLUDE, src, "-o", exe])
+    build_sc_example_reference(force)
+    return exe if os.path.exists(exe) else None
+
+
+def build_sc_example_reference(force=False):
+    """TEST INFRASTRUCTURE: sc_sequence.cpp compiled over the REFERENCE'S OWN scancontext/Scancontext.{h,cpp} (stand-in headers of
+    oracle/ref_stubs/) -> examples/sc_sequence_ref.  Built only where /root/reference exists; the binary travels to the GPU box."""
+    src = os.path.join(EXAMPLES, "sc_sequence.cpp")
+    exe = os.path.join(EXAMPLES, "sc_sequence_ref")
+    stubs = os.path.join(HERE, "..", "oracle", "ref_stubs")
+    if os.path.exists(os.path.join(REFERENCE_INCLUDE, "scancontext", "Scancontext.cpp")):
+        deps = [src] + [os.path.join(d, f) for d, _, fs in os.walk(stubs) for f in fs]
+        if force or _stale(exe, deps):
+            subprocess.check_call(["g++", "-std=c++17", "-O2", "-fopenmp", "-ffp-contract=off", "-w", "-DSC_USE_REFERENCE", "-I" + stubs,
                                    "-I" + REFERENCE_INCLUDE, src, "-o", exe])
     return exe if os.path.exists(exe) else None
 

@@ -280,3 +280,17 @@ def write_sequence(path, n_scans=1000, n_points=20000, seed=BASE_SEED, traj_star
             f.write(np.ascontiguousarray(pts, dtype=np.float32).tobytes())
     os.replace(tmp, path)
     return path
+
+
+def read_sequence(path):
+    """Inverse of write_sequence: ([(n, 4) float32 scan, ...], (n_scans, 6) float64 ground-truth poses)."""
+    with open(path, "rb") as f:
+        if f.read(8) != b"NDTSEQ1\0":
+            raise ValueError("not an NDTSEQ1 file: " + path)
+        n_scans = int(np.frombuffer(f.read(4), np.int32)[0])
+        scans, gts = [], []
+        for _ in range(n_scans):
+            n = int(np.frombuffer(f.read(4), np.int32)[0])
+            gts.append(np.frombuffer(f.read(48), np.float64).copy())
+            scans.append(np.frombuffer(f.read(16 * n), np.float32).reshape(n, 4).copy())
+    return scans, np.stack(gts) if gts else np.zeros((0, 6))
