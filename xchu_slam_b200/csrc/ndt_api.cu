@@ -169,6 +169,7 @@ struct Engine {
   float4* lane_cat[16] = {};         // the same per build lane (ndtb_batch_add_submaps)
   size_t lane_cat_cap[16] = {};
   SubmapSeg* lane_segs[16] = {};
+  NNGridStorage* lane_nn[16] = {};   // one NN grid per build lane (ndtb_batch_fitness over distinct targets)
   size_t lane_segs_cap[16] = {};
   PinnedBuf st_d2;                   // host landing zone of the per-point squared NN distances (getFitnessScore)
   PinnedBuf st_src;                  // host staging of strided sources (x y z intensity packed to 16 B)
@@ -232,7 +233,7 @@ struct Engine {
     for (auto& k : kfs) cudaFree(k.p);
     kfs.clear();
     cudaFree(d_segs); cudaFree(kf_cat);
-    for (int g = 0; g < 16; ++g) { cudaFree(lane_cat[g]); cudaFree(lane_segs[g]); }
+    for (int g = 0; g < 16; ++g) { cudaFree(lane_cat[g]); cudaFree(lane_segs[g]); nn_destroy(lane_nn[g]); }
     for (auto& e : ev) if (e) cudaEventDestroy(e);
     for (auto& e : deriv_events) cudaEventDestroy(e);
     if (stream && own_stream) cudaStreamDestroy(stream);
@@ -1222,7 +1223,24 @@ int ndtb_batch_fitness(ndtb_batch* b, double max_range, double* out) {
   if (cudaMemcpyAsync(e.d_fit_items, order.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, e.stream) != cudaSuccess)
     return e.fail("upload failed");
   if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");   // `order` is pageable: landed before it goes away
-  for (int g0 = 0; g0 < n;) {
+  // distinct targets are independent (each item owns its slice of the partials): their grid builds and fitness launches go round
+  // the build lanes' streams, one NN grid per lane, so that the ~12 small launches of a build overlap those of the other targets
+  int n_groups = 0;
+  for (int g0 = 0; g0 < n; ++n_groups) {
+    const int tid = e.last_item_target[order[g0]];
+    while (g0 < n && e.last_item_target[order[g0]] == tid) ++g0;
+  }
+  const int lanes = n_groups > 1 ? std::min(e.build_lanes(), n_groups) : 0;
+  if (lanes) {
+    if (e.ensure_lanes(lanes)) return 1;
+    for (int g = 0; g < lanes; ++g)
+      if (!e.lane_nn[g]) e.lane_nn[g] = nn_create();
+    if (cudaEventRecord(e.bstart, e.stream) != cudaSuccess) return e.fail("event record failed");
+    for (int g = 0; g < lanes; ++g)
+      if (cudaStreamWaitEvent(e.bstream[g], e.bstart, 0) != cudaSuccess) return e.fail("stream wait failed");
+  }
+  int group = 0;
+  for (int g0 = 0; g0 < n; ++group) {
     const int tid = e.last_item_target[order[g0]];
     int g1 = g0;
     while (g1 < n && e.last_item_target[order[g1]] == tid) ++g1;
@@ -1231,12 +1249,19 @@ int ndtb_batch_fitness(ndtb_batch* b, double max_range, double* out) {
     const float cell = e.params.resolution > 0.25f ? e.params.resolution : 0.25f;
     float bb[6];
     for (int a = 0; a < 3; ++a) { bb[a] = t.ts.mn[a]; bb[3 + a] = t.ts.mx[a]; }
-    cudaError_t ce = nn_build(e.nn, e.ws, t.use ? t.use : t.pts, t.n, cell, t.ts.have_bbox ? bb : nullptr, e.stream, &e.stats.kernel_launches);
-    if (ce == cudaSuccess) ce = nn_fitness_batch(e.nn, e.d_states, e.d_fit_items + g0, g1 - g0, max_range, bpi, e.d_fit_partial, e.stream);
+    const int lane = lanes ? group % lanes : 0;
+    NNGridStorage* nn = lanes ? e.lane_nn[lane] : e.nn;
+    BuildWorkspace* ws = lanes ? e.bws[lane] : e.ws;
+    cudaStream_t st = lanes ? e.bstream[lane] : e.stream;
+    cudaError_t ce = nn_build(nn, ws, t.use ? t.use : t.pts, t.n, cell, t.ts.have_bbox ? bb : nullptr, st, &e.stats.kernel_launches);
+    if (ce == cudaSuccess) ce = nn_fitness_batch(nn, e.d_states, e.d_fit_items + g0, g1 - g0, max_range, bpi, e.d_fit_partial, st);
     if (ce != cudaSuccess) return e.fail(std::string("batch fitness: ") + cudaGetErrorString(ce));
     ++e.stats.kernel_launches;
     g0 = g1;
   }
+  for (int g = 0; g < lanes; ++g)
+    if (cudaEventRecord(e.bdone[g], e.bstream[g]) != cudaSuccess || cudaStreamWaitEvent(e.stream, e.bdone[g], 0) != cudaSuccess)
+      return e.fail("stream wait failed");
   e.nn_valid = false;
   if (fitness_finish(e.d_fit_partial, n, bpi, e.d_fit_out, e.stream) != cudaSuccess) return e.fail("fitness_finish failed");
   if (cudaMemcpyAsync(out, e.d_fit_out, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, e.stream) != cudaSuccess) return e.fail("copy failed");
