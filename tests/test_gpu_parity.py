@@ -86,6 +86,47 @@ def test_neighbor_sets_bit_exact(case_small, method, dense):
     assert co.sum() > 0
 
 
+def test_target_replaced_within_the_same_bounding_cells(case_small):
+    """setInputTarget with a second cloud whose bounding cells equal the first one's (the first with a hole cut around the
+    sensor): the dense cell index is refilled only when its box changes, so the cells of the voxels that went away must have
+    been taken out of it -- the neighbour sets and the derivatives are those of a handle that only ever saw the second cloud."""
+    from oracle import oracle
+    from xchu_slam_b200 import ndt
+    src, tgt, gt, guess = case_small
+    c = guess[:3, 3]
+    hole = np.hypot(tgt[:, 0] - c[0], tgt[:, 1] - c[1]) < 12.0
+    tgt_b = np.ascontiguousarray(tgt[~hole])
+    assert 0.05 < hole.mean() < 0.95
+    assert np.array_equal(np.floor(tgt.min(0)[:3]), np.floor(tgt_b.min(0)[:3])) and np.array_equal(np.floor(tgt.max(0)[:3]), np.floor(tgt_b.max(0)[:3]))
+    o, g = _mk(case_small)
+    p = oracle.matrix_to_pose(guess)
+    pts = o.transform_source(guess)
+    ca, _ = g.neighbors(pts, 2)                 # builds the first table and its dense index
+    o.set_target(tgt_b)
+    g.setInputTarget(tgt_b)
+    _compare_voxels(o, g)
+    co, io = o.neighbors(pts, 2)
+    cg, ig = g.neighbors(pts, 2)
+    assert co.sum() < ca.sum()                   # the hole took neighbours away ...
+    assert np.array_equal(co, cg) and np.array_equal(io, ig)      # ... and the device agrees, cell by cell
+    so_, go_, Ho_, _ = o.eval_derivatives(guess, p, True)
+    sg_, gg_, Hg_ = g.evalDerivatives(guess, p, True)
+    assert abs(sg_ - so_) <= TOL * abs(so_) and rel_err(gg_, go_) < TOL and rel_err(Hg_, Ho_) < TOL
+    # the batch engine reuses a target slot after clear() the same way
+    b = ndt.BatchNDT()
+    b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2)
+    b.add_target(tgt); b.add_source(src)
+    b.run([0], [0], [guess])
+    b.clear()
+    b.add_target(tgt_b); b.add_source(src)
+    r1 = b.run([0], [0], [guess])[0]
+    f = ndt.BatchNDT()
+    f.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2)
+    f.add_target(tgt_b); f.add_source(src)
+    r2 = f.run([0], [0], [guess])[0]
+    assert r1["iterations"] == r2["iterations"] and np.array_equal(r1["T"], r2["T"])
+
+
 @pytest.mark.parametrize("strict", [False, True])
 @pytest.mark.parametrize("method", [2, 3, 0, 1])
 @pytest.mark.parametrize("ch", [True, False])

@@ -147,16 +147,33 @@ cudaError_t table_reserve(TableStorage& ts, size_t need, cudaStream_t s, long lo
   return cudaSuccess;
 }
 
+// Empties the hash slots and takes the voxels that go away out of the dense cell index (their cells back to -1), in one launch:
+// table_build_dense refills the dense array only when its box changes, so a target REPLACED by a cloud with the same bounding
+// cells must not find the old cloud's codes in cells the new cloud leaves empty.
+__global__ void k_clear_table(VoxelTable t, size_t n_slots, int n_vox_old) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < (size_t)n_vox_old) {
+    int a, b, c;
+    unpack_key(t.vkey[i], a, b, c);
+    t.dense[((size_t)(c - t.dlo[2]) * t.dn[1] + (b - t.dlo[1])) * t.dn[0] + (a - t.dlo[0])] = -1;
+  }
+  if (i < n_slots) { HashSlot s; s.key = kEmptyKey; s.vidx = -1; s.nr_points = 0; t.slots[i] = s; }
+}
 cudaError_t table_clear(TableStorage& ts, cudaStream_t s, long long* launches) {
+  // the dense index is live (built over every voxel at the end of the last append): un-scatter those voxels; otherwise its
+  // contents are not known to be clean, and the next dense build refills it (dn[0] = -1 never equals a real box)
+  const int unscatter = ts.t.dense != nullptr && ts.n_vox > 0 ? ts.n_vox : 0;
+  if (!unscatter) ts.t.dn[0] = -1;
+  const size_t threads = ts.slot_cap > (size_t)unscatter ? ts.slot_cap : (size_t)unscatter;
+  if (threads) {
+    k_clear_table<<<(unsigned)((threads + 255) / 256), 256, 0, s>>>(ts.t, ts.slot_cap, unscatter);
+    if (launches) ++*launches;
+    CK(cudaGetLastError());
+  }
   ts.t.dense = nullptr;
   ts.n_vox = 0;
   ts.valid = false;
   ts.have_bbox = false;
-  if (ts.slot_cap) {
-    k_fill_slots<<<(unsigned)((ts.slot_cap + 255) / 256), 256, 0, s>>>(ts.t.slots, ts.slot_cap);
-    if (launches) ++*launches;
-    CK(cudaGetLastError());
-  }
   return cudaSuccess;
 }
 
@@ -525,6 +542,7 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
     ts.valid = false;
     ts.n_vox = 0;
     t.dense = nullptr;
+    t.dn[0] = -1;   // the dense array still holds the voxels dropped here: refill it at the next build
     if (ts.slot_cap) { k_fill_slots<<<(unsigned)((ts.slot_cap + 255) / 256), 256, 0, s>>>(t.slots, ts.slot_cap); ++L; }
     return cudaGetLastError();
   }
