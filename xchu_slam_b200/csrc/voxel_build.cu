@@ -70,8 +70,11 @@ static cudaError_t ws_reserve(BuildWorkspace* ws, size_t n) {
   CK(cudaMalloc(&ws->flags, cap * 4)); CK(cudaMalloc(&ws->scan, cap * 4));
   CK(cudaMalloc(&ws->run_start, (cap + 1) * 4)); CK(cudaMalloc(&ws->run_vidx, cap * 4)); CK(cudaMalloc(&ws->run_slot, cap * 4));
   CK(cudaMalloc(&ws->run_isnew, cap * 4)); CK(cudaMalloc(&ws->new_prefix, cap * 4));
-  size_t b1 = 0, b2 = 0;
+  size_t b1 = 0, b2 = 0, b3 = 0;
   cub::DeviceRadixSort::SortPairs(nullptr, b1, ws->keys_in, ws->keys_out, ws->idx_in, ws->idx_out, (int)cap, 0, 64);
+  cub::DeviceRadixSort::SortPairs(nullptr, b3, reinterpret_cast<unsigned int*>(ws->keys_in), reinterpret_cast<unsigned int*>(ws->keys_out),
+                                  ws->idx_in, ws->idx_out, (int)cap, 0, 32);
+  if (b3 > b1) b1 = b3;
   cub::DeviceScan::InclusiveSum(nullptr, b2, ws->flags, ws->scan, (int)cap);
   ws->cub_bytes = (b1 > b2 ? b1 : b2) + 256;
   CK(cudaMalloc(&ws->cub_temp, ws->cub_bytes));
@@ -230,18 +233,22 @@ __global__ void k_minmax_decode(float* out6) {
 // float(min_b) there is exact for |cell| < 2^24, so the absolute cell is the same integer).
 __device__ __forceinline__ int build_cell(float x, float inv_leaf) { return (int)floorf(x * inv_leaf); }
 
+// KeyT: unsigned long long, or unsigned int when bi + bj + bk <= 32 and NDTB_SORT_KEY32=1 (sort_key32 below): the same integers in
+// the same (stable) order, two thirds of the bytes per radix pass.
+template <typename KeyT>
 __global__ void k_keys(const float4* __restrict__ pts, size_t n, float inv_leaf, int i0, int j0, int k0, int bi, int bj,
-                       unsigned long long* __restrict__ keys, unsigned int* __restrict__ idx) {
+                       KeyT* __restrict__ keys, unsigned int* __restrict__ idx) {
   size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
   const float4 p = pts[t];
   const unsigned long long i = (unsigned long long)(build_cell(p.x, inv_leaf) - i0);
   const unsigned long long j = (unsigned long long)(build_cell(p.y, inv_leaf) - j0);
   const unsigned long long k = (unsigned long long)(build_cell(p.z, inv_leaf) - k0);
-  keys[t] = (k << (bi + bj)) | (j << bi) | i;   // ascending == reference linear index order (k, j, i)
+  keys[t] = (KeyT)((k << (bi + bj)) | (j << bi) | i);   // ascending == reference linear index order (k, j, i)
   idx[t] = (unsigned int)t;
 }
-__global__ void k_flags(const unsigned long long* __restrict__ keys, size_t n, int* __restrict__ flags) {
+template <typename KeyT>
+__global__ void k_flags(const KeyT* __restrict__ keys, size_t n, int* __restrict__ flags) {
   size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
   flags[t] = (t == 0 || keys[t] != keys[t - 1]) ? 1 : 0;
@@ -510,6 +517,27 @@ static int bits_for(long long range) {
   return b;
 }
 
+// NDTB_SORT_KEY32=1 (off by default until the whole GPU suite has run with it; DESIGN.md section 9 lead 1): cell keys of at most
+// 32 bits are generated, sorted and compared as 32-bit words in the lower halves of the same workspace arrays.
+static bool sort_key32(int bits) {
+  static const bool on = [] { const char* e = getenv("NDTB_SORT_KEY32"); return e && atoi(e) > 0; }();
+  return on && bits <= 32;
+}
+// keys_in / idx_in -> keys_out / idx_out (stable), then flags[t] = key t starts a run
+static cudaError_t sort_and_flag(BuildWorkspace* ws, size_t n, int bits, cudaStream_t s) {
+  size_t tb = ws->cub_bytes;
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  if (sort_key32(bits)) {
+    unsigned int *ki = reinterpret_cast<unsigned int*>(ws->keys_in), *ko = reinterpret_cast<unsigned int*>(ws->keys_out);
+    CK(cub::DeviceRadixSort::SortPairs(ws->cub_temp, tb, ki, ko, ws->idx_in, ws->idx_out, (int)n, 0, bits, s));
+    k_flags<unsigned int><<<nb, 256, 0, s>>>(ko, n, ws->flags);
+  } else {
+    CK(cub::DeviceRadixSort::SortPairs(ws->cub_temp, tb, ws->keys_in, ws->keys_out, ws->idx_in, ws->idx_out, (int)n, 0, bits, s));
+    k_flags<unsigned long long><<<nb, 256, 0, s>>>(ws->keys_out, n, ws->flags);
+  }
+  return cudaGetLastError();
+}
+
 cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts, size_t n, cudaStream_t s, long long* launches) {
   if (n == 0) return cudaSuccess;
   VoxelTable& t = ts.t;
@@ -554,13 +582,14 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
   for (int a = 0; a < 3; ++a) { c0[a] = (int)floorf(nmn[a] * inv); c1[a] = (int)floorf(nmx[a] * inv); }
   const int bi = bits_for((long long)c1[0] - c0[0] + 1), bj = bits_for((long long)c1[1] - c0[1] + 1), bk = bits_for((long long)c1[2] - c0[2] + 1);
   const unsigned nb = (unsigned)((n + 255) / 256);
-  k_keys<<<nb, 256, 0, s>>>(pts, n, inv, c0[0], c0[1], c0[2], bi, bj, ws->keys_in, ws->idx_in);
+  if (sort_key32(bi + bj + bk))
+    k_keys<unsigned int><<<nb, 256, 0, s>>>(pts, n, inv, c0[0], c0[1], c0[2], bi, bj, reinterpret_cast<unsigned int*>(ws->keys_in), ws->idx_in);
+  else
+    k_keys<unsigned long long><<<nb, 256, 0, s>>>(pts, n, inv, c0[0], c0[1], c0[2], bi, bj, ws->keys_in, ws->idx_in);
   ++L;
-  size_t tb = ws->cub_bytes;
-  CK(cub::DeviceRadixSort::SortPairs(ws->cub_temp, tb, ws->keys_in, ws->keys_out, ws->idx_in, ws->idx_out, (int)n, 0, bi + bj + bk, s));
+  CK(sort_and_flag(ws, n, bi + bj + bk, s));
   L += (bi + bj + bk + 7) / 8 + 2;  // CUB onesweep: histogram + scan + one pass per 8 key bits (library kernels)
-  k_flags<<<nb, 256, 0, s>>>(ws->keys_out, n, ws->flags);
-  tb = ws->cub_bytes;
+  size_t tb = ws->cub_bytes;
   CK(cub::DeviceScan::InclusiveSum(ws->cub_temp, tb, ws->flags, ws->scan, (int)n, s));
   k_run_starts<<<nb, 256, 0, s>>>(ws->flags, ws->scan, n, ws->run_start, ws->counts);
   L += 4;
@@ -647,11 +676,12 @@ cudaError_t voxelgrid_downsample(BuildWorkspace* ws, const float4* in, size_t n,
   }
   const int bi = bits_for((long long)c1[0] - c0[0] + 1), bj = bits_for((long long)c1[1] - c0[1] + 1), bk = bits_for((long long)c1[2] - c0[2] + 1);
   const unsigned nb = (unsigned)((n + 255) / 256);
-  k_keys<<<nb, 256, 0, s>>>(in, n, inv, c0[0], c0[1], c0[2], bi, bj, ws->keys_in, ws->idx_in);
+  if (sort_key32(bi + bj + bk))
+    k_keys<unsigned int><<<nb, 256, 0, s>>>(in, n, inv, c0[0], c0[1], c0[2], bi, bj, reinterpret_cast<unsigned int*>(ws->keys_in), ws->idx_in);
+  else
+    k_keys<unsigned long long><<<nb, 256, 0, s>>>(in, n, inv, c0[0], c0[1], c0[2], bi, bj, ws->keys_in, ws->idx_in);
+  CK(sort_and_flag(ws, n, bi + bj + bk, s));
   size_t tb = ws->cub_bytes;
-  CK(cub::DeviceRadixSort::SortPairs(ws->cub_temp, tb, ws->keys_in, ws->keys_out, ws->idx_in, ws->idx_out, (int)n, 0, bi + bj + bk, s));
-  k_flags<<<nb, 256, 0, s>>>(ws->keys_out, n, ws->flags);
-  tb = ws->cub_bytes;
   CK(cub::DeviceScan::InclusiveSum(ws->cub_temp, tb, ws->flags, ws->scan, (int)n, s));
   k_run_starts<<<nb, 256, 0, s>>>(ws->flags, ws->scan, n, ws->run_start, ws->counts);
   L += 5 + (bi + bj + bk + 7) / 8 + 2;
@@ -688,14 +718,15 @@ void nn_destroy(NNGridStorage* g) {
   cudaFree(g->sorted); cudaFree(g->slots); cudaFree(g->far_idx); cudaFree(g->far_count);
   delete g;
 }
+template <typename KeyT>
 __global__ void k_nn_keys(const float4* __restrict__ pts, size_t n, float cell, int i0, int j0, int k0, int bi, int bj,
-                          unsigned long long* __restrict__ keys, unsigned int* __restrict__ idx) {
+                          KeyT* __restrict__ keys, unsigned int* __restrict__ idx) {
   size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n) return;
   const float4 p = pts[t];
   const unsigned long long i = (unsigned long long)((int)floorf(p.x / cell) - i0), j = (unsigned long long)((int)floorf(p.y / cell) - j0),
                            k = (unsigned long long)((int)floorf(p.z / cell) - k0);
-  keys[t] = (k << (bi + bj)) | (j << bi) | i;
+  keys[t] = (KeyT)((k << (bi + bj)) | (j << bi) | i);
   idx[t] = (unsigned int)t;
 }
 __global__ void k_nn_gather(const float4* __restrict__ pts, const unsigned int* __restrict__ idx, size_t n, float4* __restrict__ out) {
@@ -756,12 +787,13 @@ cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, si
   }
   const int bi = bits_for((long long)c1[0] - c0[0] + 1), bj = bits_for((long long)c1[1] - c0[1] + 1), bk = bits_for((long long)c1[2] - c0[2] + 1);
   const unsigned nb = (unsigned)((n + 255) / 256);
-  k_nn_keys<<<nb, 256, 0, s>>>(pts, n, cell, c0[0], c0[1], c0[2], bi, bj, ws->keys_in, ws->idx_in);
-  size_t tb = ws->cub_bytes;
-  CK(cub::DeviceRadixSort::SortPairs(ws->cub_temp, tb, ws->keys_in, ws->keys_out, ws->idx_in, ws->idx_out, (int)n, 0, bi + bj + bk, s));
+  if (sort_key32(bi + bj + bk))
+    k_nn_keys<unsigned int><<<nb, 256, 0, s>>>(pts, n, cell, c0[0], c0[1], c0[2], bi, bj, reinterpret_cast<unsigned int*>(ws->keys_in), ws->idx_in);
+  else
+    k_nn_keys<unsigned long long><<<nb, 256, 0, s>>>(pts, n, cell, c0[0], c0[1], c0[2], bi, bj, ws->keys_in, ws->idx_in);
+  CK(sort_and_flag(ws, n, bi + bj + bk, s));
   k_nn_gather<<<nb, 256, 0, s>>>(pts, ws->idx_out, n, g->sorted);
-  k_flags<<<nb, 256, 0, s>>>(ws->keys_out, n, ws->flags);
-  tb = ws->cub_bytes;
+  size_t tb = ws->cub_bytes;
   CK(cub::DeviceScan::InclusiveSum(ws->cub_temp, tb, ws->flags, ws->scan, (int)n, s));
   k_run_starts<<<nb, 256, 0, s>>>(ws->flags, ws->scan, n, ws->run_start, ws->counts);
   // occupied cells <= points: a table of >= 2n slots keeps the load factor <= 0.5 without asking the device how many there are
