@@ -7,6 +7,7 @@
 //
 // Reference: xchu_mapping/include/pclomp/ndt_omp_impl.hpp (NDT_I), ndt_omp.h (NDT_H),
 // voxel_grid_covariance_omp_impl.hpp (VGC_I), voxel_grid_covariance_omp.h (VGC_H).
+#include <atomic>
 #include <cfloat>
 #include <cmath>
 
@@ -894,11 +895,15 @@ template <int METHOD>
 static cudaError_t launch_deriv_m(const AlignState* states, const VoxelTable* tables, const float4* src_pool, const int2* blockmap,
                                   int n_blocks, int chunk, double* partials, bool both, cudaStream_t s) {
   const size_t sm = reduce_smem_bytes(kThreads);
-  static bool configured = false;
-  if (!configured) {
+  // the attribute is per device: one flag per device of the process (handles / batches on distinct GPUs, distinct host threads)
+  static std::atomic<unsigned long long> configured{0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (!(configured.load(std::memory_order_acquire) & bit)) {
     cudaFuncSetAttribute(k_derivatives<METHOD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     cudaFuncSetAttribute(k_derivatives<METHOD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    configured = true;
+    configured.fetch_or(bit, std::memory_order_release);
   }
   k_derivatives<METHOD, true><<<n_blocks, kThreads, sm, s>>>(states, tables, src_pool, blockmap, chunk, partials);
   if (both) k_derivatives<METHOD, false><<<n_blocks, kThreads, sm, s>>>(states, tables, src_pool, blockmap, chunk, partials);

@@ -19,6 +19,7 @@
 // factorisation, expf instead of exp(double)), which moves score / gradient / Hessian by ~1e-7
 // relative -- inside the 1e-6 parity gate, tested against the oracle and against the strict
 // term-by-term kernel in ndt_core.cu.  This file is compiled WITHOUT -fmad=false.
+#include <atomic>
 #include <cfloat>
 #include <cmath>
 
@@ -360,11 +361,15 @@ template <int METHOD>
 static cudaError_t launch_fast_m(const AlignState* states, const VoxelTable* tables, const float4* src_pool, const int2* blockmap,
                                  int n_blocks, int chunk, double* partials, bool both, cudaStream_t s) {
   const size_t sm = fast_smem_bytes();
-  static bool configured = false;
-  if (!configured) {
+  // the attribute is per device: one flag per device of the process (handles / batches on distinct GPUs, distinct host threads)
+  static std::atomic<unsigned long long> configured{0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (!(configured.load(std::memory_order_acquire) & bit)) {
     cudaFuncSetAttribute(k_derivatives_fast<METHOD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     cudaFuncSetAttribute(k_derivatives_fast<METHOD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-    configured = true;
+    configured.fetch_or(bit, std::memory_order_release);
   }
   k_derivatives_fast<METHOD, true><<<n_blocks, kFT, sm, s>>>(states, tables, src_pool, blockmap, chunk, partials);
   if (both) k_derivatives_fast<METHOD, false><<<n_blocks, kFT, sm, s>>>(states, tables, src_pool, blockmap, chunk, partials);
