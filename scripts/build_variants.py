@@ -1,0 +1,36 @@
+"""Kernel variants for scripts/gpurun_variants.sh: each entry is compiled into variants/lib_<name>.so (git-ignored, travels to the
+GPU box), then the in-tree library is rebuilt with the default macros (the variant builds share its object paths).
+    python scripts/build_variants.py [name ...]
+"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from xchu_slam_b200 import build as b  # noqa: E402
+
+VARIANTS = {
+    # 64-B aligned voxel records, one 256-bit + one 128-bit load per (point, voxel) pair (ndt_internal.h, ndt_fast.cu)
+    "rec64": ("NDTB_FAST_REC64=1",),
+    # the same with the next point's seven cell codes fetched one iteration ahead
+    "rec64_pfp2": ("NDTB_FAST_REC64=1", "NDTB_FAST_PFP=2"),
+    # three resident blocks per SM (more registers per thread, fewer warps)
+    "minblocks3": ("NDTB_FAST_MINBLOCKS=3",),
+}
+
+
+def main():
+    names = sys.argv[1:] or list(VARIANTS)
+    out = os.path.join(ROOT, "variants")
+    os.makedirs(out, exist_ok=True)
+    try:
+        for n in names:
+            b.build_cuda(defines=VARIANTS[n], lib=os.path.join(out, "lib_%s.so" % n))
+            print("built variants/lib_%s.so  (%s)" % (n, " ".join(VARIANTS[n])))
+    finally:
+        b.build_cuda(force=True)
+        print("in-tree library rebuilt with the default macros")
+
+
+if __name__ == "__main__":
+    main()

@@ -65,7 +65,15 @@ struct FRec { float4 a, b, c; };
 __device__ __forceinline__ FRec load_frec(const FastRec* __restrict__ r) {
   FRec f;
   const float4* p = reinterpret_cast<const float4*>(r);
+#if NDTB_FAST_REC64
+  // LDG.E.ENL2.256 (sm_100+): bytes 0..31 of the 64-B aligned record in one request, bytes 32..47 in a second
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(f.a.x), "=f"(f.a.y), "=f"(f.a.z), "=f"(f.a.w), "=f"(f.b.x), "=f"(f.b.y), "=f"(f.b.z), "=f"(f.b.w)
+               : "l"(p));
+  f.c = __ldg(p + 2);
+#else
   f.a = __ldg(p); f.b = __ldg(p + 1); f.c = __ldg(p + 2);
+#endif
   return f;
 }
 
