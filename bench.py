@@ -168,8 +168,9 @@ def cpu_sample(a, w, n_aligns, gpu_res=None):
 
 
 def run_reference(a):
-    """Reference arm: the reference algorithm on the host cores (oracle port; the reference's own
-    sources need PCL/Eigen/FLANN/Boost, absent here -- DESIGN.md section 7)."""
+    """Reference arm: the reference algorithm on the host cores.  `value` times the oracle port (the faster of the two CPU
+    builds, so the conservative baseline); `reference_build` beside it times oracle/_ref, the reference's own ndt_omp sources
+    compiled over stand-in Eigen/PCL headers (the real ones are absent from this image) -- DESIGN.md sections 6 and 7."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
