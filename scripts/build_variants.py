@@ -16,6 +16,12 @@ VARIANTS = {
     "rec64_pfp2": ("NDTB_FAST_REC64=1", "NDTB_FAST_PFP=2"),
     # three resident blocks per SM (more registers per thread, fewer warps)
     "minblocks3": ("NDTB_FAST_MINBLOCKS=3",),
+    # FP64 accumulators in shared memory free ~56 registers: the next point's record AND cell codes prefetched without spills
+    # (ptxas: 124 registers at 4 blocks/SM, 96 at 5 blocks/SM, 0 spill bytes); combinations not in the r01 sweeps
+    "smem_pfp2": ("NDTB_FAST_ACC_SMEM=1", "NDTB_FAST_PFP=2"),
+    "smem_pfp2_rec64": ("NDTB_FAST_ACC_SMEM=1", "NDTB_FAST_PFP=2", "NDTB_FAST_REC64=1"),
+    "smem_pfp2_mb5": ("NDTB_FAST_ACC_SMEM=1", "NDTB_FAST_PFP=2", "NDTB_FAST_MINBLOCKS=5"),
+    "smem_pfp2_rec64_mb5": ("NDTB_FAST_ACC_SMEM=1", "NDTB_FAST_PFP=2", "NDTB_FAST_REC64=1", "NDTB_FAST_MINBLOCKS=5"),
 }
 
 
