@@ -5,12 +5,12 @@
 cd $GRAFT_REPO_ROOT
 mkdir -p gpurun_out
 one() {
-  NDTB_SORT_KEY32=$2 timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline 2>/dev/null | tail -1 | python -c "
+  NDTB_SORT_KEY32=$2 timeout 60 python bench.py --steps 5 --warmup 3 --no-cpu-baseline 2>/dev/null | tail -1 | python -c "
 import json,sys
 d=json.loads(sys.stdin.read()); print('$1', 'value %.0f'%d['value'], 'build_ms %.3f'%d['breakdown_ms_per_step']['voxel_build'], 'step %.3f'%d['ms_per_step'], 'launches', d['gpu_launches'])"
 }
 {
-NDTB_SORT_KEY32=1 timeout 1500 python -m pytest tests -q -x -m gpu 2>&1 | tail -3
+NDTB_SORT_KEY32=1 timeout 300 python -m pytest tests -q -x -m gpu 2>&1 | tail -3
 one key32_on 1
 one key32_off 0
 one key32_on 1
