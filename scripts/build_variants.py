@@ -18,6 +18,12 @@ VARIANTS = {
     "minblocks3": ("NDTB_FAST_MINBLOCKS=3",),
     # FP64 accumulators in shared memory free ~56 registers: the next point's record AND cell codes prefetched without spills
     # (ptxas: 124 registers at 4 blocks/SM, 96 at 5 blocks/SM, 0 spill bytes); combinations not in the r01 sweeps
+    # unpredicated record loads on a clamped index: ~64 fewer static instructions in the DIRECT7 kernel (no 12-register copy per
+    # cell); 72 B of spills at 128 registers alone, none with shared-memory accumulators
+    "uncond": ("NDTB_FAST_UNCOND=1",),
+    "uncond_rec64": ("NDTB_FAST_UNCOND=1", "NDTB_FAST_REC64=1"),
+    "uncond_smem": ("NDTB_FAST_UNCOND=1", "NDTB_FAST_ACC_SMEM=1"),
+    "uncond_smem_pfp2_rec64": ("NDTB_FAST_UNCOND=1", "NDTB_FAST_ACC_SMEM=1", "NDTB_FAST_PFP=2", "NDTB_FAST_REC64=1"),
     "smem_pfp2": ("NDTB_FAST_ACC_SMEM=1", "NDTB_FAST_PFP=2"),
     "smem_pfp2_rec64": ("NDTB_FAST_ACC_SMEM=1", "NDTB_FAST_PFP=2", "NDTB_FAST_REC64=1"),
     "smem_pfp2_mb5": ("NDTB_FAST_ACC_SMEM=1", "NDTB_FAST_PFP=2", "NDTB_FAST_MINBLOCKS=5"),

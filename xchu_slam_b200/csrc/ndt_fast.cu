@@ -43,6 +43,9 @@ namespace ndtb {
 #ifndef NDTB_FAST_AB         // 1 (DIRECT7): voxel records alternate between two register sets instead of being copied
 #define NDTB_FAST_AB 0       //    (measured 6 % slower on B200: profiles/r01_v9_kernel_variants.txt)
 #endif
+#ifndef NDTB_FAST_UNCOND     // 1 (DIRECT7): voxel-record loads unpredicated on a clamped index -- no register copies between cells
+#define NDTB_FAST_UNCOND 0   //    (variant for the A/B sweep; ~90 fewer instructions per point in the SASS, not yet measured)
+#endif
 #ifndef NDTB_FAST_DENSE32    // 1 (DIRECT7): dense-index lookup with block-uniform set-up hoisted and 32-bit index arithmetic
 #define NDTB_FAST_DENSE32 1
 #endif
@@ -300,6 +303,17 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
           if (v[o] >= 0) NDTB_PAIR(rB)
           if (o + 2 < 7) { if (v[o + 2] >= 0) rB = load_frec(recs + v[o + 2]); }
         }
+      }
+#elif NDTB_FAST_UNCOND
+      // unpredicated record loads: an absent cell fetches record 0 (one broadcast address, an L1 hit; cnt > 0 here, so record 0
+      // exists) and its pair is skipped as before.  Every load then has a fresh destination: no zero-initialised record and no
+      // 12-register copy per cell (the predicated form needs both to merge "loaded" with "not loaded").
+      FRec nxt = load_frec(recs + max(v[0], 0));
+#pragma unroll
+      for (int o = 0; o < 7; ++o) {
+        const FRec r = nxt;
+        if (o + 1 < 7) nxt = load_frec(recs + max(v[o + 1], 0));
+        if (v[o] >= 0) NDTB_PAIR(r)
       }
 #else
       FRec nxt = {};
