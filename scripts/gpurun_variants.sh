@@ -7,6 +7,10 @@ import json,sys
 d=json.loads(sys.stdin.read()); print('$1', 'chunk=${3:-auto}', 'value %.0f'%d['value'], 'deriv_ms/step %.3f'%d['breakdown_ms_per_step']['derivatives'], 'step %.3f'%d['ms_per_step'], 'frac %.3f'%d['roofline']['frac'])"
 }
 python -m pytest tests/test_gpu_parity.py tests/test_golden.py -m gpu -q -x 2>&1 | tail -3
+# every variant keeps the arithmetic of the default kernel (only loads / register allocation differ): the parity file must stay green
+for lib in $(ls variants/lib_*.so); do
+  echo "parity $lib: $(NDTB_LIB=$GRAFT_REPO_ROOT/$lib timeout 200 python -m pytest tests/test_gpu_parity.py -m gpu -q -x 2>&1 | tail -1)"
+done
 for pass in 1 2; do
 one intree "" ""
 for lib in $(ls variants/lib_*.so); do one $lib $lib ""; done
