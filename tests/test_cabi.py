@@ -90,3 +90,21 @@ def test_product_does_not_import_oracle():
                     if re.search(r"from oracle|import oracle|ndt_oracle|libndt_oracle", t):
                         bad.append(os.path.join(d, f))
     assert not bad, bad
+
+
+def test_variant_macros_exist_and_default_off():
+    """scripts/build_variants.py may only name macros the kernels know, and every experiment macro that changes the data
+    path defaults to the measured configuration (the in-tree library is what profiles/ was measured with)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("build_variants", os.path.join(ROOT, "scripts", "build_variants.py"))
+    bv = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bv)
+    csrc = os.path.join(ROOT, "xchu_slam_b200", "csrc")
+    src = "".join(open(os.path.join(csrc, f)).read() for f in os.listdir(csrc) if f.endswith((".cu", ".h", ".cuh")))
+    defaults = dict(re.findall(r"#define\s+(NDTB_FAST_[A-Z0-9_]+)\s+(\d+)", src))
+    for name, defs in bv.VARIANTS.items():
+        for d in defs:
+            macro = d.split("=")[0]
+            assert macro in defaults, (name, macro)
+    assert defaults["NDTB_FAST_REC64"] == "0" and defaults["NDTB_FAST_UNCOND"] == "0" and defaults["NDTB_FAST_ACC_SMEM"] == "0"
+    assert defaults["NDTB_FAST_AB"] == "0" and defaults["NDTB_FAST_PFP"] == "1" and defaults["NDTB_FAST_MINBLOCKS"] == "4"
