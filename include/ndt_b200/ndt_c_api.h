@@ -46,12 +46,21 @@ typedef struct ndtb_params {
   int strict_math;       /* which derivative kernel runs.  1: the term-by-term kernel that reproduces every float
                             operation of NDT_I:491-548 in the reference's order (bit-identical per-pair terms: a whole
                             odometry sequence then replays the reference's trajectory exactly); 0: the per-point factorised
-                            kernel (3.5x faster per evaluation; score / gradient / Hessian within 1e-6 relative of the
-                            reference arithmetic); -1 (default): 1 for an ndtb_handle (single registrations are
-                            latency-bound, the strict kernel costs nothing measurable), 0 for an ndtb_batch */
+                            kernel only (3.5x faster per evaluation; score / gradient / Hessian within 1e-6 relative of the
+                            reference arithmetic, but a registration whose Newton iteration does not contract can end
+                            centimetres from the reference's result); -1 (default): 1 for an ndtb_handle (single
+                            registrations are latency-bound, the strict kernel costs nothing measurable); for an ndtb_batch
+                            HYBRID: every registration runs with the factorised kernel, and those that took more than
+                            `replay_iters` iterations, did not converge, or took a discrete decision of the loop (the
+                            |step| < eps test NDT_I:152-157, the descent-direction flip NDT_I:774-784) within 1e-3 of its
+                            threshold are replayed from their initial guess with the term-by-term kernel inside the same
+                            ndtb_batch_run, so that every result of the batch -- iteration counts included -- is the
+                            reference arithmetic's */
   long long dense_max_cells; /* cell -> voxel lookups go through a dense int32 index over the target's bounding box
                             when that box (padded by 2 cells) holds at most this many cells, else through the
                             hash table; 0 = hash only.  default 2^26 (256 MB of index per target at most) */
+  int replay_iters;      /* hybrid batches (strict_math = -1): iteration count above which a registration is replayed with
+                            the term-by-term kernel; <= 0: only non-converged / borderline registrations.  default 12 */
 } ndtb_params;
 
 typedef struct ndtb_result {
@@ -228,8 +237,19 @@ typedef struct ndtb_batch_stats {
   double build_ms, deriv_ms, total_ms;
   long long kernel_launches, deriv_launches;
   long long points_evaluated, pairs_evaluated, probes;
+  /* hybrid batches: registrations replayed with the term-by-term kernel, device time of that pass (ms), of its derivative
+   * launches, their number, and the points / pairs they evaluated.  deriv_ms / deriv_launches / points_evaluated /
+   * pairs_evaluated above count the first (factorised-kernel) pass only. */
+  long long replayed;
+  double replay_ms, replay_deriv_ms;
+  long long replay_deriv_launches, replay_points, replay_pairs;
 } ndtb_batch_stats;
 int ndtb_batch_get_stats(ndtb_batch* b, ndtb_batch_stats* s);
+/* Per item of the last ndtb_batch_run (arrays of that many entries, any may be NULL): replayed[i] = 1 when the hybrid mode ran
+ * registration i again with the term-by-term kernel; borderline[i] / n_rise[i] / last_norm[i] = the loop diagnostics of its FINAL
+ * pass (a discrete decision taken within 1e-3 of its threshold; line-search steps that grew after having dropped below
+ * step_size; |delta_p| of the last Newton solve, NDT_I:119-125).  Test / tuning hook. */
+int ndtb_batch_get_diag(ndtb_batch* b, int* replayed, int* borderline, int* n_rise, double* last_norm);
 /* Run all of the batch's copies and kernels on the caller's CUDA stream (a cudaStream_t) instead of
  * the batch's own, so that the caller's CUDA events bracket the work. */
 int ndtb_batch_set_stream(ndtb_batch* b, void* cuda_stream);

@@ -234,12 +234,19 @@ def test_align_identity_guess(case_tiny):
 
 
 @pytest.mark.parametrize("strict", [False, True])
-def test_align_more_thuente_live(case_tiny, strict):
+@pytest.mark.parametrize("step,eps,max_iter,trials", [(0.004, 0.01, 6, False), (0.5, 2.0, 4, True), (0.3, 1.0, 4, True)])
+def test_align_more_thuente_live(case_tiny, strict, step, eps, max_iter, trials):
     """step_size <= trans_eps/2 makes the reference's inverted predicate (NDT_I:807) run the MT loop
-    and computeHessian; the device state machine must take the same trial steps."""
-    o, g = _mk(case_tiny, step=0.004, eps=0.01, max_iter=6, strict=strict)
+    and computeHessian; the device state machine must take the same trial steps.  The small-step case passes the Wolfe test
+    at its first trial; the metre-sized ones fail it, run trialValueSelectionMT / updateIntervalMT for the full ten trials
+    (kind 2) and end in computeHessian (kind 3)."""
+    o, g = _mk(case_tiny, step=step, eps=eps, max_iter=max_iter, strict=strict)
     ro, rg = _check_align(o, g, case_tiny[3], strict=strict)
-    assert any(t["kind"] == 2 for t in ro["trace"]) or any(t["kind"] == 3 for t in ro["trace"]) or True
+    kinds = [t["kind"] for t in ro["trace"]]
+    assert [t["kind"] for t in g.trace()] == kinds
+    assert 1 in kinds
+    if trials:
+        assert 2 in kinds and 3 in kinds
 
 
 def test_compute_hessian_f64(case_tiny):
@@ -457,26 +464,49 @@ def test_align_c4_dense_scan(case_c4, strict):
     assert abs(g.getFitnessScore() - o.fitness()) <= 1e-9 * o.fitness()
 
 
+def _oracle_batch(w, n_threads=None):
+    """The CPU oracle over every registration of a batch workload (one grid build per submap)."""
+    from oracle import oracle
+    o = oracle.OracleNDT()
+    o.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2, num_threads=n_threads or oracle.max_threads())
+    ref_res = [None] * len(w["item_target"])
+    it = np.asarray(w["item_target"])
+    for t in range(len(w["targets"])):
+        ids = np.flatnonzero(it == t)
+        if len(ids) == 0:
+            continue
+        o.set_target(w["targets"][t])
+        for i in ids:
+            o.set_source(w["sources"][w["item_source"][i]])
+            ref_res[i] = o.align(w["guesses"][i])
+            ref_res[i].pop("trace", None)
+    return o, ref_res
+
+
+def _assert_item_parity(r, q, tag):
+    """north_star gate, per registration: iteration counts match; final transform within 1e-4 m / 1e-5 rad."""
+    dT = np.max(np.abs(r["T"][:3, 3] - q["T"][:3, 3]))
+    dR = np.max(np.abs(r["T"][:3, :3] - q["T"][:3, :3]))
+    assert r["iterations"] == q["iterations"] and r["converged"] == q["converged"] and dT < 1e-4 and dR < 1e-5, \
+        (tag, r["iterations"], q["iterations"], dT, dR)
+
+
 def test_batch_c5_shape_against_oracle():
     """BASELINE configs[4] shape (20k-pt scans vs 1M-pt submaps, 2 submaps x 8 scans x 4 hypotheses = 64 registrations in
-    one batch) against the oracle, registration by registration: equal iteration counts and convergence flags, final
-    transforms within 1e-4 m / 1e-5 rad.  Strict kernel: every registration.  Production kernel: every registration
-    that settles; the few that do not (fixed-step Newton wandering for > 14 iterations) are
-    outside what any non-bit-replaying implementation can promise and must stay a small minority."""
+    one batch) against the oracle, registration by registration, NO waiver: equal iteration counts and convergence flags,
+    final transforms within 1e-4 m / 1e-5 rad -- with the term-by-term kernel (strict_math 1) and in the batch's default
+    HYBRID mode (factorised kernel, then a strict replay of the registrations that give a 1e-7 difference room to grow)."""
     from oracle import oracle
     from xchu_slam_b200 import ndt, synth
     w = synth.batch_workload(n_submaps=2, scans_per_submap=8, hyps_per_scan=4)
-    o = oracle.OracleNDT()
-    o.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2, num_threads=oracle.max_threads())
-    ref_res = [None] * len(w["item_target"])
+    o, ref_res = _oracle_batch(w)
     for t in range(2):
         o.set_target(w["targets"][t])
         for i in np.flatnonzero(np.asarray(w["item_target"]) == t):
             o.set_source(w["sources"][w["item_source"][i]])
-            ref_res[i] = o.align(w["guesses"][i])
-            ref_res[i]["fitness"] = o.fitness()
-            ref_res[i]["fitness_1m"] = o.fitness(1.0)
-    for strict in (1, 0):
+            ref_res[i]["fitness"] = o.fitness(T=ref_res[i]["T"])
+            ref_res[i]["fitness_1m"] = o.fitness(1.0, T=ref_res[i]["T"])
+    for strict in (1, -1):
         b = ndt.BatchNDT()
         b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2, strict_math=strict)
         for t in w["targets"]:
@@ -486,20 +516,110 @@ def test_batch_c5_shape_against_oracle():
         res = b.run(w["item_target"], w["item_source"], w["guesses"])
         # getFitnessScore of every registration of the batch (the loop-closure gate, pgo_node.cpp:460-476)
         fit, fit1 = b.fitness(len(res)), b.fitness(len(res), 1.0)
-        n_off = 0
         for k, (r, q) in enumerate(zip(res, ref_res)):
-            dT = np.max(np.abs(r["T"][:3, 3] - q["T"][:3, 3]))
-            dR = np.max(np.abs(r["T"][:3, :3] - q["T"][:3, :3]))
-            ok = r["iterations"] == q["iterations"] and r["converged"] == q["converged"] and dT < 1e-4 and dR < 1e-5
-            if strict or q["iterations"] <= 14:
-                assert ok, (strict, r["iterations"], q["iterations"], dT, dR)
-            if ok:
-                assert abs(fit[k] - q["fitness"]) <= 1e-5 * q["fitness"] and abs(fit1[k] - q["fitness_1m"]) <= 1e-5 * q["fitness_1m"]
-            n_off += 0 if ok else 1
-        assert n_off <= 2
+            _assert_item_parity(r, q, (strict, k))
+            assert abs(fit[k] - q["fitness"]) <= 1e-5 * q["fitness"] and abs(fit1[k] - q["fitness_1m"]) <= 1e-5 * q["fitness_1m"]
+        st = b.stats()
+        assert (st["replayed"] == 0) if strict == 1 else (0 <= st["replayed"] < len(res))
         # the registrations recover the ground truth (the batch is not trivially wrong everywhere)
         gt_err = [np.max(np.abs(r["T"][:3, 3] - synth.pose6_to_matrix(g6)[:3, 3])) for r, g6 in zip(res, w["gt"])]
         assert np.median(gt_err) < 0.05
+
+
+def test_batch_c5_hybrid_512_registrations():
+    """The batch path the headline is measured on, at scale: 8 one-million-point submaps x 8 scans x 8 hypotheses = 512
+    registrations in ONE ndtb_batch_run in the default hybrid mode, every one of them against the CPU oracle -- iteration
+    counts and convergence flags equal, final transform within 1e-4 m / 1e-5 rad (north_star; the loop NDT_I:114-159 and
+    its iteration test :152-157).  The replayed minority must exist (the workload has non-settling registrations) and stay a
+    minority (it is what the hybrid mode costs)."""
+    from xchu_slam_b200 import ndt, synth
+    w = synth.batch_workload(n_submaps=8, scans_per_submap=8, hyps_per_scan=8)
+    _, ref_res = _oracle_batch(w)
+    b = ndt.BatchNDT()
+    b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2)
+    assert b.params.strict_math == -1
+    for t in w["targets"]:
+        b.add_target(t)
+    for s in w["sources"]:
+        b.add_source(s)
+    res = b.run(w["item_target"], w["item_source"], w["guesses"])
+    assert len(res) == 512
+    for k, (r, q) in enumerate(zip(res, ref_res)):
+        _assert_item_parity(r, q, k)
+    st, dg = b.stats(), b.diag(len(res))
+    assert st["replayed"] == int(dg["replayed"].sum())
+    assert 0 < st["replayed"] < len(res) // 2
+    # every registration beyond the iteration threshold was replayed
+    its = np.array([q["iterations"] for q in ref_res])
+    assert np.all(dg["replayed"][its > b.params.replay_iters] == 1)
+
+
+def test_batch_edge_cases_hybrid(case_tiny):
+    """The degenerate inputs of test_edge_cases as items of ONE default (hybrid) batch: the one-point source (rank-3 Hessian,
+    pseudo-inverse step) is flagged by the device and replayed, so the batch follows the oracle there too."""
+    from test_reference_build import _edge_cases
+    from oracle import oracle
+    from xchu_slam_b200 import ndt
+    cases = _edge_cases(case_tiny)
+    names = ["source outside the grid", "one-point source", "no voxel reaches 6 points"]
+    b = ndt.BatchNDT()
+    b.set_params(resolution=1.0, trans_eps=0.01, max_iter=30, search_method=2)
+    it, isrc, G, refs = [], [], [], []
+    for nme in names:
+        s, t, g0 = cases[nme]
+        o = oracle.OracleNDT()
+        o.set_params(resolution=1.0, trans_eps=0.01, max_iter=30, search_method=2, num_threads=1)
+        o.set_target(t); o.set_source(s)
+        refs.append(o.align(g0))
+        it.append(b.add_target(t)); isrc.append(b.add_source(s)); G.append(g0)
+    res = b.run(it, isrc, G)
+    for nme, r, q in zip(names, res, refs):
+        assert r["iterations"] == q["iterations"] and r["converged"] == q["converged"], nme
+        assert np.max(np.abs(r["T"] - q["T"])) < 1e-4, nme
+    assert b.diag(len(res))["replayed"][1] == 1
+
+
+def test_batch_empty_target_slot_reuse(case_small):
+    """A target slot reused after clear() for an EMPTY cloud (an empty loop-closure submap legally gets an id) presents an
+    empty grid, as the reference's empty leaves_ does -- not the previous cloud's voxel table."""
+    from oracle import oracle
+    from xchu_slam_b200 import ndt
+    src, tgt, gt, guess = case_small
+    b = ndt.BatchNDT()
+    b.set_params(resolution=1.0, trans_eps=0.01, max_iter=30, search_method=2)
+    b.add_target(tgt); b.add_source(src)
+    r0 = b.run([0], [0], [guess])[0]
+    assert r0["iterations"] > 1
+    b.clear()
+    b.add_target(np.zeros((0, 4), np.float32)); b.add_source(src)
+    r1 = b.run([0], [0], [guess])[0]
+    o = oracle.OracleNDT()
+    o.set_params(resolution=1.0, trans_eps=0.01, max_iter=30, search_method=2, num_threads=1)
+    o.set_target(np.zeros((0, 4), np.float32)); o.set_source(src)
+    q = o.align(guess)
+    assert r1["iterations"] == q["iterations"] and r1["converged"] == q["converged"] and r1["score"] == 0.0
+    assert np.array_equal(r1["T"], q["T"])
+
+
+def test_set_target_auto_non_extension_of_overlapping_size(case_small):
+    """setInputTarget through the auto entry point with a cloud that is NOT an extension of the resident one and whose size
+    lies in (old_n, 2 old_n]: the fallback moves the fresh copy down over itself (source and destination ranges overlap) and
+    must still build the table of exactly that cloud."""
+    from oracle import oracle
+    from xchu_slam_b200 import ndt
+    src, tgt, gt, guess = case_small
+    old_n = 25000
+    g = ndt.NormalDistributionsTransform()
+    g.setInputTarget(tgt[:old_n])
+    o = oracle.OracleNDT()
+    o.set_params(resolution=1.0)
+    for n in (old_n + 1, old_n + old_n // 2):
+        fresh = np.ascontiguousarray(tgt[len(tgt) - n:][::-1])        # unrelated order and content
+        g2 = ndt.NormalDistributionsTransform()
+        g2.setInputTarget(tgt[:old_n])
+        assert g2.setInputTargetAuto(fresh) is False
+        o.set_target(fresh)
+        _compare_voxels(o, g2)
 
 
 @pytest.mark.parametrize("strict", [False, True])

@@ -173,11 +173,17 @@ def test_align_resolutions(case_small, res):
     _same_align(o, r, case_small[3])
 
 
-def test_align_more_thuente_live(case_tiny):
-    """step_size <= eps/2 makes the inverted predicate (NDT_I:807) run the More-Thuente loop and computeHessian."""
-    o, r = _pair(case_tiny, step=0.004, eps=0.01, max_iter=6)
+@pytest.mark.parametrize("step,eps,max_iter,trials", [(0.004, 0.01, 6, False), (0.5, 2.0, 4, True), (0.3, 1.0, 4, True)])
+def test_align_more_thuente_live(case_tiny, step, eps, max_iter, trials):
+    """step_size <= eps/2 makes the inverted predicate (NDT_I:807) run the More-Thuente loop and computeHessian.  The
+    metre-sized steps fail the Wolfe test at the first trial: ten trialValueSelectionMT / updateIntervalMT rounds (kind 2),
+    then computeHessian (kind 3, NDT_I:912-913)."""
+    o, r = _pair(case_tiny, step=step, eps=eps, max_iter=max_iter)
     ro, _ = _same_align(o, r, case_tiny[3])
-    assert any(t["kind"] != 0 for t in ro["trace"][1:])
+    kinds = [t["kind"] for t in ro["trace"]]
+    assert any(k != 0 for k in kinds[1:])
+    if trials:
+        assert 2 in kinds and 3 in kinds
 
 
 def test_align_iteration_cap(case_tiny):

@@ -183,9 +183,7 @@ struct Engine {
   // measurable there and replays the reference's float arithmetic bit for bit) gets the strict kernel, a batch the
   // factorised one.
   bool single = false;
-  bool use_strict() const {
-    return params.strict_math > 0 || (params.strict_math < 0 && single) || params.search_method == NDTB_DIRECT26;
-  }
+  bool use_strict() const { return kernel_mode() == KM_STRICT; }
 
   int init(int dev) {
     device = dev;
@@ -193,6 +191,8 @@ struct Engine {
     if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return fail("no CUDA device available (this library has no CPU fallback)");
     if (dev < 0 || dev >= count) return fail("invalid device ordinal");
     CKE(cudaSetDevice(dev));
+    CKE(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+    if (sm_count < 1) sm_count = 1;
     CKE(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     CKE(cudaStreamCreateWithFlags(&copy_stream, cudaStreamNonBlocking));
     CKE(cudaEventCreateWithFlags(&sources_uploaded, cudaEventDisableTiming));
@@ -222,7 +222,7 @@ struct Engine {
     targets.clear();
     build_ws_destroy(ws);
     nn_destroy(nn);
-    st_states.release(); st_bmap.release(); st_tables.release();
+    st_states.release(); st_bmap.release(); st_tables.release(); st_idx.release();
     cudaFree(d_tables); cudaFree(src_pool); cudaFree(d_states); cudaFree(d_blockmap); cudaFree(d_partials);
     cudaFree(d_trace); cudaFree(d_active); cudaFreeHost(h_active); cudaFree(d_T16); cudaFree(d_p6);
     cudaFree(d_output); cudaFree(d_d2);
@@ -281,8 +281,9 @@ struct Engine {
   int build_target(Target& t) {
     table_config(t);
     if (t.pending_upload) { CKE(cudaStreamWaitEvent(stream, t.uploaded, 0)); t.pending_upload = false; }
+    t.built = false;
     CKE(table_clear(t.ts, stream, &stats.kernel_launches));
-    CKE(table_append(t.ts, ws, t.use ? t.use : t.pts, t.n, stream, &stats.kernel_launches));
+    CKE(table_append(t.ts, ws, t.use ? t.use : t.pts, t.n, stream, &stats.kernel_launches));   // n == 0: an empty grid, as the reference's empty leaves_
     t.built = true;
     return 0;
   }
@@ -303,8 +304,10 @@ struct Engine {
   // lanes are already building; targets are handed out dynamically, so the calling thread joins in late at no cost.
   int build_pending_targets(const std::function<void()>& overlap = std::function<void()>()) {
     std::vector<Target*> todo;
-    for (auto& t : targets)
-      if (!t.built && t.n > 0) todo.push_back(&t);
+    // (a target without points -- an empty submap -- is "built" into an empty grid, so that a slot reused after
+    // ndtb_batch_clear never presents the previous cloud's voxel table)
+    for (int k = 0; k < (single ? (int)targets.size() : n_targets_live); ++k)
+      if (!targets[k].built) todo.push_back(&targets[k]);
     if (todo.size() <= 1) {
       if (overlap) overlap();
       return todo.empty() ? 0 : build_target(*todo[0]);
@@ -325,7 +328,8 @@ struct Engine {
         if (t.pending_upload) { ce = cudaStreamWaitEvent(bs, t.uploaded, 0); t.pending_upload = false; }
         if (ce == cudaSuccess) ce = table_clear(t.ts, bs, &launches[g]);
         if (ce == cudaSuccess) ce = table_append(t.ts, bws[g], t.use ? t.use : t.pts, t.n, bs, &launches[g]);
-        t.built = true;
+        t.built = (ce == cudaSuccess);
+        if (ce != cudaSuccess) t.ts.valid = false;
       }
       if (ce == cudaSuccess) ce = cudaEventRecord(bdone[g], bs);
       if (ce != cudaSuccess) errs[g] = std::string("table build: ") + cudaGetErrorString(ce);
@@ -430,14 +434,93 @@ struct Engine {
     st.phase = kPhaseStart;
   }
 
+  // Which derivative kernel(s) a run uses.  KM_HYBRID (a batch with strict_math < 0, the default): every registration runs
+  // with the factorised kernel; those whose Newton iteration gives a 1e-7 arithmetic difference room to grow -- more than
+  // params.replay_iters iterations, not converged, a non-contracting step sequence, or a discrete decision of the loop taken
+  // at its threshold (AlignState::borderline) -- are then REPLAYED from their initial guess with the term-by-term kernel, in
+  // the same call, so that every result of the batch is the reference arithmetic's (iteration counts included).
+  enum { KM_FAST = 0, KM_STRICT = 1, KM_HYBRID = 2 };
+  int kernel_mode() const {
+    if (params.strict_math > 0 || params.search_method == NDTB_DIRECT26) return KM_STRICT;
+    if (params.strict_math < 0) return single ? KM_STRICT : KM_HYBRID;
+    return KM_FAST;
+  }
+  int sm_count = 148;                 // cudaDevAttrMultiProcessorCount of `device` (init)
+  int target_blocks() const { return sm_count * 8; }
+  PinnedBuf st_idx;                   // replay pass: ids of the registrations run again
+  std::vector<unsigned char> replay_flag;   // per item of the last run: 1 = replayed with the strict kernel
+
+  int plan_chunk(size_t total_pts) const {
+    // small blocks keep the tail iterations (few registrations still active) balanced over the SMs
+    int chunk = (int)((total_pts / (size_t)target_blocks() + 255) / 256 * 256);
+    if (chunk < 256) chunk = 256;
+    if (chunk > 1024) chunk = 1024;   // 1024 amortises the per-block set-up and reduction best (profiles/r01_v9_kernel_variants.txt)
+    if (const char* ev = getenv("NDTB_CHUNK")) { const int c = atoi(ev); if (c >= 128) chunk = c; }   // tuning knob
+    return chunk;
+  }
+
+  // The evaluation loop of one pass: derivatives -> newton pairs until the device reports no unfinished registration.
+  int newton_loop(int n_items, bool strict, bool want_trace, bool replan, int n_blocks, int chunk, size_t& ev_used, size_t ev_first) {
+    const bool mt_live = !((params.step_size - params.trans_eps / 2) > 0);   // NDT_I:807: the inner loop runs only then
+    const int evals_per_iter = mt_live ? 12 : 1;
+    const int max_evals = 1 + (params.max_iter + 2) * evals_per_iter;
+    (void)ev_first;
+    // PH_START: set up the first evaluation request
+    CKE(launch_newton(d_states, n_items, d_partials, want_trace ? d_trace : nullptr, trace_cap, d_active, stream));
+    stats.kernel_launches++;
+    int poll = 4;
+    if (const char* ev = getenv("NDTB_POLL")) { const int v = atoi(ev); if (v >= 1) poll = v; }   // tuning knob
+    for (int it = 0; it < max_evals; ++it) {
+      if (deriv_events.size() < ev_used + 2) {
+        cudaEvent_t a, b;
+        CKE(cudaEventCreate(&a)); CKE(cudaEventCreate(&b));
+        deriv_events.push_back(a); deriv_events.push_back(b);
+      }
+      CKE(cudaEventRecord(deriv_events[ev_used], stream));
+      CKE((strict ? launch_derivatives : launch_derivatives_fast)(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk,
+                                                                  d_partials, params.search_method, mt_live, stream));
+      CKE(cudaEventRecord(deriv_events[ev_used + 1], stream));
+      ev_used += 2;
+      stats.kernel_launches += mt_live ? 2 : 1;
+      if (mt_live) {
+        CKE(launch_hessian_f64(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk, d_partials, stream));
+        stats.kernel_launches++;
+      }
+      CKE(launch_newton(d_states, n_items, d_partials, want_trace ? d_trace : nullptr, trace_cap, d_active, stream));
+      stats.kernel_launches++;
+      if ((it + 1) % poll == 0 || it + 1 == max_evals) {
+        // published by a one-thread kernel straight into mapped host memory: a D2H memcpy would queue on a copy engine
+        // behind another batch's multi-megabyte uploads and stall this loop for their whole duration
+        if (replan) { CKE(launch_replan(d_states, n_items, d_blockmap, h_active_dev + 1, target_blocks(), stream)); stats.kernel_launches++; }
+        CKE(launch_publish(d_active, h_active_dev, stream));
+        stats.kernel_launches++;
+        CKE(cudaStreamSynchronize(stream));
+        if (*(volatile int*)h_active <= 0) break;
+        if (replan) { n_blocks = ((volatile int*)h_active)[1]; chunk = ((volatile int*)h_active)[2]; }
+      }
+    }
+    return 0;
+  }
+
+  static void state_to_result(const AlignState& st, ndtb_result& r) {
+    std::memcpy(r.T, st.final_T, sizeof(r.T));
+    r.iterations = st.nr_iterations;
+    r.converged = st.done ? st.converged : 0;
+    r.score = st.score;
+    r.trans_probability = st.trans_probability;
+    r.n_evals = st.n_evals;
+  }
+
   // Run n_items registrations to completion on the device.  want_trace: per-evaluation records.
   int run_items(int n_items, const int* item_target, const int* item_source, const float* guesses, ndtb_result* results,
                 bool want_trace) {
     last_item_target.clear();
+    replay_flag.clear();
     if (n_items <= 0) return 0;
     CKE(cudaSetDevice(device));
     last_item_target.assign(item_target, item_target + n_items);
     stats = ndtb_batch_stats{};
+    const int mode = kernel_mode();
     // work decomposition: one block per `chunk` source points of one registration
     size_t total_pts = 0;
     for (int i = 0; i < n_items; ++i) {
@@ -445,22 +528,21 @@ struct Engine {
       if (item_source[i] < 0 || item_source[i] >= (int)sources.size()) return fail("item source id out of range");
       total_pts += sources[item_source[i]].n;
     }
-    // small blocks keep the tail iterations (few registrations still active) balanced over the 148 SMs
-    int chunk = (int)((total_pts / (148 * 8) + 255) / 256 * 256);
-    if (chunk < 256) chunk = 256;
-    if (chunk > 1024) chunk = 1024;   // 1024 amortises the per-block set-up and reduction best (profiles/r01_v9_kernel_variants.txt)
-    if (const char* ev = getenv("NDTB_CHUNK")) { const int c = atoi(ev); if (c >= 128) chunk = c; }   // tuning knob
+    int chunk = plan_chunk(total_pts);
     size_t total_blocks = 0;
     for (int i = 0; i < n_items; ++i) total_blocks += (sources[item_source[i]].n + chunk - 1) / chunk;
     CKE(cudaStreamSynchronize(stream));     // the staging buffers may still be read by the previous run's pulls
     CKE(st_states.reserve((size_t)n_items * sizeof(AlignState)));
-    CKE(st_bmap.reserve(total_blocks * sizeof(int2) + 16));
+    // (the replay pass plans its own, smaller, set of blocks at 256 points each at worst: room for that too)
+    size_t blocks256 = 0;
+    for (int i = 0; i < n_items; ++i) blocks256 += (sources[item_source[i]].n + 255) / 256;
+    CKE(st_bmap.reserve(std::max(total_blocks, blocks256) * sizeof(int2) + 16));
     h_states = static_cast<AlignState*>(st_states.h);
     int2* bmap = static_cast<int2*>(st_bmap.h);
     size_t nb_fill = 0;
     // the registration states and the block map are filled on this thread WHILE the other lanes build the voxel tables
-    // k_replan never needs more blocks than the start (chunk at its cap) or 148 * 8 + one per registration (smaller chunks)
-    const size_t blocks_cap = std::max(total_blocks, (size_t)(148 * 8 + n_items)) + 16;
+    // k_replan never needs more blocks than the start (chunk at its cap) or target_blocks() + one per registration (smaller chunks)
+    const size_t blocks_cap = std::max(std::max(total_blocks, blocks256), (size_t)(target_blocks() + n_items)) + 16;
     // (a block size forced through NDTB_CHUNK may exceed the planner's cap, which is what blocks_cap assumes: no re-planning then)
     const bool replan = n_items > 1 && !getenv("NDTB_NO_REPLAN") && !getenv("NDTB_CHUNK");
     if (ensure(d_states, states_cap, (size_t)n_items)) return 1;
@@ -485,51 +567,63 @@ struct Engine {
     CKE(cudaEventRecord(ev[1], stream));
     if (sources_pending) { CKE(cudaStreamWaitEvent(stream, sources_uploaded, 0)); sources_pending = false; }
     if (sync_tables()) return 1;
-    int n_blocks = (int)nb_fill;
-    const bool mt_live = !((params.step_size - params.trans_eps / 2) > 0);   // NDT_I:807: the inner loop runs only then
-    const int evals_per_iter = mt_live ? 12 : 1;
-    const int max_evals = 1 + (params.max_iter + 2) * evals_per_iter;
+    const bool mt_live = !((params.step_size - params.trans_eps / 2) > 0);
+    const int max_evals = 1 + (params.max_iter + 2) * (mt_live ? 12 : 1);
     trace_cap = want_trace ? max_evals + 1 : 0;
     if (want_trace && ensure(d_trace, trace_doubles, (size_t)n_items * trace_cap * kTraceRec)) return 1;
     CKE(launch_set_int(d_active, n_items, stream));
     stats.kernel_launches += 3;
     CKE(cudaEventRecord(ev[2], stream));
-    // PH_START: set up the first evaluation request
-    CKE(launch_newton(d_states, n_items, d_partials, want_trace ? d_trace : nullptr, trace_cap, d_active, stream));
-    stats.kernel_launches++;
     size_t ev_used = 0;
-    int poll = 4;
-    if (const char* ev = getenv("NDTB_POLL")) { const int v = atoi(ev); if (v >= 1) poll = v; }   // tuning knob
-    for (int it = 0; it < max_evals; ++it) {
-      if (deriv_events.size() < ev_used + 2) {
-        cudaEvent_t a, b;
-        CKE(cudaEventCreate(&a)); CKE(cudaEventCreate(&b));
-        deriv_events.push_back(a); deriv_events.push_back(b);
+    if (newton_loop(n_items, mode == KM_STRICT, want_trace, replan, (int)nb_fill, chunk, ev_used, 0)) return 1;
+    const size_t ev_pass1 = ev_used;
+    CKE(cudaMemcpyAsync(h_states, d_states, (size_t)n_items * sizeof(AlignState), cudaMemcpyDeviceToHost, stream));
+    CKE(cudaStreamSynchronize(stream));
+    for (int i = 0; i < n_items; ++i) {
+      const AlignState& st = h_states[i];
+      state_to_result(st, results[i]);
+      stats.points_evaluated += (long long)st.n_src * st.n_evals;
+      stats.pairs_evaluated += st.pairs_total;
+    }
+    // ---- replay pass of a hybrid batch --------------------------------------------------------------------------
+    int n_replay = 0;
+    if (mode == KM_HYBRID) {
+      replay_flag.assign((size_t)n_items, 0);
+      CKE(st_idx.reserve((size_t)n_items * sizeof(int)));
+      int* idx = static_cast<int*>(st_idx.h);
+      int k_iters = params.replay_iters;
+      if (const char* ev = getenv("NDTB_REPLAY_ITERS")) k_iters = atoi(ev);   // tuning knob
+      int k_rise = 1 << 30;
+      if (const char* ev = getenv("NDTB_REPLAY_RISE")) k_rise = atoi(ev);     // tuning knob: replay when n_rise >= this
+      size_t pts = 0;
+      for (int i = 0; i < n_items; ++i) {
+        const AlignState& st = h_states[i];
+        const bool again = !st.done || !st.converged || st.borderline || (k_iters > 0 && st.nr_iterations > k_iters) || st.n_rise >= k_rise;
+        if (!again || st.n_src <= 0) continue;
+        idx[n_replay++] = i;
+        replay_flag[i] = 1;
+        pts += (size_t)st.n_src;
       }
-      CKE(cudaEventRecord(deriv_events[ev_used], stream));
-      CKE((use_strict() ? launch_derivatives : launch_derivatives_fast)(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk,
-                                                                                d_partials, params.search_method, mt_live, stream));
-      CKE(cudaEventRecord(deriv_events[ev_used + 1], stream));
-      ev_used += 2;
-      stats.kernel_launches += mt_live ? 2 : 1; stats.deriv_launches++;
-      if (mt_live) {
-        CKE(launch_hessian_f64(d_states, d_tables, src_pool, d_blockmap, n_blocks, chunk, d_partials, stream));
-        stats.kernel_launches++;
-      }
-      CKE(launch_newton(d_states, n_items, d_partials, want_trace ? d_trace : nullptr, trace_cap, d_active, stream));
-      stats.kernel_launches++;
-      if ((it + 1) % poll == 0 || it + 1 == max_evals) {
-        // published by a one-thread kernel straight into mapped host memory: a D2H memcpy would queue on a copy engine
-        // behind another batch's multi-megabyte uploads and stall this loop for their whole duration
-        if (replan) { CKE(launch_replan(d_states, n_items, d_blockmap, h_active_dev + 1, stream)); stats.kernel_launches++; }
-        CKE(launch_publish(d_active, h_active_dev, stream));
-        CKE(cudaStreamSynchronize(stream));
-        if (*(volatile int*)h_active <= 0) break;
-        if (replan) { n_blocks = ((volatile int*)h_active)[1]; chunk = ((volatile int*)h_active)[2]; }
+      if (n_replay > 0) {
+        chunk = plan_chunk(pts);
+        nb_fill = 0;
+        for (int k = 0; k < n_replay; ++k) {
+          const int i = idx[k];
+          AlignState& st = h_states[i];
+          fill_state(st, item_target[i], sources[item_source[i]], guesses + (size_t)i * 16);
+          st.first_block = (int)nb_fill;
+          st.n_blocks = (st.n_src + chunk - 1) / chunk;
+          for (int b = 0; b < st.n_blocks; ++b) bmap[nb_fill++] = make_int2(i, b * chunk);
+        }
+        CKE(launch_pull_items(d_states, static_cast<const AlignState*>(st_states.d), static_cast<const int*>(st_idx.d), n_replay, stream));
+        CKE(launch_pull(d_blockmap, st_bmap.d, nb_fill * sizeof(int2), stream));
+        CKE(launch_set_int(d_active, n_replay, stream));
+        stats.kernel_launches += 3;
+        if (newton_loop(n_items, true, false, replan, (int)nb_fill, chunk, ev_used, ev_pass1)) return 1;
+        CKE(cudaMemcpyAsync(h_states, d_states, (size_t)n_items * sizeof(AlignState), cudaMemcpyDeviceToHost, stream));
       }
     }
     CKE(cudaEventRecord(ev[3], stream));
-    CKE(cudaMemcpyAsync(h_states, d_states, (size_t)n_items * sizeof(AlignState), cudaMemcpyDeviceToHost, stream));
     if (want_trace) {
       h_trace.resize((size_t)n_items * trace_cap * kTraceRec);
       CKE(cudaMemcpyAsync(h_trace.data(), d_trace, h_trace.size() * sizeof(double), cudaMemcpyDeviceToHost, stream));
@@ -540,19 +634,20 @@ struct Engine {
     CKE(cudaEventElapsedTime(&ms, ev[0], ev[3])); stats.total_ms = ms;
     CKE(cudaEventElapsedTime(&ms, ev[2], ev[3])); last_align_ms = ms;
     stats.deriv_ms = 0;
-    for (size_t k = 0; k + 1 < ev_used; k += 2) { CKE(cudaEventElapsedTime(&ms, deriv_events[k], deriv_events[k + 1])); stats.deriv_ms += ms; }
-    for (int i = 0; i < n_items; ++i) {
-      const AlignState& st = h_states[i];
-      ndtb_result& r = results[i];
-      std::memcpy(r.T, st.final_T, sizeof(r.T));
-      r.iterations = st.nr_iterations;
-      r.converged = st.converged;
-      r.score = st.score;
-      r.trans_probability = st.trans_probability;
-      r.n_evals = st.n_evals;
-      if (!st.done) { r.converged = 0; }
-      stats.points_evaluated += (long long)st.n_src * st.n_evals;
-      stats.pairs_evaluated += st.pairs_total;
+    for (size_t k = 0; k + 1 < ev_pass1; k += 2) { CKE(cudaEventElapsedTime(&ms, deriv_events[k], deriv_events[k + 1])); stats.deriv_ms += ms; }
+    stats.deriv_launches = (long long)(ev_pass1 / 2);
+    for (size_t k = ev_pass1; k + 1 < ev_used; k += 2) { CKE(cudaEventElapsedTime(&ms, deriv_events[k], deriv_events[k + 1])); stats.replay_deriv_ms += ms; }
+    stats.replay_deriv_launches = (long long)((ev_used - ev_pass1) / 2);
+    stats.replayed = n_replay;
+    if (n_replay > 0) {
+      CKE(cudaEventElapsedTime(&ms, deriv_events[ev_pass1], ev[3])); stats.replay_ms = ms;
+      const int* idx = static_cast<const int*>(st_idx.h);
+      for (int k = 0; k < n_replay; ++k) {
+        const AlignState& st = h_states[idx[k]];
+        state_to_result(st, results[idx[k]]);
+        stats.replay_points += (long long)st.n_src * st.n_evals;
+        stats.replay_pairs += st.pairs_total;
+      }
     }
     return 0;
   }
@@ -568,6 +663,7 @@ extern "C" {
 void ndtb_default_params(ndtb_params* p) {
   p->resolution = 1.0f; p->step_size = 0.1; p->trans_eps = 0.1; p->max_iter = 35; p->outlier_ratio = 0.55;
   p->search_method = NDTB_DIRECT7; p->min_points = 6; p->eig_mult = 0.01; p->strict_math = -1; p->dense_max_cells = 1ll << 26;
+  p->replay_iters = 12;
 }
 
 static int create_engine(int device, Engine& e) { return e.init(device); }
@@ -680,7 +776,7 @@ int ndtb_set_target_auto(ndtb_handle* h, const void* pts, size_t n, size_t strid
     // the tail [old_n, n) of the fresh copy already sits at t.pts + old_n + old_n; move it down
     const size_t tail = n - old_n;
     if (tail > 0) {
-      // regions may overlap when tail > old_n: go through the (free) upper half safely with memmove semantics
+      // tail <= old_n (the guard above): [2 old_n, 2 old_n + tail) -> [old_n, old_n + tail) never overlap
       cudaMemcpyAsync(t.pts + old_n, fresh + old_n, tail * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
       e.table_config(t);
       ce = table_append(t.ts, e.ws, t.pts + old_n, tail, e.stream, &e.stats.kernel_launches);
@@ -691,7 +787,15 @@ int ndtb_set_target_auto(ndtb_handle* h, const void* pts, size_t n, size_t strid
     }
     if (was_incremental) *was_incremental = 1;
   } else {
-    cudaMemcpyAsync(t.pts, fresh, n * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
+    // not an extension of the old cloud: move the fresh copy down to the front.  Source [old_n, old_n + n) and destination
+    // [0, n) overlap whenever n > old_n, and an overlapping cudaMemcpy is undefined: ascending chunks of at most old_n points
+    // (the shift) on the one stream are each disjoint from their own source, and a chunk only overwrites source ranges that
+    // earlier chunks have already consumed.
+    for (size_t off = 0; off < n; off += old_n) {
+      const size_t len = std::min(old_n, n - off);
+      if (cudaMemcpyAsync(t.pts + off, fresh + off, len * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream) != cudaSuccess)
+        return e.fail("device copy failed");
+    }
     t.n = n;
     e.nn_valid = false;
     e.tgt_gen = 0;
@@ -1212,7 +1316,7 @@ int ndtb_batch_fitness(ndtb_batch* b, double max_range, double* out) {
     std::vector<int> cnt(e.targets.size(), 0);
     for (int i = 0; i < n; ++i) g_max = std::max(g_max, ++cnt[e.last_item_target[i]]);
   }
-  const int bpi = std::min(160, std::max(8, (148 * 8 + g_max - 1) / g_max));
+  const int bpi = std::min(160, std::max(8, (e.target_blocks() + g_max - 1) / g_max));
   if (e.ensure(e.d_fit_partial, e.fit_partial_cap, (size_t)n * bpi * 2)) return 1;
   if (e.ensure(e.d_fit_out, e.fit_out_cap, (size_t)n)) return 1;
   if (e.ensure(e.d_fit_items, e.fit_items_cap, (size_t)n)) return 1;
@@ -1512,6 +1616,19 @@ int ndtb_batch_download(ndtb_batch* b, int is_target, int id, void* pts, size_t 
 }
 
 int ndtb_batch_get_stats(ndtb_batch* b, ndtb_batch_stats* s) { *s = b->e.stats; return 0; }
+int ndtb_batch_get_diag(ndtb_batch* b, int* replayed, int* borderline, int* n_rise, double* last_norm) {
+  Engine& e = b->e;
+  const size_t n = e.last_item_target.size();
+  if (n == 0 || !e.h_states) return e.fail("ndtb_batch_get_diag needs a completed ndtb_batch_run");
+  for (size_t i = 0; i < n; ++i) {
+    const AlignState& st = e.h_states[i];
+    if (replayed) replayed[i] = i < e.replay_flag.size() ? e.replay_flag[i] : 0;
+    if (borderline) borderline[i] = st.borderline;
+    if (n_rise) n_rise[i] = st.n_rise;
+    if (last_norm) last_norm[i] = st.last_norm;
+  }
+  return 0;
+}
 int ndtb_batch_set_stream(ndtb_batch* b, void* cuda_stream) {
   Engine& e = b->e;
   cudaSetDevice(e.device);

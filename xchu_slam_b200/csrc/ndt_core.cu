@@ -543,9 +543,10 @@ __device__ __forceinline__ void lu_apply6(const LU6& f, const double* b, double*
     x[i] = v / f.a[i][i];
   }
 }
-__device__ void solve6(const double* H, const double* b, double* x) {
+// returns true when the pseudo-inverse (SVD) branch produced the step
+__device__ bool solve6(const double* H, const double* b, double* x) {
   LU6 f;
-  if (!lu_factor6(H, f)) { svd_solve6(H, b, x); return; }
+  if (!lu_factor6(H, f)) { svd_solve6(H, b, x); return true; }
   lu_apply6(f, b, x);
   double r[6], d[6];
 #pragma unroll
@@ -560,6 +561,7 @@ __device__ void solve6(const double* H, const double* b, double* x) {
 #pragma unroll
   for (int i = 0; i < 6; ++i) { x[i] += d[i]; ok = ok && (fabs(x[i]) <= DBL_MAX); }
   if (!ok) svd_solve6(H, b, x);
+  return !ok;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -652,7 +654,9 @@ __device__ void newton_top(NewtonCtx& c) {
   while (true) {
     double neg_g[6], delta[6];
     for (int k = 0; k < 6; ++k) neg_g[k] = -st.g[k];
-    solve6(st.H, neg_g, delta);
+    // a rank-deficient Hessian sends the step through the pseudo-inverse, where a 1e-7 difference in H is amplified
+    // without bound: such a registration is one the hybrid mode replays with the term-by-term kernel
+    if (solve6(st.H, neg_g, delta)) st.borderline = 1;
     double n2 = 0;
     for (int k = 0; k < 6; ++k) n2 += delta[k] * delta[k];
     const double norm = sqrt(n2);
@@ -665,6 +669,11 @@ __device__ void newton_top(NewtonCtx& c) {
     double dp = 0;
     for (int k = 0; k < 6; ++k) dp += st.g[k] * st.dir[k];
     st.d_phi_0 = -dp;
+    {   // the sign test below is a discrete decision: note when it is taken within 1e-3 (relative to |g|, dir is a unit vector) of zero
+      double g2 = 0;
+      for (int k = 0; k < 6; ++k) g2 += st.g[k] * st.g[k];
+      if (fabs(st.d_phi_0) <= 1e-3 * sqrt(g2)) st.borderline = 1;
+    }
     if (st.d_phi_0 >= 0) {
       if (st.d_phi_0 == 0) {
         // return 0 (NDT_I:776-777): delta_p = 0, p unchanged, no evaluation
@@ -689,6 +698,10 @@ __device__ void newton_top(NewtonCtx& c) {
     a_t = fmin(a_t, step_max);
     a_t = fmax(a_t, step_min);
     st.a_t = a_t;
+    st.last_norm = norm;
+    if (st.nr_iterations > 0 && a_t > st.prev_at && st.prev_at < step_max) st.n_rise++;
+    st.prev_at = a_t;
+    st.min_at = st.nr_iterations > 0 ? fmin(st.min_at, a_t) : a_t;
     for (int k = 0; k < 6; ++k) st.x_t[k] = st.p[k] + st.dir[k] * a_t;
     request_eval(st, 1);
     st.phase = PH_MT_FIRST;
@@ -703,6 +716,7 @@ __device__ void post_step(NewtonCtx& c) {
   for (int k = 0; k < 6; ++k) st.p[k] = st.p[k] + st.dir[k] * a;
   int conv = 0;
   if (st.nr_iterations > st.max_iter || (st.nr_iterations && (fabs(a) < st.trans_eps))) conv = 1;
+  if (fabs(fabs(a) - st.trans_eps) <= 1e-3 * st.trans_eps) st.borderline = 1;   // the |step| < eps test taken at its threshold
   st.nr_iterations++;
   if (conv) { finish(c, 1); return; }
   newton_top(c);
@@ -985,7 +999,7 @@ cudaError_t launch_pull(void* dst_dev, const void* src_mapped_dev, size_t bytes,
 // at the start), so the tail iterations -- a few stragglers of a batch of thousands -- neither walk a grid of finished
 // blocks nor serialise 1024 points behind one block.  One block; plan = {blocks, chunk} in mapped host memory.
 __global__ void __launch_bounds__(1024) k_replan(AlignState* __restrict__ states, int n_items, int2* __restrict__ blockmap,
-                                                 int* __restrict__ plan_mapped) {
+                                                 int* __restrict__ plan_mapped, int target_blocks) {
   __shared__ unsigned long long s_pts[32];
   __shared__ int s_scan[32];
   __shared__ int s_base, s_chunk;
@@ -999,7 +1013,7 @@ __global__ void __launch_bounds__(1024) k_replan(AlignState* __restrict__ states
   if (tid == 0) {
     unsigned long long tot = 0;
     for (int w = 0; w < 32; ++w) tot += s_pts[w];
-    long long c = (long long)((tot / (148 * 8) + 255) / 256 * 256);
+    long long c = (long long)((tot / (unsigned long long)target_blocks + 255) / 256 * 256);
     s_chunk = (int)(c < 256 ? 256 : (c > 1024 ? 1024 : c));
     s_base = 0;
   }
@@ -1035,8 +1049,22 @@ __global__ void __launch_bounds__(1024) k_replan(AlignState* __restrict__ states
     __threadfence_system();
   }
 }
-cudaError_t launch_replan(AlignState* states, int n_items, int2* blockmap, int* plan_mapped, cudaStream_t s) {
-  k_replan<<<1, 1024, 0, s>>>(states, n_items, blockmap, plan_mapped);
+cudaError_t launch_replan(AlignState* states, int n_items, int2* blockmap, int* plan_mapped, int target_blocks, cudaStream_t s) {
+  k_replan<<<1, 1024, 0, s>>>(states, n_items, blockmap, plan_mapped, target_blocks < 1 ? 1 : target_blocks);
+  return cudaGetLastError();
+}
+// One block per selected registration: its state record copied out of mapped pinned host memory (the replay pass of a
+// hybrid batch re-arms only the registrations it runs again; the others keep their finished state on the device).
+__global__ void k_pull_items(AlignState* __restrict__ states, const AlignState* __restrict__ src, const int* __restrict__ idx, int n) {
+  if ((int)blockIdx.x >= n) return;
+  const int i = idx[blockIdx.x];
+  const unsigned long long* s = reinterpret_cast<const unsigned long long*>(src + i);
+  unsigned long long* d = reinterpret_cast<unsigned long long*>(states + i);
+  for (int k = threadIdx.x; k < (int)(sizeof(AlignState) / 8); k += blockDim.x) d[k] = s[k];
+}
+cudaError_t launch_pull_items(AlignState* states, const AlignState* src_mapped_dev, const int* idx_mapped_dev, int n, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  k_pull_items<<<n, 64, 0, s>>>(states, src_mapped_dev, idx_mapped_dev, n);
   return cudaGetLastError();
 }
 __global__ void k_set_int(int* dst, int v) { *dst = v; }

@@ -131,6 +131,13 @@ struct AlignState {
   int step_iterations, open_interval, interval_converged;
   long long pairs;           // (point, voxel) pairs of the last evaluation (diagnostics)
   long long pairs_total;     // ... summed over all evaluations of this registration
+  // What decides whether a registration run with the factorised kernel is replayed with the term-by-term one (ndt_api.cu
+  // run_items): `borderline` = a discrete decision of the Newton loop (the |step| < eps convergence test NDT_I:152-157, the
+  // descent-direction flip NDT_I:774-784) was taken within a relative 1e-3 of its threshold, so a 1e-7 difference in score /
+  // gradient could have taken it the other way; n_rise = line-search steps that grew again after the step had dropped below
+  // step_size (the iteration is not contracting); last_norm = |delta_p| of the last Newton solve; prev_at = previous step.
+  int borderline, n_rise;
+  double last_norm, prev_at, min_at;
 };
 
 constexpr int kTraceRec = 52;  // doubles per trace record (see ndtb_get_trace)
@@ -182,7 +189,9 @@ struct SubmapSeg { const float4* src; long long offset; size_t n; float T[12]; }
 cudaError_t launch_submap_gather(const SubmapSeg* segs_dev, int n_seg, size_t max_n, float4* out, cudaStream_t s);
 cudaError_t launch_prepare_eval(AlignState* st, const float* T16_dev, const double* p6_dev, int mode, cudaStream_t s);
 cudaError_t launch_pull(void* dst_dev, const void* src_mapped_dev, size_t bytes, cudaStream_t s);
-cudaError_t launch_replan(AlignState* states, int n_items, int2* blockmap, int* plan_mapped_host, cudaStream_t s);
+cudaError_t launch_replan(AlignState* states, int n_items, int2* blockmap, int* plan_mapped_host, int target_blocks, cudaStream_t s);
+// states[idx[k]] = src_mapped[idx[k]] for k < n (selected registration states pulled out of mapped host memory)
+cudaError_t launch_pull_items(AlignState* states, const AlignState* src_mapped_dev, const int* idx_mapped_dev, int n, cudaStream_t s);
 cudaError_t launch_set_int(int* dst, int v, cudaStream_t s);
 cudaError_t launch_publish(const int* src_dev, int* dst_mapped_host, cudaStream_t s);
 cudaError_t launch_prefix_equal(const float4* a, const float4* b, size_t n, int* flag, cudaStream_t s);

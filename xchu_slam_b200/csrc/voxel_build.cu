@@ -17,6 +17,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
+#include <cstring>
 
 #include "ndt_internal.h"
 
@@ -32,16 +33,24 @@ struct BuildWorkspace {
       *run_isnew = nullptr, *new_prefix = nullptr;
   void* cub_temp = nullptr;
   size_t cub_bytes = 0;
-  float* mm = nullptr;      // device: 6 floats (min xyz, max xyz)
-  int* counts = nullptr;    // device: [0] = num_runs, [1] = n_new
+  float* mm = nullptr;      // device: 6 floats (min xyz, max xyz) + [6] = non-finite points seen (int)
+  int* counts = nullptr;    // device: [0] = num_runs, [1] = n_new, [2] = largest voxel population, [3] = voxels above the warp kernel's capacity
   float* h_mm = nullptr;    // pinned
   int* h_counts = nullptr;  // pinned
+  // counting-sort build (table_build_counting): exclusive scan over the cells of the dense index
+  unsigned long long* cellscan = nullptr;
+  size_t cellscan_cap = 0;
+  void* scan_temp = nullptr;
+  size_t scan_temp_bytes = 0;
+  bool mm_ready = false;          // mm holds the identity of min / max (k_minmax_init ran since the last read)
+  float4* finite_pts = nullptr;   // the cloud without its non-finite points (only when it has any)
+  size_t finite_cap = 0;
 };
 
 BuildWorkspace* build_ws_create() {
   BuildWorkspace* ws = new BuildWorkspace();
-  if (cudaMalloc(&ws->mm, 6 * sizeof(float)) != cudaSuccess || cudaMalloc(&ws->counts, 4 * sizeof(int)) != cudaSuccess ||
-      cudaMallocHost(&ws->h_mm, 6 * sizeof(float)) != cudaSuccess || cudaMallocHost(&ws->h_counts, 4 * sizeof(int)) != cudaSuccess) {
+  if (cudaMalloc(&ws->mm, 8 * sizeof(float)) != cudaSuccess || cudaMalloc(&ws->counts, 4 * sizeof(int)) != cudaSuccess ||
+      cudaMallocHost(&ws->h_mm, 8 * sizeof(float)) != cudaSuccess || cudaMallocHost(&ws->h_counts, 4 * sizeof(int)) != cudaSuccess) {
     delete ws;
     return nullptr;
   }
@@ -59,6 +68,7 @@ void build_ws_destroy(BuildWorkspace* ws) {
   if (!ws) return;
   ws_free_arrays(ws);
   cudaFree(ws->mm); cudaFree(ws->counts); cudaFreeHost(ws->h_mm); cudaFreeHost(ws->h_counts);
+  cudaFree(ws->cellscan); cudaFree(ws->scan_temp); cudaFree(ws->finite_pts);
   delete ws;
 }
 static cudaError_t ws_reserve(BuildWorkspace* ws, size_t n) {
@@ -187,10 +197,18 @@ __global__ void k_minmax(const float4* __restrict__ pts, size_t n, float* __rest
   // single-block-per-grid-stride reduction; launched with a modest grid, finished with atomics on
   // order-preserving integer images of the floats.
   float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+  int bad = 0;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     const float4 p = pts[i];
+    // non-finite points take no part in the grid (the reference skips them for non-dense clouds: the pcl_isfinite test of
+    // VGC_I's first pass and of pcl::getMinMax3D); they are counted so that the caller can compact the cloud
+    if (!(isfinite(p.x) && isfinite(p.y) && isfinite(p.z))) { ++bad; continue; }
     mn[0] = fminf(mn[0], p.x); mn[1] = fminf(mn[1], p.y); mn[2] = fminf(mn[2], p.z);
     mx[0] = fmaxf(mx[0], p.x); mx[1] = fmaxf(mx[1], p.y); mx[2] = fmaxf(mx[2], p.z);
+  }
+  if (__any_sync(0xffffffffu, bad != 0)) {
+    for (int o = 16; o > 0; o >>= 1) bad += __shfl_xor_sync(0xffffffffu, bad, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(reinterpret_cast<int*>(out6) + 6, bad);
   }
   for (int a = 0; a < 3; ++a)
     for (int o = 16; o > 0; o >>= 1) {
@@ -223,10 +241,30 @@ __global__ void k_minmax_init(float* out6) {
   int* o = reinterpret_cast<int*>(out6);
   if (threadIdx.x < 3) o[threadIdx.x] = 0x7FFFFFFF;
   else if (threadIdx.x < 6) o[threadIdx.x] = (int)0x80000000;
+  else if (threadIdx.x == 6) o[6] = 0;
 }
-__global__ void k_minmax_decode(float* out6) {
-  int* o = reinterpret_cast<int*>(out6);
-  if (threadIdx.x < 6) { int i = o[threadIdx.x]; i = i >= 0 ? i : i ^ 0x7FFFFFFF; out6[threadIdx.x] = __int_as_float(i); }
+// Bounding box of the finite points of pts[0 .. n) on the host (blocks the stream once); *n_bad = non-finite points.
+// The accumulator is re-armed behind the read, off the critical path, and the order-preserving integer images are decoded here.
+static cudaError_t minmax_host(BuildWorkspace* ws, const float4* pts, size_t n, cudaStream_t s, float mn[3], float mx[3], int* n_bad,
+                               long long& L) {
+  if (!ws->mm_ready) { k_minmax_init<<<1, 32, 0, s>>>(ws->mm); ++L; }
+  k_minmax<<<minmax_grid(n), 256, 0, s>>>(pts, n, ws->mm, 1);
+  ++L;
+  CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 7 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
+  ++L;
+  ws->mm_ready = true;
+  const int* h = reinterpret_cast<const int*>(ws->h_mm);
+  for (int a = 0; a < 6; ++a) {
+    int i = h[a];
+    i = i >= 0 ? i : i ^ 0x7FFFFFFF;
+    float f;
+    memcpy(&f, &i, 4);
+    (a < 3 ? mn[a] : mx[a - 3]) = f;
+  }
+  if (n_bad) *n_bad = h[6];
+  return cudaGetLastError();
 }
 
 // Build-time cell coordinate: floor(x * inverse_leaf_size) (VGC_I:218-220; the subtraction of
@@ -538,6 +576,323 @@ static cudaError_t sort_and_flag(BuildWorkspace* ws, size_t n, int bits, cudaStr
   return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------
+// Counting-sort build of an EMPTY table over the dense cell grid (the full rebuild of a target: every setInputTarget of the
+// batch path and of the keyframe-count refresh strategy).  The radix sort of (64-bit key, index) pairs -- two thirds of the
+// old build's device time -- is replaced by: cell histogram (atomics on the dense array, which is L2-resident) -> exclusive
+// scan over the cells (cell -> first slot AND cell -> voxel number, one packed 64-bit sum; voxels come out in ascending
+// (k, j, i) order, the reference's leaf order) -> scatter of the point indices.  The scatter leaves the indices of a voxel in
+// arbitrary order; the sequential f64 / f32 sums of the reference (VGC_I:233-243) need INPUT order, so the merge kernel
+// sorts each voxel's handful of indices (a warp per voxel, bitonic network in shared memory), gathers the points a warp-wide
+// tile at a time and lets twelve lanes carry the twelve running sums (3 + 6 doubles, 3 floats) in exactly the reference's
+// order of additions.  Finalisation (eigen-decomposition, inverse, hash insert, dense code) is a thread per voxel.
+// ---------------------------------------------------------------------------------------
+constexpr int kWarpVoxelCap = 512;    // indices a warp sorts in its shared-memory slice; larger voxels go to k_cs_merge_big
+constexpr int kBigVoxelCap = 8192;    // larger than this: fall back to the radix-sort build (nothing to sort per voxel there)
+
+struct CellScanIn {
+  __host__ __device__ __forceinline__ unsigned long long operator()(const int& c) const {
+    return (unsigned long long)(unsigned)c | (c > 0 ? (1ull << 32) : 0ull);
+  }
+};
+
+// cell of every point (dense-grid linear index; -1: outside the box, i.e. not finite) and the per-cell populations
+__global__ void k_cs_hist(const float4* __restrict__ pts, size_t n, float inv_leaf, int lo0, int lo1, int lo2, int dn0, int dn1, int dn2,
+                          int* __restrict__ cell_of, int* __restrict__ dense) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const float4 p = pts[t];
+  const int a = build_cell(p.x, inv_leaf) - lo0, b = build_cell(p.y, inv_leaf) - lo1, c = build_cell(p.z, inv_leaf) - lo2;
+  int cell = -1;
+  if ((unsigned)a < (unsigned)dn0 && (unsigned)b < (unsigned)dn1 && (unsigned)c < (unsigned)dn2 && isfinite(p.x) && isfinite(p.y) && isfinite(p.z)) {
+    cell = (c * dn1 + b) * dn0 + a;
+    atomicAdd(dense + cell, 1);
+  }
+  cell_of[t] = cell;
+}
+// per occupied cell: voxel number, first slot, population; the dense entry becomes the scatter cursor (occupied) or -1 (final)
+__global__ void k_cs_cells(int* __restrict__ dense, const unsigned long long* __restrict__ scan, size_t cells, int* __restrict__ v_start,
+                           int* __restrict__ v_cnt, int* __restrict__ v_cell, int* __restrict__ counts) {
+  const size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = c < cells;       // (no early return: the warp-wide reductions below need every lane)
+  const int cnt = live ? dense[c] : 0;
+  const unsigned long long e = live ? scan[c] : 0ull;
+  const int start = (int)(unsigned)(e & 0xFFFFFFFFull), v = (int)(unsigned)(e >> 32);
+  int mx = 0;
+  if (cnt > 0) {
+    v_start[v] = start; v_cnt[v] = cnt; v_cell[v] = (int)c;
+    dense[c] = start;
+    mx = cnt;
+  } else if (live) {
+    dense[c] = -1;
+  }
+  if (live && c == cells - 1) counts[0] = v + (cnt > 0 ? 1 : 0);
+  // largest population / voxels beyond the warp kernel's capacity: one atomic per warp that has something to report
+  const int wmx = __reduce_max_sync(0xffffffffu, mx);
+  const unsigned big = __ballot_sync(0xffffffffu, cnt > kWarpVoxelCap);
+  if ((threadIdx.x & 31) == 0) {
+    if (wmx > kWarpVoxelCap / 2) atomicMax(counts + 2, wmx);
+    if (big) atomicAdd(counts + 3, __popc(big));
+  }
+}
+__global__ void k_cs_scatter(const int* __restrict__ cell_of, size_t n, int* __restrict__ dense, unsigned int* __restrict__ sorted_idx) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int cell = cell_of[t];
+  if (cell < 0) return;
+  sorted_idx[atomicAdd(dense + cell, 1)] = (unsigned int)t;
+}
+
+// the twelve running sums of a voxel: lanes 0-2 sum x (f64), 3-8 Identity + sum xx^T (f64; xx xy xz yy yz zz), 9-11 f32 centroid sum
+struct VoxelSums {
+  double d;   // lanes 0..8
+  float f;    // lanes 9..11
+};
+__device__ __forceinline__ void sums_init(VoxelSums& a, int lane) {
+  a.d = (lane == 3 || lane == 6 || lane == 8) ? 1.0 : 0.0;   // Leaf::cov_ starts at Identity (VGC_H:101)
+  a.f = 0.f;
+}
+// The lane's two factors out of (x, y, z, 1), chosen once: the product of two floats is exact in double, so x * 1.0 is x and
+// every lane performs exactly the reference's addition for its component (mean_ += pt3d; cov_ += pt3d * pt3d^T; centroid += pt).
+__device__ __forceinline__ void sums_roles(int lane, int& ia, int& ib) {
+  const int ra[12] = {0, 1, 2, 0, 0, 0, 1, 1, 2, 0, 1, 2}, rb[12] = {3, 3, 3, 0, 1, 2, 1, 2, 2, 3, 3, 3};
+  ia = 0; ib = 3;
+#pragma unroll
+  for (int k = 0; k < 12; ++k)
+    if (lane == k) { ia = ra[k]; ib = rb[k]; }
+}
+__device__ __forceinline__ float pick4(const float4 p, int i) { return i == 0 ? p.x : (i == 1 ? p.y : (i == 2 ? p.z : 1.f)); }
+__device__ __forceinline__ void sums_add(VoxelSums& a, int lane, int ia, int ib, const float4 p) {
+  const float fa = pick4(p, ia), fb = pick4(p, ib);
+  if (lane < 9) a.d = __dadd_rn(a.d, __dmul_rn((double)fa, (double)fb));
+  else a.f = __fadd_rn(a.f, fa);
+}
+__device__ __forceinline__ void sums_store(const VoxelSums& a, int lane, const VoxelTable& t, int v) {
+  if (lane < 3) t.vsum[(size_t)v * 3 + lane] = a.d;
+  else if (lane < 9) t.vsxx[(size_t)v * 6 + (lane - 3)] = a.d;
+  else if (lane < 12) t.vcsum[(size_t)v * 3 + (lane - 9)] = a.f;
+}
+__device__ __forceinline__ unsigned long long cell_to_key(int cell, const VoxelTable& t) {
+  const int a = cell % t.dn[0], r = cell / t.dn[0];
+  const int b = r % t.dn[1], c = r / t.dn[1];
+  return pack_key(a + t.dlo[0], b + t.dlo[1], c + t.dlo[2]);
+}
+
+// warp per voxel (population <= kWarpVoxelCap)
+__global__ void __launch_bounds__(128) k_cs_merge(const float4* __restrict__ pts, unsigned int* __restrict__ sorted_idx, const int* __restrict__ v_start,
+                                                  const int* __restrict__ v_cnt, const int* __restrict__ v_cell, int n_vox, VoxelTable t,
+                                                  int* __restrict__ big_list, int* __restrict__ big_count) {
+  __shared__ unsigned int s_idx[4][kWarpVoxelCap];
+  __shared__ float4 s_pts[4][32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int v = blockIdx.x * 4 + warp;
+  if (v >= n_vox) return;
+  const int start = v_start[v], n = v_cnt[v];
+  if (lane == 0) { t.vkey[v] = cell_to_key(v_cell[v], t); t.vn[v] = n; }
+  if (n > kWarpVoxelCap) {
+    if (lane == 0) big_list[atomicAdd(big_count, 1)] = v;
+    return;
+  }
+  unsigned int* idx = s_idx[warp];
+  int m = 32;
+  while (m < n) m <<= 1;
+  for (int k = lane; k < m; k += 32) idx[k] = k < n ? sorted_idx[start + k] : 0xFFFFFFFFu;
+  __syncwarp();
+  // bitonic sort of m (a power of two) indices, ascending
+  for (int size = 2; size <= m; size <<= 1)
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int k = lane; k < (m >> 1); k += 32) {
+        const int lo = 2 * k - (k & (stride - 1));      // index with bit `stride` clear
+        const int hi = lo + stride;
+        const bool up = (lo & size) == 0;
+        const unsigned int x = idx[lo], y = idx[hi];
+        if ((x > y) == up) { idx[lo] = y; idx[hi] = x; }
+      }
+      __syncwarp();
+    }
+  // the sorted order is what every later reader of this voxel's points wants too (incremental appends never look back, but the
+  // debug dumps and the big-voxel kernel share the buffer): write it back
+  for (int k = lane; k < n; k += 32) sorted_idx[start + k] = idx[k];
+  VoxelSums acc;
+  sums_init(acc, lane);
+  int ia, ib;
+  sums_roles(lane, ia, ib);
+  float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (lane < n) nxt = __ldg(pts + idx[lane]);
+  for (int base = 0; base < n; base += 32) {
+    s_pts[warp][lane] = nxt;
+    __syncwarp();
+    if (base + 32 + lane < n) nxt = __ldg(pts + idx[base + 32 + lane]);
+    const int cnt = min(32, n - base);
+    if (lane < 12)
+      for (int k = 0; k < cnt; ++k) sums_add(acc, lane, ia, ib, s_pts[warp][k]);
+    __syncwarp();
+  }
+  sums_store(acc, lane, t, v);
+}
+// block per voxel with kWarpVoxelCap < population <= kBigVoxelCap: rank-by-counting sort into `scratch`, then the same sums
+__global__ void __launch_bounds__(256) k_cs_merge_big(const float4* __restrict__ pts, unsigned int* __restrict__ sorted_idx, unsigned int* __restrict__ scratch,
+                                                      const int* __restrict__ v_start, const int* __restrict__ v_cnt, const int* __restrict__ big_list,
+                                                      const int* __restrict__ big_count, VoxelTable t) {
+  __shared__ unsigned int s_tile[1024];
+  __shared__ float4 s_pts[256];
+  const int n_big = *big_count;
+  for (int b = blockIdx.x; b < n_big; b += gridDim.x) {
+    const int v = big_list[b];
+    const int start = v_start[v], n = v_cnt[v];
+    const unsigned int* seg = sorted_idx + start;
+    unsigned int* out = scratch + start;
+    // rank of every element = number of smaller elements (indices are distinct)
+    for (int e0 = 0; e0 < n; e0 += 256) {
+      const int e = e0 + threadIdx.x;
+      const unsigned int mine = e < n ? seg[e] : 0u;
+      int rank = 0;
+      for (int j0 = 0; j0 < n; j0 += 1024) {
+        __syncthreads();
+        for (int j = threadIdx.x; j < 1024; j += 256) s_tile[j] = j0 + j < n ? seg[j0 + j] : 0xFFFFFFFFu;
+        __syncthreads();
+        const int lim = min(1024, n - j0);
+        for (int j = 0; j < lim; ++j) rank += s_tile[j] < mine ? 1 : 0;
+      }
+      if (e < n) out[rank] = mine;
+    }
+    __syncthreads();
+    VoxelSums acc;
+    sums_init(acc, threadIdx.x);
+    int ia, ib;
+    sums_roles(threadIdx.x, ia, ib);
+    for (int base = 0; base < n; base += 256) {
+      __syncthreads();
+      if (base + threadIdx.x < n) s_pts[threadIdx.x] = __ldg(pts + out[base + threadIdx.x]);
+      __syncthreads();
+      const int cnt = min(256, n - base);
+      if (threadIdx.x < 12)
+        for (int k = 0; k < cnt; ++k) sums_add(acc, threadIdx.x, ia, ib, s_pts[k]);
+    }
+    if (threadIdx.x < 12) sums_store(acc, threadIdx.x, t, v);
+    __syncthreads();
+    for (int k = threadIdx.x; k < n; k += 256) sorted_idx[start + k] = out[k];
+    __syncthreads();
+  }
+}
+// thread per voxel: hash insert, finalisation (VGC_I:282-367), dense code
+__global__ void __launch_bounds__(128) k_cs_finalize(VoxelTable t, int n_vox, const int* __restrict__ v_cell) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_vox) return;
+  const unsigned long long key = t.vkey[v];
+  uint32_t h = hash_key(key) & t.mask;
+  while (true) {
+    const unsigned long long prev = atomicCAS(&t.slots[h].key, kEmptyKey, key);
+    if (prev == kEmptyKey) break;
+    h = (h + 1) & t.mask;
+  }
+  t.slots[h].vidx = v;
+  const int n = t.vn[v];
+  double sum[3], sxx[6];
+  float cs[3];
+  for (int a = 0; a < 3; ++a) { sum[a] = t.vsum[(size_t)v * 3 + a]; cs[a] = t.vcsum[(size_t)v * 3 + a]; }
+  for (int a = 0; a < 6; ++a) sxx[a] = t.vsxx[(size_t)v * 6 + a];
+  finalize_voxel(t, v, n, sum, sxx, cs, (int)h);
+  const int nr = t.rec[v].nr_points;
+  int code = -1;
+  if (nr >= t.min_points) code = v;
+  else if (nr == -1 && n >= t.min_points) code = -2 - v;
+  t.dense[v_cell[v]] = code;
+}
+
+static bool counting_build_enabled() {
+  static const bool on = [] { const char* e = getenv("NDTB_BUILD_RADIX"); return !(e && atoi(e) > 0); }();   // NDTB_BUILD_RADIX=1: the radix-sort build only
+  return on;
+}
+
+// Fresh build over the dense grid.  Preconditions: ts holds no voxel, ts.min_b / max_b / valid are set, hash slots are empty.
+// *done = false: the caller builds with the radix-sort path instead (box too large for a dense index, or a voxel too populous
+// to sort in shared memory) -- the dense array is then marked for a refill.
+static cudaError_t table_build_counting(TableStorage& ts, BuildWorkspace* ws, const float4* pts, size_t n, cudaStream_t s, long long& L,
+                                        long long* launches, bool* done) {
+  *done = false;
+  VoxelTable& t = ts.t;
+  if (!counting_build_enabled() || ts.dense_max_cells <= 0 || n >= (size_t)1 << 31) return cudaSuccess;
+  int lo[3], dn[3];
+  long long cells = 1;
+  for (int a = 0; a < 3; ++a) {
+    lo[a] = ts.min_b[a] - 2;
+    dn[a] = ts.max_b[a] - ts.min_b[a] + 5;
+    cells *= dn[a];
+    if (cells > ts.dense_max_cells) return cudaSuccess;
+  }
+  if (cells > 32ll * (long long)n + (1ll << 21) || cells >= (1ll << 31)) return cudaSuccess;   // a scan over mostly empty cells would cost more than the sort
+  if ((size_t)cells > ts.dense_cap) {
+    cudaFree(ts.dense_buf);
+    ts.dense_buf = nullptr;
+    ts.dense_cap = 0;
+    const size_t cap = (size_t)cells + (size_t)cells / 8;
+    CK(cudaMalloc(&ts.dense_buf, cap * sizeof(int)));
+    ts.dense_cap = cap;
+  }
+  if ((size_t)cells > ws->cellscan_cap) {
+    cudaFree(ws->cellscan);
+    ws->cellscan = nullptr;
+    ws->cellscan_cap = 0;
+    const size_t cap = (size_t)cells + (size_t)cells / 4;
+    CK(cudaMalloc(&ws->cellscan, cap * sizeof(unsigned long long)));
+    ws->cellscan_cap = cap;
+  }
+  cub::TransformInputIterator<unsigned long long, CellScanIn, const int*> scan_in(ts.dense_buf, CellScanIn());
+  size_t need = 0;
+  CK(cub::DeviceScan::ExclusiveSum(nullptr, need, scan_in, ws->cellscan, (int)cells, s));
+  if (need > ws->scan_temp_bytes) {
+    cudaFree(ws->scan_temp);
+    ws->scan_temp = nullptr;
+    ws->scan_temp_bytes = 0;
+    CK(cudaMalloc(&ws->scan_temp, need + need / 2 + 256));
+    ws->scan_temp_bytes = need + need / 2 + 256;
+  }
+  for (int a = 0; a < 3; ++a) { t.dlo[a] = lo[a]; t.dn[a] = dn[a]; }
+  t.dense = ts.dense_buf;
+  int* cell_of = reinterpret_cast<int*>(ws->idx_in);
+  int *v_start = ws->run_start, *v_cnt = ws->run_vidx, *v_cell = ws->run_slot, *big_list = ws->run_isnew;
+  CK(cudaMemsetAsync(t.dense, 0, (size_t)cells * sizeof(int), s));
+  CK(cudaMemsetAsync(ws->counts, 0, 4 * sizeof(int), s));
+  const unsigned nb = (unsigned)((n + 255) / 256);
+  k_cs_hist<<<nb, 256, 0, s>>>(pts, n, t.inv_leaf, lo[0], lo[1], lo[2], dn[0], dn[1], dn[2], cell_of, t.dense);
+  size_t tb = ws->scan_temp_bytes;
+  CK(cub::DeviceScan::ExclusiveSum(ws->scan_temp, tb, scan_in, ws->cellscan, (int)cells, s));
+  k_cs_cells<<<(unsigned)((cells + 255) / 256), 256, 0, s>>>(t.dense, ws->cellscan, (size_t)cells, v_start, v_cnt, v_cell, ws->counts);
+  CK(cudaMemcpyAsync(ws->h_counts, ws->counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, s));
+  k_cs_scatter<<<nb, 256, 0, s>>>(cell_of, n, t.dense, ws->idx_out);
+  L += 8;
+  CK(cudaStreamSynchronize(s));
+  const int n_vox = ws->h_counts[0], max_pop = ws->h_counts[2], n_big = ws->h_counts[3];
+  if (max_pop > kBigVoxelCap) {     // the dense array holds scatter cursors now: the radix path refills it
+    t.dense = nullptr;
+    t.dn[0] = -1;
+    return cudaSuccess;
+  }
+  CK(table_reserve(ts, (size_t)n_vox, s, launches));
+  if (n_vox > 0) {
+    CK(cudaMemsetAsync(ws->counts + 1, 0, sizeof(int), s));     // [1] = big voxels listed by k_cs_merge
+    k_cs_merge<<<(unsigned)((n_vox + 3) / 4), 128, 0, s>>>(pts, ws->idx_out, v_start, v_cnt, v_cell, n_vox, t, big_list, ws->counts + 1);
+    L += 2;
+    if (n_big > 0) {
+      k_cs_merge_big<<<(unsigned)(n_big < 296 ? n_big : 296), 256, 0, s>>>(pts, ws->idx_out, ws->idx_in, v_start, v_cnt, big_list, ws->counts + 1, t);
+      ++L;
+    }
+    k_cs_finalize<<<(unsigned)((n_vox + 127) / 128), 128, 0, s>>>(t, n_vox, v_cell);
+    ++L;
+  }
+  ts.n_vox = n_vox;
+  *done = true;
+  return cudaGetLastError();
+}
+
+static __global__ void k_finite_flags(const float4* __restrict__ pts, size_t n, int* __restrict__ flags) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 p = pts[i];
+  flags[i] = (isfinite(p.x) && isfinite(p.y) && isfinite(p.z)) ? 1 : 0;
+}
+
 cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts, size_t n, cudaStream_t s, long long* launches) {
   if (n == 0) return cudaSuccess;
   VoxelTable& t = ts.t;
@@ -545,14 +900,29 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
   long long dummy = 0;
   long long& L = launches ? *launches : dummy;
   // bounding box of the new points
-  k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
-  k_minmax<<<minmax_grid(n), 256, 0, s>>>(pts, n, ws->mm, 1);
-  k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
-  L += 3;
-  CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
-  CK(cudaStreamSynchronize(s));
   float nmn[3], nmx[3];
-  for (int a = 0; a < 3; ++a) { nmn[a] = ws->h_mm[a]; nmx[a] = ws->h_mm[3 + a]; }
+  int n_bad = 0;
+  CK(minmax_host(ws, pts, n, s, nmn, nmx, &n_bad, L));
+  if (n_bad > 0) {
+    // non-finite points are dropped before keying, in input order, as the reference's first pass skips them (VGC_I:209-216)
+    if ((size_t)n_bad >= n) return cudaSuccess;
+    if (n > ws->finite_cap) {
+      cudaFree(ws->finite_pts);
+      ws->finite_pts = nullptr;
+      ws->finite_cap = 0;
+      CK(cudaMalloc(&ws->finite_pts, (n + n / 4) * sizeof(float4)));
+      ws->finite_cap = n + n / 4;
+    }
+    k_finite_flags<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(pts, n, ws->flags);
+    size_t need = 0;
+    CK(cub::DeviceSelect::Flagged(nullptr, need, pts, ws->flags, ws->finite_pts, ws->counts, (int)n, s));
+    if (need > ws->cub_bytes) return cudaErrorMemoryAllocation;
+    size_t tb2 = ws->cub_bytes;
+    CK(cub::DeviceSelect::Flagged(ws->cub_temp, tb2, pts, ws->flags, ws->finite_pts, ws->counts, (int)n, s));
+    L += 3;
+    pts = ws->finite_pts;
+    n -= (size_t)n_bad;
+  }
   for (int a = 0; a < 3; ++a) {
     ts.mn[a] = ts.have_bbox ? fminf(ts.mn[a], nmn[a]) : nmn[a];
     ts.mx[a] = ts.have_bbox ? fmaxf(ts.mx[a], nmx[a]) : nmx[a];
@@ -578,6 +948,11 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
     return cudaGetLastError();
   }
   ts.valid = true;
+  if (ts.n_vox == 0) {
+    bool done = false;
+    CK(table_build_counting(ts, ws, pts, n, s, L, launches, &done));
+    if (done) return cudaSuccess;
+  }
   int c0[3], c1[3];
   for (int a = 0; a < 3; ++a) { c0[a] = (int)floorf(nmn[a] * inv); c1[a] = (int)floorf(nmx[a] * inv); }
   const int bi = bits_for((long long)c1[0] - c0[0] + 1), bj = bits_for((long long)c1[1] - c0[1] + 1), bk = bits_for((long long)c1[2] - c0[2] + 1);
@@ -652,15 +1027,9 @@ cudaError_t voxelgrid_downsample(BuildWorkspace* ws, const float4* in, size_t n,
   CK(ws_reserve(ws, n));
   long long dummy = 0;
   long long& L = launches ? *launches : dummy;
-  k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
-  k_minmax<<<minmax_grid(n), 256, 0, s>>>(in, n, ws->mm, 1);
-  k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
-  L += 3;
-  CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
-  CK(cudaStreamSynchronize(s));
+  float mn[3], mx[3];
+  CK(minmax_host(ws, in, n, s, mn, mx, nullptr, L));
   const float inv = 1.0f / leaf;     // pcl::VoxelGrid::setLeafSize
-  const float* mn = ws->h_mm;
-  const float* mx = ws->h_mm + 3;
   const long long dx = (long long)((mx[0] - mn[0]) * inv) + 1, dy = (long long)((mx[1] - mn[1]) * inv) + 1, dz = (long long)((mx[2] - mn[2]) * inv) + 1;
   int c0[3], c1[3];
   bool ok = dx * dy * dz <= 2147483647ll;
@@ -772,13 +1141,7 @@ cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, si
   if (bbox) {
     for (int a = 0; a < 6; ++a) bb[a] = bbox[a];
   } else {
-    k_minmax_init<<<1, 32, 0, s>>>(ws->mm);
-    k_minmax<<<minmax_grid(n), 256, 0, s>>>(pts, n, ws->mm, 1);
-    k_minmax_decode<<<1, 32, 0, s>>>(ws->mm);
-    L += 3;
-    CK(cudaMemcpyAsync(ws->h_mm, ws->mm, 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
-    CK(cudaStreamSynchronize(s));
-    for (int a = 0; a < 6; ++a) bb[a] = ws->h_mm[a];
+    CK(minmax_host(ws, pts, n, s, bb, bb + 3, nullptr, L));
   }
   int c0[3], c1[3];
   for (int a = 0; a < 3; ++a) {

@@ -23,7 +23,7 @@ class NdtError(RuntimeError):
 class Params(C.Structure):
     _fields_ = [("resolution", C.c_float), ("step_size", C.c_double), ("trans_eps", C.c_double), ("max_iter", C.c_int),
                 ("outlier_ratio", C.c_double), ("search_method", C.c_int), ("min_points", C.c_int), ("eig_mult", C.c_double),
-                ("strict_math", C.c_int), ("dense_max_cells", C.c_longlong)]
+                ("strict_math", C.c_int), ("dense_max_cells", C.c_longlong), ("replay_iters", C.c_int)]
 
 
 class Result(C.Structure):
@@ -43,7 +43,9 @@ assert RESULT_DTYPE.itemsize == C.sizeof(Result)
 class BatchStats(C.Structure):
     _fields_ = [("build_ms", C.c_double), ("deriv_ms", C.c_double), ("total_ms", C.c_double),
                 ("kernel_launches", C.c_longlong), ("deriv_launches", C.c_longlong),
-                ("points_evaluated", C.c_longlong), ("pairs_evaluated", C.c_longlong), ("probes", C.c_longlong)]
+                ("points_evaluated", C.c_longlong), ("pairs_evaluated", C.c_longlong), ("probes", C.c_longlong),
+                ("replayed", C.c_longlong), ("replay_ms", C.c_double), ("replay_deriv_ms", C.c_double),
+                ("replay_deriv_launches", C.c_longlong), ("replay_points", C.c_longlong), ("replay_pairs", C.c_longlong)]
 
 
 # every symbol include/ndt_b200/ndt_c_api.h declares
@@ -57,7 +59,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_localmap_roll", "ndtb_localmap_sizes", "ndtb_localmap_download", "ndtb_default_filter_params", "ndtb_filter_scan",
            "ndtb_get_source", "ndtb_batch_add_keyframe", "ndtb_batch_clear_keyframes", "ndtb_batch_num_keyframes",
            "ndtb_batch_add_submap", "ndtb_batch_download", "ndtb_batch_add_targets", "ndtb_batch_add_sources",
-           "ndtb_batch_add_submaps"]
+           "ndtb_batch_add_submaps", "ndtb_batch_get_diag"]
 
 _lib = None
 
@@ -108,6 +110,7 @@ def load_library():
     L.ndtb_batch_wait_uploads.argtypes = [vp]
     L.ndtb_batch_run.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
+    L.ndtb_batch_get_diag.argtypes = [vp, vp, vp, vp, vp]
     L.ndtb_batch_set_stream.argtypes = [vp, vp]
     L.ndtb_batch_fitness.argtypes = [vp, C.c_double, vp]
     L.ndtb_batch_add_keyframe.argtypes = [vp, vp, sz, sz, C.POINTER(C.c_int)]
@@ -539,6 +542,13 @@ class BatchNDT:
         m = C.c_size_t()
         self._ck(self._L.ndtb_batch_download(self._h, int(bool(is_target)), int(id), _p(out), n, 16, C.byref(m)))
         return out[:m.value]
+
+    def diag(self, n_items):
+        """Per item of the last run: replayed (hybrid mode ran it again with the strict kernel), borderline, n_rise, last_norm."""
+        rp, bl, nr = (np.zeros(n_items, np.int32) for _ in range(3))
+        ln = np.zeros(n_items, np.float64)
+        self._ck(self._L.ndtb_batch_get_diag(self._h, _p(rp), _p(bl), _p(nr), _p(ln)))
+        return dict(replayed=rp, borderline=bl, n_rise=nr, last_norm=ln)
 
     def stats(self):
         s = BatchStats()
