@@ -8,7 +8,17 @@
 // the NDT calls below are the reference's own lines (odom_node.cpp:70-78, 228, 278-283, 349).
 // ROS plumbing, IMU/odometry guesses and publishers are out of scope.
 //
-//   odom_sequence <sequence.bin> <out.txt> [--res R] [--no-incremental] [--device-localmap] [--strict|--fast] [--threads N] [--max-scans N] [--device D]
+//   odom_sequence <sequence.bin> <out.txt> [--res R] [--refresh distance|surround] [--no-incremental] [--device-localmap] [--strict|--fast]
+//                 [--threads N] [--max-scans N] [--device D]
+//
+// --refresh distance (default): LidarOdom::Run as shipped -- the localmap is refreshed by OdomEstimate's distance-threshold
+//   strategy alone (odom_node.cpp:329-356).
+// --refresh surround: the keyframe-count sliding window, i.e. LidarOdom::Run with its commented call
+//   `ExtractSurroundKeyframes();` (odom_node.cpp:186, 201) enabled in front of OdomEstimate and nothing else changed:
+//   the newest surround_search_num_ = 20 keyframes, each moved by its pose and 1.0 m-downsampled, concatenated newest first,
+//   0.5 m-downsampled, setInputTarget (odom_node.cpp:737-802) -- a full voxel-table build per scan, because every scan is
+//   pushed to cloud_keyframes_ (:303-304).  OdomEstimate's own setInputTarget(pc_target_) (:349) still runs, as in the
+//   reference; the window's target replaces it before the next align.
 //
 // sequence.bin: "NDTSEQ1\0", int32 n_scans, then per scan: int32 n, double gt[6] (sensor pose
 // x y z roll pitch yaw), float xyzi[n][4] (filter_node output, sensor frame).
@@ -18,6 +28,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <algorithm>
+#include <deque>
 #include <map>
 #include <string>
 #include <vector>
@@ -136,13 +147,16 @@ int main(int argc, char** argv) {
   const double step_size = 0.1, trans_eps = 0.01, min_add_scan_shift = 0.5;   // odom_node.cpp:44-47
   const int max_iter = 30;
   double max_localmap_size = 5;      // odom_node.cpp:49
-  bool incremental = true, device_localmap = false;
+  bool incremental = true, device_localmap = false, surround = false;
+  const int surround_search_num_ = 20;   // odom_node.cpp:48
+  const float down_size = 0.5f;          // odom_node.cpp:97-98: downSizeFilterKeyFrames 0.5 m, downSizeFilterLocalmap 1.0 m
   int strict = -1;   // library default: a handle runs the term-by-term kernel
   int max_scans = 1 << 30, device = 0, threads = 1;   // odom_node.cpp:74 runs ndt_omp with one thread
   for (int a = 3; a < argc; ++a) {
     if (!strcmp(argv[a], "--res") && a + 1 < argc) ndt_res = (float)atof(argv[++a]);
     else if (!strcmp(argv[a], "--no-incremental")) incremental = false;
     else if (!strcmp(argv[a], "--device-localmap")) device_localmap = true;   // localmap kept in HBM (ndtb_localmap_*)
+    else if (!strcmp(argv[a], "--refresh") && a + 1 < argc) surround = !strcmp(argv[++a], "surround");
     else if (!strcmp(argv[a], "--strict")) strict = 1;                         // term-by-term derivative kernel (the default for a handle)
     else if (!strcmp(argv[a], "--fast")) strict = 0;                           // factorised derivative kernel
     else if (!strcmp(argv[a], "--max-scans") && a + 1 < argc) max_scans = atoi(argv[++a]);
@@ -188,6 +202,16 @@ int main(int argc, char** argv) {
   Pose6D previous_pose, current_pose, diff_pose, guess_pose;
   double localmap_size = 0, shift_dis = 0;
   int initial_scan_loaded = 0, n_incremental = 0, n_target_sets = 0;
+  // ExtractSurroundKeyframes state (odom_node.h:128-135)
+  std::vector<Cloud::Ptr> cloud_keyframes_;
+  std::vector<Eigen::Matrix4f> cloud_keyposes_;
+  std::deque<Cloud::Ptr> recent_keyframes_;
+  std::deque<int> recent_ids_;          // device mode: the window clouds' ids, same deque discipline
+  std::vector<int> keyframe_win_id_;    // device mode: window cloud of keyframe k
+  int latest_frame_id = -1;             // the function-local `static int latest_frame_id` of odom_node.cpp:762
+  bool latest_frame_id_set = false;
+  int n_surround_sets = 0;
+  double total_surround_ms = 0;
   double total_align_ms = 0, total_target_ms = 0, total_fitness_ms = 0, total_source_ms = 0;
   const auto wall0 = std::chrono::steady_clock::now();
 
@@ -204,6 +228,63 @@ int main(int argc, char** argv) {
     if (s == 0) {   // start the odometry at the first scan's pose (the reference starts at init_x.. = 0)
       previous_pose.x = gt[0]; previous_pose.y = gt[1]; previous_pose.z = gt[2]; previous_pose.roll = gt[3]; previous_pose.pitch = gt[4]; previous_pose.yaw = gt[5];
       current_pose = previous_pose;
+    }
+    // ---- ExtractSurroundKeyframes, odom_node.cpp:737-802 (only with --refresh surround) ------
+    if (surround && !cloud_keyposes_.empty()) {
+      const auto tw0 = std::chrono::steady_clock::now();
+      bool target_updated = false;
+      const size_t have = device_localmap ? recent_ids_.size() : recent_keyframes_.size();
+      if ((int)have < surround_search_num_) {                           // :743-760
+        recent_keyframes_.clear();
+        recent_ids_.clear();
+        for (int i = (int)cloud_keyposes_.size() - 1; i >= 0; --i) {
+          const int this_key_id = i;
+          if (device_localmap) {
+#ifndef ODOM_USE_REFERENCE
+            recent_ids_.push_back(keyframe_win_id_[this_key_id]);       // the cloud :749-753 computes, made when the keyframe was stored
+#endif
+          } else {
+            Cloud::Ptr tf_cloud(new Cloud());
+            transformPointCloud(*cloud_keyframes_[this_key_id], *tf_cloud, cloud_keyposes_[this_key_id]);
+            voxelDownsample(*tf_cloud, *tf_cloud, down_size * 2);
+            recent_keyframes_.push_back(tf_cloud);
+          }
+          if ((int)(device_localmap ? recent_ids_.size() : recent_keyframes_.size()) >= surround_search_num_) break;
+        }
+        target_updated = true;
+      } else {                                                          // :761-775
+        if (!latest_frame_id_set) { latest_frame_id = (int)cloud_keyposes_.size() - 1; latest_frame_id_set = true; }
+        if (latest_frame_id != (int)cloud_keyposes_.size() - 1) {
+          latest_frame_id = (int)cloud_keyposes_.size() - 1;
+          if (device_localmap) {
+#ifndef ODOM_USE_REFERENCE
+            recent_ids_.pop_back();
+            recent_ids_.push_front(keyframe_win_id_[latest_frame_id]);
+#endif
+          } else {
+            recent_keyframes_.pop_back();
+            Cloud::Ptr tf_cloud(new Cloud());
+            transformPointCloud(*cloud_keyframes_[latest_frame_id], *tf_cloud, cloud_keyposes_[latest_frame_id]);
+            voxelDownsample(*tf_cloud, *tf_cloud, down_size * 2);
+            recent_keyframes_.push_front(tf_cloud);
+          }
+          target_updated = true;
+        }
+      }
+      if (target_updated) {                                             // :777-792
+        if (device_localmap) {
+#ifndef ODOM_USE_REFERENCE
+          omp_ndt->windowSetTarget(recent_ids_, down_size);
+#endif
+        } else {
+          pc_target_->clear();
+          for (auto keyframe : recent_keyframes_) *pc_target_ += *keyframe;
+          voxelDownsample(*pc_target_, *pc_target_, down_size);
+          omp_ndt->setInputTarget(pc_target_);
+        }
+        ++n_surround_sets;
+      }
+      total_surround_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tw0).count();
     }
     transformed_scan_ptr->clear();
     // ---- OdomEstimate, odom_node.cpp:218-231 ----------------------------------------------
@@ -257,6 +338,22 @@ int main(int argc, char** argv) {
     const auto t1 = std::chrono::steady_clock::now();
     if (!device_localmap) transformPointCloud(*filtered_scan_ptr, *transformed_scan_ptr, t_localizer);   // :290
     current_pose = Matrix2Pose6D(t_localizer);                           // :291-296 (tf_l2b = identity)
+    if (surround) {                                                      // :303-304: EVERY scan is a keyframe of the window
+      cloud_keyposes_.push_back(t_localizer);
+      if (device_localmap) {
+#ifndef ODOM_USE_REFERENCE
+        keyframe_win_id_.push_back(omp_ndt->windowAddSource(t_localizer, down_size * 2));
+        // a keyframe the deque can no longer reach is dropped: the window only ever looks at the newest surround_search_num_ + 1
+        const int dead = (int)keyframe_win_id_.size() - 1 - (surround_search_num_ + 2);
+        if (dead >= 0 && std::find(recent_ids_.begin(), recent_ids_.end(), keyframe_win_id_[dead]) == recent_ids_.end() && keyframe_win_id_[dead] >= 0) {
+          omp_ndt->windowDrop(keyframe_win_id_[dead]);
+          keyframe_win_id_[dead] = -1;
+        }
+#endif
+      } else {
+        cloud_keyframes_.push_back(filtered_scan_ptr);
+      }
+    }
     diff_pose = current_pose - previous_pose;                            // :309
     shift_dis = sqrt(pow(current_pose.x - previous_pose.x, 2.0) + pow(current_pose.y - previous_pose.y, 2.0));   // :322
     previous_pose = current_pose;
@@ -305,9 +402,9 @@ int main(int argc, char** argv) {
             target_points, was_inc, align_ms, target_ms, gt[0], gt[1], gt[2]);
   }
   const double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
-  fprintf(out, "# scans %d wall_s %.4f scans_per_s %.2f align_ms_mean %.4f target_ms_mean %.4f target_sets %d incremental %d fitness_ms_mean %.4f source_ms_mean %.4f\n",
+  fprintf(out, "# scans %d wall_s %.4f scans_per_s %.2f align_ms_mean %.4f target_ms_mean %.4f target_sets %d incremental %d fitness_ms_mean %.4f source_ms_mean %.4f surround_sets %d surround_ms_mean %.4f\n",
           n_scans, wall, n_scans / wall, total_align_ms / n_scans, n_target_sets ? total_target_ms / n_target_sets : 0.0, n_target_sets, n_incremental,
-          total_fitness_ms / n_scans, total_source_ms / n_scans);
+          total_fitness_ms / n_scans, total_source_ms / n_scans, n_surround_sets, n_surround_sets ? total_surround_ms / n_surround_sets : 0.0);
   fclose(out);
   fclose(f);
   return 0;

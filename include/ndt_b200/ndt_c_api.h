@@ -51,7 +51,8 @@ typedef struct ndtb_params {
                             centimetres from the reference's result); -1 (default): 1 for an ndtb_handle (single
                             registrations are latency-bound, the strict kernel costs nothing measurable); for an ndtb_batch
                             HYBRID: every registration runs with the factorised kernel, and those that took more than
-                            `replay_iters` iterations, did not converge, or took a discrete decision of the loop (the
+                            `replay_iters` iterations, did not converge, ended on a Newton step shorter than
+                            `replay_min_norm`, solved an ill-conditioned system, or took a discrete decision of the loop (the
                             |step| < eps test NDT_I:152-157, the descent-direction flip NDT_I:774-784) within 1e-3 of its
                             threshold are replayed from their initial guess with the term-by-term kernel inside the same
                             ndtb_batch_run, so that every result of the batch -- iteration counts included -- is the
@@ -60,7 +61,10 @@ typedef struct ndtb_params {
                             when that box (padded by 2 cells) holds at most this many cells, else through the
                             hash table; 0 = hash only.  default 2^26 (256 MB of index per target at most) */
   int replay_iters;      /* hybrid batches (strict_math = -1): iteration count above which a registration is replayed with
-                            the term-by-term kernel; <= 0: only non-converged / borderline registrations.  default 12 */
+                            the term-by-term kernel; <= 0: only non-converged / borderline registrations.  default 11 */
+  double replay_min_norm;/* hybrid batches: a registration whose LAST Newton step |delta_p| (NDT_I:119-125) was shorter than this
+                            is replayed too -- its final move is the clamped eps / 2 along delta_p / |delta_p|, which a tiny
+                            |delta_p| leaves ill-defined.  < 0 (default): 0.05 * trans_eps */
 } ndtb_params;
 
 typedef struct ndtb_result {
@@ -159,6 +163,24 @@ int ndtb_localmap_sizes(ndtb_handle* h, size_t sizes[3]);
  * intensity at offset 16.  `cap` = records `pts` can hold; *n = records written. */
 int ndtb_localmap_download(ndtb_handle* h, int which, void* pts, size_t cap, size_t stride_bytes, size_t* n);
 
+/* ---- the keyframe-count (sliding window) localmap on the device -------------------------------
+ * LidarOdom::ExtractSurroundKeyframes (reference xchu_mapping/src/odom_node.cpp:737-802, ODOM below): the target is the
+ * newest surround_search_num_ (20) keyframes, each moved by its pose and downsampled with downSizeFilterLocalmap (1.0 m,
+ * ODOM:749-753 / :767-771), concatenated newest first (ODOM:778-781), downsampled with downSizeFilterKeyFrames (0.5 m,
+ * ODOM:783-784) and handed to setInputTarget (ODOM:786-791) -- a NON-prefix cloud at every refresh, i.e. a full voxel-table
+ * build at keyframe rate.  The clouds stay in HBM; which keyframes are in the window (recent_keyframes_, a deque the caller
+ * pushes and pops, including the reference's `static latest_frame_id` quirk) stays the caller's business: it holds ids. */
+/* tf_cloud = downSizeFilterLocalmap(T * current source) kept on the device; *id names it (ids count up from 0, never reused).
+ * leaf <= 0: no downsample.  *n_points (may be NULL) = its size. */
+int ndtb_window_add_source(ndtb_handle* h, const float T[16], float leaf, int* id, size_t* n_points);
+int ndtb_window_drop(ndtb_handle* h, int id);      /* the cloud leaves recent_keyframes_ for good */
+int ndtb_window_clear(ndtb_handle* h);
+/* pc_target_ = the listed clouds concatenated in the order given, downsampled at `leaf` (<= 0: not), setInputTarget(pc_target_).
+ * *n_target (may be NULL) = points of pc_target_. */
+int ndtb_window_set_target(ndtb_handle* h, const int* ids, int n_ids, float leaf, size_t* n_target);
+/* Copies the current target cloud to the host (whatever set it); records as in ndtb_localmap_download.  Test hook. */
+int ndtb_get_target(ndtb_handle* h, void* pts, size_t cap, size_t stride_bytes, size_t* n);
+
 /* ---- filter_node's front end on the device ---------------------
  * What CloudFilter::PcCB does to a raw scan before odom_node sees it (reference xchu_mapping/src/filter_node.cpp:236-262):
  * pcl::removeNaNFromPointCloud, the range gate r_min < sqrt(x^2 + y^2) < r_max (:242-247), downSizeFilterKeyFrames
@@ -253,6 +275,27 @@ int ndtb_batch_get_diag(ndtb_batch* b, int* replayed, int* borderline, int* n_ri
 /* Run all of the batch's copies and kernels on the caller's CUDA stream (a cudaStream_t) instead of
  * the batch's own, so that the caller's CUDA events bracket the work. */
 int ndtb_batch_set_stream(ndtb_batch* b, void* cuda_stream);
+
+/* ---- one job over several GPUs of one box (north_star item 4) ---------
+ * The C5 job -- n_items independent registrations over n_targets submaps -- cut over the listed devices: items are ordered by
+ * target id (stable) and dealt in contiguous blocks whose sizes differ by at most one, so that every submap's voxel table is
+ * built on as few devices as possible; a device uploads and builds only the targets and sources its block names.  One host
+ * thread per device inside the library, one ndtb_batch each; there is NO collective: a single registration does not shard, the
+ * only exchange is the gather of the result records into `results` (item order), which is a host memcpy here.  All pointers
+ * are HOST pointers.  The same device may be listed more than once (two batches on one GPU; what the tests on a one-GPU box do).
+ * Results do not depend on how the job was cut up to the FP64 summation order of a derivative evaluation (block sizes follow
+ * the number of points a device has in flight), i.e. to ~1e-16 relative per evaluation. */
+typedef struct ndtb_multi ndtb_multi;
+int ndtb_multi_create(int n_devices, const int* devices, ndtb_multi** out);
+int ndtb_multi_destroy(ndtb_multi* m);
+const char* ndtb_multi_last_error(const ndtb_multi* m);
+int ndtb_multi_set_params(ndtb_multi* m, const ndtb_params* p);
+int ndtb_multi_run(ndtb_multi* m, int n_targets, const void* const* target_pts, const size_t* target_n, int n_sources,
+                   const void* const* source_pts, const size_t* source_n, size_t stride_bytes, int n_items, const int* item_target,
+                   const int* item_source, const float* guesses, ndtb_result* results);
+/* Per device of the last ndtb_multi_run (arrays of n_devices, any may be NULL): items it ran, targets it built, its device
+ * time (ms, CUDA events) and the host wall time of its thread (ms). */
+int ndtb_multi_get_stats(ndtb_multi* m, int* items, int* targets, double* device_ms, double* wall_ms);
 
 #ifdef __cplusplus
 }

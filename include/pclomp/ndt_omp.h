@@ -33,6 +33,7 @@
 #include <limits>
 #include <stdexcept>
 #include <string>
+#include <vector>
 
 #include "../ndt_b200/ndt_c_api.h"
 
@@ -168,6 +169,23 @@ class NormalDistributionsTransform {
     target_set_ = true;
   }
   inline void localmapRoll() { ck(ndtb_localmap_roll(h_)); }                         // localmap = tmp_map; tmp_map.clear()
+  // the keyframe-count window kept in HBM (ndt_c_api.h "sliding window" section; reference src/odom_node.cpp:737-802)
+  inline int windowAddSource(const Matrix4& T, float leaf) {                         // tf_cloud = downSizeFilterLocalmap(T * source)
+    int id = -1;
+    ck(ndtb_window_add_source(h_, T.data(), leaf, &id, nullptr));
+    return id;
+  }
+  inline void windowDrop(int id) { ck(ndtb_window_drop(h_, id)); }
+  template <typename IdContainer>
+  inline size_t windowSetTarget(const IdContainer& ids, float leaf) {                // pc_target_ = VoxelGrid(concat); setInputTarget
+    std::vector<int> v(ids.begin(), ids.end());
+    push_search_method();
+    size_t n = 0;
+    ck(ndtb_window_set_target(h_, v.data(), (int)v.size(), leaf, &n));
+    last_target_incremental_ = false;
+    target_set_ = true;
+    return n;
+  }
   inline size_t localmapSize(int which = 0) { size_t s[3]; ck(ndtb_localmap_sizes(h_, s)); return s[which]; }
   void setStrictMath(bool on) { p_.strict_math = on ? 1 : 0; push(); }
   ndtb_handle* handle() { return h_; }

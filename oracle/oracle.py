@@ -28,54 +28,84 @@ class _Result(C.Structure):
 
 
 _lib = None
+_lib_native = None
+_NATIVE = os.path.join(_HERE, "_native", "libndt_oracle_native.so")
+NATIVE_FLAGS = "-O3 -march=native -std=c++17 -fopenmp -ffp-contract=off -fPIC"
 
 
-def lib():
-    global _lib
+def build_native():
+    """The oracle compiled ON THIS MACHINE with BASELINE.md section 2's flags (-O3 -march=native -fopenmp -ffp-contract=off) for the
+    timed CPU baseline: a -march=native object built in the build container could not be trusted to run on the GPU box's host CPU,
+    so this one is never shipped.  Same source, same IEEE arithmetic (no contraction, no fast-math): same results.  Returns the
+    path, or None when the compiler is missing or fails."""
+    src = os.path.join(_HERE, "ndt_oracle.cpp")
+    try:
+        if not os.path.exists(_NATIVE) or os.path.getmtime(_NATIVE) < os.path.getmtime(src):
+            os.makedirs(os.path.dirname(_NATIVE), exist_ok=True)
+            tmp = _NATIVE + ".tmp%d" % os.getpid()
+            subprocess.check_call(["g++"] + NATIVE_FLAGS.split() + ["-w", "-shared", "-o", tmp, src], cwd=_HERE)
+            os.replace(tmp, _NATIVE)
+        return _NATIVE
+    except Exception:
+        return None
+
+
+def lib(native=False):
+    global _lib, _lib_native
+    if native:
+        if _lib_native is None:
+            path = build_native()
+            if path is None:
+                return lib(False)
+            _lib_native = _bind(C.CDLL(path))
+        return _lib_native
     if _lib is None:
         build()
-        L = C.CDLL(_LIB)
-        L.oracle_create.restype = C.c_void_p
-        L.oracle_destroy.argtypes = [C.c_void_p]
-        L.oracle_set_params.argtypes = [C.c_void_p, C.c_float, C.c_double, C.c_double, C.c_int, C.c_double, C.c_int, C.c_int]
-        L.oracle_set_voxel_params.argtypes = [C.c_void_p, C.c_int, C.c_double]
-        for name in ("oracle_set_target", "oracle_update_target", "oracle_set_source"):
-            getattr(L, name).argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t]
-        L.oracle_grid_valid.argtypes = [C.c_void_p]
-        L.oracle_grid_bounds.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
-        L.oracle_num_leaves.argtypes = [C.c_void_p]
-        L.oracle_num_leaves.restype = C.c_size_t
-        L.oracle_dump_leaves.argtypes = [C.c_void_p] + [C.c_void_p] * 8
-        L.oracle_neighbors.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p]
-        L.oracle_gauss.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
-        L.oracle_eval_derivatives.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
-        L.oracle_eval_derivatives.restype = C.c_double
-        L.oracle_compute_hessian.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
-        L.oracle_transform_source.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
-        L.oracle_align.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(_Result)]
-        L.oracle_get_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
-        L.oracle_get_trace.restype = C.c_int
-        L.oracle_get_output.argtypes = [C.c_void_p, C.c_void_p]
-        L.oracle_fitness.argtypes = [C.c_void_p, C.c_double]
-        L.oracle_fitness.restype = C.c_double
-        L.oracle_build_nn.argtypes = [C.c_void_p]
-        L.oracle_set_final_transform.argtypes = [C.c_void_p, C.c_void_p]
-        L.oracle_calculate_score.argtypes = [C.c_void_p, C.c_void_p]
-        L.oracle_calculate_score.restype = C.c_double
-        L.oracle_pose_to_matrix.argtypes = [C.c_void_p, C.c_void_p]
-        L.oracle_matrix_to_pose.argtypes = [C.c_void_p, C.c_void_p]
-        L.oracle_svd_solve6.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
-        L.oracle_mt_trial.argtypes = [C.c_double] * 9
-        L.oracle_mt_trial.restype = C.c_double
-        L.oracle_mt_update.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double]
-        L.oracle_max_threads.restype = C.c_int
-        L.oracle_voxelgrid_downsample.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_float, C.c_void_p]
-        L.oracle_voxelgrid_downsample.restype = C.c_size_t
-        L.oracle_filter_scan.argtypes = [C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_float, C.c_int, C.c_double, C.c_void_p,
-                                         C.c_void_p, C.c_void_p]
-        L.oracle_filter_scan.restype = C.c_size_t
-        _lib = L
+        _lib = _bind(C.CDLL(_LIB))
     return _lib
+
+
+def _bind(L):
+    L.oracle_create.restype = C.c_void_p
+    L.oracle_destroy.argtypes = [C.c_void_p]
+    L.oracle_set_params.argtypes = [C.c_void_p, C.c_float, C.c_double, C.c_double, C.c_int, C.c_double, C.c_int, C.c_int]
+    L.oracle_set_voxel_params.argtypes = [C.c_void_p, C.c_int, C.c_double]
+    for name in ("oracle_set_target", "oracle_update_target", "oracle_set_source"):
+        getattr(L, name).argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t]
+    L.oracle_grid_valid.argtypes = [C.c_void_p]
+    L.oracle_grid_bounds.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_num_leaves.argtypes = [C.c_void_p]
+    L.oracle_num_leaves.restype = C.c_size_t
+    L.oracle_dump_leaves.argtypes = [C.c_void_p] + [C.c_void_p] * 8
+    L.oracle_neighbors.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p]
+    L.oracle_gauss.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_eval_derivatives.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_eval_derivatives.restype = C.c_double
+    L.oracle_compute_hessian.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_transform_source.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_align.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(_Result)]
+    L.oracle_get_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    L.oracle_get_trace.restype = C.c_int
+    L.oracle_get_output.argtypes = [C.c_void_p, C.c_void_p]
+    L.oracle_fitness.argtypes = [C.c_void_p, C.c_double]
+    L.oracle_fitness.restype = C.c_double
+    L.oracle_build_nn.argtypes = [C.c_void_p]
+    L.oracle_set_final_transform.argtypes = [C.c_void_p, C.c_void_p]
+    L.oracle_calculate_score.argtypes = [C.c_void_p, C.c_void_p]
+    L.oracle_calculate_score.restype = C.c_double
+    L.oracle_pose_to_matrix.argtypes = [C.c_void_p, C.c_void_p]
+    L.oracle_matrix_to_pose.argtypes = [C.c_void_p, C.c_void_p]
+    L.oracle_svd_solve6.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    L.oracle_mt_trial.argtypes = [C.c_double] * 9
+    L.oracle_mt_trial.restype = C.c_double
+    L.oracle_mt_update.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double]
+    L.oracle_max_threads.restype = C.c_int
+    L.oracle_voxelgrid_downsample.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_float, C.c_void_p]
+    L.oracle_voxelgrid_downsample.restype = C.c_size_t
+    L.oracle_filter_scan.argtypes = [C.c_void_p, C.c_size_t, C.c_double, C.c_double, C.c_float, C.c_int, C.c_double, C.c_void_p,
+                                     C.c_void_p, C.c_void_p]
+    L.oracle_filter_scan.restype = C.c_size_t
+    return L
 
 
 def _pts(a):
@@ -200,8 +230,10 @@ def max_threads():
 class OracleNDT:
     """Mirror of pclomp::NormalDistributionsTransform (NDT_H:110-204) over the CPU oracle."""
 
-    def __init__(self):
-        self.L = lib()
+    def __init__(self, native=False):
+        """native=True: the -O3 -march=native build made on this machine (bench.py's timed CPU legs only)."""
+        self.L = lib(native)
+        self.native = native and self.L is _lib_native
         self.h = C.c_void_p(self.L.oracle_create())
         # NDT_I:46-69 ctor defaults
         self.resolution, self.step_size, self.trans_eps = 1.0, 0.1, 0.1

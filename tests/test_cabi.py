@@ -60,7 +60,7 @@ def test_default_params_match_reference_ctor(lib):
     lib.ndtb_default_params(C.byref(p))
     assert p.resolution == 1.0 and p.step_size == 0.1 and p.trans_eps == 0.1 and p.max_iter == 35
     assert p.outlier_ratio == 0.55 and p.search_method == ndt.DIRECT7 and p.min_points == 6 and p.eig_mult == 0.01
-    assert p.strict_math == -1 and p.dense_max_cells == 1 << 26
+    assert p.strict_math == -1 and p.dense_max_cells == 1 << 26 and p.replay_iters == 11 and p.replay_min_norm == -1.0
     assert (ndt.KDTREE, ndt.DIRECT26, ndt.DIRECT7, ndt.DIRECT1) == (0, 1, 2, 3)      # ndt_omp.h:52-57
 
 

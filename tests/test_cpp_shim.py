@@ -56,11 +56,16 @@ def test_odometry_sequence_tracks_ground_truth_and_refreshes_incrementally(exe, 
 
 
 @pytest.mark.gpu
-def test_same_caller_two_backends_same_trajectory(exe, tmp_path):
+@pytest.mark.parametrize("strategy", ["distance", "surround"])
+def test_same_caller_two_backends_same_trajectory(exe, tmp_path, strategy):
     """Drop-in check at the caller level: examples/odom_sequence.cpp (the mirror of odom_node's loop) compiled twice --
     against include/pclomp/ndt_omp.h (libndt_b200.so, GPU) and against the reference's own pclomp headers
     (examples/odom_sequence_ref, CPU, over the stand-in Eigen/PCL headers) -- must produce the SAME odometry on the same
-    sequence.  A handle runs the term-by-term derivative kernel by default (strict_math -1), whose per-pair float terms
+    sequence, for BOTH localmap refresh strategies north_star names: `distance` = OdomEstimate's distance-threshold refresh
+    (odom_node.cpp:329-356, res 1.0), `surround` = the keyframe-count sliding window ExtractSurroundKeyframes
+    (odom_node.cpp:737-802: newest 20 keyframes, a non-prefix target and a full table build every scan; at the reference's
+    default ndt_res 2.0, the resolution at which one 1.0 m-downsampled keyframe can fill a voxel).
+    A handle runs the term-by-term derivative kernel by default (strict_math -1), whose per-pair float terms
     are the reference's bit for bit; each pose feeds the next guess and the localmap, so the trajectories can only stay
     identical if every align is: iteration counts, convergence flags, localmap sizes and poses are required to be EQUAL,
     fitness scores within 1e-9 relative (exact 1-NN on both sides, f64 mean).
@@ -71,14 +76,21 @@ def test_same_caller_two_backends_same_trajectory(exe, tmp_path):
     if ref_exe is None:
         pytest.skip("examples/odom_sequence_ref not built (needs /root/reference)")
     seq = synth.write_sequence(str(tmp_path / "seq.bin"), n_scans=60, n_points=20000)
-    b, sb = _run(ref_exe, seq, str(tmp_path / "ref.txt"), "--res", "1.0", "--threads", str(os.cpu_count() or 1))
+    common = ["--res", "1.0"] if strategy == "distance" else ["--res", "2.0", "--refresh", "surround"]
+    b, sb = _run(ref_exe, seq, str(tmp_path / "ref.txt"), *common, "--threads", str(os.cpu_count() or 1))
+    if strategy == "surround":
+        assert int(sb["surround_sets"]) == 58      # every scan but the first and the `static latest_frame_id` call (:762-763)
+        assert np.max(np.linalg.norm(b[:, 4:6] - b[:, 14:16], axis=1)) < 0.5
     for flags in ([], ["--device-localmap"]):
-        a, sa = _run(exe, seq, str(tmp_path / "gpu.txt"), "--res", "1.0", *flags)
+        a, sa = _run(exe, seq, str(tmp_path / "gpu.txt"), *common, *flags)
         assert a.shape == b.shape and a.shape[0] == 60
+        assert sa["surround_sets"] == sb["surround_sets"]
         assert np.array_equal(a[:, 1:3], b[:, 1:3])                       # iterations, converged
         assert np.array_equal(a[:, 10], b[:, 10])                         # localmap sizes
         assert np.array_equal(a[:, 4:10], b[:, 4:10])                     # poses: identical
         assert np.max(np.abs(a[:, 3] - b[:, 3]) / b[:, 3]) < 1e-9
+    if strategy == "surround":
+        return
     f, sf = _run(exe, seq, str(tmp_path / "fast.txt"), "--res", "1.0", "--fast")
     same = np.flatnonzero(f[:, 10] != b[:, 10])
     upto = int(same[0]) if len(same) else 60                              # scans before the localmaps first differ

@@ -118,3 +118,62 @@ def test_device_localmap_errors_and_edges():
     g.localmapAppendSource(np.eye(4, dtype=np.float32), leaf=0.0)
     out = g.localmapDownload(0)
     assert np.array_equal(out[:, :3], s[:, :3]) and np.array_equal(out[:, 3], rec[:, 4])
+
+
+def _surround_target_oracle(scans, ids, leaf_kf=1.0, leaf_target=0.5):
+    """Oracle restatement of LidarOdom::ExtractSurroundKeyframes (reference src/odom_node.cpp:737-802): each keyframe moved by its
+    pose (pcl::transformPointCloud, :749-751) and downsampled with downSizeFilterLocalmap (:752-753), concatenated in deque
+    order (:778-781), downsampled with downSizeFilterKeyFrames (:783-784)."""
+    from oracle import oracle
+    clouds = [oracle.voxelgrid_downsample(oracle.transform_cloud(scans[i][0], scans[i][1]), leaf_kf) for i in ids]
+    cat = np.concatenate(clouds, axis=0) if clouds else np.zeros((0, 4), np.float32)
+    return clouds, oracle.voxelgrid_downsample(cat, leaf_target)
+
+
+def test_oracle_surround_target_properties():
+    """CPU: the window target is a function of the SET of keyframes in deque order -- newest first -- and one point per
+    occupied 0.5 m leaf of the stacked 1.0 m-downsampled keyframes."""
+    scans = _scans(n_scans=5, n_points=3000)
+    clouds, tgt = _surround_target_oracle(scans, [4, 3, 2, 1, 0])
+    assert all(len(c) <= len(s[0]) for c, s in zip(clouds, scans[::-1]))
+    cells = np.unique(np.floor(np.concatenate(clouds)[:, :3] * np.float32(2.0)).astype(np.int64), axis=0)
+    assert tgt.shape[0] == cells.shape[0]
+    _, tgt2 = _surround_target_oracle(scans, [0, 1, 2, 3, 4])
+    assert tgt2.shape == tgt.shape and not np.array_equal(tgt2, tgt)      # float sums follow the concatenation order
+
+
+@pytest.mark.gpu
+def test_device_surround_window_matches_oracle_bit_exact():
+    """ndtb_window_*: the keyframe-count window kept in HBM.  Window clouds, the target cloud and the voxel table built from it
+    must equal the oracle's restatement bit for bit, through pushes, a pop of the oldest keyframe and a skipped keyframe."""
+    from oracle import oracle
+    from xchu_slam_b200 import ndt
+    scans = _scans(n_scans=8, n_points=6000)
+    g = ndt.NormalDistributionsTransform()
+    g.setResolution(2.0)
+    ids = []
+    for s, T in scans:
+        g.setInputSource(s)
+        i, n = g.windowAddSource(T, 1.0)
+        ids.append(i)
+        assert n == oracle.voxelgrid_downsample(oracle.transform_cloud(s, T), 1.0).shape[0]
+    assert ids == list(range(8))
+    o = oracle.OracleNDT()
+    o.set_params(resolution=2.0)
+    for order in ([2, 1, 0], [5, 4, 3, 2, 1], [7, 6, 4, 3, 2]):          # growing window; oldest popped; keyframe 5 skipped
+        _, want = _surround_target_oracle(scans, order)
+        n = g.windowSetTarget(order, 0.5)
+        got = g.getTarget(n + 8)
+        assert n == want.shape[0] and got.tobytes() == want.tobytes()
+        o.set_target(want)
+        lo, lg = o.dump_leaves(), g.dumpVoxels()
+        so, sg = np.lexsort((lo["ijk"][:, 0], lo["ijk"][:, 1], lo["ijk"][:, 2])), np.lexsort((lg["ijk"][:, 0], lg["ijk"][:, 1], lg["ijk"][:, 2]))
+        assert np.array_equal(lo["ijk"][so], lg["ijk"][sg]) and np.array_equal(lo["n_raw"][so], lg["n_raw"][sg])
+        assert np.array_equal(lo["nr_points"][so], lg["nr_points"][sg]) and np.array_equal(lo["mean"][so], lg["mean"][sg])
+        assert np.array_equal(lo["centroid"][so], lg["centroid"][sg])
+    g.windowDrop(0)
+    with pytest.raises(ndt.NdtError):
+        g.windowSetTarget([0, 1], 0.5)
+    g.windowClear()
+    with pytest.raises(ndt.NdtError):
+        g.windowSetTarget([1], 0.5)

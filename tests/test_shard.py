@@ -114,3 +114,113 @@ def test_run_sharded_world2_gloo_matches_single_rank():
     for r in range(2):                       # every rank holds the full, identically ordered result list
         assert np.array_equal(got[r], single)
     assert np.all(single[:, 16] >= 1)
+
+
+# ---- the same job on real devices (marked gpu; the two-device tests skip on a one-GPU box) --------------------------------
+def _c5_small():
+    from xchu_slam_b200 import synth
+    return synth.batch_workload(n_submaps=4, scans_per_submap=4, hyps_per_scan=4, n_target=200000, n_source=8000)
+
+
+def _single_batch(w, device=0):
+    from xchu_slam_b200 import ndt
+    b = ndt.BatchNDT(device=device)
+    b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2)
+    for t in w["targets"]:
+        b.add_target(t)
+    for s in w["sources"]:
+        b.add_source(s)
+    return b.run_raw(w["item_target"], w["item_source"], w["guesses"])
+
+
+def _same_results(a, b):
+    """SURVEY.md section 4, multi-GPU row: identical per-item results regardless of sharding.  Iteration counts, convergence
+    flags and evaluation counts EQUAL; transforms equal to float rounding (the FP64 partial sums of an evaluation are grouped
+    by the block size, which follows the number of points a device has in flight: ~1e-16 per evaluation)."""
+    assert np.array_equal(a["iterations"], b["iterations"]) and np.array_equal(a["converged"], b["converged"])
+    assert np.array_equal(a["n_evals"], b["n_evals"])
+    assert np.max(np.abs(a["T"] - b["T"])) < 1e-6
+    assert np.max(np.abs(a["score"] - b["score"]) / np.maximum(1.0, np.abs(b["score"]))) < 1e-9
+    return float(np.mean(np.all(a["T"] == b["T"], axis=1)))
+
+
+@pytest.mark.gpu
+def test_multi_entry_point_one_device_listed_twice_matches_single_batch():
+    """ndtb_multi_run (the library-side sharding a C++ caller such as pgo_node gets) with device 0 listed twice: two
+    ndtb_batches on two host threads, each with half of the items, must return what one batch returns."""
+    from xchu_slam_b200 import ndt
+    w = _c5_small()
+    single = _single_batch(w)
+    m = ndt.MultiNDT([0, 0])
+    m.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2)
+    res = m.run_raw(w["targets"], w["sources"], w["item_target"], w["item_source"], w["guesses"])
+    frac_bitwise = _same_results(res, single)
+    assert frac_bitwise > 0.9
+    st = m.stats()
+    assert st["items"].tolist() == [32, 32] and st["targets"].tolist() == [2, 2]     # each half builds only its own submaps
+    # one listed device = the single batch, bit for bit (same block decomposition)
+    m1 = ndt.MultiNDT([0])
+    m1.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2)
+    r1 = m1.run_raw(w["targets"], w["sources"], w["item_target"], w["item_source"], w["guesses"])
+    assert np.array_equal(r1["T"], single["T"]) and np.array_equal(r1["iterations"], single["iterations"])
+
+
+@pytest.mark.gpu
+def test_multi_entry_point_two_devices():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    from xchu_slam_b200 import ndt
+    w = _c5_small()
+    single = _single_batch(w)
+    m = ndt.MultiNDT([0, 1])
+    m.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2)
+    res = m.run_raw(w["targets"], w["sources"], w["item_target"], w["item_source"], w["guesses"])
+    _same_results(res, single)
+
+
+def _nccl_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import torch
+    import torch.distributed as dist
+    from xchu_slam_b200 import shard
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    w = _c5_small()
+    runner = shard.gpu_runner(rank, resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2)
+    res = shard.run_sharded(runner, w["targets"], w["sources"], w["item_target"], w["item_source"], w["guesses"],
+                            device=torch.device("cuda", rank))
+    q.put((rank, shard.pack_results(res)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_run_sharded_world2_nccl_matches_one_gpu():
+    """shard.run_sharded with the product runner on two GPUs: NCCL all_gather of the 21-double result rows; every rank ends
+    with the full list, equal to the one-GPU run."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    import torch.multiprocessing as mp
+    from xchu_slam_b200 import shard
+    w = _c5_small()
+    one = shard.pack_results(shard.run_sharded(shard.gpu_runner(0, resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2),
+                                               w["targets"], w["sources"], w["item_target"], w["item_source"], w["guesses"]))
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_nccl_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=300) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert np.array_equal(got[0], got[1])
+    assert np.array_equal(got[0][:, 16:18], one[:, 16:18]) and np.array_equal(got[0][:, 20], one[:, 20])     # iterations, converged, n_evals
+    assert np.max(np.abs(got[0][:, :16] - one[:, :16])) < 1e-6

@@ -57,8 +57,10 @@ def _build_cuda(force=False, verbose=False, defines=()):
         if verbose:
             sys.stderr.write(out)
     if force or procs or _stale(LIB, objs):
-        subprocess.check_call(["nvcc", "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a",
+        tmp = LIB + ".tmp%d" % os.getpid()     # linked beside the target, then renamed: a reader never sees a half-written library
+        subprocess.check_call(["nvcc", "-shared", "-o", tmp] + objs + ["-gencode", "arch=compute_100a,code=sm_100a",
                                                                        "-Xcompiler", "-fPIC", "-ccbin", "g++", "-lcudart"])
+        os.replace(tmp, LIB)
     return LIB
 
 

@@ -149,6 +149,11 @@ struct Engine {
   unsigned long long lm_gen = 1;     // bumped whenever the localmap's contents stop being an extension of what they were
   unsigned long long tgt_gen = 0;    // localmap generation the target's points were taken from (0: not from the localmap)
   size_t tgt_from_lm = 0;            // leading localmap points already merged into the target
+  // the keyframe-count window (ndtb_window_*): per id one transformed + downsampled keyframe cloud
+  std::vector<DevCloud> win;           // index = id; p == nullptr once dropped
+  std::vector<DevCloud> win_free;      // buffers of dropped clouds, reused
+  float4* win_cat = nullptr;           // concatenation scratch
+  size_t win_cat_cap = 0;
   std::vector<int> last_item_target;   // targets of the items of the last run (ndtb_batch_fitness)
   double* d_fit_partial = nullptr;
   size_t fit_partial_cap = 0;
@@ -226,7 +231,13 @@ struct Engine {
     cudaFree(d_tables); cudaFree(src_pool); cudaFree(d_states); cudaFree(d_blockmap); cudaFree(d_partials);
     cudaFree(d_trace); cudaFree(d_active); cudaFreeHost(h_active); cudaFree(d_T16); cudaFree(d_p6);
     cudaFree(d_output); cudaFree(d_d2);
+    destroy_align_graph();
+    cudaFree(ag.d_state); cudaFree(ag.d_bmap); cudaFree(ag.d_partials); cudaFree(ag.d_trace); cudaFree(ag.d_active);
+    ag.h_in.release(); ag.h_out.release();
     cudaFree(lm.p); cudaFree(lm_tmp.p); cudaFree(lm_last.p); cudaFree(lm_scratch);
+    for (auto& c : win) cudaFree(c.p);
+    for (auto& c : win_free) cudaFree(c.p);
+    cudaFree(win_cat);
     st_src.release(); st_d2.release();
     filter_ws_destroy(flt); cudaFree(flt_raw);
     cudaFree(d_fit_partial); cudaFree(d_fit_out); cudaFree(d_fit_items);
@@ -282,6 +293,7 @@ struct Engine {
     table_config(t);
     if (t.pending_upload) { CKE(cudaStreamWaitEvent(stream, t.uploaded, 0)); t.pending_upload = false; }
     t.built = false;
+    tables_dirty = true;
     CKE(table_clear(t.ts, stream, &stats.kernel_launches));
     CKE(table_append(t.ts, ws, t.use ? t.use : t.pts, t.n, stream, &stats.kernel_launches));   // n == 0: an empty grid, as the reference's empty leaves_
     t.built = true;
@@ -450,6 +462,162 @@ struct Engine {
   PinnedBuf st_idx;                   // replay pass: ids of the registrations run again
   std::vector<unsigned char> replay_flag;   // per item of the last run: 1 = replayed with the strict kernel
 
+  // ---- a single registration as ONE CUDA graph launch (the loop NDT_I:114-159) -----------------
+  // ndtb_align used to enqueue derivatives -> newton pairs and poll the device every fourth pair: ~0.23 ms of launch and
+  // synchronisation latency around ~60 us of kernel time.  The graph: pull the registration state out of mapped host memory ->
+  // newton (first request) -> WHILE conditional node { derivatives; newton (advances computeTransformation / the line search,
+  // then tells the node whether another evaluation is wanted) } -> state back into mapped host memory.  One launch, one
+  // synchronisation, convergence tested on the device.  The derivative grid is fixed (room for `blocks` 256-point blocks; blocks
+  // past the source's end find nothing to do), buffers are the graph's own, so neither the source size nor the test hooks
+  // disturb it; it is rebuilt when the kernel selection, the table descriptor's address or the capacity changes.
+  struct AlignGraph {
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    int blocks = 0, method = -1, trace_cap = 0, eval_cap = 0;
+    bool strict = false, mt_live = false;
+    const VoxelTable* tables = nullptr;
+    AlignState* d_state = nullptr;      // one registration
+    int2* d_bmap = nullptr;
+    double* d_partials = nullptr;
+    double* d_trace = nullptr;
+    size_t trace_doubles = 0;
+    int* d_active = nullptr;
+    PinnedBuf h_in, h_out;              // the state as the host fills it / as the device leaves it
+    bool failed = false;                // graph construction failed once: stay on the eager path
+  } ag;
+  bool use_align_graph() const {
+    static const bool off = [] { const char* e = getenv("NDTB_NO_ALIGN_GRAPH"); return e && atoi(e) > 0; }();
+    return single && !off && !ag.failed && !getenv("NDTB_CHUNK");
+  }
+  void destroy_align_graph() {
+    if (ag.exec) cudaGraphExecDestroy(ag.exec);
+    if (ag.graph) cudaGraphDestroy(ag.graph);
+    ag.exec = nullptr; ag.graph = nullptr;
+  }
+  int build_align_graph(int blocks_needed, bool strict, bool mt_live, int eval_cap, int tcap) {
+    destroy_align_graph();
+    const int chunk = 256;
+    int blocks = 128;
+    while (blocks < blocks_needed) blocks *= 2;
+    if (!ag.d_state) CKE(cudaMalloc(&ag.d_state, sizeof(AlignState) + 16));
+    if (!ag.d_active) CKE(cudaMalloc(&ag.d_active, sizeof(int)));
+    if (blocks > ag.blocks || !ag.d_bmap) {
+      cudaFree(ag.d_bmap); cudaFree(ag.d_partials);
+      ag.d_bmap = nullptr; ag.d_partials = nullptr;
+      CKE(cudaMalloc(&ag.d_bmap, (size_t)blocks * sizeof(int2)));
+      CKE(cudaMalloc(&ag.d_partials, (size_t)blocks * 44 * sizeof(double)));
+    }
+    std::vector<int2> bm((size_t)blocks);
+    for (int b = 0; b < blocks; ++b) bm[b] = make_int2(0, b * chunk);
+    CKE(cudaMemcpyAsync(ag.d_bmap, bm.data(), bm.size() * sizeof(int2), cudaMemcpyHostToDevice, stream));
+    CKE(cudaStreamSynchronize(stream));
+    const size_t need_trace = (size_t)tcap * kTraceRec;
+    if (need_trace > ag.trace_doubles) {
+      cudaFree(ag.d_trace);
+      ag.d_trace = nullptr;
+      CKE(cudaMalloc(&ag.d_trace, need_trace * sizeof(double)));
+      ag.trace_doubles = need_trace;
+    }
+    CKE(ag.h_in.reserve(sizeof(AlignState)));
+    CKE(ag.h_out.reserve(sizeof(AlignState)));
+    ag.blocks = blocks; ag.method = params.search_method; ag.strict = strict; ag.mt_live = mt_live;
+    ag.trace_cap = tcap; ag.eval_cap = eval_cap; ag.tables = d_tables;
+    // capture: prologue on the engine's stream, the loop body into the conditional node's graph on a second stream
+    cudaStream_t s2 = nullptr;
+    CKE(cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking));
+    auto bail = [&](const std::string& m) {
+      cudaGraph_t junk = nullptr;
+      cudaStreamEndCapture(stream, &junk);
+      if (junk) cudaGraphDestroy(junk);
+      cudaStreamDestroy(s2);
+      cudaGetLastError();
+      ag.failed = true;
+      return fail("align graph: " + m);
+    };
+    if (cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) { cudaStreamDestroy(s2); ag.failed = true; return fail("align graph: begin capture failed"); }
+    if (launch_pull(ag.d_state, ag.h_in.d, sizeof(AlignState), stream) != cudaSuccess) return bail("prologue");
+    if (launch_set_int(ag.d_active, 1, stream) != cudaSuccess) return bail("prologue");
+    if (launch_newton(ag.d_state, 1, ag.d_partials, ag.d_trace, tcap, ag.d_active, stream) != cudaSuccess) return bail("prologue");
+    cudaStreamCaptureStatus st_;
+    cudaGraph_t g = nullptr;
+    const cudaGraphNode_t* deps = nullptr;
+    size_t n_deps = 0;
+    if (cudaStreamGetCaptureInfo(stream, &st_, nullptr, &g, &deps, &n_deps) != cudaSuccess || st_ != cudaStreamCaptureStatusActive) return bail("capture info");
+    cudaGraphConditionalHandle cond;
+    if (cudaGraphConditionalHandleCreate(&cond, g, 1, cudaGraphCondAssignDefault) != cudaSuccess) return bail("conditional handle");
+    cudaGraphNodeParams cp = {};
+    cp.type = cudaGraphNodeTypeConditional;
+    cp.conditional.handle = cond;
+    cp.conditional.type = cudaGraphCondTypeWhile;
+    cp.conditional.size = 1;
+    cudaGraphNode_t cnode;
+    if (cudaGraphAddNode(&cnode, g, deps, n_deps, &cp) != cudaSuccess) return bail("conditional node");
+    cudaGraph_t body = cp.conditional.phGraph_out[0];
+    if (cudaStreamUpdateCaptureDependencies(stream, &cnode, 1, cudaStreamSetCaptureDependencies) != cudaSuccess) return bail("capture dependencies");
+    if (cudaStreamBeginCaptureToGraph(s2, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal) != cudaSuccess) return bail("body capture");
+    cudaError_t ce = (strict ? launch_derivatives : launch_derivatives_fast)(ag.d_state, d_tables, src_pool, ag.d_bmap, blocks, chunk, ag.d_partials,
+                                                                             params.search_method, mt_live, s2);
+    if (ce == cudaSuccess && mt_live) ce = launch_hessian_f64(ag.d_state, d_tables, src_pool, ag.d_bmap, blocks, chunk, ag.d_partials, s2);
+    if (ce == cudaSuccess) ce = launch_newton(ag.d_state, 1, ag.d_partials, ag.d_trace, tcap, ag.d_active, s2, (unsigned long long)cond, eval_cap);
+    cudaGraph_t body_out = nullptr;
+    if (cudaStreamEndCapture(s2, &body_out) != cudaSuccess || ce != cudaSuccess) return bail("body");
+    if (launch_pull(ag.h_out.d, ag.d_state, sizeof(AlignState), stream) != cudaSuccess) return bail("epilogue");
+    if (cudaStreamEndCapture(stream, &ag.graph) != cudaSuccess) { cudaStreamDestroy(s2); cudaGetLastError(); ag.failed = true; return fail("align graph: end capture failed"); }
+    cudaStreamDestroy(s2);
+    if (cudaGraphInstantiate(&ag.exec, ag.graph, 0) != cudaSuccess) { cudaGetLastError(); destroy_align_graph(); ag.failed = true; return fail("align graph: instantiate failed"); }
+    return 0;
+  }
+  // ndtb_align through the graph.  Returns 0 ok, 1 error, 2 = not applicable (the caller takes the eager path).
+  int align_graph(const float* guess, ndtb_result* out) {
+    if (!use_align_graph()) return 2;
+    const Source& src = sources[0];
+    const int mode = kernel_mode();
+    if (mode == KM_HYBRID) return 2;
+    const bool strict = mode == KM_STRICT;
+    const bool mt_live = !((params.step_size - params.trans_eps / 2) > 0);
+    const int eval_cap = 1 + (params.max_iter + 2) * (mt_live ? 12 : 1);
+    const int tcap = eval_cap + 1;
+    const int nb = (int)((src.n + 255) / 256);
+    if (sync_tables_if_dirty()) return 1;
+    if (!ag.exec || ag.blocks < nb || ag.method != params.search_method || ag.strict != strict || ag.mt_live != mt_live || ag.tables != d_tables ||
+        ag.eval_cap != eval_cap || ag.trace_cap != tcap) {
+      // the kernels' shared-memory attributes are set by their first ordinary launch: the first align of a configuration
+      // runs eagerly, the graph is built behind it
+      if (!ag_warm) { ag_warm = true; return 2; }
+      if (build_align_graph(nb, strict, mt_live, eval_cap, tcap)) { err.clear(); return 2; }
+    }
+    AlignState& st = *static_cast<AlignState*>(ag.h_in.h);
+    fill_state(st, 0, src, guess);
+    st.first_block = 0;
+    st.n_blocks = nb;
+    stats = ndtb_batch_stats{};
+    CKE(cudaEventRecord(ev[2], stream));
+    CKE(cudaGraphLaunch(ag.exec, stream));
+    CKE(cudaEventRecord(ev[3], stream));
+    CKE(cudaStreamSynchronize(stream));
+    float ms = 0;
+    CKE(cudaEventElapsedTime(&ms, ev[2], ev[3]));
+    last_align_ms = ms;
+    const AlignState& r = *static_cast<const AlignState*>(ag.h_out.h);
+    state_to_result(r, *out);
+    stats.points_evaluated = (long long)r.n_src * r.n_evals;
+    stats.pairs_evaluated = r.pairs_total;
+    stats.deriv_launches = r.n_evals;
+    stats.kernel_launches = 4 + 2ll * r.n_evals;
+    trace_cap = tcap;
+    trace_on_device = true;
+    return 0;
+  }
+  bool ag_warm = false;
+  bool trace_on_device = false;     // the last align's trace still sits in ag.d_trace (copied on demand, ndtb_get_trace)
+  bool tables_dirty = true;         // the table descriptor on the device is older than targets[0].ts.t
+  int sync_tables_if_dirty() {
+    if (!tables_dirty && d_tables) return 0;
+    if (sync_tables()) return 1;
+    tables_dirty = false;
+    return 0;
+  }
+
   int plan_chunk(size_t total_pts) const {
     // small blocks keep the tail iterations (few registrations still active) balanced over the SMs
     int chunk = (int)((total_pts / (size_t)target_blocks() + 255) / 256 * 256);
@@ -593,12 +761,17 @@ struct Engine {
       int* idx = static_cast<int*>(st_idx.h);
       int k_iters = params.replay_iters;
       if (const char* ev = getenv("NDTB_REPLAY_ITERS")) k_iters = atoi(ev);   // tuning knob
+      double min_norm = params.replay_min_norm >= 0 ? params.replay_min_norm : 0.05 * params.trans_eps;
+      if (const char* ev = getenv("NDTB_REPLAY_MIN_NORM")) min_norm = atof(ev);   // tuning knob
       int k_rise = 1 << 30;
       if (const char* ev = getenv("NDTB_REPLAY_RISE")) k_rise = atoi(ev);     // tuning knob: replay when n_rise >= this
       size_t pts = 0;
       for (int i = 0; i < n_items; ++i) {
         const AlignState& st = h_states[i];
-        const bool again = !st.done || !st.converged || st.borderline || (k_iters > 0 && st.nr_iterations > k_iters) || st.n_rise >= k_rise;
+        // last Newton step far below the step clamp (eps / 2): the final move is eps / 2 along delta_p / |delta_p|, a direction
+        // that a difference of ~1e-6 in delta_p (one voxel flip of one point) turns by 1e-6 / |delta_p|
+        const bool tiny_last = st.last_norm < min_norm;
+        const bool again = !st.done || !st.converged || st.borderline || tiny_last || (k_iters > 0 && st.nr_iterations > k_iters) || st.n_rise >= k_rise;
         if (!again || st.n_src <= 0) continue;
         idx[n_replay++] = i;
         replay_flag[i] = 1;
@@ -663,7 +836,7 @@ extern "C" {
 void ndtb_default_params(ndtb_params* p) {
   p->resolution = 1.0f; p->step_size = 0.1; p->trans_eps = 0.1; p->max_iter = 35; p->outlier_ratio = 0.55;
   p->search_method = NDTB_DIRECT7; p->min_points = 6; p->eig_mult = 0.01; p->strict_math = -1; p->dense_max_cells = 1ll << 26;
-  p->replay_iters = 12;
+  p->replay_iters = 11; p->replay_min_norm = -1.0;
 }
 
 static int create_engine(int device, Engine& e) { return e.init(device); }
@@ -741,6 +914,7 @@ int ndtb_update_target(ndtb_handle* h, const void* pts, size_t n, size_t stride_
   cudaEventRecord(e.ev[0], e.stream);
   if (e.upload_points(t.pts + t.n, pts, n, stride_bytes, false, e.stream)) return 1;
   e.table_config(t);
+  e.tables_dirty = true;
   cudaError_t ce = table_append(t.ts, e.ws, t.pts + t.n, n, e.stream, &e.stats.kernel_launches);
   if (ce != cudaSuccess) return e.fail(std::string("table_append: ") + cudaGetErrorString(ce));
   t.n += n;
@@ -779,6 +953,7 @@ int ndtb_set_target_auto(ndtb_handle* h, const void* pts, size_t n, size_t strid
       // tail <= old_n (the guard above): [2 old_n, 2 old_n + tail) -> [old_n, old_n + tail) never overlap
       cudaMemcpyAsync(t.pts + old_n, fresh + old_n, tail * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream);
       e.table_config(t);
+      e.tables_dirty = true;
       ce = table_append(t.ts, e.ws, t.pts + old_n, tail, e.stream, &e.stats.kernel_launches);
       if (ce != cudaSuccess) return e.fail(std::string("table_append: ") + cudaGetErrorString(ce));
       t.n = n;
@@ -838,7 +1013,13 @@ int ndtb_align(ndtb_handle* h, const float guess[16], ndtb_result* out) {
   if (e.sources.empty()) return e.fail("no source cloud set");
   if (!e.targets[0].built) return e.fail("no target cloud set");
   const int zero = 0;
-  if (e.run_items(1, &zero, &zero, guess, &e.last, true)) return 1;
+  if (cudaSetDevice(e.device) != cudaSuccess) return e.fail("cudaSetDevice failed");
+  const int via_graph = e.align_graph(guess, &e.last);
+  if (via_graph == 1) return 1;
+  if (via_graph == 2) {
+    e.trace_on_device = false;
+    if (e.run_items(1, &zero, &zero, guess, &e.last, true)) return 1;
+  }
   e.have_result = true;
   e.h_trace_n = e.last.n_evals;
   if (out) *out = e.last;
@@ -1002,6 +1183,14 @@ int ndtb_neighbors(ndtb_handle* h, const float* xyz, size_t n, int method, int* 
 int ndtb_get_trace(ndtb_handle* h, double* out, int max_recs, int* n) {
   Engine& e = h->e;
   if (!e.have_result) return e.fail("no align result");
+  if (e.trace_on_device) {     // the align ran as a graph: its trace is fetched when somebody asks for it
+    cudaSetDevice(e.device);
+    const int have = e.h_trace_n < e.trace_cap ? e.h_trace_n : e.trace_cap;
+    e.h_trace.resize((size_t)(have > 0 ? have : 1) * kTraceRec);
+    if (have > 0 && cudaMemcpy(e.h_trace.data(), e.ag.d_trace, (size_t)have * kTraceRec * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess)
+      return e.fail("trace copy failed");
+    e.trace_on_device = false;
+  }
   const int avail = e.h_trace_n < e.trace_cap ? e.h_trace_n : e.trace_cap;
   if (n) *n = avail;
   const int m = avail < max_recs ? avail : max_recs;
@@ -1096,6 +1285,7 @@ int ndtb_localmap_set_target(ndtb_handle* h, int force_full, int* was_incrementa
       if (e.reserve_target(t, n)) return 1;
       if (cudaMemcpyAsync(t.pts + t.n, e.lm.p + e.tgt_from_lm, tail * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream) != cudaSuccess) return e.fail("device copy failed");
       e.table_config(t);
+      e.tables_dirty = true;
       cudaError_t ce = table_append(t.ts, e.ws, t.pts + t.n, tail, e.stream, &e.stats.kernel_launches);
       if (ce != cudaSuccess) return e.fail(std::string("table_append: ") + cudaGetErrorString(ce));
       t.n = n;
@@ -1153,6 +1343,116 @@ int ndtb_localmap_download(ndtb_handle* h, int which, void* pts, size_t cap, siz
     if (stride_bytes >= 20)
       if (cudaMemcpy2DAsync(static_cast<char*>(pts) + 16, stride_bytes, reinterpret_cast<const char*>(c->p) + 12, 16, 4, m, cudaMemcpyDeviceToHost, e.stream) != cudaSuccess) return e.fail("device copy failed");
   }
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  return 0;
+}
+
+// ---- keyframe-count window (reference src/odom_node.cpp:737-802) ----------------------------------------
+static int copy_cloud_to_host(Engine& e, const float4* d, size_t m, void* pts, size_t stride_bytes);
+int ndtb_window_add_source(ndtb_handle* h, const float T[16], float leaf, int* id, size_t* n_points) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  if (n_points) *n_points = 0;
+  if (e.sources.empty()) return e.fail("ndtb_window_add_source needs a source (ndtb_set_source)");
+  const size_t n = e.sources[0].n;
+  Engine::DevCloud c;
+  // a buffer of a dropped cloud that is large enough, else a fresh one
+  for (size_t k = 0; k < e.win_free.size(); ++k)
+    if (e.win_free[k].cap >= n) { c = e.win_free[k]; e.win_free.erase(e.win_free.begin() + (long)k); break; }
+  c.n = 0;
+  if (c.cap < n || !c.p) {
+    cudaFree(c.p);
+    c.p = nullptr;
+    c.cap = n + n / 4 + 256;
+    if (cudaMalloc(&c.p, c.cap * sizeof(float4)) != cudaSuccess) return e.fail("window cloud allocation failed");
+  }
+  size_t m = n;
+  if (n > 0) {
+    const bool ds = leaf > 0.f;
+    if (ds && n > e.lm_scratch_cap) {
+      cudaFree(e.lm_scratch);
+      e.lm_scratch = nullptr;
+      if (cudaMalloc(&e.lm_scratch, (n + n / 4) * sizeof(float4)) != cudaSuccess) return e.fail("alloc");
+      e.lm_scratch_cap = n + n / 4;
+    }
+    if (cudaMemcpyAsync(e.d_T16, T, 64, cudaMemcpyHostToDevice, e.stream) != cudaSuccess) return e.fail("device copy failed");
+    if (launch_transform(e.source_ptr(e.sources[0]), n, e.d_T16, ds ? e.lm_scratch : c.p, e.stream) != cudaSuccess) return e.fail("transform failed");
+    ++e.stats.kernel_launches;
+    if (ds) {
+      cudaError_t ce = voxelgrid_downsample(e.ws, e.lm_scratch, n, leaf, c.p, &m, e.stream, &e.stats.kernel_launches);
+      if (ce != cudaSuccess) return e.fail(std::string("voxelgrid_downsample: ") + cudaGetErrorString(ce));
+    }
+  }
+  c.n = m;
+  e.win.push_back(c);
+  if (id) *id = (int)e.win.size() - 1;
+  if (n_points) *n_points = m;
+  return 0;
+}
+int ndtb_window_drop(ndtb_handle* h, int id) {
+  Engine& e = h->e;
+  if (id < 0 || id >= (int)e.win.size() || !e.win[id].p) return e.fail("ndtb_window_drop: no such window cloud");
+  e.win_free.push_back(e.win[id]);
+  e.win[id] = Engine::DevCloud();
+  return 0;
+}
+int ndtb_window_clear(ndtb_handle* h) {
+  Engine& e = h->e;
+  for (auto& c : e.win)
+    if (c.p) e.win_free.push_back(c);
+  e.win.clear();
+  return 0;
+}
+int ndtb_window_set_target(ndtb_handle* h, const int* ids, int n_ids, float leaf, size_t* n_target) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  if (n_target) *n_target = 0;
+  size_t total = 0;
+  for (int k = 0; k < n_ids; ++k) {
+    if (ids[k] < 0 || ids[k] >= (int)e.win.size() || !e.win[ids[k]].p) return e.fail("ndtb_window_set_target: no such window cloud");
+    total += e.win[ids[k]].n;
+  }
+  Target& t = e.targets[0];
+  cudaEventRecord(e.ev[0], e.stream);
+  const bool ds = leaf > 0.f && total > 0;
+  if (ds && e.ensure(e.win_cat, e.win_cat_cap, total)) return 1;
+  if (e.reserve_target(t, total)) return 1;
+  t.n = 0;
+  float4* dst = ds ? e.win_cat : t.pts;
+  size_t off = 0;
+  for (int k = 0; k < n_ids; ++k) {
+    const Engine::DevCloud& c = e.win[ids[k]];
+    if (c.n && cudaMemcpyAsync(dst + off, c.p, c.n * sizeof(float4), cudaMemcpyDeviceToDevice, e.stream) != cudaSuccess) return e.fail("device copy failed");
+    off += c.n;
+  }
+  size_t m = total;
+  if (ds) {
+    cudaError_t ce = voxelgrid_downsample(e.ws, e.win_cat, total, leaf, t.pts, &m, e.stream, &e.stats.kernel_launches);
+    if (ce != cudaSuccess) return e.fail(std::string("voxelgrid_downsample: ") + cudaGetErrorString(ce));
+  }
+  t.use = nullptr;
+  t.n = m;
+  e.nn_valid = false;
+  e.tgt_gen = 0;
+  t.ts.have_bbox = false;
+  if (e.build_target(t)) return 1;
+  cudaEventRecord(e.ev[1], e.stream);
+  if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
+  float ms = 0;
+  cudaEventElapsedTime(&ms, e.ev[0], e.ev[1]);
+  e.last_build_ms = ms;
+  if (n_target) *n_target = m;
+  return 0;
+}
+int ndtb_get_target(ndtb_handle* h, void* pts, size_t cap, size_t stride_bytes, size_t* n) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  if (stride_bytes < 12) return e.fail("stride_bytes must be >= 12");
+  const Target& t = e.targets[0];
+  const size_t m = t.n < cap ? t.n : cap;
+  if (n) *n = m;
+  if (m == 0) return 0;
+  if (copy_cloud_to_host(e, t.use ? t.use : t.pts, m, pts, stride_bytes)) return 1;
   if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
   return 0;
 }
@@ -1635,6 +1935,121 @@ int ndtb_batch_set_stream(ndtb_batch* b, void* cuda_stream) {
   if (e.stream && e.own_stream) { cudaStreamSynchronize(e.stream); cudaStreamDestroy(e.stream); }
   e.stream = (cudaStream_t)cuda_stream;
   e.own_stream = false;
+  return 0;
+}
+
+}  // extern "C"
+
+// ---- one job over several devices ---------------------------------------------------------------
+#include <chrono>
+struct ndtb_multi {
+  std::vector<int> devices;
+  std::vector<ndtb_batch*> batches;
+  std::string err;
+  std::vector<int> st_items, st_targets;
+  std::vector<double> st_dev_ms, st_wall_ms;
+};
+
+extern "C" {
+
+int ndtb_multi_create(int n_devices, const int* devices, ndtb_multi** out) {
+  if (!out) return 1;
+  *out = nullptr;
+  if (n_devices <= 0 || !devices) { g_create_error = "ndtb_multi_create needs at least one device"; return 1; }
+  ndtb_multi* m = new ndtb_multi();
+  for (int k = 0; k < n_devices; ++k) {
+    ndtb_batch* b = nullptr;
+    if (ndtb_batch_create(devices[k], &b)) {
+      for (auto* q : m->batches) ndtb_batch_destroy(q);
+      delete m;
+      return 1;                                         // g_create_error holds the batch's message
+    }
+    m->devices.push_back(devices[k]);
+    m->batches.push_back(b);
+  }
+  m->st_items.assign(n_devices, 0); m->st_targets.assign(n_devices, 0);
+  m->st_dev_ms.assign(n_devices, 0.0); m->st_wall_ms.assign(n_devices, 0.0);
+  *out = m;
+  return 0;
+}
+int ndtb_multi_destroy(ndtb_multi* m) {
+  if (!m) return 0;
+  for (auto* b : m->batches) ndtb_batch_destroy(b);
+  delete m;
+  return 0;
+}
+const char* ndtb_multi_last_error(const ndtb_multi* m) { return m ? m->err.c_str() : g_create_error.c_str(); }
+int ndtb_multi_set_params(ndtb_multi* m, const ndtb_params* p) {
+  for (auto* b : m->batches)
+    if (ndtb_batch_set_params(b, p)) { m->err = ndtb_batch_last_error(b); return 1; }
+  return 0;
+}
+
+int ndtb_multi_run(ndtb_multi* m, int n_targets, const void* const* target_pts, const size_t* target_n, int n_sources,
+                   const void* const* source_pts, const size_t* source_n, size_t stride_bytes, int n_items, const int* item_target,
+                   const int* item_source, const float* guesses, ndtb_result* results) {
+  const int D = (int)m->batches.size();
+  for (int d = 0; d < D; ++d) { m->st_items[d] = m->st_targets[d] = 0; m->st_dev_ms[d] = m->st_wall_ms[d] = 0.0; }
+  if (n_items <= 0) return 0;
+  for (int i = 0; i < n_items; ++i) {
+    if (item_target[i] < 0 || item_target[i] >= n_targets) { m->err = "item target id out of range"; return 1; }
+    if (item_source[i] < 0 || item_source[i] >= n_sources) { m->err = "item source id out of range"; return 1; }
+  }
+  // plan: items by target id (stable), contiguous blocks of n/D (+1 for the first n%D devices) -- shard.plan_shards in Python
+  std::vector<int> order((size_t)n_items);
+  for (int i = 0; i < n_items; ++i) order[i] = i;
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return item_target[a] < item_target[b]; });
+  std::vector<std::string> errs((size_t)D);
+  auto work = [&](int d, int first, int count) {
+    const auto t0 = std::chrono::steady_clock::now();
+    ndtb_batch* b = m->batches[d];
+    auto failb = [&]() { errs[d] = std::string("device ") + std::to_string(m->devices[d]) + ": " + ndtb_batch_last_error(b); };
+    if (ndtb_batch_clear(b)) return failb();
+    // local ids in order of first use
+    std::vector<int> tmap((size_t)n_targets, -1), smap((size_t)n_sources, -1), lt((size_t)count), ls((size_t)count);
+    std::vector<const void*> tp, sp;
+    std::vector<size_t> tn, sn;
+    std::vector<float> G((size_t)count * 16);
+    for (int k = 0; k < count; ++k) {
+      const int i = order[first + k];
+      int& a = tmap[item_target[i]];
+      if (a < 0) { a = (int)tp.size(); tp.push_back(target_pts[item_target[i]]); tn.push_back(target_n[item_target[i]]); }
+      int& c = smap[item_source[i]];
+      if (c < 0) { c = (int)sp.size(); sp.push_back(source_pts[item_source[i]]); sn.push_back(source_n[item_source[i]]); }
+      lt[k] = a; ls[k] = c;
+      std::memcpy(&G[(size_t)k * 16], guesses + (size_t)i * 16, 64);
+    }
+    if (ndtb_batch_add_targets(b, (int)tp.size(), tp.data(), tn.data(), stride_bytes, 0, nullptr)) return failb();
+    if (ndtb_batch_add_sources(b, (int)sp.size(), sp.data(), sn.data(), stride_bytes, 0, nullptr)) return failb();
+    std::vector<ndtb_result> res((size_t)count);
+    if (ndtb_batch_run(b, count, lt.data(), ls.data(), G.data(), res.data())) return failb();
+    for (int k = 0; k < count; ++k) results[order[first + k]] = res[k];      // the gather: disjoint entries per device
+    ndtb_batch_stats st;
+    ndtb_batch_get_stats(b, &st);
+    m->st_items[d] = count; m->st_targets[d] = (int)tp.size(); m->st_dev_ms[d] = st.total_ms;
+    m->st_wall_ms[d] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  };
+  std::vector<std::thread> th;
+  const int base = n_items / D, extra = n_items % D;
+  int pos = 0;
+  for (int d = 0; d < D; ++d) {
+    const int cnt = base + (d < extra ? 1 : 0);
+    if (cnt > 0) th.emplace_back(work, d, pos, cnt);
+    pos += cnt;
+  }
+  for (auto& t : th) t.join();
+  for (int d = 0; d < D; ++d)
+    if (!errs[d].empty()) { m->err = errs[d]; return 1; }
+  return 0;
+}
+
+int ndtb_multi_get_stats(ndtb_multi* m, int* items, int* targets, double* device_ms, double* wall_ms) {
+  for (size_t d = 0; d < m->batches.size(); ++d) {
+    if (items) items[d] = m->st_items[d];
+    if (targets) targets[d] = m->st_targets[d];
+    if (device_ms) device_ms[d] = m->st_dev_ms[d];
+    if (wall_ms) wall_ms[d] = m->st_wall_ms[d];
+  }
   return 0;
 }
 

@@ -476,7 +476,8 @@ struct LU6 {
   double a[6][6];   // L (unit diagonal, below) and U (on and above the diagonal) of the row-permuted matrix
   int piv[6];       // row chosen at step k
 };
-__device__ __forceinline__ bool lu_factor6(const double* H, LU6& f) {
+__device__ __forceinline__ bool lu_factor6(const double* H, LU6& f, double* pivot_ratio) {
+  *pivot_ratio = 0.0;
 #pragma unroll
   for (int i = 0; i < 6; ++i)
 #pragma unroll
@@ -514,6 +515,7 @@ __device__ __forceinline__ bool lu_factor6(const double* H, LU6& f) {
       for (int j = k + 1; j < 6; ++j) f.a[i][j] -= m * f.a[k][j];
     }
   }
+  *pivot_ratio = pmin / pmax;
   return pmin > 1e-10 * pmax;
 }
 __device__ __forceinline__ void lu_apply6(const LU6& f, const double* b, double* x) {
@@ -543,10 +545,14 @@ __device__ __forceinline__ void lu_apply6(const LU6& f, const double* b, double*
     x[i] = v / f.a[i][i];
   }
 }
-// returns true when the pseudo-inverse (SVD) branch produced the step
+// returns true when the pseudo-inverse (SVD) branch produced the step, or when the system is so ill-conditioned (smallest /
+// largest pivot below 1e-6; a registration's Hessian sits around 1e-3) that a 1e-7 perturbation of H decides the step: the
+// factorised kernel's arithmetic noise turns an exactly rank-deficient Hessian (one source point: rank 3) into such a system
 __device__ bool solve6(const double* H, const double* b, double* x) {
   LU6 f;
-  if (!lu_factor6(H, f)) { svd_solve6(H, b, x); return true; }
+  double ratio;
+  if (!lu_factor6(H, f, &ratio)) { svd_solve6(H, b, x); return true; }
+  const bool ill = ratio < 1e-6;
   lu_apply6(f, b, x);
   double r[6], d[6];
 #pragma unroll
@@ -561,7 +567,7 @@ __device__ bool solve6(const double* H, const double* b, double* x) {
 #pragma unroll
   for (int i = 0; i < 6; ++i) { x[i] += d[i]; ok = ok && (fabs(x[i]) <= DBL_MAX); }
   if (!ok) svd_solve6(H, b, x);
-  return !ok;
+  return !ok || ill;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -816,11 +822,18 @@ __device__ void newton_advance(AlignState& st, const double* sums, double* trace
   }
 }
 
+// cond != 0 (a single registration run as ONE CUDA graph, ndt_api.cu AlignGraph): the kernel is the last node of the body of a
+// WHILE conditional node and decides whether the body runs again -- until the registration is done, or eval_cap evaluations
+// have run (a loop that cannot end would hang the device).
 __global__ void __launch_bounds__(64) k_newton(AlignState* __restrict__ states, int n_items, const double* __restrict__ partials,
-                                               double* __restrict__ trace, int trace_cap, int* __restrict__ n_active) {
+                                               double* __restrict__ trace, int trace_cap, int* __restrict__ n_active,
+                                               unsigned long long cond, int eval_cap) {
   const int item = blockIdx.x;
   if (item >= n_items) return;
-  if (states[item].done) return;
+  if (states[item].done) {
+    if (cond && threadIdx.x == 0) cudaGraphSetConditional((cudaGraphConditionalHandle)cond, 0u);
+    return;
+  }
   __shared__ double sums[kPartialStride];
   __shared__ AlignState st;
   static_assert(sizeof(AlignState) % 8 == 0, "AlignState is copied as 64-bit words");
@@ -849,7 +862,10 @@ __global__ void __launch_bounds__(64) k_newton(AlignState* __restrict__ states, 
     sums[tid] = v;
   }
   __syncthreads();
-  if (tid == 0) newton_advance(st, sums, trace ? trace + (size_t)item * trace_cap * kTraceRec : nullptr, trace_cap, n_active);
+  if (tid == 0) {
+    newton_advance(st, sums, trace ? trace + (size_t)item * trace_cap * kTraceRec : nullptr, trace_cap, n_active);
+    if (cond) cudaGraphSetConditional((cudaGraphConditionalHandle)cond, (!st.done && st.n_evals < eval_cap) ? 1u : 0u);
+  }
   __syncthreads();
   {
     const unsigned long long* src = reinterpret_cast<const unsigned long long*>(&st);
@@ -942,9 +958,9 @@ cudaError_t launch_hessian_f64(const AlignState* states, const VoxelTable* table
   return cudaGetLastError();
 }
 cudaError_t launch_newton(AlignState* states, int n_items, const double* partials, double* trace, int trace_cap, int* n_active,
-                          cudaStream_t s) {
+                          cudaStream_t s, unsigned long long cond, int eval_cap) {
   if (n_items <= 0) return cudaSuccess;
-  k_newton<<<n_items, 64, 0, s>>>(states, n_items, partials, trace, trace_cap, n_active);
+  k_newton<<<n_items, 64, 0, s>>>(states, n_items, partials, trace, trace_cap, n_active, cond, eval_cap);
   return cudaGetLastError();
 }
 cudaError_t launch_neighbors(const VoxelTable* table, const float* xyz, size_t n, int method, int* cnt, int* ijk, cudaStream_t s) {

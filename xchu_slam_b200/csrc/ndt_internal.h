@@ -180,7 +180,7 @@ cudaError_t launch_derivatives_fast(const AlignState* states, const VoxelTable* 
 cudaError_t launch_hessian_f64(const AlignState* states, const VoxelTable* tables, const float4* src_pool,
                                const int2* blockmap, int n_blocks, int chunk, double* partials, cudaStream_t s);
 cudaError_t launch_newton(AlignState* states, int n_items, const double* partials, double* trace, int trace_cap,
-                          int* n_active, cudaStream_t s);
+                          int* n_active, cudaStream_t s, unsigned long long cond_handle = 0, int eval_cap = 0);
 cudaError_t launch_neighbors(const VoxelTable* table, const float* xyz, size_t n, int method, int* cnt, int* ijk,
                              cudaStream_t s);
 cudaError_t launch_transform(const float4* src, size_t n, const float* T16_colmajor_dev, float4* out, cudaStream_t s);

@@ -23,7 +23,7 @@ class NdtError(RuntimeError):
 class Params(C.Structure):
     _fields_ = [("resolution", C.c_float), ("step_size", C.c_double), ("trans_eps", C.c_double), ("max_iter", C.c_int),
                 ("outlier_ratio", C.c_double), ("search_method", C.c_int), ("min_points", C.c_int), ("eig_mult", C.c_double),
-                ("strict_math", C.c_int), ("dense_max_cells", C.c_longlong), ("replay_iters", C.c_int)]
+                ("strict_math", C.c_int), ("dense_max_cells", C.c_longlong), ("replay_iters", C.c_int), ("replay_min_norm", C.c_double)]
 
 
 class Result(C.Structure):
@@ -59,7 +59,9 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_localmap_roll", "ndtb_localmap_sizes", "ndtb_localmap_download", "ndtb_default_filter_params", "ndtb_filter_scan",
            "ndtb_get_source", "ndtb_batch_add_keyframe", "ndtb_batch_clear_keyframes", "ndtb_batch_num_keyframes",
            "ndtb_batch_add_submap", "ndtb_batch_download", "ndtb_batch_add_targets", "ndtb_batch_add_sources",
-           "ndtb_batch_add_submaps", "ndtb_batch_get_diag"]
+           "ndtb_batch_add_submaps", "ndtb_batch_get_diag", "ndtb_multi_create", "ndtb_multi_destroy", "ndtb_multi_last_error",
+           "ndtb_multi_set_params", "ndtb_multi_run", "ndtb_multi_get_stats", "ndtb_window_add_source", "ndtb_window_drop",
+           "ndtb_window_clear", "ndtb_window_set_target", "ndtb_get_target"]
 
 _lib = None
 
@@ -111,6 +113,18 @@ def load_library():
     L.ndtb_batch_run.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
     L.ndtb_batch_get_diag.argtypes = [vp, vp, vp, vp, vp]
+    L.ndtb_window_add_source.argtypes = [vp, vp, C.c_float, C.POINTER(C.c_int), C.POINTER(sz)]
+    L.ndtb_window_drop.argtypes = [vp, C.c_int]
+    L.ndtb_window_clear.argtypes = [vp]
+    L.ndtb_window_set_target.argtypes = [vp, vp, C.c_int, C.c_float, C.POINTER(sz)]
+    L.ndtb_get_target.argtypes = [vp, vp, sz, sz, C.POINTER(sz)]
+    L.ndtb_multi_create.argtypes = [C.c_int, vp, C.POINTER(vp)]
+    L.ndtb_multi_destroy.argtypes = [vp]
+    L.ndtb_multi_last_error.argtypes = [vp]
+    L.ndtb_multi_last_error.restype = C.c_char_p
+    L.ndtb_multi_set_params.argtypes = [vp, C.POINTER(Params)]
+    L.ndtb_multi_run.argtypes = [vp, C.c_int, vp, vp, C.c_int, vp, vp, sz, C.c_int, vp, vp, vp, vp]
+    L.ndtb_multi_get_stats.argtypes = [vp, vp, vp, vp, vp]
     L.ndtb_batch_set_stream.argtypes = [vp, vp]
     L.ndtb_batch_fitness.argtypes = [vp, C.c_double, vp]
     L.ndtb_batch_add_keyframe.argtypes = [vp, vp, sz, sz, C.POINTER(C.c_int)]
@@ -390,6 +404,34 @@ class NormalDistributionsTransform:
         self._ck(self._L.ndtb_localmap_download(self._h, int(which), _p(out), cap, 16, C.byref(n)))
         return out[:n.value].copy()
 
+    # ---- the keyframe-count window on the device (reference src/odom_node.cpp:737-802 ExtractSurroundKeyframes) ----
+    def windowAddSource(self, T, leaf=1.0):
+        """tf_cloud = VoxelGrid(leaf)(T * source) kept in HBM.  Returns (id, points)."""
+        i, n = C.c_int(), C.c_size_t()
+        Tc = _colmajor(T)
+        self._ck(self._L.ndtb_window_add_source(self._h, _p(Tc), float(leaf), C.byref(i), C.byref(n)))
+        return i.value, n.value
+
+    def windowDrop(self, id):
+        self._ck(self._L.ndtb_window_drop(self._h, int(id)))
+
+    def windowClear(self):
+        self._ck(self._L.ndtb_window_clear(self._h))
+
+    def windowSetTarget(self, ids, leaf=0.5):
+        """pc_target_ = VoxelGrid(leaf)(concatenation of the listed clouds, in that order); setInputTarget.  Returns its size."""
+        a = np.ascontiguousarray(ids, dtype=np.int32)
+        n = C.c_size_t()
+        self._ck(self._L.ndtb_window_set_target(self._h, _p(a), a.shape[0], float(leaf), C.byref(n)))
+        self._n_target = n.value
+        return n.value
+
+    def getTarget(self, cap):
+        out = np.zeros((max(1, int(cap)), 4), np.float32)
+        n = C.c_size_t()
+        self._ck(self._L.ndtb_get_target(self._h, _p(out), out.shape[0], 16, C.byref(n)))
+        return out[:n.value].copy()
+
     def lastTiming(self):
         b, a = C.c_double(), C.c_double()
         self._L.ndtb_last_timing(self._h, C.byref(b), C.byref(a))
@@ -554,3 +596,60 @@ class BatchNDT:
         s = BatchStats()
         self._ck(self._L.ndtb_batch_get_stats(self._h, C.byref(s)))
         return {k: getattr(s, k) for k, _ in BatchStats._fields_}
+
+
+class MultiNDT:
+    """One batch job cut over several GPUs of one box inside the library (ndtb_multi_*): one host thread and one
+    ndtb_batch per listed device, items dealt in contiguous blocks by target id, results gathered in item order."""
+
+    def __init__(self, devices):
+        self._L = load_library()
+        self._h = C.c_void_p()
+        self.devices = [int(d) for d in devices]
+        dv = (C.c_int * len(self.devices))(*self.devices)
+        if self._L.ndtb_multi_create(len(self.devices), dv, C.byref(self._h)):
+            raise NdtError(self._L.ndtb_multi_last_error(None).decode())
+        self.params = Params()
+        self._L.ndtb_default_params(C.byref(self.params))
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._L.ndtb_multi_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc:
+            raise NdtError(self._L.ndtb_multi_last_error(self._h).decode())
+
+    def set_params(self, **kw):
+        for k, v in kw.items():
+            if not hasattr(self.params, k):
+                raise KeyError(k)
+            setattr(self.params, k, v)
+        self._ck(self._L.ndtb_multi_set_params(self._h, C.byref(self.params)))
+
+    def run_raw(self, targets, sources, item_target, item_source, guesses):
+        """targets / sources: lists of (n, 4) float32 host arrays (kept alive by the caller for the call)."""
+        tg = [_cloud(t) for t in targets]
+        sc = [_cloud(s) for s in sources]
+        stride = tg[0].strides[0] if tg else 16
+        assert all(a.strides[0] == stride for a in tg + sc)
+        tp, tn, _ = BatchNDT.pointer_table([a.ctypes.data for a in tg], [a.shape[0] for a in tg])
+        sp, sn, _ = BatchNDT.pointer_table([a.ctypes.data for a in sc], [a.shape[0] for a in sc])
+        it = np.ascontiguousarray(item_target, dtype=np.int32)
+        isrc = np.ascontiguousarray(item_source, dtype=np.int32)
+        n = it.shape[0]
+        G = np.ascontiguousarray(np.asarray(guesses, dtype=np.float32).reshape(n, 4, 4).transpose(0, 2, 1)).reshape(n, 16)
+        res = np.zeros(n, dtype=RESULT_DTYPE)
+        self._ck(self._L.ndtb_multi_run(self._h, len(tg), tp, tn, len(sc), sp, sn, stride, n, _p(it), _p(isrc), _p(G), _p(res)))
+        return res
+
+    def stats(self):
+        d = len(self.devices)
+        items, targets = np.zeros(d, np.int32), np.zeros(d, np.int32)
+        dev_ms, wall_ms = np.zeros(d), np.zeros(d)
+        self._ck(self._L.ndtb_multi_get_stats(self._h, _p(items), _p(targets), _p(dev_ms), _p(wall_ms)))
+        return dict(items=items, targets=targets, device_ms=dev_ms, wall_ms=wall_ms)
