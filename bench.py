@@ -593,7 +593,7 @@ def roofline_block(agg, ms_total, clocks, K=7, sm_count=148, shared_tables=True)
 
 def c5_line(a, world, mode, value, e2e, M, agg, clocks, job, n_per_step):
     ms, steps = M["ms"], a.steps
-    rf = roofline_block(agg, ms)
+    rf = roofline_block(agg, ms, clocks)
     ae = M["agg_e2e"]
     return {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": a.warmup,
             "ms_per_step": ms / steps, "higher_is_better": True, "scaling": mode, "vs_baseline": None,

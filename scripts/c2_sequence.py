@@ -13,6 +13,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+from oracle import ref_examples  # noqa: E402
 from xchu_slam_b200 import build, synth  # noqa: E402
 
 
@@ -34,7 +35,7 @@ def main():
     os.makedirs(tmp, exist_ok=True)
     build.build_cuda()
     exe = build.build_examples()
-    ref_exe = build.build_example_reference()
+    ref_exe = ref_examples.build_example_reference()
     seq = synth.write_sequence(os.path.join(tmp, "seq%d.bin" % n_scans), n_scans=n_scans, n_points=20000)
     out = {"config": "C2: %d-scan synthetic sequence (20k-pt scans, ~0.86 m/scan), NDT res %s, DIRECT7, eps 0.01, <= 30 iterations, "
                      "localmap window 5 m, keyframe every >= 0.5 m" % (n_scans, res)}

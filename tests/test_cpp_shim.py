@@ -71,8 +71,9 @@ def test_same_caller_two_backends_same_trajectory(exe, tmp_path, strategy):
     fitness scores within 1e-9 relative (exact 1-NN on both sides, f64 mean).
     The factorised kernel (--fast, 1e-6 per evaluation) is held to the north-star gate per align instead: it tracks the
     reference within 1e-4 m / 1e-5 rad until the first voxel-membership flip of the localmap feedback loop."""
+    from oracle import ref_examples
     from xchu_slam_b200 import build, synth
-    ref_exe = build.build_example_reference()
+    ref_exe = ref_examples.build_example_reference()
     if ref_exe is None:
         pytest.skip("examples/odom_sequence_ref not built (needs /root/reference)")
     seq = synth.write_sequence(str(tmp_path / "seq.bin"), n_scans=60, n_points=20000)
@@ -117,9 +118,10 @@ def test_device_localmap_mode_gives_the_same_odometry(exe, tmp_path):
 
 # ---- include/scancontext/Scancontext.h: the SCManager drop-in ------------------------------------
 def _sc_exes():
+    from oracle import ref_examples
     from xchu_slam_b200 import build
     build.build_cuda()
-    return build.build_sc_example(), build.build_sc_example_reference()
+    return build.build_sc_example(), ref_examples.build_sc_example_reference()
 
 
 def test_sc_shim_compiles_and_fails_loudly_without_gpu(tmp_path):

@@ -93,46 +93,11 @@ def build_sc_example(force=False):
     return exe
 
 
-REFERENCE_INCLUDE = "/root/reference/xchu_mapping/include"
-
-
-def build_example_reference(force=False):
-    """TEST INFRASTRUCTURE: the same odom_sequence.cpp compiled against the REFERENCE'S OWN pclomp headers (over the
-    stand-in Eigen/PCL headers of oracle/ref_stubs/) -> examples/odom_sequence_ref, the CPU arm of config C2 and the
-    trajectory oracle of the drop-in header.  Built only where /root/reference exists; the binary travels to the GPU box.
-    Returns the path, or None when it is neither buildable nor prebuilt."""
-    src = os.path.join(EXAMPLES, "odom_sequence.cpp")
-    exe = os.path.join(EXAMPLES, "odom_sequence_ref")
-    stubs = os.path.join(HERE, "..", "oracle", "ref_stubs")
-    if os.path.exists(os.path.join(REFERENCE_INCLUDE, "pclomp", "ndt_omp_impl.hpp")):
-        deps = [src] + [os.path.join(d, f) for d, _, fs in os.walk(stubs) for f in fs] + [os.path.join(HERE, "..", "oracle", "thirdparty_math.h")]
-        if force or _stale(exe, deps):
-            subprocess.check_call(["g++", "-std=c++17", "-O2", "-fopenmp", "-ffp-contract=off", "-w", "-DODOM_USE_REFERENCE", "-I" + stubs,
-                                   "-I" + REFERENCE_INCLUDE, src, "-o", exe])
-    build_sc_example_reference(force)
-    return exe if os.path.exists(exe) else None
-
-
-def build_sc_example_reference(force=False):
-    """TEST INFRASTRUCTURE: sc_sequence.cpp compiled over the REFERENCE'S OWN scancontext/Scancontext.{h,cpp} (stand-in headers of
-    oracle/ref_stubs/) -> examples/sc_sequence_ref.  Built only where /root/reference exists; the binary travels to the GPU box."""
-    src = os.path.join(EXAMPLES, "sc_sequence.cpp")
-    exe = os.path.join(EXAMPLES, "sc_sequence_ref")
-    stubs = os.path.join(HERE, "..", "oracle", "ref_stubs")
-    if os.path.exists(os.path.join(REFERENCE_INCLUDE, "scancontext", "Scancontext.cpp")):
-        deps = [src] + [os.path.join(d, f) for d, _, fs in os.walk(stubs) for f in fs]
-        if force or _stale(exe, deps):
-            subprocess.check_call(["g++", "-std=c++17", "-O2", "-fopenmp", "-ffp-contract=off", "-w", "-DSC_USE_REFERENCE", "-I" + stubs,
-                                   "-I" + REFERENCE_INCLUDE, src, "-o", exe])
-    return exe if os.path.exists(exe) else None
-
-
 def build_all(force=False, verbose=False):
     from . import synth
     synth.build(force)
     lib = build_cuda(force, verbose)
     build_examples(force)
-    build_example_reference(force)
     return lib
 
 

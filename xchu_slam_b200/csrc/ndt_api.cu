@@ -771,7 +771,11 @@ struct Engine {
         // last Newton step far below the step clamp (eps / 2): the final move is eps / 2 along delta_p / |delta_p|, a direction
         // that a difference of ~1e-6 in delta_p (one voxel flip of one point) turns by 1e-6 / |delta_p|
         const bool tiny_last = st.last_norm < min_norm;
-        const bool again = !st.done || !st.converged || st.borderline || tiny_last || (k_iters > 0 && st.nr_iterations > k_iters) || st.n_rise >= k_rise;
+        // fewer source points than unknowns: every point adds rank <= 3 to H, the 6x6 solve is (nearly) rank-deficient and
+        // amplifies the factorised kernel's 1e-7 differences by the condition number (the one-point source of the edge tests)
+        const bool underdetermined = st.n_src < 6;
+        const bool again = !st.done || !st.converged || st.borderline || tiny_last || underdetermined ||
+                           (k_iters > 0 && st.nr_iterations > k_iters) || st.n_rise >= k_rise;
         if (!again || st.n_src <= 0) continue;
         idx[n_replay++] = i;
         replay_flag[i] = 1;

@@ -662,10 +662,11 @@ __device__ __forceinline__ void sums_roles(int lane, int& ia, int& ib) {
     if (lane == k) { ia = ra[k]; ib = rb[k]; }
 }
 __device__ __forceinline__ float pick4(const float4 p, int i) { return i == 0 ? p.x : (i == 1 ? p.y : (i == 2 ? p.z : 1.f)); }
-__device__ __forceinline__ void sums_add(VoxelSums& a, int lane, int ia, int ib, const float4 p) {
+// Both chains advance in every lane (a lane keeps the one its role names): no divergent branch inside the per-point loop.
+__device__ __forceinline__ void sums_add(VoxelSums& a, int ia, int ib, const float4 p) {
   const float fa = pick4(p, ia), fb = pick4(p, ib);
-  if (lane < 9) a.d = __dadd_rn(a.d, __dmul_rn((double)fa, (double)fb));
-  else a.f = __fadd_rn(a.f, fa);
+  a.d = __dadd_rn(a.d, __dmul_rn((double)fa, (double)fb));
+  a.f = __fadd_rn(a.f, fa);
 }
 __device__ __forceinline__ void sums_store(const VoxelSums& a, int lane, const VoxelTable& t, int v) {
   if (lane < 3) t.vsum[(size_t)v * 3 + lane] = a.d;
@@ -678,7 +679,9 @@ __device__ __forceinline__ unsigned long long cell_to_key(int cell, const VoxelT
   return pack_key(a + t.dlo[0], b + t.dlo[1], c + t.dlo[2]);
 }
 
-// warp per voxel (population <= kWarpVoxelCap)
+// warp per voxel (population <= kWarpVoxelCap).  Up to 32 points (three voxels in four): every lane fetches its index and
+// its point at once, ranks the index among the warp's by 32 shuffles and drops the point at its rank in shared memory -- one
+// round trip to memory, no sorting network.  Larger voxels sort their indices with a bitonic network in shared memory first.
 __global__ void __launch_bounds__(128) k_cs_merge(const float4* __restrict__ pts, unsigned int* __restrict__ sorted_idx, const int* __restrict__ v_start,
                                                   const int* __restrict__ v_cnt, const int* __restrict__ v_cell, int n_vox, VoxelTable t,
                                                   int* __restrict__ big_list, int* __restrict__ big_count) {
@@ -693,8 +696,29 @@ __global__ void __launch_bounds__(128) k_cs_merge(const float4* __restrict__ pts
     if (lane == 0) big_list[atomicAdd(big_count, 1)] = v;
     return;
   }
+  VoxelSums acc;
+  sums_init(acc, lane);
+  int ia, ib;
+  sums_roles(lane, ia, ib);
+  float4* sp = s_pts[warp];
+  if (n <= 32) {
+    const unsigned int mine = lane < n ? sorted_idx[start + lane] : 0xFFFFFFFFu;
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (lane < n) p = __ldg(pts + mine);
+    int rank = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) rank += __shfl_sync(0xffffffffu, mine, j) < mine ? 1 : 0;   // indices are distinct
+    if (lane < n) { sp[rank] = p; sorted_idx[start + rank] = mine; }
+    __syncwarp();
+    if (lane < 12) {
+#pragma unroll 4
+      for (int k = 0; k < n; ++k) sums_add(acc, ia, ib, sp[k]);
+    }
+    sums_store(acc, lane, t, v);
+    return;
+  }
   unsigned int* idx = s_idx[warp];
-  int m = 32;
+  int m = 64;
   while (m < n) m <<= 1;
   for (int k = lane; k < m; k += 32) idx[k] = k < n ? sorted_idx[start + k] : 0xFFFFFFFFu;
   __syncwarp();
@@ -710,22 +734,18 @@ __global__ void __launch_bounds__(128) k_cs_merge(const float4* __restrict__ pts
       }
       __syncwarp();
     }
-  // the sorted order is what every later reader of this voxel's points wants too (incremental appends never look back, but the
-  // debug dumps and the big-voxel kernel share the buffer): write it back
+  // the sorted order is what every later reader of this voxel's points wants too (the debug dumps share the buffer): write it back
   for (int k = lane; k < n; k += 32) sorted_idx[start + k] = idx[k];
-  VoxelSums acc;
-  sums_init(acc, lane);
-  int ia, ib;
-  sums_roles(lane, ia, ib);
-  float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (lane < n) nxt = __ldg(pts + idx[lane]);
+  float4 nxt = __ldg(pts + idx[lane]);
   for (int base = 0; base < n; base += 32) {
-    s_pts[warp][lane] = nxt;
+    sp[lane] = nxt;
     __syncwarp();
     if (base + 32 + lane < n) nxt = __ldg(pts + idx[base + 32 + lane]);
     const int cnt = min(32, n - base);
-    if (lane < 12)
-      for (int k = 0; k < cnt; ++k) sums_add(acc, lane, ia, ib, s_pts[warp][k]);
+    if (lane < 12) {
+#pragma unroll 4
+      for (int k = 0; k < cnt; ++k) sums_add(acc, ia, ib, sp[k]);
+    }
     __syncwarp();
   }
   sums_store(acc, lane, t, v);
@@ -767,7 +787,7 @@ __global__ void __launch_bounds__(256) k_cs_merge_big(const float4* __restrict__
       __syncthreads();
       const int cnt = min(256, n - base);
       if (threadIdx.x < 12)
-        for (int k = 0; k < cnt; ++k) sums_add(acc, threadIdx.x, ia, ib, s_pts[k]);
+        for (int k = 0; k < cnt; ++k) sums_add(acc, ia, ib, s_pts[k]);
     }
     if (threadIdx.x < 12) sums_store(acc, threadIdx.x, t, v);
     __syncthreads();
@@ -871,6 +891,10 @@ static cudaError_t table_build_counting(TableStorage& ts, BuildWorkspace* ws, co
   }
   CK(table_reserve(ts, (size_t)n_vox, s, launches));
   if (n_vox > 0) {
+    // 10 KB of static shared memory per 4-voxel block: ask for the large carve-out, or the default split keeps one or two
+    // blocks per SM resident and the kernel runs at a fraction of its occupancy
+    static const cudaError_t carve = cudaFuncSetAttribute(k_cs_merge, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    (void)carve;
     CK(cudaMemsetAsync(ws->counts + 1, 0, sizeof(int), s));     // [1] = big voxels listed by k_cs_merge
     k_cs_merge<<<(unsigned)((n_vox + 3) / 4), 128, 0, s>>>(pts, ws->idx_out, v_start, v_cnt, v_cell, n_vox, t, big_list, ws->counts + 1);
     L += 2;
