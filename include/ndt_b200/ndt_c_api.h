@@ -119,6 +119,13 @@ int ndtb_num_voxels(ndtb_handle* h, size_t* n_all);  /* all occupied voxels (any
  * derivative kernel reads it (f32, row-major 3x3), f32 centroid (VGC_I:242-243, 289). */
 int ndtb_dump_voxels(ndtb_handle* h, int* ijk, int* nr_points, int* n_raw, double* mean, float* icov,
                      float* centroid);
+
+/* Leaf::icov_ as the device holds it in f64 (VGC_H:213 getInverseCov; the kernels of computeHessian / calculateScore read this
+ * copy, the derivative kernels its float rounding), [n_all][9] row-major, same voxel order as ndtb_dump_voxels. */
+int ndtb_dump_icov64(ndtb_handle* h, double* icov);
+/* NormalDistributionsTransform::convertTransform (NDT_H:210-229): [x y z roll pitch yaw] -> column-major float 4x4,
+ * Translation * AngleAxis(X) * AngleAxis(Y) * AngleAxis(Z) in float, the chain the device uses.  Host only, no device call. */
+void ndtb_pose_to_matrix(const double p[6], float T[16]);
 /* Neighbour voxels (VGC_I:373-442 / VGC_H:470-499) of n already transformed xyz points;
  * cnt[n], ijk[n][27][3] in visiting order. */
 int ndtb_neighbors(ndtb_handle* h, const float* xyz, size_t n, int method, int* cnt, int* ijk);
@@ -170,11 +177,12 @@ int ndtb_localmap_download(ndtb_handle* h, int which, void* pts, size_t cap, siz
  * ODOM:783-784) and handed to setInputTarget (ODOM:786-791) -- a NON-prefix cloud at every refresh, i.e. a full voxel-table
  * build at keyframe rate.  The clouds stay in HBM; which keyframes are in the window (recent_keyframes_, a deque the caller
  * pushes and pops, including the reference's `static latest_frame_id` quirk) stays the caller's business: it holds ids. */
-/* tf_cloud = downSizeFilterLocalmap(T * current source) kept on the device; *id names it (ids count up from 0, never reused).
+/* tf_cloud = downSizeFilterLocalmap(T * current source) kept on the device; *id names it (ids count up from 0; an id is not reused until
+ * ndtb_window_clear, which drops every cloud and restarts the count at 0).
  * leaf <= 0: no downsample.  *n_points (may be NULL) = its size. */
 int ndtb_window_add_source(ndtb_handle* h, const float T[16], float leaf, int* id, size_t* n_points);
 int ndtb_window_drop(ndtb_handle* h, int id);      /* the cloud leaves recent_keyframes_ for good */
-int ndtb_window_clear(ndtb_handle* h);
+int ndtb_window_clear(ndtb_handle* h);             /* every cloud dropped, ids restart at 0 */
 /* pc_target_ = the listed clouds concatenated in the order given, downsampled at `leaf` (<= 0: not), setInputTarget(pc_target_).
  * *n_target (may be NULL) = points of pc_target_. */
 int ndtb_window_set_target(ndtb_handle* h, const int* ids, int n_ids, float leaf, size_t* n_target);

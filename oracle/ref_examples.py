@@ -50,3 +50,23 @@ def build_sc_example_reference(force=False):
     return exe if os.path.exists(exe) else None
 
 
+
+
+def build_shim_pcl_mode(force=False):
+    """TEST INFRASTRUCTURE: tests/cpp/shim_pcl_mode.cpp -- include/pclomp/ndt_omp.h in its PCL build (derived from
+    pcl::Registration), compiled over the stand-in PCL / Eigen headers of oracle/ref_stubs (whose kd-tree stand-in wraps the
+    reference's nanoflann, hence the reference include path) and linked to libndt_b200.so -> examples/shim_pcl_mode.
+    Built only where /root/reference exists; the binary travels to the GPU box."""
+    root = os.path.join(HERE, "..")
+    src = os.path.join(root, "tests", "cpp", "shim_pcl_mode.cpp")
+    exe = os.path.join(EXAMPLES, "shim_pcl_mode")
+    stubs = os.path.join(HERE, "ref_stubs")
+    libdir = os.path.join(root, "xchu_slam_b200")
+    hdr = os.path.join(root, "include", "pclomp", "ndt_omp.h")
+    if os.path.exists(os.path.join(REFERENCE_INCLUDE, "scancontext", "nanoflann.hpp")):
+        deps = [src, hdr, os.path.join(root, "include", "ndt_b200", "ndt_c_api.h")]
+        if force or _stale(exe, deps):
+            subprocess.check_call(["g++", "-std=c++17", "-O2", "-w", "-I" + os.path.join(root, "include"), "-I" + stubs,
+                                   "-I" + REFERENCE_INCLUDE, src, "-o", exe, "-L" + libdir, "-lndt_b200",
+                                   "-Wl,-rpath,$ORIGIN/../xchu_slam_b200"])
+    return exe if os.path.exists(exe) else None

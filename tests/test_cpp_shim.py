@@ -55,6 +55,46 @@ def test_odometry_sequence_tracks_ground_truth_and_refreshes_incrementally(exe, 
     assert np.array_equal(a[:, 4:10], b[:, 4:10])
 
 
+def _pcl_mode_exe():
+    from oracle import ref_examples
+    exe = ref_examples.build_shim_pcl_mode()
+    if exe is None:
+        pytest.skip("neither /root/reference (to build it) nor a prebuilt examples/shim_pcl_mode")
+    return exe
+
+
+def test_header_in_pcl_build_derives_from_registration_and_converts_transforms(exe):
+    """include/pclomp/ndt_omp.h compiled in its PCL build (over the stand-in PCL headers): the static_assert in
+    tests/cpp/shim_pcl_mode.cpp holds (derived from pcl::Registration, NDT_H:70-71) and both static convertTransform overloads
+    (NDT_H:210-229) give the oracle's float chain bit for bit -- no device involved."""
+    from oracle import oracle
+    r = subprocess.run([_pcl_mode_exe(), "--static-only"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    got = [float(v) for v in r.stdout.split()[1:5]]
+    T = oracle.pose_to_matrix(np.array([1.0, 2.0, 3.0, 0.1, -0.2, 0.3]))
+    want = [T[0, 0], T[1, 0], T[2, 1], T[0, 3]]
+    assert [np.float32(g) for g in got] == [np.float32(w) for w in want]
+
+
+def test_convert_transform_host_entry_matches_oracle():
+    """ndtb_pose_to_matrix (host only) against the oracle's restatement of the Eigen float chain, bit-exact over random poses."""
+    from oracle import oracle
+    from xchu_slam_b200 import ndt
+    rng = np.random.default_rng(5)
+    for _ in range(200):
+        p = np.concatenate([rng.uniform(-50, 50, 3), rng.uniform(-3.2, 3.2, 3)])
+        assert np.array_equal(ndt.NormalDistributionsTransform.convertTransform(p), oracle.pose_to_matrix(p))
+
+
+@pytest.mark.gpu
+def test_align_through_registration_base_pointer(exe):
+    """The PCL build of the header driven through a pcl::Registration pointer: the base's setters and align() reach the device
+    (virtual setInputTarget / setInputSource / computeTransformation), and calculateScore(cloud) == calculateScore(T)."""
+    r = subprocess.run([_pcl_mode_exe()], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "base-pointer align" in r.stdout
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("strategy", ["distance", "surround"])
 def test_same_caller_two_backends_same_trajectory(exe, tmp_path, strategy):

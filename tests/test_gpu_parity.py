@@ -57,6 +57,10 @@ def _compare_voxels(o, g, rtol_mean=1e-12, rtol_icov=1e-10):
     scale = np.max(np.abs(ico), axis=(1, 2), keepdims=True)
     # GPU record stores float(icov): compare against the oracle's icov rounded the same way, then in relative terms
     assert np.max(np.abs(ico.astype(np.float32).astype(np.float64) - icg) / scale) < 2e-7
+    # the f64 inverse the device keeps for computeHessian / calculateScore (1e-10 relative)
+    ic64 = lg["icov64"][sg][valid]
+    assert np.max(np.abs(ico - ic64) / scale) < rtol_icov
+    assert np.array_equal(ic64.astype(np.float32), lg["icov"][sg][valid])     # the f32 record is its rounding
     return lo, lg, so, sg
 
 

@@ -1165,6 +1165,18 @@ int ndtb_dump_voxels(ndtb_handle* h, int* ijk, int* nr_points, int* n_raw, doubl
   return 0;
 }
 
+int ndtb_dump_icov64(ndtb_handle* h, double* icov) {
+  Engine& e = h->e;
+  cudaSetDevice(e.device);
+  Target& t = e.targets[0];
+  const size_t n = t.ts.valid ? (size_t)t.ts.n_vox : 0;
+  if (n == 0) return 0;
+  if (cudaMemcpy(icov, t.ts.t.icov64, n * 9 * sizeof(double), cudaMemcpyDeviceToHost) != cudaSuccess) return e.fail("dump copy failed");
+  return 0;
+}
+
+void ndtb_pose_to_matrix(const double p[6], float T[16]) { pose_to_matrix_host(p, T); }
+
 int ndtb_neighbors(ndtb_handle* h, const float* xyz, size_t n, int method, int* cnt, int* ijk) {
   Engine& e = h->e;
   cudaSetDevice(e.device);

@@ -343,13 +343,17 @@ __global__ void __launch_bounds__(128) k_hessian_f64(const AlignState* __restric
 // ---------------------------------------------------------------------------------------
 // pose helpers (float; Eigen::Translation * AngleAxis(x) * AngleAxis(y) * AngleAxis(z))
 // ---------------------------------------------------------------------------------------
-__device__ void angle_axis_matrix(float angle, int axis_id, float R[3][3]) {
+__host__ __device__ void angle_axis_matrix(float angle, int axis_id, float R[3][3]) {
   // Eigen AngleAxis<float>::toRotationMatrix() for a unit coordinate axis; sinf/cosf evaluated in
   // double and rounded (the libm-independent definition shared with the oracle)
   float ax[3] = {0.f, 0.f, 0.f};
   ax[axis_id] = 1.f;
+#ifdef __CUDA_ARCH__
   double sd, cd;
   sincos((double)angle, &sd, &cd);
+#else
+  const double sd = std::sin((double)angle), cd = std::cos((double)angle);
+#endif
   const float s = (float)sd, c = (float)cd;
   const float sa[3] = {s * ax[0], s * ax[1], s * ax[2]};
   const float one_c = 1.f - c;
@@ -360,12 +364,12 @@ __device__ void angle_axis_matrix(float angle, int axis_id, float R[3][3]) {
   tmp = ca[1] * ax[2]; R[1][2] = tmp - sa[0]; R[2][1] = tmp + sa[0];
   for (int i = 0; i < 3; ++i) R[i][i] = ca[i] * ax[i] + c;
 }
-__device__ void mul3f(const float A[3][3], const float B[3][3], float C[3][3]) {
+__host__ __device__ void mul3f(const float A[3][3], const float B[3][3], float C[3][3]) {
   for (int i = 0; i < 3; ++i)
     for (int j = 0; j < 3; ++j) C[i][j] = (A[i][0] * B[0][j] + A[i][1] * B[1][j]) + A[i][2] * B[2][j];
 }
 // NDT_H:210-217, NDT_I:815-819: column-major float 4x4
-__device__ void pose_to_matrix(const double p[6], float T[16]) {
+__host__ __device__ void pose_to_matrix(const double p[6], float T[16]) {
   float Rx[3][3], Ry[3][3], Rz[3][3], Rxy[3][3], R[3][3];
   angle_axis_matrix((float)p[3], 0, Rx);
   angle_axis_matrix((float)p[4], 1, Ry);
@@ -378,6 +382,8 @@ __device__ void pose_to_matrix(const double p[6], float T[16]) {
   }
   T[12] = (float)p[0]; T[13] = (float)p[1]; T[14] = (float)p[2]; T[15] = 1.f;
 }
+
+void pose_to_matrix_host(const double p[6], float T[16]) { pose_to_matrix(p, T); }
 
 // computeAngleDerivatives (NDT_I:286-398)
 __device__ void angle_derivatives(const double p[6], EvalReq& rq) {

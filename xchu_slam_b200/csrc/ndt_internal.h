@@ -191,6 +191,8 @@ cudaError_t launch_prepare_eval(AlignState* st, const float* T16_dev, const doub
 cudaError_t launch_pull(void* dst_dev, const void* src_mapped_dev, size_t bytes, cudaStream_t s);
 cudaError_t launch_replan(AlignState* states, int n_items, int2* blockmap, int* plan_mapped_host, int target_blocks, cudaStream_t s);
 // states[idx[k]] = src_mapped[idx[k]] for k < n (selected registration states pulled out of mapped host memory)
+// host evaluation of the float pose chain the device uses (NDT_H:210-229)
+void pose_to_matrix_host(const double p[6], float T[16]);
 cudaError_t launch_pull_items(AlignState* states, const AlignState* src_mapped_dev, const int* idx_mapped_dev, int n, cudaStream_t s);
 cudaError_t launch_set_int(int* dst, int v, cudaStream_t s);
 cudaError_t launch_publish(const int* src_dev, int* dst_mapped_host, cudaStream_t s);

@@ -51,7 +51,7 @@ class BatchStats(C.Structure):
 # every symbol include/ndt_b200/ndt_c_api.h declares
 SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_params", "ndtb_set_params", "ndtb_get_params",
            "ndtb_set_target", "ndtb_set_target_auto", "ndtb_update_target", "ndtb_set_source", "ndtb_align", "ndtb_get_output",
-           "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_neighbors",
+           "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_dump_icov64", "ndtb_pose_to_matrix", "ndtb_neighbors",
            "ndtb_eval_derivatives", "ndtb_compute_hessian", "ndtb_get_trace", "ndtb_last_timing", "ndtb_batch_create",
            "ndtb_batch_destroy", "ndtb_batch_last_error", "ndtb_batch_set_params", "ndtb_batch_clear", "ndtb_batch_add_target",
            "ndtb_batch_add_source", "ndtb_batch_wait_uploads", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream", "ndtb_batch_fitness",
@@ -94,6 +94,9 @@ def load_library():
     L.ndtb_calculate_score.argtypes = [vp, vp, C.POINTER(C.c_double)]
     L.ndtb_num_voxels.argtypes = [vp, C.POINTER(sz)]
     L.ndtb_dump_voxels.argtypes = [vp] + [vp] * 6
+    L.ndtb_dump_icov64.argtypes = [vp, vp]
+    L.ndtb_pose_to_matrix.argtypes = [vp, vp]
+    L.ndtb_pose_to_matrix.restype = None
     L.ndtb_neighbors.argtypes = [vp, vp, sz, C.c_int, vp, vp]
     L.ndtb_eval_derivatives.argtypes = [vp, vp, vp, C.c_int, C.POINTER(C.c_double), vp, vp]
     L.ndtb_compute_hessian.argtypes = [vp, vp, vp, vp]
@@ -322,11 +325,21 @@ class NormalDistributionsTransform:
         self._ck(self._L.ndtb_num_voxels(self._h, C.byref(n)))
         n = n.value
         out = dict(ijk=np.zeros((n, 3), np.int32), nr_points=np.zeros(n, np.int32), n_raw=np.zeros(n, np.int32),
-                   mean=np.zeros((n, 3)), icov=np.zeros((n, 3, 3), np.float32), centroid=np.zeros((n, 3), np.float32))
+                   mean=np.zeros((n, 3)), icov=np.zeros((n, 3, 3), np.float32), centroid=np.zeros((n, 3), np.float32),
+                   icov64=np.zeros((n, 3, 3)))
         if n:
             self._ck(self._L.ndtb_dump_voxels(self._h, _p(out["ijk"]), _p(out["nr_points"]), _p(out["n_raw"]), _p(out["mean"]),
                                               _p(out["icov"]), _p(out["centroid"])))
+            self._ck(self._L.ndtb_dump_icov64(self._h, _p(out["icov64"])))
         return out
+
+    @staticmethod
+    def convertTransform(x):
+        """NDT_H:210-229 (static in the reference too): [x y z roll pitch yaw] -> 4x4 float, row/column indexable."""
+        x = np.ascontiguousarray(np.asarray(x, dtype=np.float64).reshape(6))
+        T = np.zeros(16, np.float32)
+        load_library().ndtb_pose_to_matrix(_p(x), _p(T))
+        return T.reshape(4, 4).T.copy()
 
     def neighbors(self, xyz, method=None):
         xyz = np.ascontiguousarray(np.asarray(xyz, dtype=np.float32)[:, :3])
