@@ -126,6 +126,10 @@ int ndtb_dump_icov64(ndtb_handle* h, double* icov);
 /* NormalDistributionsTransform::convertTransform (NDT_H:210-229): [x y z roll pitch yaw] -> column-major float 4x4,
  * Translation * AngleAxis(X) * AngleAxis(Y) * AngleAxis(Z) in float, the chain the device uses.  Host only, no device call. */
 void ndtb_pose_to_matrix(const double p[6], float T[16]);
+/* Page-locked host memory (cudaHostAlloc, portable across devices) for clouds handed to the upload entry points: pageable
+ * memory works too but is staged by the driver at a fraction of the link rate.  0 on success. */
+int ndtb_host_alloc(size_t bytes, void** out);
+int ndtb_host_free(void* p);
 /* Neighbour voxels (VGC_I:373-442 / VGC_H:470-499) of n already transformed xyz points;
  * cnt[n], ijk[n][27][3] in visiting order. */
 int ndtb_neighbors(ndtb_handle* h, const float* xyz, size_t n, int method, int* cnt, int* ijk);

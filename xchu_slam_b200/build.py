@@ -77,6 +77,18 @@ def build_examples(force=False):
         subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", src, "-o", exe, "-L" + HERE, "-lndt_b200",
                                "-Wl,-rpath,$ORIGIN/../xchu_slam_b200"])
     build_sc_example(force)
+    build_batch_pipeline(force)
+    return exe
+
+
+def build_batch_pipeline(force=False):
+    """examples/batch_pipeline.cpp: the batch entry points driven from C++ (two-stage upload / compute pipeline)."""
+    src = os.path.join(EXAMPLES, "batch_pipeline.cpp")
+    exe = os.path.join(EXAMPLES, "batch_pipeline")
+    deps = [src, LIB, os.path.join(HERE, "..", "include", "ndt_b200", "ndt_c_api.h")]
+    if force or _stale(exe, deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-pthread", src, "-o", exe, "-L" + HERE, "-lndt_b200",
+                               "-Wl,-rpath,$ORIGIN/../xchu_slam_b200"])
     return exe
 
 

@@ -96,6 +96,8 @@ struct Engine {
   }
   cudaEvent_t bstart = nullptr;
   cudaStream_t copy_stream = nullptr;      // batch uploads from host memory run here, overlapped with table builds
+  struct PackedStage { void* p = nullptr; size_t cap = 0; };
+  PackedStage stage_main, stage_copy;      // device landing zones of packed (12-byte) uploads, one per stream
   cudaEvent_t sources_uploaded = nullptr;
   bool sources_pending = false;
   std::string err;
@@ -222,6 +224,7 @@ struct Engine {
       if (bdone[g]) cudaEventDestroy(bdone[g]);
     }
     if (bstart) cudaEventDestroy(bstart);
+    cudaFree(stage_main.p); cudaFree(stage_copy.p);
     if (copy_stream) cudaStreamDestroy(copy_stream);
     if (sources_uploaded) cudaEventDestroy(sources_uploaded);
     targets.clear();
@@ -260,7 +263,21 @@ struct Engine {
       CKE(cudaMemcpyAsync(dst, pts, n * 16, kind, stream));
     } else if (stride > 16) {
       CKE(cudaMemcpy2DAsync(dst, 16, pts, stride, 16, n, kind, stream));
-    } else {  // packed xyz (12..15 bytes): widen on the way
+    } else if (stride == 12) {
+      // packed xyz: one contiguous copy (3/4 of the bytes of a 16-byte upload) into a staging buffer, widened by a kernel
+      // behind it on the same stream -- a 2-D copy of a million 12-byte rows runs at a fraction of the link rate
+      PackedStage& ps = (stream == copy_stream) ? stage_copy : stage_main;
+      if (n * 12 > ps.cap) {
+        CKE(cudaStreamSynchronize(stream));      // the buffer may still feed a widen kernel
+        cudaFree(ps.p);
+        ps.p = nullptr; ps.cap = 0;
+        const size_t nc = n * 12 + n * 3 + 4096;
+        CKE(cudaMalloc(&ps.p, nc));
+        ps.cap = nc;
+      }
+      CKE(cudaMemcpyAsync(ps.p, pts, n * 12, kind, stream));
+      CKE(launch_widen_xyz(static_cast<const float*>(ps.p), dst, n, stream));
+    } else {  // 13..15 bytes: widen on the way
       CKE(cudaMemsetAsync(dst, 0, n * 16, stream));
       CKE(cudaMemcpy2DAsync(dst, 16, pts, stride, 12, n, kind, stream));
     }
@@ -1176,6 +1193,12 @@ int ndtb_dump_icov64(ndtb_handle* h, double* icov) {
 }
 
 void ndtb_pose_to_matrix(const double p[6], float T[16]) { pose_to_matrix_host(p, T); }
+
+int ndtb_host_alloc(size_t bytes, void** out) {
+  *out = nullptr;
+  return cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable) == cudaSuccess ? 0 : 1;
+}
+int ndtb_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? 0 : 1; }
 
 int ndtb_neighbors(ndtb_handle* h, const float* xyz, size_t n, int method, int* cnt, int* ijk) {
   Engine& e = h->e;

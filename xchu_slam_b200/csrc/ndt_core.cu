@@ -1089,6 +1089,17 @@ cudaError_t launch_pull_items(AlignState* states, const AlignState* src_mapped_d
   k_pull_items<<<n, 64, 0, s>>>(states, src_mapped_dev, idx_mapped_dev, n);
   return cudaGetLastError();
 }
+// packed x y z records (12 bytes) -> the 16-byte records the kernels read (w = 0)
+__global__ void k_widen_xyz(const float* __restrict__ packed, float4* __restrict__ dst, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  dst[i] = make_float4(packed[i * 3], packed[i * 3 + 1], packed[i * 3 + 2], 0.f);
+}
+cudaError_t launch_widen_xyz(const float* packed_dev, float4* dst, size_t n, cudaStream_t s) {
+  if (n == 0) return cudaSuccess;
+  k_widen_xyz<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(packed_dev, dst, n);
+  return cudaGetLastError();
+}
 __global__ void k_set_int(int* dst, int v) { *dst = v; }
 cudaError_t launch_set_int(int* dst, int v, cudaStream_t s) {
   k_set_int<<<1, 1, 0, s>>>(dst, v);

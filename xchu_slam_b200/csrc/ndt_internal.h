@@ -195,6 +195,7 @@ cudaError_t launch_replan(AlignState* states, int n_items, int2* blockmap, int* 
 void pose_to_matrix_host(const double p[6], float T[16]);
 cudaError_t launch_pull_items(AlignState* states, const AlignState* src_mapped_dev, const int* idx_mapped_dev, int n, cudaStream_t s);
 cudaError_t launch_set_int(int* dst, int v, cudaStream_t s);
+cudaError_t launch_widen_xyz(const float* packed_dev, float4* dst, size_t n, cudaStream_t s);
 cudaError_t launch_publish(const int* src_dev, int* dst_mapped_host, cudaStream_t s);
 cudaError_t launch_prefix_equal(const float4* a, const float4* b, size_t n, int* flag, cudaStream_t s);
 

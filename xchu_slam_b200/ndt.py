@@ -51,7 +51,7 @@ class BatchStats(C.Structure):
 # every symbol include/ndt_b200/ndt_c_api.h declares
 SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_params", "ndtb_set_params", "ndtb_get_params",
            "ndtb_set_target", "ndtb_set_target_auto", "ndtb_update_target", "ndtb_set_source", "ndtb_align", "ndtb_get_output",
-           "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_dump_icov64", "ndtb_pose_to_matrix", "ndtb_neighbors",
+           "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_dump_icov64", "ndtb_pose_to_matrix", "ndtb_host_alloc", "ndtb_host_free", "ndtb_neighbors",
            "ndtb_eval_derivatives", "ndtb_compute_hessian", "ndtb_get_trace", "ndtb_last_timing", "ndtb_batch_create",
            "ndtb_batch_destroy", "ndtb_batch_last_error", "ndtb_batch_set_params", "ndtb_batch_clear", "ndtb_batch_add_target",
            "ndtb_batch_add_source", "ndtb_batch_wait_uploads", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream", "ndtb_batch_fitness",
@@ -97,6 +97,8 @@ def load_library():
     L.ndtb_dump_icov64.argtypes = [vp, vp]
     L.ndtb_pose_to_matrix.argtypes = [vp, vp]
     L.ndtb_pose_to_matrix.restype = None
+    L.ndtb_host_alloc.argtypes = [sz, C.POINTER(vp)]
+    L.ndtb_host_free.argtypes = [vp]
     L.ndtb_neighbors.argtypes = [vp, vp, sz, C.c_int, vp, vp]
     L.ndtb_eval_derivatives.argtypes = [vp, vp, vp, C.c_int, C.POINTER(C.c_double), vp, vp]
     L.ndtb_compute_hessian.argtypes = [vp, vp, vp, vp]
