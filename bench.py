@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--cpu-aligns", type=int, default=1024, help="aligns in the bounded CPU sample (~10 ms each on 16 cores)")
     ap.add_argument("--cpu-passes", type=int, default=4, help="the CPU sample is timed in this many passes: median / min / max")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpp-pipeline", action="store_true", help="skip the examples/batch_pipeline.cpp arm of the e2e number")
     ap.add_argument("--no-variants", action="store_true", help="skip value_strict / value_factorised_only / the other scaling mode")
     ap.add_argument("--strict-math", type=int, default=int(os.environ.get("NDTB_BENCH_STRICT", -1)),
                     help="-1 hybrid (library default for a batch), 0 factorised kernel only, 1 term-by-term kernel only")
@@ -525,6 +526,11 @@ def run_c5(a):
                             "note": "the job cut over the GPUs, results gathered over NCCL" if other == "strong" else
                                     "every GPU runs its own copy of the whole job (per-GPU work fixed)"}
 
+    # ---- the same job through examples/batch_pipeline.cpp: the end-to-end pipeline with no interpreter in the loop, 16-byte and
+    # packed 12-byte host records (rank 0, one GPU: it is a second process on this rank's device, run while this one is idle) ----
+    if rank == 0 and world == 1 and not a.no_cpp_pipeline:
+        extra["e2e_cpp"] = cpp_pipeline(a, w, jobs[main_mode], local)
+
     rc = 0
     if rank == 0:
         ms, agg = M["ms"], M["agg"]
@@ -558,6 +564,31 @@ def run_c5(a):
     if rc:
         sys.stderr.write("bench.py: GPU results outside the parity gate (see parity_vs_cpu_sample)\n")
         sys.exit(rc)
+
+
+def cpp_pipeline(a, w, job, device):
+    import subprocess
+    import tempfile
+    from xchu_slam_b200 import build, jobfile
+    out = {}
+    try:
+        exe = build.build_batch_pipeline()
+        tids, sids = sorted(set(int(t) for t in np.asarray(w["item_target"])[job.idx])), sorted(set(int(s) for s in np.asarray(w["item_source"])[job.idx]))
+        for stride in (16, 12):
+            with tempfile.TemporaryDirectory(prefix="ndtb_job_") as d:
+                path = jobfile.write_job(os.path.join(d, "job.bin"), [w["targets"][t] for t in tids], [w["sources"][s] for s in sids],
+                                         job.it, job.isrc, np.asarray(w["guesses"], dtype=np.float32)[job.idx], stride=stride)
+                r = subprocess.run([exe, path, "--steps", str(a.steps), "--warmup", str(max(2, a.warmup)), "--inflight", str(max(1, a.inflight_e2e)),
+                                    "--strict-math", str(a.strict_math), "--device", str(device)], capture_output=True, text=True, timeout=900)
+            if r.returncode != 0:
+                out["stride_%d" % stride] = {"error": r.stderr.strip()[-300:]}
+                continue
+            out["stride_%d" % stride] = json.loads(r.stdout.strip().splitlines()[-1])
+        out["note"] = ("examples/batch_pipeline.cpp over the C ABI: page-locked host clouds, two batches in flight, host clock around whole steps "
+                       "(uploads, table builds, registrations, results back); stride_12 = packed x y z records, 3/4 of the bytes")
+    except Exception as e:      # the C++ arm is an explanation of the e2e number, not the number: never fail the line for it
+        out["error"] = repr(e)[:300]
+    return out
 
 
 def roofline_block(agg, ms_total, clocks, K=7, sm_count=148, shared_tables=True):

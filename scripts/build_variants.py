@@ -10,6 +10,10 @@ sys.path.insert(0, ROOT)
 from xchu_slam_b200 import build as b  # noqa: E402
 
 VARIANTS = {
+    # strict (term-by-term) kernel: FP64 accumulators in shared memory, 128 registers, two blocks per SM (ncu r02: 241 registers,
+    # one block = 8 warps per SM, 59 % of cycles with no eligible warp)
+    "strict_smem": ("NDTB_STRICT_ACC_SMEM=1", "NDTB_MINBLOCKS=2"),
+    "strict_mb2": ("NDTB_MINBLOCKS=2",),
     # 64-B aligned voxel records, one 256-bit + one 128-bit load per (point, voxel) pair (ndt_internal.h, ndt_fast.cu)
     "rec64": ("NDTB_FAST_REC64=1",),
     # the same with the next point's seven cell codes fetched one iteration ahead

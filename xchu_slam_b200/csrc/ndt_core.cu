@@ -30,7 +30,16 @@ namespace ndtb {
 #ifndef NDTB_PREFETCH     // 1: fetch the next voxel record behind the current pair's math
 #define NDTB_PREFETCH 1
 #endif
+#ifndef NDTB_STRICT_ACC_SMEM   // 1: the 43 FP64 accumulators of a thread live in shared memory ([k][thread], conflict-free), which
+#define NDTB_STRICT_ACC_SMEM 0  //    takes 86 registers off the kernel -> two resident blocks per SM instead of one
+#endif
 constexpr int kThreads = NDTB_THREADS;
+#if NDTB_STRICT_ACC_SMEM
+constexpr int kAccStride = kThreads + 1;
+#define ACC(k) acc[(k) * kAccStride]
+#else
+#define ACC(k) acc[(k)]
+#endif
 
 struct EvalShared {
   float T[12];
@@ -83,7 +92,7 @@ __device__ __forceinline__ void pair_update_r(double* acc, const RecRegs& rr, fl
   e = d2f * e;                                                  // NDT_I:511
   if (e > 1.f || e < 0.f || e != e) return;                     // NDT_I:514-515 (score not counted either)
   e = (float)((double)e * d1);                                  // NDT_I:518
-  acc[0] += (double)score_inc;
+  ACC(0) += (double)score_inc;
   const float g13 = PGV(0), g23 = PGV(1), g04 = PGV(2), g14 = PGV(3), g24 = PGV(4), g05 = PGV(5), g15 = PGV(6), g25 = PGV(7);
   // CJ = c_inv4 * point_gradient4 (NDT_I:520); columns 0..2 are the columns of C
   float CJ[3][6];
@@ -98,7 +107,7 @@ __device__ __forceinline__ void pair_update_r(double* acc, const RecRegs& rr, fl
 #pragma unroll
   for (int c = 3; c < 6; ++c) xCJ[c] = (x0 * CJ[0][c] + x1 * CJ[1][c]) + x2 * CJ[2][c];   // NDT_I:521
 #pragma unroll
-  for (int c = 0; c < 6; ++c) acc[1 + c] += (double)(e * xCJ[c]);                          // NDT_I:523
+  for (int c = 0; c < 6; ++c) ACC(1 + c) += (double)(e * xCJ[c]);                          // NDT_I:523
   if (!CH) return;
   // xCH(i,j) = (x_trans4 * c_inv4) * point_hessian_.block<4,1>(4i, j)  (NDT_I:534-535); non-zero for i,j >= 3
   const float ha = xC1 * PHV(0) + xC2 * PHV(1);
@@ -123,7 +132,7 @@ __device__ __forceinline__ void pair_update_r(double* acc, const RecRegs& rr, fl
       float v = nda * xCJ[j];
       if (i >= 3 && j >= 3) v = v + xCH[i - 3][j - 3];
       v = v + jt;
-      acc[7 + i * 6 + j] += (double)(e * v);                                               // NDT_I:539-542
+      ACC(7 + i * 6 + j) += (double)(e * v);                                               // NDT_I:539-542
     }
   }
 }
@@ -156,10 +165,39 @@ __device__ __forceinline__ void block_reduce_store(const double* acc, int npairs
     out[tid] = v;
   }
 }
+#if NDTB_STRICT_ACC_SMEM
+// The same reduction when the accumulators already sit in shared memory as [k][thread]: lane k of every warp adds the warp's 32
+// columns of row k in lane order, then 44 threads add the warps in warp order -- the additions of block_reduce_store, one for one.
+__device__ __forceinline__ void block_reduce_store_resident(int npairs, double* __restrict__ out) {
+  extern __shared__ double red_sm[];                 // [44][kAccStride] + [warps][44]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+  red_sm[kAccN * kAccStride + tid] = (double)npairs;
+  __syncthreads();
+  double* wsum = red_sm + (size_t)kPartialStride * kAccStride;
+  for (int k = lane; k < kPartialStride; k += 32) {
+    const double* row = red_sm + (size_t)k * kAccStride + warp * 32;
+    double v = 0;
+#pragma unroll 8
+    for (int l = 0; l < 32; ++l) v += row[l];
+    wsum[warp * kPartialStride + k] = v;
+  }
+  __syncthreads();
+  if (tid < kPartialStride) {
+    double v = 0;
+    for (int w = 0; w < nwarps; ++w) v += wsum[w * kPartialStride + tid];
+    out[tid] = v;
+  }
+}
+static size_t reduce_smem_bytes(int threads) {
+  const int nw = threads / 32;
+  return ((size_t)kPartialStride * (threads + 1) + (size_t)nw * kPartialStride) * sizeof(double);
+}
+#else
 static size_t reduce_smem_bytes(int threads) {
   const int nw = threads / 32;
   return ((size_t)nw * kPartialStride * kRedPad + (size_t)nw * kPartialStride) * sizeof(double);
 }
+#endif
 
 template <int METHOD, bool CH>
 __global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const AlignState* __restrict__ states, const VoxelTable* __restrict__ tables,
@@ -183,9 +221,14 @@ __global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const 
     sh.tab = tables[st.target];
   }
   __syncthreads();
+#if NDTB_STRICT_ACC_SMEM
+  extern __shared__ double red_sm[];
+  double* acc = red_sm + tid;
+#else
   double acc[kAccN];
+#endif
 #pragma unroll
-  for (int k = 0; k < kAccN; ++k) acc[k] = 0.0;
+  for (int k = 0; k < kAccN; ++k) ACC(k) = 0.0;
   int npairs = 0;
   const float4* __restrict__ src = st.src;
   const int end = min(bm.y + chunk, st.n_src);
@@ -234,7 +277,11 @@ __global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const 
 #endif
     npairs += cnt;
   }
+#if NDTB_STRICT_ACC_SMEM
+  block_reduce_store_resident(npairs, partials + (size_t)blockIdx.x * kPartialStride);
+#else
   block_reduce_store(acc, npairs, partials + (size_t)blockIdx.x * kPartialStride);
+#endif
 }
 
 // ---------------------------------------------------------------------------------------
@@ -939,6 +986,11 @@ static cudaError_t launch_deriv_m(const AlignState* states, const VoxelTable* ta
   if (!(configured.load(std::memory_order_acquire) & bit)) {
     cudaFuncSetAttribute(k_derivatives<METHOD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
     cudaFuncSetAttribute(k_derivatives<METHOD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+#if NDTB_STRICT_ACC_SMEM
+    // two 93 KB blocks per SM: ask for the large shared-memory carve-out
+    cudaFuncSetAttribute(k_derivatives<METHOD, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(k_derivatives<METHOD, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+#endif
     configured.fetch_or(bit, std::memory_order_release);
   }
   k_derivatives<METHOD, true><<<n_blocks, kThreads, sm, s>>>(states, tables, src_pool, blockmap, chunk, partials);

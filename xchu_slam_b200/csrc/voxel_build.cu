@@ -679,75 +679,113 @@ __device__ __forceinline__ unsigned long long cell_to_key(int cell, const VoxelT
   return pack_key(a + t.dlo[0], b + t.dlo[1], c + t.dlo[2]);
 }
 
-// warp per voxel (population <= kWarpVoxelCap).  Up to 32 points (three voxels in four): every lane fetches its index and
-// its point at once, ranks the index among the warp's by 32 shuffles and drops the point at its rank in shared memory -- one
-// round trip to memory, no sorting network.  Larger voxels sort their indices with a bitonic network in shared memory first.
+// Bitonic sort of R * 32 keys held in registers, key (r * 32 + lane) in v[r], ascending.  Exchanges at a distance of 32 or more
+// stay inside a lane (register to register, direction known at compile time); closer ones are one shuffle + min / max.
+template <int R>
+__device__ __forceinline__ void warp_bitonic(unsigned int (&v)[R], int lane) {
+  constexpr int M = R * 32;
+#pragma unroll
+  for (int size = 2; size <= M; size <<= 1) {
+#pragma unroll
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      if (stride >= 32) {
+        const int rs = stride >> 5;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          if ((r & rs) == 0) {
+            const bool up = ((r << 5) & size) == 0;          // size >= 64: the bit is one of r's
+            const unsigned int a = v[r], b = v[r | rs];
+            const unsigned int mn = min(a, b), mx = max(a, b);
+            v[r] = up ? mn : mx;
+            v[r | rs] = up ? mx : mn;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          const unsigned int other = __shfl_xor_sync(0xffffffffu, v[r], stride);
+          const bool up = ((((r << 5) + lane) & size) == 0);
+          const bool lower = (lane & stride) == 0;
+          const unsigned int mn = min(v[r], other), mx = max(v[r], other);
+          v[r] = (lower == up) ? mn : mx;
+        }
+      }
+    }
+  }
+}
+
+constexpr int kSumRow = 33;     // doubles per row of a warp's staging tile: rows land in different banks for the role-indexed reads
+struct MergeTile {
+  double d[4][kSumRow];         // x, y, z of 32 points widened to f64 (once per point, not once per sum), and a row of ones
+  float f[3][kSumRow];          // x, y, z as they are, for the f32 centroid sums
+};
+
+// One voxel of up to R * 32 points by one warp: indices sorted in registers, points fetched a warp-wide tile at a time (the next
+// tile in flight behind the current one's additions), twelve lanes carrying the twelve running sums in the reference's order.
+template <int R>
+__device__ __forceinline__ void merge_voxel(const float4* __restrict__ pts, unsigned int* __restrict__ sorted_idx, int start, int n, int lane,
+                                            MergeTile& tile, int ia, int ib, int fr, double& sum_d, float& sum_f) {
+  unsigned int v[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int k = (r << 5) + lane;
+    v[r] = k < n ? sorted_idx[start + k] : 0xFFFFFFFFu;
+  }
+  warp_bitonic<R>(v, lane);
+  float4 nxt = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (lane < n) nxt = __ldg(pts + v[0]);
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int base = r << 5;
+    if (base < n) {                                   // warp-uniform
+      const float4 p = nxt;
+      if (r + 1 < R && base + 32 + lane < n) nxt = __ldg(pts + v[r + 1 < R ? r + 1 : r]);
+      if (base + lane < n) sorted_idx[start + base + lane] = v[r];     // later readers of the voxel's points (appends, dumps) want input order
+      tile.d[0][lane] = (double)p.x; tile.d[1][lane] = (double)p.y; tile.d[2][lane] = (double)p.z;
+      tile.f[0][lane] = p.x; tile.f[1][lane] = p.y; tile.f[2][lane] = p.z;
+      __syncwarp();
+      const int cnt = min(32, n - base);
+      if (lane < 12) {
+        const double* da = tile.d[ia];
+        const double* db = tile.d[ib];
+        const float* fa = tile.f[fr];
+#pragma unroll 4
+        for (int k = 0; k < cnt; ++k) {
+          sum_d = __dadd_rn(sum_d, __dmul_rn(da[k], db[k]));   // the product of two widened floats is exact; x * 1.0 is x
+          sum_f = __fadd_rn(sum_f, fa[k]);
+        }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// warp per voxel (population <= kWarpVoxelCap)
 __global__ void __launch_bounds__(128) k_cs_merge(const float4* __restrict__ pts, unsigned int* __restrict__ sorted_idx, const int* __restrict__ v_start,
-                                                  const int* __restrict__ v_cnt, const int* __restrict__ v_cell, int n_vox, VoxelTable t,
-                                                  int* __restrict__ big_list, int* __restrict__ big_count) {
-  __shared__ unsigned int s_idx[4][kWarpVoxelCap];
-  __shared__ float4 s_pts[4][32];
+                                                  const int* __restrict__ v_cnt, int n_vox, VoxelTable t, int* __restrict__ big_list,
+                                                  int* __restrict__ big_count) {
+  __shared__ MergeTile s_tile[4];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int v = blockIdx.x * 4 + warp;
   if (v >= n_vox) return;
   const int start = v_start[v], n = v_cnt[v];
-  if (lane == 0) { t.vkey[v] = cell_to_key(v_cell[v], t); t.vn[v] = n; }
   if (n > kWarpVoxelCap) {
     if (lane == 0) big_list[atomicAdd(big_count, 1)] = v;
     return;
   }
-  VoxelSums acc;
-  sums_init(acc, lane);
+  MergeTile& tile = s_tile[warp];
+  tile.d[3][lane] = 1.0;
+  // lanes 0-2: sum x (x_a * 1); 3-8: Identity + sum xx^T (xx xy xz yy yz zz); 9-11: f32 centroid sum (their f64 chain is idle work)
   int ia, ib;
   sums_roles(lane, ia, ib);
-  float4* sp = s_pts[warp];
-  if (n <= 32) {
-    const unsigned int mine = lane < n ? sorted_idx[start + lane] : 0xFFFFFFFFu;
-    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (lane < n) p = __ldg(pts + mine);
-    int rank = 0;
-#pragma unroll
-    for (int j = 0; j < 32; ++j) rank += __shfl_sync(0xffffffffu, mine, j) < mine ? 1 : 0;   // indices are distinct
-    if (lane < n) { sp[rank] = p; sorted_idx[start + rank] = mine; }
-    __syncwarp();
-    if (lane < 12) {
-#pragma unroll 4
-      for (int k = 0; k < n; ++k) sums_add(acc, ia, ib, sp[k]);
-    }
-    sums_store(acc, lane, t, v);
-    return;
-  }
-  unsigned int* idx = s_idx[warp];
-  int m = 64;
-  while (m < n) m <<= 1;
-  for (int k = lane; k < m; k += 32) idx[k] = k < n ? sorted_idx[start + k] : 0xFFFFFFFFu;
-  __syncwarp();
-  // bitonic sort of m (a power of two) indices, ascending
-  for (int size = 2; size <= m; size <<= 1)
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      for (int k = lane; k < (m >> 1); k += 32) {
-        const int lo = 2 * k - (k & (stride - 1));      // index with bit `stride` clear
-        const int hi = lo + stride;
-        const bool up = (lo & size) == 0;
-        const unsigned int x = idx[lo], y = idx[hi];
-        if ((x > y) == up) { idx[lo] = y; idx[hi] = x; }
-      }
-      __syncwarp();
-    }
-  // the sorted order is what every later reader of this voxel's points wants too (the debug dumps share the buffer): write it back
-  for (int k = lane; k < n; k += 32) sorted_idx[start + k] = idx[k];
-  float4 nxt = __ldg(pts + idx[lane]);
-  for (int base = 0; base < n; base += 32) {
-    sp[lane] = nxt;
-    __syncwarp();
-    if (base + 32 + lane < n) nxt = __ldg(pts + idx[base + 32 + lane]);
-    const int cnt = min(32, n - base);
-    if (lane < 12) {
-#pragma unroll 4
-      for (int k = 0; k < cnt; ++k) sums_add(acc, ia, ib, sp[k]);
-    }
-    __syncwarp();
-  }
+  const int fr = (lane >= 9 && lane < 12) ? lane - 9 : 0;
+  VoxelSums acc;
+  sums_init(acc, lane);
+  if (n <= 32) merge_voxel<1>(pts, sorted_idx, start, n, lane, tile, ia, ib, fr, acc.d, acc.f);
+  else if (n <= 64) merge_voxel<2>(pts, sorted_idx, start, n, lane, tile, ia, ib, fr, acc.d, acc.f);
+  else if (n <= 128) merge_voxel<4>(pts, sorted_idx, start, n, lane, tile, ia, ib, fr, acc.d, acc.f);
+  else if (n <= 256) merge_voxel<8>(pts, sorted_idx, start, n, lane, tile, ia, ib, fr, acc.d, acc.f);
+  else merge_voxel<16>(pts, sorted_idx, start, n, lane, tile, ia, ib, fr, acc.d, acc.f);
   sums_store(acc, lane, t, v);
 }
 // block per voxel with kWarpVoxelCap < population <= kBigVoxelCap: rank-by-counting sort into `scratch`, then the same sums
@@ -796,10 +834,12 @@ __global__ void __launch_bounds__(256) k_cs_merge_big(const float4* __restrict__
   }
 }
 // thread per voxel: hash insert, finalisation (VGC_I:282-367), dense code
-__global__ void __launch_bounds__(128) k_cs_finalize(VoxelTable t, int n_vox, const int* __restrict__ v_cell) {
+__global__ void __launch_bounds__(128) k_cs_finalize(VoxelTable t, int n_vox, const int* __restrict__ v_cell, const int* __restrict__ v_cnt) {
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= n_vox) return;
-  const unsigned long long key = t.vkey[v];
+  const unsigned long long key = cell_to_key(v_cell[v], t);
+  t.vkey[v] = key;
+  t.vn[v] = v_cnt[v];
   uint32_t h = hash_key(key) & t.mask;
   while (true) {
     const unsigned long long prev = atomicCAS(&t.slots[h].key, kEmptyKey, key);
@@ -807,7 +847,7 @@ __global__ void __launch_bounds__(128) k_cs_finalize(VoxelTable t, int n_vox, co
     h = (h + 1) & t.mask;
   }
   t.slots[h].vidx = v;
-  const int n = t.vn[v];
+  const int n = v_cnt[v];
   double sum[3], sxx[6];
   float cs[3];
   for (int a = 0; a < 3; ++a) { sum[a] = t.vsum[(size_t)v * 3 + a]; cs[a] = t.vcsum[(size_t)v * 3 + a]; }
@@ -891,18 +931,17 @@ static cudaError_t table_build_counting(TableStorage& ts, BuildWorkspace* ws, co
   }
   CK(table_reserve(ts, (size_t)n_vox, s, launches));
   if (n_vox > 0) {
-    // 10 KB of static shared memory per 4-voxel block: ask for the large carve-out, or the default split keeps one or two
-    // blocks per SM resident and the kernel runs at a fraction of its occupancy
+    // 6 KB of static shared memory per 4-voxel block, 16 blocks per SM: ask for the large carve-out
     static const cudaError_t carve = cudaFuncSetAttribute(k_cs_merge, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     (void)carve;
     CK(cudaMemsetAsync(ws->counts + 1, 0, sizeof(int), s));     // [1] = big voxels listed by k_cs_merge
-    k_cs_merge<<<(unsigned)((n_vox + 3) / 4), 128, 0, s>>>(pts, ws->idx_out, v_start, v_cnt, v_cell, n_vox, t, big_list, ws->counts + 1);
+    k_cs_merge<<<(unsigned)((n_vox + 3) / 4), 128, 0, s>>>(pts, ws->idx_out, v_start, v_cnt, n_vox, t, big_list, ws->counts + 1);
     L += 2;
     if (n_big > 0) {
       k_cs_merge_big<<<(unsigned)(n_big < 296 ? n_big : 296), 256, 0, s>>>(pts, ws->idx_out, ws->idx_in, v_start, v_cnt, big_list, ws->counts + 1, t);
       ++L;
     }
-    k_cs_finalize<<<(unsigned)((n_vox + 127) / 128), 128, 0, s>>>(t, n_vox, v_cell);
+    k_cs_finalize<<<(unsigned)((n_vox + 127) / 128), 128, 0, s>>>(t, n_vox, v_cell, v_cnt);
     ++L;
   }
   ts.n_vox = n_vox;
