@@ -101,10 +101,11 @@ def test_variant_macros_exist_and_default_off():
     spec.loader.exec_module(bv)
     csrc = os.path.join(ROOT, "xchu_slam_b200", "csrc")
     src = "".join(open(os.path.join(csrc, f)).read() for f in os.listdir(csrc) if f.endswith((".cu", ".h", ".cuh")))
-    defaults = dict(re.findall(r"#define\s+(NDTB_FAST_[A-Z0-9_]+)\s+(\d+)", src))
+    defaults = dict(re.findall(r"#define\s+(NDTB_[A-Z0-9_]+)\s+(\d+)", src))
     for name, defs in bv.VARIANTS.items():
         for d in defs:
             macro = d.split("=")[0]
             assert macro in defaults, (name, macro)
-    assert defaults["NDTB_FAST_REC64"] == "0" and defaults["NDTB_FAST_UNCOND"] == "0" and defaults["NDTB_FAST_ACC_SMEM"] == "0"
-    assert defaults["NDTB_FAST_AB"] == "0" and defaults["NDTB_FAST_PFP"] == "1" and defaults["NDTB_FAST_MINBLOCKS"] == "4"
+    assert defaults["NDTB_FAST_MINBLOCKS"] == "4" and defaults["NDTB_FAST_THREADS"] == "128"
+    # the factorised-kernel variants of rounds 1-2 were measured slower and removed: no dormant data-path switches left behind
+    assert not [m for m in defaults if m.startswith("NDTB_FAST_") and m not in ("NDTB_FAST_MINBLOCKS", "NDTB_FAST_THREADS")]

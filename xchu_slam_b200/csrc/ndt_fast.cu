@@ -34,21 +34,6 @@ namespace ndtb {
 #ifndef NDTB_FAST_MINBLOCKS
 #define NDTB_FAST_MINBLOCKS 4
 #endif
-#ifndef NDTB_FAST_ACC_SMEM   // 1: the 28 FP64 accumulators of a thread live in shared memory (in the reduction layout)
-#define NDTB_FAST_ACC_SMEM 0
-#endif
-#ifndef NDTB_FAST_PFP        // 1: the thread's NEXT source record is fetched one iteration ahead; 2 (DIRECT7): and its seven cell codes
-#define NDTB_FAST_PFP 1       //    (1: -3 % kernel time, 2: +2 %, register spills; profiles/r01_v9_kernel_variants.txt)
-#endif
-#ifndef NDTB_FAST_AB         // 1 (DIRECT7): voxel records alternate between two register sets instead of being copied
-#define NDTB_FAST_AB 0       //    (measured 6 % slower on B200: profiles/r01_v9_kernel_variants.txt)
-#endif
-#ifndef NDTB_FAST_UNCOND     // 1 (DIRECT7): voxel-record loads unpredicated on a clamped index -- no register copies between cells
-#define NDTB_FAST_UNCOND 0   //    (variant for the A/B sweep; ~90 fewer instructions per point in the SASS, not yet measured)
-#endif
-#ifndef NDTB_FAST_DENSE32    // 1 (DIRECT7): dense-index lookup with block-uniform set-up hoisted and 32-bit index arithmetic
-#define NDTB_FAST_DENSE32 1
-#endif
 constexpr int kFT = NDTB_FAST_THREADS;
 constexpr int kFAcc = 28;          // score, g[6], H upper triangle [21]
 constexpr int kFCols = kFAcc + 1;  // + pair count
@@ -68,15 +53,7 @@ struct FRec { float4 a, b, c; };
 __device__ __forceinline__ FRec load_frec(const FastRec* __restrict__ r) {
   FRec f;
   const float4* p = reinterpret_cast<const float4*>(r);
-#if NDTB_FAST_REC64
-  // LDG.E.ENL2.256 (sm_100+): bytes 0..31 of the 64-B aligned record in one request, bytes 32..47 in a second
-  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-               : "=f"(f.a.x), "=f"(f.a.y), "=f"(f.a.z), "=f"(f.a.w), "=f"(f.b.x), "=f"(f.b.y), "=f"(f.b.z), "=f"(f.b.w)
-               : "l"(p));
-  f.c = __ldg(p + 2);
-#else
   f.a = __ldg(p); f.b = __ldg(p + 1); f.c = __ldg(p + 2);
-#endif
   return f;
 }
 
@@ -86,10 +63,8 @@ __device__ __forceinline__ void fast_reduce_store(const double* acc, int npairs,
   extern __shared__ double red_sm[];                 // [warps][kFCols][kFPad] + [warps][kFCols]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = kFT >> 5;
   double* mine = red_sm + (size_t)warp * kFCols * kFPad;
-#if !NDTB_FAST_ACC_SMEM
 #pragma unroll
   for (int k = 0; k < kFAcc; ++k) mine[k * kFPad + lane] = acc[k];
-#endif
   mine[kFAcc * kFPad + lane] = (double)npairs;
   __syncwarp();
   double* wsum = red_sm + (size_t)nwarps * kFCols * kFPad;
@@ -132,7 +107,7 @@ __device__ __forceinline__ Dense7 make_dense7(const VoxelTable& t, bool direct7)
   d.dlo0 = t.dlo[0]; d.dlo1 = t.dlo[1]; d.dlo2 = t.dlo[2];
   d.dn0 = t.dn[0]; d.dn1 = t.dn[1]; d.dn2 = t.dn[2];
   d.sxy = d.dn0 * d.dn1;
-  d.dense32 = NDTB_FAST_DENSE32 && direct7 && t.dense != nullptr && t.slots != nullptr && (long long)d.dn0 * d.dn1 < (1ll << 31) &&
+  d.dense32 = direct7 && t.dense != nullptr && t.slots != nullptr && (long long)d.dn0 * d.dn1 < (1ll << 31) &&
               (long long)d.sxy * d.dn2 < (1ll << 31);
   d.leaf = t.leaf;
   const unsigned leaf_bits = __float_as_uint(d.leaf);
@@ -184,15 +159,8 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
     sh.tab = tables[st.target];
   }
   __syncthreads();
-#if NDTB_FAST_ACC_SMEM
-  extern __shared__ double red_sm[];
-  double* const acc_sm = red_sm + (size_t)(tid >> 5) * kFCols * kFPad + (tid & 31);
-  const double* acc = nullptr;
-#define ACC(k) acc_sm[(k) * kFPad]
-#else
   double acc[kFAcc];
 #define ACC(k) acc[k]
-#endif
 #pragma unroll
   for (int k = 0; k < kFAcc; ++k) ACC(k) = 0.0;
   int npairs = 0;
@@ -201,54 +169,19 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
   const FastRec* __restrict__ recs = sh.tab.frec;
   const float d2f = sh.d2f, nhalf_d2f = sh.nhalf_d2f, d1d2f = sh.d1d2f;
   const Dense7 d7 = make_dense7(sh.tab, METHOD == 2);
-#if NDTB_FAST_PFP
   // the source record (PFP >= 1) and the seven cell codes (PFP == 2) of the thread's NEXT point are fetched before this point's
   // pairs are evaluated: one / two of the three dependent global loads of a point leave the critical path
   float4 p_nx = make_float4(0.f, 0.f, 0.f, 0.f);
-#if NDTB_FAST_PFP >= 2
-  float xt_nx = 0.f, yt_nx = 0.f, zt_nx = 0.f;
-  int v_nx[7];
-#endif
   if (bm.y + tid < end) {
     p_nx = __ldg(src + bm.y + tid);
-#if NDTB_FAST_PFP >= 2
-    if (METHOD == 2) {
-      xform(sh.T, p_nx.x, p_nx.y, p_nx.z, xt_nx, yt_nx, zt_nx);
-      lookup7(d7, sh.tab, xt_nx, yt_nx, zt_nx, v_nx);
-    }
-#endif
   }
-#endif
   for (int i = bm.y + tid; i < end; i += kFT) {
-#if NDTB_FAST_PFP
     const float4 p = p_nx;
     float xt, yt, zt;
-#if NDTB_FAST_PFP >= 2
-    int v[7];
-    if (METHOD == 2) {
-      xt = xt_nx; yt = yt_nx; zt = zt_nx;
-#pragma unroll
-      for (int o = 0; o < 7; ++o) v[o] = v_nx[o];
-    } else {
-      xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
-    }
-#else
     xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
-#endif
     if (i + kFT < end) {
       p_nx = __ldg(src + i + kFT);
-#if NDTB_FAST_PFP >= 2
-      if (METHOD == 2) {
-        xform(sh.T, p_nx.x, p_nx.y, p_nx.z, xt_nx, yt_nx, zt_nx);
-        lookup7(d7, sh.tab, xt_nx, yt_nx, zt_nx, v_nx);
-      }
-#endif
     }
-#else
-    const float4 p = __ldg(src + i);
-    float xt, yt, zt;
-    xform(sh.T, p.x, p.y, p.z, xt, yt, zt);
-#endif
     float S = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f;
     float M00 = 0.f, M01 = 0.f, M02 = 0.f, M11 = 0.f, M12 = 0.f, M22 = 0.f;
     float B00 = 0.f, B01 = 0.f, B02 = 0.f, B11 = 0.f, B12 = 0.f, B22 = 0.f;
@@ -279,43 +212,13 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
     if (METHOD == 2) {
       // DIRECT7: the seven cells in the reference's order, fully unrolled and predicated (no compaction,
       // no local memory); the record of cell o+1 is in flight while cell o is being evaluated.
-#if NDTB_FAST_PFP < 2
       int v[7];
       lookup7(d7, sh.tab, xt, yt, zt, v);
-#endif
       int cnt = 0;
 #pragma unroll
       for (int o = 0; o < 7; ++o) cnt += v[o] >= 0 ? 1 : 0;
       if (cnt == 0) continue;
       npairs += cnt;
-#if NDTB_FAST_AB
-      // two register sets used alternately: the record of cell o+1 is already in flight when cell o is evaluated, and no
-      // register copies are needed between cells (a predicated load writes its set in place)
-      FRec rA = {}, rB = {};
-      if (v[0] >= 0) rA = load_frec(recs + v[0]);
-      if (v[1] >= 0) rB = load_frec(recs + v[1]);
-#pragma unroll
-      for (int o = 0; o < 7; ++o) {
-        if ((o & 1) == 0) {
-          if (v[o] >= 0) NDTB_PAIR(rA)
-          if (o + 2 < 7) { if (v[o + 2] >= 0) rA = load_frec(recs + v[o + 2]); }
-        } else {
-          if (v[o] >= 0) NDTB_PAIR(rB)
-          if (o + 2 < 7) { if (v[o + 2] >= 0) rB = load_frec(recs + v[o + 2]); }
-        }
-      }
-#elif NDTB_FAST_UNCOND
-      // unpredicated record loads: an absent cell fetches record 0 (one broadcast address, an L1 hit; cnt > 0 here, so record 0
-      // exists) and its pair is skipped as before.  Every load then has a fresh destination: no zero-initialised record and no
-      // 12-register copy per cell (the predicated form needs both to merge "loaded" with "not loaded").
-      FRec nxt = load_frec(recs + max(v[0], 0));
-#pragma unroll
-      for (int o = 0; o < 7; ++o) {
-        const FRec r = nxt;
-        if (o + 1 < 7) nxt = load_frec(recs + max(v[o + 1], 0));
-        if (v[o] >= 0) NDTB_PAIR(r)
-      }
-#else
       FRec nxt = {};
       if (v[0] >= 0) nxt = load_frec(recs + v[0]);
 #pragma unroll
@@ -324,7 +227,6 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
         if (o + 1 < 7) { if (v[o + 1] >= 0) nxt = load_frec(recs + v[o + 1]); }
         if (v[o] >= 0) NDTB_PAIR(r)
       }
-#endif
     } else {
       int nb[27];
       const int cnt = find_neighbors(sh.tab, METHOD, xt, yt, zt, nb);

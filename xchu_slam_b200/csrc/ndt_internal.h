@@ -56,22 +56,14 @@ struct __align__(64) VoxelRec {
 // The f64 mean is carried as an unevaluated float sum hi + lo (48 significant bits) so that
 // x - mean is formed in two float subtractions to the same float the reference's double
 // subtraction rounds to (NDT_I:257-260, 500).
-// NDTB_FAST_REC64=1 (kernel variant for the A/B sweep, default 0): records padded to 64 B and 64-B aligned, so that a record never
-// straddles a 128-B line and is fetched by one 256-bit + one 128-bit load (two L1 tag look-ups per pair instead of three) at the
-// price of a third more L2 footprint.  The macro must reach every translation unit (build_cuda(defines=...)).
-#ifndef NDTB_FAST_REC64
-#define NDTB_FAST_REC64 0
-#endif
-#if NDTB_FAST_REC64
-struct __align__(64) FastRec {
-#else
+// (A 64-byte, 64-B aligned record -- one 256-bit + one 128-bit load per pair -- was measured 3 % slower on B200:
+// profiles/r02/r02_c3_variants.txt; the 48-byte record stays.)
 struct __align__(16) FastRec {
-#endif
   float mh[3];     // (float)mean
   float ml[3];     // (float)(mean - (double)mh)
   float c[6];      // icov (float) upper triangle: 00 01 02 11 12 22
 };
-static_assert(sizeof(FastRec) == (NDTB_FAST_REC64 ? 64 : 48), "FastRec layout");
+static_assert(sizeof(FastRec) == 48, "FastRec layout");
 
 struct VoxelTable {          // all pointers device
   HashSlot* slots;
