@@ -16,6 +16,10 @@ VARIANTS = {
     # one block = 8 warps per SM, 59 % of cycles with no eligible warp)
     "strict_smem": ("NDTB_STRICT_ACC_SMEM=1", "NDTB_MINBLOCKS=2"),
     "strict_mb2": ("NDTB_MINBLOCKS=2",),
+    # the neighbour loop NOT unrolled: 1816 instead of 4552 instructions (ncu r02: 17 % of the stall samples are instruction-cache
+    # misses, `no_instructions`), alone and with the shared-memory accumulators at two blocks per SM
+    "strict_nounroll": ("NDTB_NOUNROLL=1",),
+    "strict_nounroll_smem": ("NDTB_NOUNROLL=1", "NDTB_STRICT_ACC_SMEM=1", "NDTB_MINBLOCKS=2"),
 }
 
 

@@ -734,10 +734,15 @@ struct Engine {
     if (ensure(d_blockmap, blockmap_cap, blocks_cap)) return 1;
     if (ensure(d_partials, partials_cap, blocks_cap * 44)) return 1;
     cudaError_t pull_err = cudaSuccess;
+    // hybrid batches: the replay threshold, known before the first pass so that it can stop registrations that cross it
+    int k_iters = params.replay_iters;
+    if (const char* ev = getenv("NDTB_REPLAY_ITERS")) k_iters = atoi(ev);   // tuning knob
+    const int abort_iters = (mode == KM_HYBRID && k_iters > 0 && !getenv("NDTB_REPLAY_NO_ABORT")) ? k_iters : 0;
     auto fill = [&]() {
       for (int i = 0; i < n_items; ++i) {
         AlignState& st = h_states[i];
         fill_state(st, item_target[i], sources[item_source[i]], guesses + (size_t)i * 16);
+        st.abort_iters = abort_iters;
         st.first_block = (int)nb_fill;
         st.n_blocks = (st.n_src + chunk - 1) / chunk;
         for (int b = 0; b < st.n_blocks; ++b) bmap[nb_fill++] = make_int2(i, b * chunk);
@@ -776,8 +781,6 @@ struct Engine {
       replay_flag.assign((size_t)n_items, 0);
       CKE(st_idx.reserve((size_t)n_items * sizeof(int)));
       int* idx = static_cast<int*>(st_idx.h);
-      int k_iters = params.replay_iters;
-      if (const char* ev = getenv("NDTB_REPLAY_ITERS")) k_iters = atoi(ev);   // tuning knob
       double min_norm = params.replay_min_norm >= 0 ? params.replay_min_norm : 0.05 * params.trans_eps;
       if (const char* ev = getenv("NDTB_REPLAY_MIN_NORM")) min_norm = atof(ev);   // tuning knob
       int k_rise = 1 << 30;

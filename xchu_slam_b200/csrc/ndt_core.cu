@@ -30,6 +30,9 @@ namespace ndtb {
 #ifndef NDTB_PREFETCH     // 1: fetch the next voxel record behind the current pair's math
 #define NDTB_PREFETCH 1
 #endif
+#ifndef NDTB_NOUNROLL          // 1: the neighbour loop of the strict kernel is not unrolled (code size 4552 -> 1816 instructions)
+#define NDTB_NOUNROLL 0
+#endif
 #ifndef NDTB_STRICT_ACC_SMEM   // 1: the 43 FP64 accumulators of a thread live in shared memory ([k][thread], conflict-free), which
 #define NDTB_STRICT_ACC_SMEM 0  //    takes 86 registers off the kernel -> two resident blocks per SM instead of one
 #endif
@@ -261,7 +264,7 @@ __global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const 
 #undef PDI
 #if NDTB_PREFETCH
     RecRegs cur = load_rec(recs + nb[0]);
-#ifdef NDTB_NOUNROLL
+#if NDTB_NOUNROLL
 #pragma unroll 1
 #endif
     for (int k = 0; k < cnt; ++k) {
@@ -778,6 +781,9 @@ __device__ void post_step(NewtonCtx& c) {
   if (fabs(fabs(a) - st.trans_eps) <= 1e-3 * st.trans_eps) st.borderline = 1;   // the |step| < eps test taken at its threshold
   st.nr_iterations++;
   if (conv) { finish(c, 1); return; }
+  // first pass of a hybrid batch: a registration past the replay threshold is going to be run again with the term-by-term
+  // kernel whatever it does from here on -- it leaves now (unconverged, which flags it) instead of riding out the tail
+  if (st.abort_iters > 0 && st.nr_iterations > st.abort_iters) { finish(c, 0); return; }
   newton_top(c);
 }
 

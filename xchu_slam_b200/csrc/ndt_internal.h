@@ -129,6 +129,7 @@ struct AlignState {
   // gradient could have taken it the other way; n_rise = line-search steps that grew again after the step had dropped below
   // step_size (the iteration is not contracting); last_norm = |delta_p| of the last Newton solve; prev_at = previous step.
   int borderline, n_rise;
+  int abort_iters;           // > 0 (first pass of a hybrid batch): leave the loop unconverged once nr_iterations exceeds it
   double last_norm, prev_at, min_at;
 };
 
