@@ -12,14 +12,10 @@ sys.path.insert(0, ROOT)
 from xchu_slam_b200 import build as b  # noqa: E402
 
 VARIANTS = {
-    # strict (term-by-term) kernel: FP64 accumulators in shared memory, 128 registers, two blocks per SM (ncu r02: 241 registers,
-    # one block = 8 warps per SM, 59 % of cycles with no eligible warp)
-    "strict_smem": ("NDTB_STRICT_ACC_SMEM=1", "NDTB_MINBLOCKS=2"),
-    "strict_mb2": ("NDTB_MINBLOCKS=2",),
-    # the neighbour loop NOT unrolled: 1816 instead of 4552 instructions (ncu r02: 17 % of the stall samples are instruction-cache
-    # misses, `no_instructions`), alone and with the shared-memory accumulators at two blocks per SM
-    "strict_nounroll": ("NDTB_NOUNROLL=1",),
-    "strict_nounroll_smem": ("NDTB_NOUNROLL=1", "NDTB_STRICT_ACC_SMEM=1", "NDTB_MINBLOCKS=2"),
+    # strict (term-by-term) kernel: the round-2 default is shared-memory FP64 accumulators + neighbour loop not unrolled + two
+    # blocks per SM (profiles/r02/r02_c4_strict_variants.txt, r02_c5_strict_variants.txt); these rebuild the earlier settings
+    "strict_r01": ("NDTB_NOUNROLL=0", "NDTB_STRICT_ACC_SMEM=0", "NDTB_MINBLOCKS=1"),
+    "strict_nounroll_regs": ("NDTB_NOUNROLL=1", "NDTB_STRICT_ACC_SMEM=0", "NDTB_MINBLOCKS=1"),
 }
 
 

@@ -178,6 +178,7 @@ struct Engine {
   SubmapSeg* lane_segs[16] = {};
   NNGridStorage* lane_nn[16] = {};   // one NN grid per build lane (ndtb_batch_fitness over distinct targets)
   size_t lane_segs_cap[16] = {};
+  double* d_fit2 = nullptr;          // {sum, count} of getFitnessScore on the device
   PinnedBuf st_d2;                   // host landing zone of the per-point squared NN distances (getFitnessScore)
   PinnedBuf st_src;                  // host staging of strided sources (x y z intensity packed to 16 B)
 
@@ -233,7 +234,7 @@ struct Engine {
     st_states.release(); st_bmap.release(); st_tables.release(); st_idx.release();
     cudaFree(d_tables); cudaFree(src_pool); cudaFree(d_states); cudaFree(d_blockmap); cudaFree(d_partials);
     cudaFree(d_trace); cudaFree(d_active); cudaFreeHost(h_active); cudaFree(d_T16); cudaFree(d_p6);
-    cudaFree(d_output); cudaFree(d_d2);
+    cudaFree(d_output); cudaFree(d_d2); cudaFree(d_fit2);
     destroy_align_graph();
     cudaFree(ag.d_state); cudaFree(ag.d_bmap); cudaFree(ag.d_partials); cudaFree(ag.d_trace); cudaFree(ag.d_active);
     ag.h_in.release(); ag.h_out.release();
@@ -1083,16 +1084,15 @@ int ndtb_fitness(ndtb_handle* h, double max_range, const float* T, double* out) 
   if (n > e.d2_cap) { cudaFree(e.d_d2); e.d_d2 = nullptr; if (cudaMalloc(&e.d_d2, n * sizeof(float)) != cudaSuccess) return e.fail("alloc"); e.d2_cap = n; }
   cudaMemcpyAsync(e.d_T16, T ? T : e.last.T, 64, cudaMemcpyHostToDevice, e.stream);
   if (nn_query(e.nn, e.src_pool + e.sources[0].offset, n, e.d_T16, e.d_d2, e.stream) != cudaSuccess) return e.fail("nn_query failed");
-  if (e.st_d2.reserve(n * sizeof(float)) != cudaSuccess) return e.fail("pinned staging allocation failed");
-  const float* d = static_cast<const float*>(e.st_d2.h);
-  cudaMemcpyAsync(e.st_d2.h, e.d_d2, n * sizeof(float), cudaMemcpyDeviceToHost, e.stream);
+  // pcl::Registration::getFitnessScore: the mean (double) of the float squared distances <= max_range.  Summed on the device in
+  // a fixed order (the reference adds in point order: same terms, grouping differs at the 1e-16 level); the host reads {sum, n}.
+  if (e.st_d2.reserve(2 * sizeof(double)) != cudaSuccess) return e.fail("pinned staging allocation failed");
+  if (!e.d_fit2 && cudaMalloc(&e.d_fit2, 2 * sizeof(double)) != cudaSuccess) return e.fail("alloc");
+  if (d2_reduce(e.d_d2, n, max_range, e.d_fit2, e.stream) != cudaSuccess) return e.fail("fitness reduction failed");
+  cudaMemcpyAsync(e.st_d2.h, e.d_fit2, 2 * sizeof(double), cudaMemcpyDeviceToHost, e.stream);
   if (cudaStreamSynchronize(e.stream) != cudaSuccess) return e.fail("sync failed");
-  // pcl::Registration::getFitnessScore: double accumulation in point order over d <= max_range
-  double s = 0;
-  long nr = 0;
-  for (size_t i = 0; i < n; ++i)
-    if ((double)d[i] <= max_range) { s += d[i]; ++nr; }
-  *out = nr > 0 ? s / nr : 1.7976931348623157e308;
+  const double* r = static_cast<const double*>(e.st_d2.h);
+  *out = r[1] > 0 ? r[0] / r[1] : 1.7976931348623157e308;
   return 0;
 }
 

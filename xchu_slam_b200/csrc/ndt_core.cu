@@ -22,7 +22,7 @@ namespace ndtb {
 #define NDTB_THREADS 256
 #endif
 #ifndef NDTB_MINBLOCKS
-#define NDTB_MINBLOCKS 1
+#define NDTB_MINBLOCKS 2
 #endif
 #ifndef NDTB_PD_SMEM      // 1: per-point derivative vectors parked in shared memory, 0: in registers
 #define NDTB_PD_SMEM 0
@@ -31,10 +31,11 @@ namespace ndtb {
 #define NDTB_PREFETCH 1
 #endif
 #ifndef NDTB_NOUNROLL          // 1: the neighbour loop of the strict kernel is not unrolled (code size 4552 -> 1816 instructions)
-#define NDTB_NOUNROLL 0
+#define NDTB_NOUNROLL 1         //    measured -6.7 % kernel time: 17 % of the stall samples were instruction-cache misses (profiles/r02)
 #endif
 #ifndef NDTB_STRICT_ACC_SMEM   // 1: the 43 FP64 accumulators of a thread live in shared memory ([k][thread], conflict-free), which
-#define NDTB_STRICT_ACC_SMEM 0  //    takes 86 registers off the kernel -> two resident blocks per SM instead of one
+#define NDTB_STRICT_ACC_SMEM 1  //    takes 86 registers off the kernel -> two resident blocks per SM instead of one (with the
+                                //    loop not unrolled: -10.7 % kernel time; with it unrolled +23 %: profiles/r02/r02_c5_strict_variants.txt)
 #endif
 constexpr int kThreads = NDTB_THREADS;
 #if NDTB_STRICT_ACC_SMEM

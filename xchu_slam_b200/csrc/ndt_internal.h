@@ -209,6 +209,7 @@ NNGridStorage* nn_create();
 void nn_destroy(NNGridStorage* g);
 cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, size_t n, float cell, const float* bbox,
                      cudaStream_t s, long long* launches);
+cudaError_t d2_reduce(const float* d2, size_t n, double max_range, double* out2_dev, cudaStream_t s);   // {sum, count} of d2 <= max_range
 cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float* T16_dev, float* d2_out,
                      cudaStream_t s);
 // getFitnessScore of every registration of a batch that shares the grid's target (items_dev: ids into states)

@@ -1348,6 +1348,29 @@ cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float*
   return cudaGetLastError();
 }
 
+// getFitnessScore of one registration: sum and count of the squared distances <= max_range, one block, fixed order (thread-
+// strided partial sums, then lanes, then warps) -- the host reads 16 bytes instead of one float per source point.
+__global__ void __launch_bounds__(1024) k_d2_reduce(const float* __restrict__ d2, size_t n, double max_range, double* __restrict__ out) {
+  __shared__ double ss[32], sc[32];
+  double s = 0.0, c = 0.0;
+  for (size_t i = threadIdx.x; i < n; i += 1024) {
+    const float d = d2[i];
+    if ((double)d <= max_range) { s += (double)d; c += 1.0; }
+  }
+  for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); c += __shfl_xor_sync(0xffffffffu, c, o); }
+  if ((threadIdx.x & 31) == 0) { ss[threadIdx.x >> 5] = s; sc[threadIdx.x >> 5] = c; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double ts = 0.0, tc = 0.0;
+    for (int w = 0; w < 32; ++w) { ts += ss[w]; tc += sc[w]; }
+    out[0] = ts; out[1] = tc;
+  }
+}
+cudaError_t d2_reduce(const float* d2, size_t n, double max_range, double* out2_dev, cudaStream_t s) {
+  k_d2_reduce<<<1, 1024, 0, s>>>(d2, n, max_range, out2_dev);
+  return cudaGetLastError();
+}
+
 // Batched getFitnessScore (loop-closure candidates are accepted on it, reference src/pgo_node.cpp:460-476): every
 // registration of a batch that shares one target, in one launch.  blockIdx.y walks `items` (ids into `states`); the
 // transform is the registration's final one.  A query the ring search cannot settle scans the whole target itself (a scan
