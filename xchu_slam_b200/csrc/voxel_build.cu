@@ -271,7 +271,7 @@ static cudaError_t minmax_host(BuildWorkspace* ws, const float4* pts, size_t n, 
 // float(min_b) there is exact for |cell| < 2^24, so the absolute cell is the same integer).
 __device__ __forceinline__ int build_cell(float x, float inv_leaf) { return (int)floorf(x * inv_leaf); }
 
-// KeyT: unsigned long long, or unsigned int when bi + bj + bk <= 32 and NDTB_SORT_KEY32=1 (sort_key32 below): the same integers in
+// KeyT: unsigned int when bi + bj + bk <= 32 (sort_key32 below), else unsigned long long: the same integers in
 // the same (stable) order, two thirds of the bytes per radix pass.
 template <typename KeyT>
 __global__ void k_keys(const float4* __restrict__ pts, size_t n, float inv_leaf, int i0, int j0, int k0, int bi, int bj,
@@ -555,10 +555,11 @@ static int bits_for(long long range) {
   return b;
 }
 
-// NDTB_SORT_KEY32=1 (off by default until the whole GPU suite has run with it; DESIGN.md section 9 lead 1): cell keys of at most
-// 32 bits are generated, sorted and compared as 32-bit words in the lower halves of the same workspace arrays.
+// Cell keys of at most 32 bits (any submap: 21 bits at 1M points / 1 m) are generated, sorted and compared as 32-bit words in
+// the lower halves of the same workspace arrays: two thirds of the bytes per radix pass (64 builds: 5.3 -> 4.7 ms, GPU suite
+// green with it: profiles/r02).  NDTB_SORT_KEY32=0 forces 64-bit keys.
 static bool sort_key32(int bits) {
-  static const bool on = [] { const char* e = getenv("NDTB_SORT_KEY32"); return e && atoi(e) > 0; }();
+  static const bool on = [] { const char* e = getenv("NDTB_SORT_KEY32"); return !(e && atoi(e) == 0); }();
   return on && bits <= 32;
 }
 // keys_in / idx_in -> keys_out / idx_out (stable), then flags[t] = key t starts a run
