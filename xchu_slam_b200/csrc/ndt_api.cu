@@ -105,6 +105,12 @@ struct Engine {
   BuildWorkspace* ws = nullptr;
   NNGridStorage* nn = nullptr;
   bool nn_valid = false;
+  // getFitnessScore's NN grid of a NEW target is built on a side stream under the next align (the caller has asked for a fitness
+  // score before: odom_node does after every align, ODOM:266-280) instead of inside the fitness call
+  bool fitness_used = false, nn_pending = false;
+  cudaStream_t nn_stream = nullptr;
+  cudaEvent_t ev_nn_dep = nullptr, ev_nn_ready = nullptr;
+  BuildWorkspace* ws_nn = nullptr;
   std::vector<Target> targets;
   int n_targets_live = 0;
   VoxelTable* d_tables = nullptr;
@@ -230,6 +236,10 @@ struct Engine {
     if (sources_uploaded) cudaEventDestroy(sources_uploaded);
     targets.clear();
     build_ws_destroy(ws);
+    if (ws_nn) build_ws_destroy(ws_nn);
+    if (nn_stream) cudaStreamDestroy(nn_stream);
+    if (ev_nn_dep) cudaEventDestroy(ev_nn_dep);
+    if (ev_nn_ready) cudaEventDestroy(ev_nn_ready);
     nn_destroy(nn);
     st_states.release(); st_bmap.release(); st_tables.release(); st_idx.release();
     cudaFree(d_tables); cudaFree(src_pool); cudaFree(d_states); cudaFree(d_blockmap); cudaFree(d_partials);
@@ -1033,18 +1043,49 @@ int ndtb_set_source(ndtb_handle* h, const void* pts, size_t n, size_t stride_byt
   return e.add_source(pts, n, stride_bytes, 0, false, nullptr);
 }
 
+static cudaError_t nn_build_for(Engine& e, BuildWorkspace* ws, cudaStream_t s) {
+  Target& t = e.targets[0];
+  const float cell = e.params.resolution > 0.25f ? e.params.resolution : 0.25f;
+  // the voxel table already holds the float bounding box of the target's points: the NN grid build never blocks
+  float bb[6];
+  for (int a = 0; a < 3; ++a) { bb[a] = t.ts.mn[a]; bb[3 + a] = t.ts.mx[a]; }
+  return nn_build(e.nn, ws, t.use ? t.use : t.pts, t.n, cell, t.built && t.ts.have_bbox ? bb : nullptr, s, &e.stats.kernel_launches);
+}
+// Enqueues the NN-grid build of a changed target on the side stream, behind everything the main stream holds so far.
+static void nn_prebuild(Engine& e) {
+  static const bool off = [] { const char* ev = getenv("NDTB_NN_PREBUILD"); return ev && atoi(ev) == 0; }();
+  Target& t = e.targets[0];
+  if (off || !e.single || !e.fitness_used || e.nn_valid || t.n == 0 || !t.built || !t.ts.have_bbox) return;
+  if (!e.nn_stream) {
+    if (cudaStreamCreateWithFlags(&e.nn_stream, cudaStreamNonBlocking) != cudaSuccess) { e.nn_stream = nullptr; return; }
+    cudaEventCreateWithFlags(&e.ev_nn_dep, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&e.ev_nn_ready, cudaEventDisableTiming);
+    e.ws_nn = build_ws_create();
+  }
+  if (!e.ws_nn || !e.ev_nn_dep || !e.ev_nn_ready) return;
+  cudaEventRecord(e.ev_nn_dep, e.stream);
+  cudaStreamWaitEvent(e.nn_stream, e.ev_nn_dep, 0);
+  if (nn_build_for(e, e.ws_nn, e.nn_stream) != cudaSuccess) { cudaGetLastError(); return; }   // fitness builds it the ordinary way
+  cudaEventRecord(e.ev_nn_ready, e.nn_stream);
+  e.nn_valid = true;
+  e.nn_pending = true;
+}
+
 int ndtb_align(ndtb_handle* h, const float guess[16], ndtb_result* out) {
   Engine& e = h->e;
   if (e.sources.empty()) return e.fail("no source cloud set");
   if (!e.targets[0].built) return e.fail("no target cloud set");
   const int zero = 0;
   if (cudaSetDevice(e.device) != cudaSuccess) return e.fail("cudaSetDevice failed");
+  nn_prebuild(e);
   const int via_graph = e.align_graph(guess, &e.last);
   if (via_graph == 1) return 1;
   if (via_graph == 2) {
     e.trace_on_device = false;
     if (e.run_items(1, &zero, &zero, guess, &e.last, true)) return 1;
   }
+  // whatever the main stream does next (the fitness query, a target refresh that rewrites the points) comes after the grid build
+  if (e.nn_pending) { cudaStreamWaitEvent(e.stream, e.ev_nn_ready, 0); e.nn_pending = false; }
   e.have_result = true;
   e.h_trace_n = e.last.n_evals;
   if (out) *out = e.last;
@@ -1070,13 +1111,9 @@ int ndtb_fitness(ndtb_handle* h, double max_range, const float* T, double* out) 
   Target& t = e.targets[0];
   if (e.sources.empty() || t.n == 0) return e.fail("fitness needs a source and a target");
   if (!T && !e.have_result) return e.fail("no align result");
+  e.fitness_used = true;
   if (!e.nn_valid) {
-    const float cell = e.params.resolution > 0.25f ? e.params.resolution : 0.25f;
-    // the voxel table already holds the float bounding box of the target's points: the NN grid build never blocks
-    float bb[6];
-    for (int a = 0; a < 3; ++a) { bb[a] = t.ts.mn[a]; bb[3 + a] = t.ts.mx[a]; }
-    cudaError_t ce = nn_build(e.nn, e.ws, t.use ? t.use : t.pts, t.n, cell, t.built && t.ts.have_bbox ? bb : nullptr, e.stream,
-                              &e.stats.kernel_launches);
+    cudaError_t ce = nn_build_for(e, e.ws, e.stream);
     if (ce != cudaSuccess) return e.fail(std::string("nn_build: ") + cudaGetErrorString(ce));
     e.nn_valid = true;
   }

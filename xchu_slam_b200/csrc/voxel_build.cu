@@ -1037,10 +1037,9 @@ cudaError_t table_append(TableStorage& ts, BuildWorkspace* ws, const float4* pts
   const int n_runs = ws->h_counts[0];
   CK(table_reserve(ts, (size_t)ts.n_vox + n_runs, s, launches));
   const unsigned rb = (unsigned)((n_runs + 127) / 128);
-  // NDTB_FRESH_MERGE=1 (off by default until the whole GPU suite has run with it): a full build skips three launches and the
-  // third blocking read of the chain, see k_run_merge<true>
-  static const bool fresh_merge = [] { const char* e = getenv("NDTB_FRESH_MERGE"); return e && atoi(e) > 0; }();
-  if (fresh_merge && ts.n_vox == 0) {
+  // a build into an empty table (the radix path's fresh build: boxes too large for the dense grid) skips the run lookup, the
+  // prefix scan and the third blocking read of the chain: every run is a new voxel, run r = voxel r (k_run_merge<true>)
+  if (ts.n_vox == 0) {
     k_run_merge<true><<<rb, 128, 0, s>>>(pts, ws->idx_out, ws->run_start, nullptr, nullptr, nullptr, n_runs, 0, t, ws->counts);
     L += 1;
     ts.n_vox = n_runs;
@@ -1242,12 +1241,20 @@ cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, si
 // Ring search over the cell grid.  A query is settled once its best squared distance is <= ((ring-1)*cell)^2, the least
 // any point of a farther ring can be away.  Queries still open after `max_ring` rings (the scan reaches far beyond a
 // small localmap) go to k_nn_far instead of walking ever larger, empty shells.
-__global__ void k_nn_query(const float4* __restrict__ sorted, size_t n_tgt, const CellSlot* __restrict__ slots, uint32_t mask, float cell,
-                           const float4* __restrict__ src, size_t n, const float* __restrict__ T16, int max_ring, float* __restrict__ d2_out,
-                           int* __restrict__ far_idx, int* __restrict__ far_count) {
-  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const float4 p = src[i];
+// Eight lanes share a query: the cells of a shell are dealt round-robin to the lanes, the minimum is taken across the group
+// after every ring (the minimum of the same float expressions whatever the order: the exact 1-NN distance).  One thread per
+// query walked up to 26 + 98 cells of dependent hash probes and point loops alone and left most SMs without a block.
+constexpr int kNNGroup = 8;
+__global__ void __launch_bounds__(128) k_nn_query(const float4* __restrict__ sorted, size_t n_tgt, const CellSlot* __restrict__ slots, uint32_t mask,
+                                                  float cell, const float4* __restrict__ src, size_t n, const float* __restrict__ T16,
+                                                  int max_ring, float* __restrict__ d2_out, int* __restrict__ far_idx,
+                                                  int* __restrict__ far_count) {
+  const size_t gt = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t i = gt / kNNGroup;
+  const int g = (int)(gt % kNNGroup);
+  const bool live = i < n;                       // (no early return: the group shuffles below need every lane of the group)
+  const unsigned gmask = 0xFFu << ((threadIdx.x & 31) & ~(kNNGroup - 1));
+  const float4 p = live ? src[i] : make_float4(0.f, 0.f, 0.f, 0.f);
   // pcl::transformPointCloud by final_transformation_ (float, left to right)
   const float qx = ((T16[0] * p.x + T16[4] * p.y) + T16[8] * p.z) + T16[12];
   const float qy = ((T16[1] * p.x + T16[5] * p.y) + T16[9] * p.z) + T16[13];
@@ -1261,31 +1268,38 @@ __global__ void k_nn_query(const float4* __restrict__ sorted, size_t n_tgt, cons
       if (best <= lim * lim) { certain = true; break; }
     }
     if (ring > max_ring) break;
-    for (int dz = -ring; dz <= ring; ++dz)
-      for (int dy = -ring; dy <= ring; ++dy)
-        for (int dx = -ring; dx <= ring; ++dx) {
-          if (max(abs(dx), max(abs(dy), abs(dz))) != ring) continue;
-          const int a = ci + dx, b = cj + dy, c = ck + dz;
-          if (!coord_ok(a) || !coord_ok(b) || !coord_ok(c)) continue;
-          const unsigned long long key = pack_key(a, b, c);
-          uint32_t h = hash_key(key) & mask;
-          int s0 = 0, s1 = 0;
-          while (true) {
-            const CellSlot sl = slots[h];
-            if (sl.key == key) { s0 = sl.start; s1 = sl.end; break; }
-            if (sl.key == kEmptyKey) break;
-            h = (h + 1) & mask;
-          }
-          for (int t = s0; t < s1; ++t) {
-            const float4 tp = sorted[t];
-            const float ex = qx - tp.x, ey = qy - tp.y, ez = qz - tp.z;
-            const float d = (ex * ex + ey * ey) + ez * ez;
-            if (d < best) best = d;
-          }
+    const int side = 2 * ring + 1, cells = side * side * side;
+    if (live)
+      for (int c = g; c < cells; c += kNNGroup) {
+        const int dx = c % side - ring, dy = (c / side) % side - ring, dz = c / (side * side) - ring;
+        if (max(abs(dx), max(abs(dy), abs(dz))) != ring) continue;
+        const int a = ci + dx, b = cj + dy, cc = ck + dz;
+        if (!coord_ok(a) || !coord_ok(b) || !coord_ok(cc)) continue;
+        const unsigned long long key = pack_key(a, b, cc);
+        uint32_t h = hash_key(key) & mask;
+        int s0 = 0, s1 = 0;
+        while (true) {
+          const CellSlot sl = slots[h];
+          if (sl.key == key) { s0 = sl.start; s1 = sl.end; break; }
+          if (sl.key == kEmptyKey) break;
+          h = (h + 1) & mask;
         }
+        for (int t = s0; t < s1; ++t) {
+          const float4 tp = sorted[t];
+          const float ex = qx - tp.x, ey = qy - tp.y, ez = qz - tp.z;
+          const float d = (ex * ex + ey * ey) + ez * ez;
+          if (d < best) best = d;
+        }
+      }
+    // the group's minimum (groups are aligned 8-lane segments of a warp and shuffle under their own mask: `best`, hence every
+    // loop exit, is uniform inside a group, while the groups of a warp leave the loop at different rings)
+#pragma unroll
+    for (int o = kNNGroup / 2; o > 0; o >>= 1) best = fminf(best, __shfl_xor_sync(gmask, best, o));
   }
-  d2_out[i] = best;
-  if (!certain) far_idx[atomicAdd(far_count, 1)] = (int)i;
+  if (live && g == 0) {
+    d2_out[i] = best;
+    if (!certain) far_idx[atomicAdd(far_count, 1)] = (int)i;
+  }
 }
 // The open queries against EVERY target point: one thread per query, the target streamed through shared memory in
 // tiles (the minimum of the same float expression, so the result is the exact 1-NN distance whatever the order).
@@ -1339,7 +1353,7 @@ cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float*
   CK(cudaMemsetAsync(g->far_count, 0, sizeof(int), s));
   // small target: hand a query to the exhaustive pass early (its cost is n_far * n_tgt); large target: keep walking rings
   const int max_ring = g->n <= (size_t)1 << 17 ? 2 : 8;
-  k_nn_query<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(g->sorted, g->n, g->slots, g->mask, g->cell, src, n, T16_dev, max_ring, d2_out,
+  k_nn_query<<<(unsigned)((n * kNNGroup + 127) / 128), 128, 0, s>>>(g->sorted, g->n, g->slots, g->mask, g->cell, src, n, T16_dev, max_ring, d2_out,
                                                          g->far_idx, g->far_count);
   unsigned slices = (unsigned)((g->n + 2047) / 2048);
   if (slices > 64) slices = 64;
