@@ -390,13 +390,20 @@ def run_c5(a):
         out[:, 19] = res["trans_probability"]; out[:, 20] = res["n_evals"]
         return out
 
+    pin_in = torch.zeros((width, shard.RESULT_WIDTH), dtype=torch.float64).pin_memory() if world > 1 else None
+    pin_out = torch.zeros((world * width, shard.RESULT_WIDTH), dtype=torch.float64).pin_memory() if world > 1 else None
+
     def gather(res):
-        """The job's only exchange: every rank's result rows to every rank (21 doubles per registration), over NCCL."""
+        """The job's only exchange: every rank's result rows to every rank (21 doubles per registration), over NCCL; staged
+        through page-locked buffers, one stream synchronisation at the end."""
         if len(res):
-            gather_buf[:len(res)].copy_(torch.from_numpy(pack(res)), non_blocking=False)
+            pin_in.numpy()[:len(res)] = pack(res)
+        gather_buf.copy_(pin_in, non_blocking=True)
         dist.all_gather_into_tensor(gather_out, gather_buf)
+        pin_out.copy_(gather_out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
         full = np.zeros((n_total, shard.RESULT_WIDTH))
-        g = gather_out.cpu().numpy()
+        g = pin_out.numpy()
         for r in range(world):
             if len(plan[r]):
                 full[plan[r]] = g[r * width:r * width + len(plan[r])]

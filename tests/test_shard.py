@@ -32,6 +32,23 @@ def test_plan_is_a_balanced_partition_grouped_by_target():
         assert n_build <= len(np.unique(it)) + world - 1                   # table builds: at most one extra per cut
 
 
+def test_plan_deals_whole_submaps_round_robin_when_that_is_balanced():
+    """The C5 shape: 64 submaps x 64 registrations.  Every submap's table is built on exactly one rank, the ranks hold equal
+    item counts, and neighbouring submaps (correlated difficulty) sit on different ranks."""
+    from xchu_slam_b200 import shard
+    it = np.repeat(np.arange(64), 64)
+    for world in (2, 4, 8):
+        plan = shard.plan_shards(it, world)
+        assert sorted(np.concatenate(plan).tolist()) == list(range(4096))
+        assert all(len(p) == 4096 // world for p in plan)
+        owners = [set(np.unique(it[p]).tolist()) for p in plan]
+        assert sum(len(o) for o in owners) == 64                            # no table built twice
+        for r, o in enumerate(owners):
+            assert o == set(range(r, 64, world))
+        for p in plan:
+            assert np.all(np.diff(it[p]) >= 0)                              # items of a rank stay grouped by target
+
+
 def test_plan_more_ranks_than_items():
     from xchu_slam_b200 import shard
     plan = shard.plan_shards([0, 0, 1], 8)

@@ -2074,10 +2074,32 @@ int ndtb_multi_run(ndtb_multi* m, int n_targets, const void* const* target_pts, 
     if (item_target[i] < 0 || item_target[i] >= n_targets) { m->err = "item target id out of range"; return 1; }
     if (item_source[i] < 0 || item_source[i] >= n_sources) { m->err = "item source id out of range"; return 1; }
   }
-  // plan: items by target id (stable), contiguous blocks of n/D (+1 for the first n%D devices) -- shard.plan_shards in Python
+  // plan (shard.plan_shards in Python): whole submaps dealt round-robin in target-id order when that leaves the devices' item
+  // counts within max(1, 2 %) of each other -- every table built once, neighbouring submaps (hard or easy together) on different
+  // devices -- else items by target id (stable) in contiguous blocks of n/D (+1 for the first n%D devices)
   std::vector<int> order((size_t)n_items);
   for (int i = 0; i < n_items; ++i) order[i] = i;
   std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return item_target[a] < item_target[b]; });
+  std::vector<int> dev_first((size_t)D, 0), dev_count((size_t)D, 0);
+  {
+    std::vector<int> rank_of_target((size_t)n_targets, -1), sizes((size_t)D, 0);
+    int distinct = 0;
+    for (int k = 0; k < n_items; ++k) {
+      int& r = rank_of_target[item_target[order[k]]];
+      if (r < 0) r = distinct++ % D;
+      ++sizes[r];
+    }
+    const int mx = *std::max_element(sizes.begin(), sizes.end()), mn = *std::min_element(sizes.begin(), sizes.end());
+    if (D > 1 && distinct >= D && mx - mn <= std::max(1, (int)(0.02 * n_items / D))) {
+      std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return rank_of_target[item_target[a]] < rank_of_target[item_target[b]]; });
+      int pos = 0;
+      for (int d = 0; d < D; ++d) { dev_first[d] = pos; dev_count[d] = sizes[d]; pos += sizes[d]; }
+    } else {
+      const int base = n_items / D, extra = n_items % D;
+      int pos = 0;
+      for (int d = 0; d < D; ++d) { dev_first[d] = pos; dev_count[d] = base + (d < extra ? 1 : 0); pos += dev_count[d]; }
+    }
+  }
   std::vector<std::string> errs((size_t)D);
   auto work = [&](int d, int first, int count) {
     const auto t0 = std::chrono::steady_clock::now();
@@ -2109,13 +2131,8 @@ int ndtb_multi_run(ndtb_multi* m, int n_targets, const void* const* target_pts, 
     m->st_wall_ms[d] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
   };
   std::vector<std::thread> th;
-  const int base = n_items / D, extra = n_items % D;
-  int pos = 0;
-  for (int d = 0; d < D; ++d) {
-    const int cnt = base + (d < extra ? 1 : 0);
-    if (cnt > 0) th.emplace_back(work, d, pos, cnt);
-    pos += cnt;
-  }
+  for (int d = 0; d < D; ++d)
+    if (dev_count[d] > 0) th.emplace_back(work, d, dev_first[d], dev_count[d]);
   for (auto& t : th) t.join();
   for (int d = 0; d < D; ++d)
     if (!errs[d].empty()) { m->err = errs[d]; return 1; }
