@@ -209,6 +209,18 @@ NNGridStorage* nn_create();
 void nn_destroy(NNGridStorage* g);
 cudaError_t nn_build(NNGridStorage* g, BuildWorkspace* ws, const float4* pts, size_t n, float cell, const float* bbox,
                      cudaStream_t s, long long* launches);
+// Morton order of the sources of a batch (ndt_api.cu run_items): every point of every source -> (source ordinal, 18-bit Morton
+// code of its 2 m cell) -> one radix sort of (key, point) pairs -> `out`, where source k occupies [first_k, first_k + n_k) as in
+// the input numbering, its points now in Morton order.  Grow-only workspace.
+struct SrcDesc { const float4* p; unsigned int first, n; };
+struct SourceOrderWs {
+  SrcDesc* desc = nullptr; size_t desc_cap = 0;
+  unsigned int *k_in = nullptr, *k_out = nullptr; float4* v_in = nullptr; size_t cap = 0;
+  void* temp = nullptr; size_t temp_bytes = 0;
+};
+void source_order_free(SourceOrderWs& w);
+cudaError_t source_order_sort(SourceOrderWs& w, const SrcDesc* desc_host, int n_src, size_t total, float4* out, cudaStream_t s,
+                              long long* launches);
 cudaError_t d2_reduce(const float* d2, size_t n, double max_range, double* out2_dev, cudaStream_t s);   // {sum, count} of d2 <= max_range
 cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float* T16_dev, float* d2_out,
                      cudaStream_t s);

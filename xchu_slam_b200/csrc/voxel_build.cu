@@ -1363,6 +1363,70 @@ cudaError_t nn_query(NNGridStorage* g, const float4* src, size_t n, const float*
   return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------
+// Morton order of a batch's sources (see ndt_internal.h)
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned int spread3(unsigned int v) {   // 6 bits -> every third bit
+  v &= 0x3Fu;
+  v = (v | (v << 8)) & 0x0000F00Fu;   // only the low 6 bits are populated: the masks of the 10-bit version, truncated
+  v = (v | (v << 4)) & 0x000C30C3u;
+  v = (v | (v << 2)) & 0x00249249u;
+  return v;
+}
+__global__ void k_source_keys(const SrcDesc* __restrict__ desc, int n_src, size_t total, unsigned int* __restrict__ keys,
+                              float4* __restrict__ vals) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  int lo = 0, hi = n_src - 1;              // the last source whose first point is <= t
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if ((size_t)desc[mid].first <= t) lo = mid; else hi = mid - 1;
+  }
+  const SrcDesc d = desc[lo];
+  const float4 p = d.p[t - d.first];
+  const int a = __float2int_rd(p.x * 0.5f), b = __float2int_rd(p.y * 0.5f), c = __float2int_rd(p.z * 0.5f);   // 2 m cells, wrapped at 64
+  const unsigned int m = spread3((unsigned int)a) | (spread3((unsigned int)b) << 1) | (spread3((unsigned int)c) << 2);
+  keys[t] = ((unsigned int)lo << 18) | m;
+  vals[t] = p;
+}
+void source_order_free(SourceOrderWs& w) {
+  cudaFree(w.desc); cudaFree(w.k_in); cudaFree(w.k_out); cudaFree(w.v_in); cudaFree(w.temp);
+  w = SourceOrderWs();
+}
+cudaError_t source_order_sort(SourceOrderWs& w, const SrcDesc* desc_host, int n_src, size_t total, float4* out, cudaStream_t s,
+                              long long* launches) {
+  if (n_src <= 0 || total == 0) return cudaSuccess;
+  if ((size_t)n_src > w.desc_cap) {
+    cudaFree(w.desc); w.desc = nullptr; w.desc_cap = 0;
+    CK(cudaMalloc(&w.desc, ((size_t)n_src + 64) * sizeof(SrcDesc)));
+    w.desc_cap = (size_t)n_src + 64;
+  }
+  if (total > w.cap) {
+    cudaFree(w.k_in); cudaFree(w.k_out); cudaFree(w.v_in);
+    w.k_in = w.k_out = nullptr; w.v_in = nullptr; w.cap = 0;
+    const size_t nc = total + total / 8;
+    CK(cudaMalloc(&w.k_in, nc * sizeof(unsigned int)));
+    CK(cudaMalloc(&w.k_out, nc * sizeof(unsigned int)));
+    CK(cudaMalloc(&w.v_in, nc * sizeof(float4)));
+    w.cap = nc;
+  }
+  int bits = 18;
+  while (bits < 32 && (1u << (bits - 18)) < (unsigned int)n_src) ++bits;
+  size_t need = 0;
+  CK(cub::DeviceRadixSort::SortPairs(nullptr, need, w.k_in, w.k_out, w.v_in, out, (int)total, 0, bits, s));
+  if (need > w.temp_bytes) {
+    cudaFree(w.temp); w.temp = nullptr; w.temp_bytes = 0;
+    CK(cudaMalloc(&w.temp, need + need / 4 + 256));
+    w.temp_bytes = need + need / 4 + 256;
+  }
+  CK(cudaMemcpyAsync(w.desc, desc_host, (size_t)n_src * sizeof(SrcDesc), cudaMemcpyHostToDevice, s));
+  k_source_keys<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(w.desc, n_src, total, w.k_in, w.v_in);
+  size_t tb = w.temp_bytes;
+  CK(cub::DeviceRadixSort::SortPairs(w.temp, tb, w.k_in, w.k_out, w.v_in, out, (int)total, 0, bits, s));
+  if (launches) *launches += 3 + (bits + 7) / 8;
+  return cudaGetLastError();
+}
+
 // getFitnessScore of one registration: sum and count of the squared distances <= max_range, one block, fixed order (thread-
 // strided partial sums, then lanes, then warps) -- the host reads 16 bytes instead of one float per source point.
 __global__ void __launch_bounds__(1024) k_d2_reduce(const float* __restrict__ d2, size_t n, double max_range, double* __restrict__ out) {
