@@ -88,7 +88,9 @@ int ndtb_set_params(ndtb_handle* h, const ndtb_params* p);
 int ndtb_get_params(const ndtb_handle* h, ndtb_params* p);
 
 /* ---- target: VoxelGridCovariance build (NDT_H:117-122 setInputTarget -> init() ->
- *      voxel_grid_covariance_omp_impl.hpp:48-370 applyFilter) ----------------------------- */
+ *      voxel_grid_covariance_omp_impl.hpp:48-370 applyFilter) ----------------------------- 
+ * Points with a NaN / Inf coordinate are skipped, as the reference's first pass skips them for non-dense clouds
+ * (voxel_grid_covariance_omp_impl.hpp:209-215); the finite points keep their relative order. */
 int ndtb_set_target(ndtb_handle* h, const void* pts, size_t n, size_t stride_bytes);
 /* If the first points of `pts` are bit-identical to the current target (odom_node only ever
  * appends between window resets, src/odom_node.cpp:336), only the new tail is merged into the

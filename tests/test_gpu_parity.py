@@ -85,6 +85,36 @@ def test_voxel_grid_build_paths_give_identical_tables(case_small):
     assert np.array_equal(a["ijk"], b["ijk"])
 
 
+@pytest.mark.parametrize("dense", [True, False])
+def test_non_finite_target_points_are_skipped(case_small, dense):
+    """VGC_I:209-215: a non-dense cloud's points with a NaN / Inf coordinate are skipped in the first pass.  The table built from a
+    cloud with such rows equals, bit for bit, the table built from its finite rows alone (same relative order) -- on both build
+    paths -- and an align against it runs as usual."""
+    from xchu_slam_b200 import ndt
+    src, tgt, gt, guess = case_small
+    rng = np.random.default_rng(11)
+    dirty = tgt.copy()
+    rows = rng.choice(len(dirty), len(dirty) // 100, replace=False)
+    dirty[rows[0::3], 0] = np.nan
+    dirty[rows[1::3], 1] = np.inf
+    dirty[rows[2::3], 2] = -np.inf
+    clean = tgt[np.all(np.isfinite(dirty[:, :3]), axis=1)]
+    tabs = []
+    for cloud in (dirty, clean):
+        g = ndt.NormalDistributionsTransform()
+        g.setTransformationEpsilon(0.01)
+        if not dense:
+            g.setDenseMaxCells(0)
+        g.setInputTarget(cloud)
+        g.setInputSource(src)
+        g.align(guess)
+        tabs.append((g.dumpVoxels(), g.result()))
+    (a, ra), (b, rb) = tabs
+    for k in ("ijk", "nr_points", "n_raw", "mean", "icov64", "centroid"):
+        assert np.array_equal(a[k], b[k]), k
+    assert ra["iterations"] == rb["iterations"] and np.array_equal(ra["T"], rb["T"])
+
+
 @pytest.mark.parametrize("res", [0.5, 2.0])
 def test_voxel_grid_build_resolutions(case_small, res):
     o, g = _mk(case_small, res=res)
