@@ -14,6 +14,11 @@ from xchu_slam_b200 import build as b  # noqa: E402
 VARIANTS = {
     # strict (term-by-term) kernel: the round-2 default is shared-memory FP64 accumulators + neighbour loop not unrolled + two
     # blocks per SM (profiles/r02/r02_c4_strict_variants.txt, r02_c5_strict_variants.txt); these rebuild the earlier settings
+    # leading accumulators (score, gradient, first Hessian rows) in registers, the rest in shared memory: the final binary's
+    # strict kernel is bound by its shared-memory traffic (L1/TEX 93 %, profiles/r02/r02_final_deriv_strict_full.txt)
+    "strict_reg7": ("NDTB_STRICT_REG_ACCS=7",),
+    "strict_reg13": ("NDTB_STRICT_REG_ACCS=13",),
+    "strict_reg19": ("NDTB_STRICT_REG_ACCS=19",),
     "strict_r01": ("NDTB_NOUNROLL=0", "NDTB_STRICT_ACC_SMEM=0", "NDTB_MINBLOCKS=1"),
     "strict_nounroll_regs": ("NDTB_NOUNROLL=1", "NDTB_STRICT_ACC_SMEM=0", "NDTB_MINBLOCKS=1"),
 }

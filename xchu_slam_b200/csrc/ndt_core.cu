@@ -37,11 +37,17 @@ namespace ndtb {
 #define NDTB_STRICT_ACC_SMEM 1  //    takes 86 registers off the kernel -> two resident blocks per SM instead of one (with the
                                 //    loop not unrolled: -10.7 % kernel time; with it unrolled +23 %: profiles/r02/r02_c5_strict_variants.txt)
 #endif
+#ifndef NDTB_STRICT_REG_ACCS   // with NDTB_STRICT_ACC_SMEM: the first N of the 43 accumulators (score, gradient, then Hessian rows) stay
+#define NDTB_STRICT_REG_ACCS 0  //    in registers, the rest live in shared memory: N / 43 less shared-memory traffic per pair
+#endif
 constexpr int kThreads = NDTB_THREADS;
 #if NDTB_STRICT_ACC_SMEM
 constexpr int kAccStride = kThreads + 1;
-#define ACC(k) acc[(k) * kAccStride]
+constexpr int kRegAccs = NDTB_STRICT_REG_ACCS;
+#define SACC(k) acc[(k) * kAccStride]
+#define ACC(k) (*((k) < kRegAccs ? &gacc[(k) < kRegAccs ? (k) : 0] : &acc[(k) * kAccStride]))
 #else
+#define SACC(k) acc[(k)]
 #define ACC(k) acc[(k)]
 #endif
 
@@ -72,7 +78,7 @@ __device__ __forceinline__ RecRegs load_rec(const VoxelRec* __restrict__ recp) {
 }
 
 template <bool CH>
-__device__ __forceinline__ void pair_update_r(double* acc, const RecRegs& rr, float xtx, float xty, float xtz,
+__device__ __forceinline__ void pair_update_r(double* acc, double* gacc, const RecRegs& rr, float xtx, float xty, float xtz,
                                               const float* __restrict__ pd /* smem column, stride kThreads */, float d2f, double d1) {
 #if NDTB_PD_SMEM
 #define PGV(r) pd[(r) * kThreads]
@@ -232,7 +238,15 @@ __global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const 
   double acc[kAccN];
 #endif
 #pragma unroll
-  for (int k = 0; k < kAccN; ++k) ACC(k) = 0.0;
+  for (int k = 0; k < kAccN; ++k) SACC(k) = 0.0;
+#if NDTB_STRICT_ACC_SMEM
+  double gacc[kRegAccs > 0 ? kRegAccs : 1];
+#pragma unroll
+  for (int k = 0; k < (kRegAccs > 0 ? kRegAccs : 1); ++k) gacc[k] = 0.0;
+#else
+  double* gacc = nullptr;
+  (void)gacc;
+#endif
   int npairs = 0;
   const float4* __restrict__ src = st.src;
   const int end = min(bm.y + chunk, st.n_src);
@@ -271,16 +285,20 @@ __global__ void __launch_bounds__(kThreads, NDTB_MINBLOCKS) k_derivatives(const 
     for (int k = 0; k < cnt; ++k) {
       const RecRegs use = cur;
       if (k + 1 < cnt) cur = load_rec(recs + nb[k + 1]);
-      pair_update_r<CH>(acc, use, xt, yt, zt, pdv, d2f, d1);
+      pair_update_r<CH>(acc, gacc, use, xt, yt, zt, pdv, d2f, d1);
     }
 #else
     for (int k = 0; k < cnt; ++k) {
       const RecRegs use = load_rec(recs + nb[k]);
-      pair_update_r<CH>(acc, use, xt, yt, zt, pdv, d2f, d1);
+      pair_update_r<CH>(acc, gacc, use, xt, yt, zt, pdv, d2f, d1);
     }
 #endif
     npairs += cnt;
   }
+#if NDTB_STRICT_ACC_SMEM
+#pragma unroll
+  for (int k = 0; k < kRegAccs; ++k) SACC(k) = gacc[k];
+#endif
 #if NDTB_STRICT_ACC_SMEM
   block_reduce_store_resident(npairs, partials + (size_t)blockIdx.x * kPartialStride);
 #else
