@@ -38,7 +38,7 @@ namespace ndtb {
                                 //    loop not unrolled: -10.7 % kernel time; with it unrolled +23 %: profiles/r02/r02_c5_strict_variants.txt)
 #endif
 #ifndef NDTB_STRICT_REG_ACCS   // with NDTB_STRICT_ACC_SMEM: the first N of the 43 accumulators (score, gradient, then Hessian rows) stay
-#define NDTB_STRICT_REG_ACCS 0  //    in registers, the rest live in shared memory: N / 43 less shared-memory traffic per pair
+#define NDTB_STRICT_REG_ACCS 7  //    in registers, the rest live in shared memory: N / 43 less shared-memory traffic per pair
 #endif
 constexpr int kThreads = NDTB_THREADS;
 #if NDTB_STRICT_ACC_SMEM
