@@ -135,6 +135,22 @@ int ndtb_host_free(void* p);
 /* Neighbour voxels (VGC_I:373-442 / VGC_H:470-499) of n already transformed xyz points;
  * cnt[n], ijk[n][27][3] in visiting order. */
 int ndtb_neighbors(ndtb_handle* h, const float* xyz, size_t n, int method, int* cnt, int* ijk);
+/* getFitnessScore without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The value is
+ * ndtb_fitness's (mean, in double, of the float squared distances <= max_range from every source point moved by T -- column-major
+ * 4x4, host memory -- to its exact nearest target point; DBL_MAX when no point is in range), computed by the exhaustive query
+ * kernel (n_source x n_target distance evaluations) instead of the cell grid, whose build allocates.
+ *   source_dev / target_dev: DEVICE pointers on `device`, 16-byte records (x y z _), caller-owned; out_dev: DEVICE pointer to one
+ *   double; cuda_stream: a cudaStream_t (NULL = the default stream).  Enqueues three kernels and returns WITHOUT synchronising;
+ *   calls no cudaMalloc / cudaFree / allocating library routine.
+ * Scratch: a file-scope __device__ array of NDTB_NOALLOC_MAX_SOURCE floats + 256 B (1 MiB; every GPU that loads the library holds
+ * it until exit).  n_source beyond that limit is rejected (returns 1, text from ndtb_noalloc_last_error).  Every call shares the
+ * array, which keeps the last call's contents -- each call re-arms what must start clean -- so two calls that overlap on the GPU
+ * (different streams or threads) RACE: serialise them.  Returns 0 on success. */
+#define NDTB_NOALLOC_MAX_SOURCE 262144
+int ndtb_fitness_noalloc(int device, const void* source_dev, size_t n_source, const void* target_dev, size_t n_target, const float T[16],
+                         double max_range, double* out_dev, void* cuda_stream);
+const char* ndtb_noalloc_last_error(void);   /* per calling thread */
 /* One computeDerivatives (ndt_omp_impl.hpp:175-283) at transform T and pose vector p. */
 int ndtb_eval_derivatives(ndtb_handle* h, const float T[16], const double p[6], int compute_hessian,
                           double* score, double g[6], double H[36]);

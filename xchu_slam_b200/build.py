@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libndt_b200.so")
-SOURCES = ["voxel_build.cu", "ndt_core.cu", "ndt_fast.cu", "ndt_api.cu", "scancontext.cu"]
+SOURCES = ["voxel_build.cu", "ndt_core.cu", "ndt_fast.cu", "ndt_api.cu", "scancontext.cu", "no_alloc.cu"]
 # ndt_fast.cu carries explicit round-to-nearest intrinsics where bits matter and wants FMA contraction elsewhere
 NO_FMAD_FALSE = {"ndt_fast.cu"}
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",

@@ -16,6 +16,21 @@ LIB_PATH = os.environ.get("NDTB_LIB") or os.path.join(_HERE, "libndt_b200.so")  
 KDTREE, DIRECT26, DIRECT7, DIRECT1 = 0, 1, 2, 3
 
 
+NOALLOC_MAX_SOURCE = 262144     # NDTB_NOALLOC_MAX_SOURCE (ndt_c_api.h)
+
+
+def fitness_noalloc(device, source_ptr, n_source, target_ptr, n_target, T, max_range, out_ptr, stream=0):
+    """ndtb_fitness_noalloc: getFitnessScore with every buffer the caller's (DEVICE pointers as integers; `out_ptr` -> one double on
+    the device; `stream` a cudaStream_t as integer) and its scratch in a static device array: no allocation, no synchronisation.
+    No counterpart in the reference.  Raises NdtError with the library's text on rejection."""
+    L = load_library()
+    Tc = _colmajor(T)
+    rc = L.ndtb_fitness_noalloc(int(device), C.c_void_p(source_ptr), int(n_source), C.c_void_p(target_ptr), int(n_target), _p(Tc),
+                                float(max_range), C.c_void_p(out_ptr), C.c_void_p(stream))
+    if rc != 0:
+        raise NdtError(L.ndtb_noalloc_last_error().decode())
+
+
 class NdtError(RuntimeError):
     pass
 
@@ -51,7 +66,7 @@ class BatchStats(C.Structure):
 # every symbol include/ndt_b200/ndt_c_api.h declares
 SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_params", "ndtb_set_params", "ndtb_get_params",
            "ndtb_set_target", "ndtb_set_target_auto", "ndtb_update_target", "ndtb_set_source", "ndtb_align", "ndtb_get_output",
-           "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_dump_icov64", "ndtb_pose_to_matrix", "ndtb_host_alloc", "ndtb_host_free", "ndtb_neighbors",
+           "ndtb_fitness", "ndtb_calculate_score", "ndtb_num_voxels", "ndtb_dump_voxels", "ndtb_dump_icov64", "ndtb_pose_to_matrix", "ndtb_host_alloc", "ndtb_host_free", "ndtb_fitness_noalloc", "ndtb_noalloc_last_error", "ndtb_neighbors",
            "ndtb_eval_derivatives", "ndtb_compute_hessian", "ndtb_get_trace", "ndtb_last_timing", "ndtb_batch_create",
            "ndtb_batch_destroy", "ndtb_batch_last_error", "ndtb_batch_set_params", "ndtb_batch_clear", "ndtb_batch_add_target",
            "ndtb_batch_add_source", "ndtb_batch_wait_uploads", "ndtb_batch_run", "ndtb_batch_get_stats", "ndtb_batch_set_stream", "ndtb_batch_fitness",
@@ -99,6 +114,9 @@ def load_library():
     L.ndtb_pose_to_matrix.restype = None
     L.ndtb_host_alloc.argtypes = [sz, C.POINTER(vp)]
     L.ndtb_host_free.argtypes = [vp]
+    L.ndtb_fitness_noalloc.argtypes = [C.c_int, vp, sz, vp, sz, vp, C.c_double, vp, vp]
+    L.ndtb_noalloc_last_error.argtypes = []
+    L.ndtb_noalloc_last_error.restype = C.c_char_p
     L.ndtb_neighbors.argtypes = [vp, vp, sz, C.c_int, vp, vp]
     L.ndtb_eval_derivatives.argtypes = [vp, vp, vp, C.c_int, C.POINTER(C.c_double), vp, vp]
     L.ndtb_compute_hessian.argtypes = [vp, vp, vp, vp]
