@@ -302,6 +302,9 @@ int ndtb_batch_get_stats(ndtb_batch* b, ndtb_batch_stats* s);
  * pass (a discrete decision taken within 1e-3 of its threshold; line-search steps that grew after having dropped below
  * step_size; |delta_p| of the last Newton solve, NDT_I:119-125).  Test / tuning hook. */
 int ndtb_batch_get_diag(ndtb_batch* b, int* replayed, int* borderline, int* n_rise, double* last_norm);
+/* norms[i * max_steps + k] = |delta_p| of the Newton solve of iteration k of item i's FINAL pass (NDT_I:119-125; the first 32
+ * iterations, 0 beyond the last one).  Test / tuning hook: the data the replay criterion of the hybrid mode is studied on. */
+int ndtb_batch_get_step_history(ndtb_batch* b, float* norms, int max_steps);
 /* Run all of the batch's copies and kernels on the caller's CUDA stream (a cudaStream_t) instead of
  * the batch's own, so that the caller's CUDA events bracket the work. */
 int ndtb_batch_set_stream(ndtb_batch* b, void* cuda_stream);

@@ -16,6 +16,13 @@ VARIANTS = {
     # blocks per SM (profiles/r02/r02_c4_strict_variants.txt, r02_c5_strict_variants.txt); these rebuild the earlier settings
     # leading accumulators (score, gradient, first Hessian rows) in registers, the rest in shared memory: the final binary's
     # strict kernel is bound by its shared-memory traffic (L1/TEX 93 %, profiles/r02/r02_final_deriv_strict_full.txt)
+    # strict kernel at three 128-thread blocks per SM (168 registers): most of the 43 accumulators fit in registers without spills
+    "strict_t128_b3_r25": ("NDTB_THREADS=128", "NDTB_MINBLOCKS=3", "NDTB_STRICT_REG_ACCS=25"),
+    "strict_t128_b3_r31": ("NDTB_THREADS=128", "NDTB_MINBLOCKS=3", "NDTB_STRICT_REG_ACCS=31"),
+    "strict_t128_b3_r37": ("NDTB_THREADS=128", "NDTB_MINBLOCKS=3", "NDTB_STRICT_REG_ACCS=37"),
+    "strict_t192_b2_r31": ("NDTB_THREADS=192", "NDTB_MINBLOCKS=2", "NDTB_STRICT_REG_ACCS=31"),
+    # factorised kernel with the scalar core of every pair (w, q, exp, f) in the reference's float operations
+    "fast_exactcore": ("NDTB_FAST_EXACT_CORE=1",),
     "strict_reg7": ("NDTB_STRICT_REG_ACCS=7",),
     "strict_reg13": ("NDTB_STRICT_REG_ACCS=13",),
     "strict_reg19": ("NDTB_STRICT_REG_ACCS=19",),

@@ -2051,6 +2051,15 @@ int ndtb_batch_get_diag(ndtb_batch* b, int* replayed, int* borderline, int* n_ri
   }
   return 0;
 }
+int ndtb_batch_get_step_history(ndtb_batch* b, float* norms, int max_steps) {
+  Engine& e = b->e;
+  const size_t n = e.last_item_target.size();
+  if (n == 0 || !e.h_states) return e.fail("ndtb_batch_get_step_history needs a completed ndtb_batch_run");
+  if (!norms || max_steps < 1) return e.fail("ndtb_batch_get_step_history: norms must hold items x max_steps floats");
+  for (size_t i = 0; i < n; ++i)
+    for (int k = 0; k < max_steps; ++k) norms[i * (size_t)max_steps + k] = k < 32 ? e.h_states[i].norm_hist[k] : 0.f;
+  return 0;
+}
 int ndtb_batch_set_stream(ndtb_batch* b, void* cuda_stream) {
   Engine& e = b->e;
   cudaSetDevice(e.device);

@@ -780,6 +780,7 @@ __device__ void newton_top(NewtonCtx& c) {
     a_t = fmax(a_t, step_min);
     st.a_t = a_t;
     st.last_norm = norm;
+    if (st.nr_iterations >= 0 && st.nr_iterations < 32) st.norm_hist[st.nr_iterations] = (float)norm;
     if (st.nr_iterations > 0 && a_t > st.prev_at && st.prev_at < step_max) st.n_rise++;
     st.prev_at = a_t;
     st.min_at = st.nr_iterations > 0 ? fmin(st.min_at, a_t) : a_t;

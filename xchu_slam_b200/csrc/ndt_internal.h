@@ -131,6 +131,7 @@ struct AlignState {
   int borderline, n_rise;
   int abort_iters;           // > 0 (first pass of a hybrid batch): leave the loop unconverged once nr_iterations exceeds it
   double last_norm, prev_at, min_at;
+  float norm_hist[32];       // |delta_p| of the Newton solve of iteration k (diagnostics: ndtb_batch_get_step_history)
 };
 
 constexpr int kTraceRec = 52;  // doubles per trace record (see ndtb_get_trace)

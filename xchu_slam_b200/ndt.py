@@ -74,7 +74,7 @@ SYMBOLS = ["ndtb_create", "ndtb_destroy", "ndtb_last_error", "ndtb_default_param
            "ndtb_localmap_roll", "ndtb_localmap_sizes", "ndtb_localmap_download", "ndtb_default_filter_params", "ndtb_filter_scan",
            "ndtb_get_source", "ndtb_batch_add_keyframe", "ndtb_batch_clear_keyframes", "ndtb_batch_num_keyframes",
            "ndtb_batch_add_submap", "ndtb_batch_download", "ndtb_batch_add_targets", "ndtb_batch_add_sources",
-           "ndtb_batch_add_submaps", "ndtb_batch_get_diag", "ndtb_multi_create", "ndtb_multi_destroy", "ndtb_multi_last_error",
+           "ndtb_batch_add_submaps", "ndtb_batch_get_diag", "ndtb_batch_get_step_history", "ndtb_multi_create", "ndtb_multi_destroy", "ndtb_multi_last_error",
            "ndtb_multi_set_params", "ndtb_multi_run", "ndtb_multi_get_stats", "ndtb_window_add_source", "ndtb_window_drop",
            "ndtb_window_clear", "ndtb_window_set_target", "ndtb_get_target"]
 
@@ -136,6 +136,7 @@ def load_library():
     L.ndtb_batch_run.argtypes = [vp, C.c_int, vp, vp, vp, vp]
     L.ndtb_batch_get_stats.argtypes = [vp, C.POINTER(BatchStats)]
     L.ndtb_batch_get_diag.argtypes = [vp, vp, vp, vp, vp]
+    L.ndtb_batch_get_step_history.argtypes = [vp, vp, C.c_int]
     L.ndtb_window_add_source.argtypes = [vp, vp, C.c_float, C.POINTER(C.c_int), C.POINTER(sz)]
     L.ndtb_window_drop.argtypes = [vp, C.c_int]
     L.ndtb_window_clear.argtypes = [vp]
@@ -624,6 +625,12 @@ class BatchNDT:
         ln = np.zeros(n_items, np.float64)
         self._ck(self._L.ndtb_batch_get_diag(self._h, _p(rp), _p(bl), _p(nr), _p(ln)))
         return dict(replayed=rp, borderline=bl, n_rise=nr, last_norm=ln)
+
+    def step_history(self, n_items, max_steps=32):
+        """|delta_p| of every Newton solve of every item's final pass, (n_items, max_steps) float32 (0 beyond the last iteration)."""
+        out = np.zeros((n_items, max_steps), np.float32)
+        self._ck(self._L.ndtb_batch_get_step_history(self._h, _p(out), max_steps))
+        return out
 
     def stats(self):
         s = BatchStats()
