@@ -10,7 +10,7 @@ step inside the timed region: STRONG scaling, value = 4096 x steps / max-over-ra
 
   value : inputs resident in HBM when the timed region starts (device pointers handed to the C ABI)
   e2e   : same job through the C ABI with HOST (pinned) buffers; H2D of every cloud and D2H of the results inside the timed region
-  value_strict / value_factorised_only : the same resident job with strict_math 1 / 0 instead of the hybrid default
+  value_hybrid / value_factorised_only : the same resident job with strict_math -2 / 0 instead of the default (term-by-term kernel)
   --impl reference : the reference algorithm's CPU restatement (oracle/, OpenMP on all host cores) on a bounded sample
   --workload c1|c3|c4 : single-align latency lines (build / align / end to end) with the derivative kernel's roofline where ONE
           registration owns the voxel table; --workload c2 : scans/s of the odometry sequence, both refresh strategies
@@ -56,7 +56,7 @@ def parse():
     ap.add_argument("--no-cpp-pipeline", action="store_true", help="skip the examples/batch_pipeline.cpp arm of the e2e number")
     ap.add_argument("--no-variants", action="store_true", help="skip value_strict / value_factorised_only / the other scaling mode")
     ap.add_argument("--strict-math", type=int, default=int(os.environ.get("NDTB_BENCH_STRICT", -1)),
-                    help="-1 hybrid (library default for a batch), 0 factorised kernel only, 1 term-by-term kernel only")
+                    help="-1 library default (term-by-term kernel: the reference arithmetic by construction), -2 hybrid (factorised kernel + strict replay of flagged registrations), 0 factorised kernel only, 1 term-by-term kernel by name")
     ap.add_argument("--inflight", type=int, default=1,
                     help="batches in flight per GPU for `value` (host threads, one BatchNDT and stream each)")
     ap.add_argument("--inflight-e2e", type=int, default=2,
@@ -226,6 +226,11 @@ def cpu_sample(a, w, n_aligns, passes=1, with_one_thread=True):
         out["one_thread_as_shipped"] = {"value": 1.0 / (t1 + (t_build_all / n_built) / per_submap), "align_ms": 1e3 * t1, "aligns": int(len(ids[:8])),
                                         "note": "odom_node configures ndt_omp with ONE thread (src/odom_node.cpp:74)"}
     return out, results
+
+
+MODE_NAMES = {-1: "term-by-term kernel (library default: every float operation of the reference in its order)",
+              -2: "hybrid: factorised kernel, then strict replay of flagged registrations inside ndtb_batch_run",
+              0: "factorised kernel only", 1: "term-by-term kernel"}
 
 
 def parity_report(cpu_results, gpu_res, mode):
@@ -498,6 +503,24 @@ def run_c5(a):
             r["ms_e2e"], r["agg_e2e"], _ = timed(job, bset, False, steps, max(1, a.inflight_e2e), do_gather)
         return r
 
+    def as_fields(res):
+        if isinstance(res, np.ndarray) and res.dtype.names is None:      # gathered rows -> the fields the parity check reads
+            return {"T": res[:, :16], "iterations": res[:, 16].astype(int), "converged": res[:, 17].astype(int)}
+        return res
+
+    def sample_parity(res, job, mode_name):
+        """The registrations of the last timed step that the CPU oracle also ran, against it."""
+        res = as_fields(res)
+        have = set(int(i) for i in (job.idx if (main_mode == "weak" or world == 1) else range(n_total)))
+        cmp_items = {i: r for i, r in cpu_results.items() if i in have}
+        if main_mode == "weak" or world == 1:      # results are in the job's local order
+            pos = {int(i): k for k, i in enumerate(job.idx)}
+            order = sorted(cmp_items)
+            res = {"T": np.asarray(res["T"])[[pos[i] for i in order]], "iterations": np.asarray(res["iterations"])[[pos[i] for i in order]],
+                   "converged": np.asarray(res["converged"])[[pos[i] for i in order]]}
+            cmp_items = {k: cmp_items[i] for k, i in enumerate(order)}
+        return parity_report(cmp_items, res, mode_name)
+
     main_mode = a.scaling
     if main_mode == "weak" and jobs["weak"] is None:
         jobs["weak"] = Job(w, np.arange(n_total), dev)
@@ -511,16 +534,19 @@ def run_c5(a):
     extra = {}
     if not a.no_variants:
         vsteps = max(2, min(3, a.steps))
-        for name, strict in (("value_strict", 1), ("value_factorised_only", 0)):
+        for name, strict in (("value_hybrid", -2), ("value_factorised_only", 0)):
             if strict == a.strict_math:
                 continue
             bs = make_batches(1, strict)
             r = measure(jobs[main_mode], bs, main_mode == "strong" and world > 1, vsteps, 1, with_e2e=False)
             extra[name] = {"value": n_per_step * vsteps / (r["ms"] / 1e3), "ms_per_step": r["ms"] / vsteps, "steps": vsteps,
                            "strict_math": strict,
-                           "note": ("every registration with the term-by-term kernel (the reference's float operations in order)" if strict else
+                           "note": ("opt-in hybrid mode: factorised kernel, then a strict replay of the flagged registrations inside the same call; "
+                                    "24571 of 24576 registrations of six synthetic worlds inside the gate (profiles/r02/r02_c11_hybrid_seeds.txt)" if strict == -2 else
                                     "factorised kernel only, no strict replay: round 1's headline path; NOT parity-clean "
-                                    "(~0.8 % of registrations end outside 1e-4 m / 1e-5 rad)")}
+                                    "(~1 % of registrations end outside 1e-4 m / 1e-5 rad)")}
+            if rank == 0 and cb is not None:
+                extra[name]["parity_vs_cpu_sample"] = sample_parity(r["res"], jobs[main_mode], MODE_NAMES[strict])
             del bs
         if world > 1:
             other = "weak" if main_mode == "strong" else "strong"
@@ -545,21 +571,12 @@ def run_c5(a):
         e2e = n_per_step * a.steps / (M["ms_e2e"] / 1e3)
         line = c5_line(a, world, main_mode, value, e2e, M, agg, clocks, jobs[main_mode], n_per_step)
         line.update(extra)
-        res = M["res"]
-        if isinstance(res, np.ndarray) and res.dtype.names is None:      # gathered rows -> the fields the parity check reads
-            res = {"T": res[:, :16], "iterations": res[:, 16].astype(int), "converged": res[:, 17].astype(int)}
+        res = as_fields(M["res"])
         conv = int(np.count_nonzero(np.asarray(res["converged"])))
         line["converged_frac"] = conv / max(1, len(res["converged"]))
         line["mean_iterations"] = float(np.mean(res["iterations"]))
         if cb is not None:
-            have = set(int(i) for i in (jobs[main_mode].idx if (main_mode == "weak" or world == 1) else range(n_total)))
-            cmp_items = {i: r for i, r in cpu_results.items() if i in have}
-            if main_mode == "weak" or world == 1:      # results are in the job's local order
-                pos = {int(i): k for k, i in enumerate(jobs[main_mode].idx)}
-                res = {"T": np.asarray(res["T"])[[pos[i] for i in sorted(cmp_items)]], "iterations": np.asarray(res["iterations"])[[pos[i] for i in sorted(cmp_items)]],
-                       "converged": np.asarray(res["converged"])[[pos[i] for i in sorted(cmp_items)]]}
-                cmp_items = {k: cmp_items[i] for k, i in enumerate(sorted(cmp_items))}
-            par = parity_report(cmp_items, res, {-1: "hybrid (factorised kernel + strict replay)", 0: "factorised kernel only", 1: "term-by-term kernel"}[a.strict_math])
+            par = sample_parity(M["res"], jobs[main_mode], MODE_NAMES[a.strict_math])
             line["parity_vs_cpu_sample"] = par
             line["cpu_baseline"] = cb
             if not par["all_within_gate"] and a.strict_math != 0:
@@ -598,15 +615,19 @@ def cpp_pipeline(a, w, job, device):
     return out
 
 
-def roofline_block(agg, ms_total, clocks, K=7, sm_count=148, shared_tables=True):
-    """B_pt = 16 + 8*K + 48*h bytes per evaluated point (points and (point, voxel) pairs COUNTED by the kernel), over
-    the kernel's own time (CUDA events around every derivative launch of the first, factorised-kernel pass).  What BINDS the
-    kernel is stated from the ncu capture: with 64 registrations sharing each submap's table the gather is served by L2 (DRAM
-    traffic ~1 % of the algorithmic bytes), and the limiter is instruction issue / L1 look-ups -- `frac_issue` is the share of
-    the SMs' issue slots the kernel's warp instructions fill at the SM clock measured during the run."""
+def roofline_block(agg, ms_total, clocks, K=7, sm_count=148, shared_tables=True, strict=False):
+    """B_pt = 16 + 8*K + R*h bytes per evaluated point (R = 64-byte voxel record of the term-by-term kernel, 48-byte
+    record of the factorised one; points and (point, voxel) pairs COUNTED by the kernel), over the kernel's own time (CUDA events
+    around every derivative launch of the first pass).  What BINDS the kernel is stated from the ncu capture: with 64 registrations
+    sharing each submap's table the gather is served by L2 (DRAM traffic ~1 % of the algorithmic bytes), and the limiter is
+    instruction issue / the L1 (shared-memory) pipe -- `frac_issue` is the share of the SMs' issue slots the kernel's warp
+    instructions fill at the SM clock measured during the run."""
     peaks, ncu = load_peaks(), load_ncu_constants()
+    if strict:
+        ncu = ncu.get("strict", {})
+    rec = 64 if strict else 48
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    alg_bytes = agg["points_evaluated"] * (16 + 8 * K) + 48 * agg["pairs_evaluated"]
+    alg_bytes = agg["points_evaluated"] * (16 + 8 * K) + rec * agg["pairs_evaluated"]
     deriv_ms = agg["deriv_ms"]
     achieved = alg_bytes / (deriv_ms / 1e3) / 1e9 if deriv_ms > 0 else 0.0
     launches = max(1, int(agg["deriv_launches"]))
@@ -615,8 +636,15 @@ def roofline_block(agg, ms_total, clocks, K=7, sm_count=148, shared_tables=True)
     frac_issue = None
     if wi32 and deriv_ms > 0:
         frac_issue = (agg["points_evaluated"] / 32.0 * wi32) / (sm_count * 4 * (deriv_ms / 1e3) * sm_mhz * 1e6)
-    return {"bound": "issue slots / L1 look-ups (L2-resident gather; HBM is NOT the binding roof here)" if shared_tables else "hbm",
-            "kernel": "k_derivatives_fast<DIRECT7>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    if not shared_tables:
+        bound = "hbm"
+    elif strict:
+        bound = ("instruction issue + the FP64 accumulate path (f32->f64 converts on the XU pipe, shared-memory accumulators); "
+                 "L2-resident gather: HBM is NOT the binding roof here")
+    else:
+        bound = "issue slots / L1 look-ups (L2-resident gather; HBM is NOT the binding roof here)"
+    return {"bound": bound,
+            "kernel": "k_derivatives<DIRECT7> (term-by-term)" if strict else "k_derivatives_fast<DIRECT7>", "achieved": achieved, "peak": peak, "unit": "GB/s",
             "frac": achieved / peak if peak else None, "traffic": ncu.get("dram_bytes_per_launch"),
             "frac_issue": frac_issue, "warp_instructions_per_32_points": wi32, "sm_mhz_used": sm_mhz,
             "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s",
@@ -624,14 +652,16 @@ def roofline_block(agg, ms_total, clocks, K=7, sm_count=148, shared_tables=True)
             "kernel_ms_per_launch": deriv_ms / launches,
             "mean_neighbours_per_point": agg["pairs_evaluated"] / max(1, agg["points_evaluated"]),
             "kernel_share_of_step": agg["deriv_ms_max_rank"] / ms_total if ms_total else None,
-            "note": "achieved = algorithmic bytes (16 + 8*7 + 48*neighbours per evaluated point, counted by the kernel) / kernel time; "
-                    "`traffic` = DRAM bytes of one launch from the ncu capture named in profiles/roofline_traffic.json. frac above 1 means "
-                    "the gather is served by L2, not HBM; the HBM-bound case is the single-align line of --workload c3"}
+            "note": "achieved = algorithmic bytes (16 + 8*7 + %d*neighbours per evaluated point, counted by the kernel) / kernel time; "
+                    "`traffic` = DRAM bytes of one launch from the ncu capture named in profiles/roofline_traffic.json. The gather is "
+                    "served by L2 (64 registrations share a table), so the fraction of the HBM roof says how close the kernel runs to "
+                    "what HBM could feed, not what binds it: that is `bound` / `frac_issue`; the HBM-bound case is the single-align "
+                    "line of --workload c3" % rec}
 
 
 def c5_line(a, world, mode, value, e2e, M, agg, clocks, job, n_per_step):
     ms, steps = M["ms"], a.steps
-    rf = roofline_block(agg, ms, clocks)
+    rf = roofline_block(agg, ms, clocks, strict=a.strict_math in (-1, 1))
     ae = M["agg_e2e"]
     return {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": a.warmup,
             "ms_per_step": ms / steps, "higher_is_better": True, "scaling": mode, "vs_baseline": None,
@@ -640,8 +670,7 @@ def c5_line(a, world, mode, value, e2e, M, agg, clocks, job, n_per_step):
                     "ms_per_step": M["ms_e2e"] / steps, "batches_in_flight": max(1, a.inflight_e2e),
                     "bytes_are": "per rank (this rank's shard of the job)" if mode == "strong" and world > 1 else "per rank"},
             "gpu_launches": int(agg["kernel_launches"]),
-            "kernel_mode": {-1: "hybrid: factorised kernel, then strict replay of flagged registrations inside ndtb_batch_run",
-                            0: "factorised kernel only", 1: "term-by-term kernel only"}[a.strict_math],
+            "kernel_mode": MODE_NAMES[a.strict_math],
             "roofline": rf,
             "breakdown_ms_per_step": {"voxel_build": agg["build_ms"] / steps / world, "derivatives": agg["deriv_ms"] / steps / world,
                                       "device_total": agg["total_ms"] / steps / world, "strict_replay": agg["replay_ms"] / steps / world,

@@ -12,22 +12,14 @@ sys.path.insert(0, ROOT)
 from xchu_slam_b200 import build as b  # noqa: E402
 
 VARIANTS = {
-    # strict (term-by-term) kernel: the round-2 default is shared-memory FP64 accumulators + neighbour loop not unrolled + two
-    # blocks per SM (profiles/r02/r02_c4_strict_variants.txt, r02_c5_strict_variants.txt); these rebuild the earlier settings
-    # leading accumulators (score, gradient, first Hessian rows) in registers, the rest in shared memory: the final binary's
-    # strict kernel is bound by its shared-memory traffic (L1/TEX 93 %, profiles/r02/r02_final_deriv_strict_full.txt)
-    # strict kernel at three 128-thread blocks per SM (168 registers): most of the 43 accumulators fit in registers without spills
-    "strict_t128_b3_r25": ("NDTB_THREADS=128", "NDTB_MINBLOCKS=3", "NDTB_STRICT_REG_ACCS=25"),
-    "strict_t128_b3_r31": ("NDTB_THREADS=128", "NDTB_MINBLOCKS=3", "NDTB_STRICT_REG_ACCS=31"),
-    "strict_t128_b3_r37": ("NDTB_THREADS=128", "NDTB_MINBLOCKS=3", "NDTB_STRICT_REG_ACCS=37"),
-    "strict_t192_b2_r31": ("NDTB_THREADS=192", "NDTB_MINBLOCKS=2", "NDTB_STRICT_REG_ACCS=31"),
-    # factorised kernel with the scalar core of every pair (w, q, exp, f) in the reference's float operations
-    "fast_exactcore": ("NDTB_FAST_EXACT_CORE=1",),
-    "strict_reg7": ("NDTB_STRICT_REG_ACCS=7",),
-    "strict_reg13": ("NDTB_STRICT_REG_ACCS=13",),
-    "strict_reg19": ("NDTB_STRICT_REG_ACCS=19",),
-    "strict_r01": ("NDTB_NOUNROLL=0", "NDTB_STRICT_ACC_SMEM=0", "NDTB_MINBLOCKS=1"),
-    "strict_nounroll_regs": ("NDTB_NOUNROLL=1", "NDTB_STRICT_ACC_SMEM=0", "NDTB_MINBLOCKS=1"),
+    # strict kernel: the default is three 128-thread blocks per SM with 25 of the 43 accumulators in registers; every other split,
+    # block shape (64 x 6, 96 x 4, 192 x 2), the per-point vectors in shared memory and a hand-written double exponential were
+    # measured slower (profiles/r02/r02_c12_strict_variants.txt, r02_c13_strict_variants.txt).  These rebuild earlier settings:
+    "strict_r02": ("NDTB_THREADS=256", "NDTB_MINBLOCKS=2", "NDTB_STRICT_REG_ACCS=7"),
+    "strict_t128_b3_r19": ("NDTB_STRICT_REG_ACCS=19",),
+    "strict_t128_b3_r31": ("NDTB_STRICT_REG_ACCS=31",),
+    "strict_r01": ("NDTB_THREADS=256", "NDTB_NOUNROLL=0", "NDTB_STRICT_ACC_SMEM=0", "NDTB_MINBLOCKS=1"),
+    "strict_nounroll_regs": ("NDTB_THREADS=256", "NDTB_NOUNROLL=1", "NDTB_STRICT_ACC_SMEM=0", "NDTB_MINBLOCKS=1"),
 }
 
 

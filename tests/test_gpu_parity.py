@@ -401,14 +401,17 @@ def test_overflow_guard_empty_grid():
     assert rg["iterations"] == ro["iterations"] and rg["converged"] == ro["converged"]
 
 
-def test_batch_matches_single(case_small):
-    """Batched entry point: per-item results identical to single aligns, independent of batch layout."""
+@pytest.mark.parametrize("strict", [True, False])
+def test_batch_matches_single(case_small, strict):
+    """Batched entry point: per-item results identical to single aligns, independent of batch layout -- with the term-by-term
+    kernel (the default of both) and with the factorised one."""
     from xchu_slam_b200 import ndt, synth
     src, tgt, gt, guess = case_small
     guesses = [synth.perturbed_guess(gt, 100 + i) for i in range(6)]
     single = []
     g = ndt.NormalDistributionsTransform()
-    g.setStrictMath(False)      # a handle defaults to the term-by-term kernel, a batch to the factorised one: compare like with like
+    if not strict:
+        g.setStrictMath(False)
     g.setTransformationEpsilon(0.01)
     g.setMaximumIterations(30)
     g.setInputTarget(tgt)
@@ -417,7 +420,7 @@ def test_batch_matches_single(case_small):
         g.align(G)
         single.append(g.result())
     b = ndt.BatchNDT()
-    b.set_params(trans_eps=0.01, max_iter=30)
+    b.set_params(trans_eps=0.01, max_iter=30, strict_math=-1 if strict else 0)
     t0 = b.add_target(tgt)
     t1 = b.add_target(tgt[:50000])
     s0 = b.add_source(src)
@@ -433,7 +436,7 @@ def test_batch_matches_single(case_small):
     assert st["deriv_launches"] > 0 and st["pairs_evaluated"] > 0
     # the same clouds registered through the many-clouds-per-call entry points (ndtb_batch_add_targets / _sources)
     b2 = ndt.BatchNDT()
-    b2.set_params(trans_eps=0.01, max_iter=30)
+    b2.set_params(trans_eps=0.01, max_iter=30, strict_math=-1 if strict else 0)
     tg = [np.ascontiguousarray(tgt, dtype=np.float32), np.ascontiguousarray(tgt[:50000], dtype=np.float32)]
     sc = [np.ascontiguousarray(src, dtype=np.float32), np.ascontiguousarray(src[:3000], dtype=np.float32)]
     assert b2.add_targets_ptr(ndt.BatchNDT.pointer_table([a.ctypes.data for a in tg], [a.shape[0] for a in tg]), 16, 0) == 0
@@ -543,8 +546,9 @@ def _assert_item_parity(r, q, tag):
 def test_batch_c5_shape_against_oracle():
     """BASELINE configs[4] shape (20k-pt scans vs 1M-pt submaps, 2 submaps x 8 scans x 4 hypotheses = 64 registrations in
     one batch) against the oracle, registration by registration, NO waiver: equal iteration counts and convergence flags,
-    final transforms within 1e-4 m / 1e-5 rad -- with the term-by-term kernel (strict_math 1) and in the batch's default
-    HYBRID mode (factorised kernel, then a strict replay of the registrations that give a 1e-7 difference room to grow)."""
+    final transforms within 1e-4 m / 1e-5 rad -- in the batch's default mode (strict_math -1: the term-by-term kernel), with
+    strict_math 1 (the same kernel, asked for by name) and in the opt-in HYBRID mode (-2: factorised kernel, then a strict replay
+    of the registrations that give a 1e-7 difference room to grow)."""
     from oracle import oracle
     from xchu_slam_b200 import ndt, synth
     w = synth.batch_workload(n_submaps=2, scans_per_submap=8, hyps_per_scan=4)
@@ -555,7 +559,7 @@ def test_batch_c5_shape_against_oracle():
             o.set_source(w["sources"][w["item_source"][i]])
             ref_res[i]["fitness"] = o.fitness(T=ref_res[i]["T"])
             ref_res[i]["fitness_1m"] = o.fitness(1.0, T=ref_res[i]["T"])
-    for strict in (1, -1):
+    for strict in (-1, 1, -2):
         b = ndt.BatchNDT()
         b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2, strict_math=strict)
         for t in w["targets"]:
@@ -569,24 +573,26 @@ def test_batch_c5_shape_against_oracle():
             _assert_item_parity(r, q, (strict, k))
             assert abs(fit[k] - q["fitness"]) <= 1e-5 * q["fitness"] and abs(fit1[k] - q["fitness_1m"]) <= 1e-5 * q["fitness_1m"]
         st = b.stats()
-        assert (st["replayed"] == 0) if strict == 1 else (0 <= st["replayed"] < len(res))
+        assert (st["replayed"] == 0) if strict != -2 else (0 <= st["replayed"] < len(res))
         # the registrations recover the ground truth (the batch is not trivially wrong everywhere)
         gt_err = [np.max(np.abs(r["T"][:3, 3] - synth.pose6_to_matrix(g6)[:3, 3])) for r, g6 in zip(res, w["gt"])]
         assert np.median(gt_err) < 0.05
 
 
-def test_batch_c5_hybrid_512_registrations():
+@pytest.mark.parametrize("mode", [-1, -2])
+def test_batch_c5_512_registrations(mode):
     """The batch path the headline is measured on, at scale: 8 one-million-point submaps x 8 scans x 8 hypotheses = 512
-    registrations in ONE ndtb_batch_run in the default hybrid mode, every one of them against the CPU oracle -- iteration
-    counts and convergence flags equal, final transform within 1e-4 m / 1e-5 rad (north_star; the loop NDT_I:114-159 and
-    its iteration test :152-157).  The replayed minority must exist (the workload has non-settling registrations) and stay a
+    registrations in ONE ndtb_batch_run, every one of them against the CPU oracle -- iteration counts and convergence flags
+    equal, final transform within 1e-4 m / 1e-5 rad (north_star; the loop NDT_I:114-159 and its iteration test :152-157).
+    mode -1: the library default (term-by-term kernel, nothing replayed).  mode -2: the opt-in hybrid mode on the world its
+    replay criterion was tuned on; the replayed minority must exist (the workload has non-settling registrations) and stay a
     minority (it is what the hybrid mode costs)."""
     from xchu_slam_b200 import ndt, synth
     w = synth.batch_workload(n_submaps=8, scans_per_submap=8, hyps_per_scan=8)
     _, ref_res = _oracle_batch(w)
     b = ndt.BatchNDT()
-    b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2)
     assert b.params.strict_math == -1
+    b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=2, strict_math=mode)
     for t in w["targets"]:
         b.add_target(t)
     for s in w["sources"]:
@@ -597,6 +603,9 @@ def test_batch_c5_hybrid_512_registrations():
         _assert_item_parity(r, q, k)
     st, dg = b.stats(), b.diag(len(res))
     assert st["replayed"] == int(dg["replayed"].sum())
+    if mode == -1:
+        assert st["replayed"] == 0
+        return
     assert 0 < st["replayed"] < len(res) // 2
     # every registration beyond the iteration threshold was replayed
     its = np.array([q["iterations"] for q in ref_res])
@@ -604,15 +613,15 @@ def test_batch_c5_hybrid_512_registrations():
 
 
 def test_batch_edge_cases_hybrid(case_tiny):
-    """The degenerate inputs of test_edge_cases as items of ONE default (hybrid) batch: the one-point source (rank-3 Hessian,
-    pseudo-inverse step) is flagged by the device and replayed, so the batch follows the oracle there too."""
+    """The degenerate inputs of test_edge_cases as items of ONE hybrid batch (strict_math -2): the one-point source (rank-3
+    Hessian, pseudo-inverse step) is flagged by the device and replayed, so the batch follows the oracle there too."""
     from test_reference_build import _edge_cases
     from oracle import oracle
     from xchu_slam_b200 import ndt
     cases = _edge_cases(case_tiny)
     names = ["source outside the grid", "one-point source", "no voxel reaches 6 points"]
     b = ndt.BatchNDT()
-    b.set_params(resolution=1.0, trans_eps=0.01, max_iter=30, search_method=2)
+    b.set_params(resolution=1.0, trans_eps=0.01, max_iter=30, search_method=2, strict_math=-2)
     it, isrc, G, refs = [], [], [], []
     for nme in names:
         s, t, g0 = cases[nme]

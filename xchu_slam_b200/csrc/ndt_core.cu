@@ -18,11 +18,14 @@ namespace ndtb {
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
 
+// Block shape of the term-by-term kernel: three 128-thread blocks per SM leave 168 registers per thread, which hold 25 of the 43
+// FP64 accumulators beside the pair arithmetic without spills (two 256-thread blocks at 128 registers held 7): 58 % less
+// shared-memory accumulator traffic for 12 instead of 16 resident warps, -3.4 % kernel time (profiles/r02/r02_c12_strict_variants.txt)
 #ifndef NDTB_THREADS
-#define NDTB_THREADS 256
+#define NDTB_THREADS 128
 #endif
 #ifndef NDTB_MINBLOCKS
-#define NDTB_MINBLOCKS 2
+#define NDTB_MINBLOCKS 3
 #endif
 #ifndef NDTB_PD_SMEM      // 1: per-point derivative vectors parked in shared memory, 0: in registers
 #define NDTB_PD_SMEM 0
@@ -38,7 +41,7 @@ namespace ndtb {
                                 //    loop not unrolled: -10.7 % kernel time; with it unrolled +23 %: profiles/r02/r02_c5_strict_variants.txt)
 #endif
 #ifndef NDTB_STRICT_REG_ACCS   // with NDTB_STRICT_ACC_SMEM: the first N of the 43 accumulators (score, gradient, then Hessian rows) stay
-#define NDTB_STRICT_REG_ACCS 7  //    in registers, the rest live in shared memory: N / 43 less shared-memory traffic per pair
+#define NDTB_STRICT_REG_ACCS 25 //    in registers, the rest live in shared memory: N / 43 less shared-memory traffic per pair
 #endif
 constexpr int kThreads = NDTB_THREADS;
 #if NDTB_STRICT_ACC_SMEM

@@ -34,9 +34,6 @@ namespace ndtb {
 #ifndef NDTB_FAST_MINBLOCKS
 #define NDTB_FAST_MINBLOCKS 4
 #endif
-#ifndef NDTB_FAST_EXACT_CORE
-#define NDTB_FAST_EXACT_CORE 0
-#endif
 constexpr int kFT = NDTB_FAST_THREADS;
 constexpr int kFAcc = 28;          // score, g[6], H upper triangle [21]
 constexpr int kFCols = kFAcc + 1;  // + pair count
@@ -171,8 +168,6 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
   const int end = min(bm.y + chunk, st.n_src);
   const FastRec* __restrict__ recs = sh.tab.frec;
   const float d2f = sh.d2f, nhalf_d2f = sh.nhalf_d2f, d1d2f = sh.d1d2f;
-  const double d1 = -sh.neg_d1;
-  (void)d1d2f; (void)d1;
   const Dense7 d7 = make_dense7(sh.tab, METHOD == 2);
   // the source record (PFP >= 1) and the seven cell codes (PFP == 2) of the thread's NEXT point are fetched before this point's
   // pairs are evaluated: one / two of the three dependent global loads of a point leave the critical path
@@ -190,37 +185,19 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
     float S = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f;
     float M00 = 0.f, M01 = 0.f, M02 = 0.f, M11 = 0.f, M12 = 0.f, M22 = 0.f;
     float B00 = 0.f, B01 = 0.f, B02 = 0.f, B11 = 0.f, B12 = 0.f, B22 = 0.f;
-    // The scalar core of a pair -- w = C x, q = x . w, e = exp(-d2 q / 2), f = d1 d2 e.  NDTB_FAST_EXACT_CORE = 1: the float
-    // operations of the reference in its order (products and sums rounded one by one as NDT_I:500-518 evaluates them, exp
-    // in double and narrowed), so x, w, q, e and f of every pair carry the reference's bits and what is left of the kernel's
-    // deviation is the per-point float accumulation and the factorised 6x6 algebra (random roundings, no bias); 0: FMAs, expf.
-#if NDTB_FAST_EXACT_CORE
-#define NDTB_PAIR_CORE(r)                                                                                    \
-      const float w0 = __fadd_rn(__fadd_rn(__fmul_rn(x0, C00), __fmul_rn(x1, C01)), __fmul_rn(x2, C02));     \
-      const float w1 = __fadd_rn(__fadd_rn(__fmul_rn(x0, C01), __fmul_rn(x1, C11)), __fmul_rn(x2, C12));     \
-      const float w2 = __fadd_rn(__fadd_rn(__fmul_rn(x0, C02), __fmul_rn(x1, C12)), __fmul_rn(x2, C22));     \
-      const float q = __fadd_rn(__fadd_rn(__fmul_rn(x0, w0), __fmul_rn(x1, w1)), __fmul_rn(x2, w2));         \
-      const float es = (float)exp((double)(nhalf_d2f * q));      /* NDT_I:507; (-d2 q) * 0.5f == (-0.5f d2) q bit for bit */ \
-      const float eg = __fmul_rn(d2f, es);                       /* NDT_I:511 */
-#define NDTB_PAIR_F ((float)((double)eg * d1))
-#else
-#define NDTB_PAIR_CORE(r)                                                                                    \
-      const float w0 = fmaf(x2, C02, fmaf(x1, C01, x0 * C00));                                               \
-      const float w1 = fmaf(x2, C12, fmaf(x1, C11, x0 * C01));                                               \
-      const float w2 = fmaf(x2, C22, fmaf(x1, C12, x0 * C02));                                               \
-      const float q = fmaf(x2, w2, fmaf(x1, w1, x0 * w0));                                                   \
-      const float es = expf(nhalf_d2f * q);                      /* NDT_I:507 */                             \
-      const float eg = d2f * es;                                 /* NDT_I:511 */
-#define NDTB_PAIR_F (d1d2f * es)
-#endif
     // one (point, voxel) pair of updateDerivatives (NDT_I:491-548), accumulated per point
 #define NDTB_PAIR(r)                                                                                         \
     {                                                                                                        \
       const float x0 = (xt - (r).a.x) - (r).a.w, x1 = (yt - (r).a.y) - (r).b.x, x2 = (zt - (r).a.z) - (r).b.y; \
       const float C00 = (r).b.z, C01 = (r).b.w, C02 = (r).c.x, C11 = (r).c.y, C12 = (r).c.z, C22 = (r).c.w;  \
-      NDTB_PAIR_CORE(r)                                                                                      \
+      const float w0 = fmaf(x2, C02, fmaf(x1, C01, x0 * C00));                                               \
+      const float w1 = fmaf(x2, C12, fmaf(x1, C11, x0 * C01));                                               \
+      const float w2 = fmaf(x2, C22, fmaf(x1, C12, x0 * C02));                                               \
+      const float q = fmaf(x2, w2, fmaf(x1, w1, x0 * w0));                                                   \
+      const float es = expf(nhalf_d2f * q);                      /* NDT_I:507 */                             \
+      const float eg = d2f * es;                                 /* NDT_I:511 */                             \
       if (!(eg > 1.f || eg < 0.f || eg != eg)) {                 /* NDT_I:514-515: else the pair adds nothing */ \
-        const float f = NDTB_PAIR_F;                             /* NDT_I:518 */                             \
+        const float f = d1d2f * es;                              /* NDT_I:518 */                             \
         S += es;                                                                                             \
         const float t0 = f * w0, t1 = f * w1, t2 = f * w2;                                                   \
         a0 += t0; a1 += t1; a2 += t2;                                                                        \
@@ -263,8 +240,6 @@ k_derivatives_fast(const AlignState* __restrict__ states, const VoxelTable* __re
       }
     }
 #undef NDTB_PAIR
-#undef NDTB_PAIR_CORE
-#undef NDTB_PAIR_F
     // ---- once per point: computePointDerivatives (NDT_I:401-445) and the 6x6 algebra ----------
     ACC(0) += sh.neg_d1 * (double)S;                             // NDT_I:509
 #define JH(r) fmaf(sh.jh[r].z, p.z, fmaf(sh.jh[r].y, p.y, sh.jh[r].x * p.x))
