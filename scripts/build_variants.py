@@ -13,8 +13,9 @@ from xchu_slam_b200 import build as b  # noqa: E402
 
 VARIANTS = {
     # strict kernel: the default is three 128-thread blocks per SM with 25 of the 43 accumulators in registers; every other split,
-    # block shape (64 x 6, 96 x 4, 192 x 2), the per-point vectors in shared memory, a hand-written double exponential and the
-    # neighbour loop unrolled by two were measured slower (profiles/r02/r02_c12 / c13 / c15_strict_variants.txt).  These rebuild earlier settings:
+    # block shape (64 x 6, 96 x 4, 192 x 2), the per-point vectors in shared memory, a hand-written double exponential, the
+    # neighbour loop unrolled by two, the next source record prefetched, the cell codes kept in registers behind a bit mask and the
+    # dense-index box in registers were all measured slower (profiles/r02/r02_c12 / c13 / c15 / c16_strict_variants.txt).  These rebuild earlier settings:
     "strict_r02": ("NDTB_THREADS=256", "NDTB_MINBLOCKS=2", "NDTB_STRICT_REG_ACCS=7"),
     "strict_t128_b3_r19": ("NDTB_STRICT_REG_ACCS=19",),
     "strict_t128_b3_r31": ("NDTB_STRICT_REG_ACCS=31",),
