@@ -616,8 +616,8 @@ def cpp_pipeline(a, w, job, device):
 
 
 def roofline_block(agg, ms_total, clocks, K=7, sm_count=148, shared_tables=True, strict=False):
-    """B_pt = 16 + 8*K + R*h bytes per evaluated point (R = 64-byte voxel record of the term-by-term kernel, 48-byte
-    record of the factorised one; points and (point, voxel) pairs COUNTED by the kernel), over the kernel's own time (CUDA events
+    """B_pt = 16 + 8*K + 48*h bytes per evaluated point (points and (point, voxel) pairs COUNTED by the kernel; the
+    term-by-term kernel actually fetches a 64-byte record per pair, the algorithmic figure stays 8d's), over the kernel's own time (CUDA events
     around every derivative launch of the first pass).  What BINDS the kernel is stated from the ncu capture: with 64 registrations
     sharing each submap's table the gather is served by L2 (DRAM traffic ~1 % of the algorithmic bytes), and the limiter is
     instruction issue / the L1 (shared-memory) pipe -- `frac_issue` is the share of the SMs' issue slots the kernel's warp
@@ -625,7 +625,7 @@ def roofline_block(agg, ms_total, clocks, K=7, sm_count=148, shared_tables=True,
     peaks, ncu = load_peaks(), load_ncu_constants()
     if strict:
         ncu = ncu.get("strict", {})
-    rec = 64 if strict else 48
+    rec = 48     # mean 3 x f64 + symmetric icov 6 x f32 per valid neighbour (the strict kernel's 64-byte record carries the full 3 x 3)
     peak = float(peaks.get("hbm_gbs", 6650.0))
     alg_bytes = agg["points_evaluated"] * (16 + 8 * K) + rec * agg["pairs_evaluated"]
     deriv_ms = agg["deriv_ms"]
