@@ -612,6 +612,29 @@ def test_batch_c5_512_registrations(mode):
     assert np.all(dg["replayed"][its > b.params.replay_iters] == 1)
 
 
+def test_batch_step_history(case_small):
+    """ndtb_batch_get_step_history: |delta_p| of every Newton solve of every item (the data the hybrid mode's replay criterion is
+    studied on): one positive entry per iteration, zeros beyond, the last one equal to the `last_norm` diagnostic."""
+    from xchu_slam_b200 import ndt, synth
+    src, tgt, gt, guess = case_small
+    guesses = [synth.perturbed_guess(gt, 300 + i) for i in range(5)]
+    b = ndt.BatchNDT()
+    b.set_params(trans_eps=0.01, max_iter=30)
+    b.add_target(tgt)
+    b.add_source(src)
+    res = b.run([0] * 5, [0] * 5, guesses)
+    h = b.step_history(5)
+    dg = b.diag(5)
+    assert h.shape == (5, 32) and h.dtype == np.float32
+    for i, r in enumerate(res):
+        n = r["iterations"]
+        assert 0 < n <= 32
+        assert np.all(h[i, :n] > 0) and np.all(h[i, n:] == 0)
+        assert h[i, n - 1] == np.float32(dg["last_norm"][i])
+    # a shorter view of the same data
+    assert np.array_equal(b.step_history(5, 8), h[:, :8])
+
+
 def test_batch_edge_cases_hybrid(case_tiny):
     """The degenerate inputs of test_edge_cases as items of ONE hybrid batch (strict_math -2): the one-point source (rank-3
     Hessian, pseudo-inverse step) is flagged by the device and replayed, so the batch follows the oracle there too."""
