@@ -612,6 +612,29 @@ def test_batch_c5_512_registrations(mode):
     assert np.all(dg["replayed"][its > b.params.replay_iters] == 1)
 
 
+@pytest.mark.parametrize("method", [3, 0, 1])
+def test_batch_default_mode_other_search_methods(case_small, method):
+    """The batch default (term-by-term kernel) with DIRECT1, KDTREE and DIRECT26 (NDT_H:52-57): six registrations of one batch
+    against the oracle, the north_star gate on every one of them."""
+    from oracle import oracle
+    from xchu_slam_b200 import ndt, synth
+    src, tgt, gt, guess = case_small
+    guesses = [synth.perturbed_guess(gt, 700 + i) for i in range(6)]
+    o = oracle.OracleNDT()
+    o.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=method, num_threads=oracle.max_threads())
+    o.set_target(tgt)
+    o.set_source(src)
+    b = ndt.BatchNDT()
+    b.set_params(resolution=1.0, step_size=0.1, trans_eps=0.01, max_iter=30, search_method=method)
+    assert b.params.strict_math == -1
+    b.add_target(tgt)
+    b.add_source(src)
+    res = b.run([0] * 6, [0] * 6, guesses)
+    assert b.stats()["replayed"] == 0
+    for k, (r, G) in enumerate(zip(res, guesses)):
+        _assert_item_parity(r, o.align(G), (method, k))
+
+
 def test_batch_step_history(case_small):
     """ndtb_batch_get_step_history: |delta_p| of every Newton solve of every item (the data the hybrid mode's replay criterion is
     studied on): one positive entry per iteration, zeros beyond, the last one equal to the `last_norm` diagnostic."""
